@@ -1,0 +1,201 @@
+/*
+ * slimg_b200.h -- C ABI of libslimg_b200.so: the B200 (sm_100a) implementation of slimg-core's
+ * per-image pixel pipeline (crop -> extend -> Lanczos3 resize, and the JPEG pre-entropy front
+ * end).  This is the drop-in boundary: plain pointers and sizes, no torch / C++ types.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the slimg
+ * repository).  Status codes are the reference's SlimgError tags
+ * (crates/slimg-ffi/src/lib.rs:195-227), so a binding maps them 1:1; error CONDITIONS match
+ * crop.rs:19-67, extend.rs:37-104 and resize.rs:23-61.
+ *
+ * There is NO CPU fallback: every pixel-producing call runs CUDA kernels and fails with
+ * SLIMG_ERR_IMAGE ("no CUDA device" / the CUDA error string) when it cannot.
+ * All functions are thread-safe; slimg_b200_last_error() is thread-local.
+ */
+#ifndef SLIMG_B200_H
+#define SLIMG_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SLIMG_B200_ABI_VERSION 1
+
+/* ---- status = SlimgError tag (crates/slimg-ffi/src/lib.rs:195-227) ---- */
+typedef enum {
+    SLIMG_OK = 0,
+    SLIMG_ERR_UNSUPPORTED_FORMAT = 1,
+    SLIMG_ERR_UNKNOWN_FORMAT = 2,
+    SLIMG_ERR_ENCODING_NOT_SUPPORTED = 3,
+    SLIMG_ERR_DECODE = 4,
+    SLIMG_ERR_ENCODE = 5,
+    SLIMG_ERR_RESIZE = 6,
+    SLIMG_ERR_CROP = 7,
+    SLIMG_ERR_EXTEND = 8,
+    SLIMG_ERR_IO = 9,
+    SLIMG_ERR_IMAGE = 10   /* also: CUDA failures, bad arguments */
+} slimg_status;
+
+/* ---- data types ---- */
+
+/* ImageData (crates/slimg-core/src/codec/mod.rs:11-39): tightly packed RGBA8, row-major,
+ * len == width*height*4.  `data` is host memory unless a function says "device". */
+typedef struct {
+    uint32_t width, height;
+    uint8_t *data;
+    size_t   len;
+} slimg_image;
+
+/* ResizeMode (crates/slimg-core/src/resize.rs:9-20; UniFFI tags slimg_ffi.kt:1759-1781) */
+enum { SLIMG_RESIZE_WIDTH = 1, SLIMG_RESIZE_HEIGHT = 2, SLIMG_RESIZE_EXACT = 3,
+       SLIMG_RESIZE_FIT = 4, SLIMG_RESIZE_SCALE = 5 };
+typedef struct {
+    int32_t  tag;
+    uint32_t a, b;      /* Width{a} | Height{a} | Exact{a=w,b=h} | Fit{a=max_w,b=max_h} */
+    double   factor;    /* Scale{factor} */
+} slimg_resize_mode;
+
+/* CropMode (crates/slimg-core/src/crop.rs:6-16) */
+enum { SLIMG_CROP_REGION = 1, SLIMG_CROP_ASPECT_RATIO = 2 };
+typedef struct {
+    int32_t  tag;
+    uint32_t x, y;            /* Region only */
+    uint32_t width, height;   /* Region size | AspectRatio w:h */
+} slimg_crop_mode;
+
+/* ExtendMode (crates/slimg-core/src/extend.rs:24-31) */
+enum { SLIMG_EXTEND_ASPECT_RATIO = 1, SLIMG_EXTEND_SIZE = 2 };
+typedef struct {
+    int32_t  tag;
+    uint32_t width, height;
+} slimg_extend_mode;
+
+/* FillColor (crates/slimg-core/src/extend.rs:6-21) */
+enum { SLIMG_FILL_SOLID = 1, SLIMG_FILL_TRANSPARENT = 2 };
+typedef struct {
+    int32_t tag;
+    uint8_t r, g, b, a;       /* Solid only; Transparent == (0,0,0,0) */
+} slimg_fill_color;
+
+/* The pixel half of PipelineOptions (crates/slimg-core/src/pipeline.rs:13-26): format/quality
+ * belong to the encoder that stays on the reference libraries.  has_* == 0 means None.
+ * has_fill == 0 with has_extend != 0 means opaque white (pipeline.rs:78-80). */
+typedef struct {
+    int32_t has_resize;  slimg_resize_mode resize;
+    int32_t has_crop;    slimg_crop_mode   crop;
+    int32_t has_extend;  slimg_extend_mode extend;
+    int32_t has_fill;    slimg_fill_color  fill;
+} slimg_pipeline_options;
+
+/* Which order the three stages run in.  CONVERT is the reference's `convert`
+ * (pipeline.rs:71-89: crop -> extend -> resize, fill pixels take part in the filter taps);
+ * CHAIN is the standalone-op chaining the bindings document (SlimgImage.kt:9-14,
+ * BASELINE.json's "resize -> crop -> extend"). */
+enum { SLIMG_ORDER_CONVERT = 0, SLIMG_ORDER_CHAIN = 1 };
+
+/* ---- geometry (host arithmetic, f64, Rust round() semantics) ---- */
+
+/* resize.rs:23-61 calculate_dimensions */
+slimg_status slimg_b200_calculate_dimensions(uint32_t w, uint32_t h, const slimg_resize_mode *mode,
+                                             uint32_t *out_w, uint32_t *out_h);
+/* resize.rs:64-90: the dimensions `resize` actually returns (image 0.25.9 re-derives them for
+ * every mode but Exact) */
+slimg_status slimg_b200_resize_output_dims(uint32_t w, uint32_t h, const slimg_resize_mode *mode,
+                                           uint32_t *out_w, uint32_t *out_h);
+/* crop.rs:19-67 calculate_crop_region */
+slimg_status slimg_b200_calculate_crop_region(uint32_t w, uint32_t h, const slimg_crop_mode *mode,
+                                              uint32_t *x, uint32_t *y, uint32_t *cw, uint32_t *ch);
+/* extend.rs:37-91 calculate_extend_region */
+slimg_status slimg_b200_calculate_extend_region(uint32_t w, uint32_t h, const slimg_extend_mode *mode,
+                                                uint32_t *cw, uint32_t *ch, uint32_t *off_x, uint32_t *off_y);
+/* Output size of the whole pixel pipeline in the given order. */
+slimg_status slimg_b200_pipeline_output_dims(uint32_t w, uint32_t h, const slimg_pipeline_options *opts,
+                                             int order, uint32_t *out_w, uint32_t *out_h);
+
+/* ---- single-image operations, host buffers in / host buffers out ----
+ * `out->data` is allocated by the library (release with slimg_b200_image_free). */
+
+/* slimg_core::crop::crop (crop.rs:70-87); FFI crop (crates/slimg-ffi/src/lib.rs:320-325) */
+slimg_status slimg_b200_crop(const slimg_image *in, const slimg_crop_mode *mode, slimg_image *out);
+/* slimg_core::extend::extend (extend.rs:94-133); FFI extend (lib.rs:327-332) */
+slimg_status slimg_b200_extend(const slimg_image *in, const slimg_extend_mode *mode,
+                               const slimg_fill_color *fill, slimg_image *out);
+/* slimg_core::resize::resize (resize.rs:64-90); FFI resize (lib.rs:334-339) */
+slimg_status slimg_b200_resize(const slimg_image *in, const slimg_resize_mode *mode, slimg_image *out);
+/* The pixel stages of slimg_core::convert (pipeline.rs:66-89), fused into one launch.
+ * order = SLIMG_ORDER_CONVERT reproduces `convert`; SLIMG_ORDER_CHAIN runs resize->crop->extend. */
+slimg_status slimg_b200_pipeline(const slimg_image *in, const slimg_pipeline_options *opts, int order,
+                                 slimg_image *out);
+void slimg_b200_image_free(slimg_image *img);
+
+/* ---- JPEG pre-entropy front end: what JpegCodec::encode (codec/jpeg.rs:51-72) makes MozJPEG
+ * compute before its entropy coder -- to_rgb (codec/mod.rs:42-48), RGB->YCbCr, 4:2:0 h2v2
+ * downsample, 8x8 islow FDCT, quantisation.  Coefficients are int16, natural order within a
+ * block, planes laid out [HB][WB][64] with MCU-padded block counts (dummy blocks included, as
+ * jccoefct.c:286-319 creates them). ---- */
+typedef struct {
+    uint32_t width, height;
+    uint32_t y_wb, y_hb, y_WB, y_HB;   /* real / padded block counts of Y */
+    uint32_t c_wb, c_hb, c_WB, c_HB;   /* same for Cb and Cr */
+} slimg_jpeg_geometry;
+
+typedef struct {
+    slimg_jpeg_geometry geom;
+    uint16_t qt_luma[64], qt_chroma[64];
+    int16_t *y, *cb, *cr;              /* host; released by slimg_b200_jpeg_coefs_free */
+} slimg_jpeg_coefs;
+
+enum { SLIMG_QT_ANNEX_K = 0,            /* libjpeg-turbo jcparam.c:73-92 */
+       SLIMG_QT_MOZJPEG = 1 };          /* MozJPEG default table set 3, luma == chroma */
+
+void slimg_b200_jpeg_geometry(uint32_t w, uint32_t h, slimg_jpeg_geometry *g);
+/* jpeg_set_quality(q, force_baseline = FALSE): jcparam.c:28-65,130-168 */
+void slimg_b200_jpeg_quant_table(int quality, int which /*0 luma,1 chroma*/, int base, uint16_t out[64]);
+slimg_status slimg_b200_jpeg_frontend(const slimg_image *in, const uint16_t qt_luma[64],
+                                      const uint16_t qt_chroma[64], slimg_jpeg_coefs *out);
+void slimg_b200_jpeg_coefs_free(slimg_jpeg_coefs *c);
+
+/* ---- batched, device-resident variants (what bench.py's `value` times) ----
+ * `src` / `dst` are DEVICE pointers on the current CUDA device; images are packed back to back
+ * (n * w*h*4 bytes in, n * out_w*out_h*4 bytes out).  `stream` is a cudaStream_t (NULL = default
+ * stream).  Calls only enqueue work; they do not synchronise. */
+slimg_status slimg_b200_pipeline_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
+                                              const slimg_pipeline_options *opts, int order,
+                                              uint8_t *dst, size_t dst_capacity, void *stream);
+/* coefficient planes packed per image: y[n][y_HB][y_WB][64], cb[...], cr[...] (device) */
+slimg_status slimg_b200_jpeg_frontend_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
+                                                   const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                                                   int16_t *y, int16_t *cb, int16_t *cr, void *stream);
+
+/* ---- batched, host buffers: the `--jobs` scheduler (cli/src/commands/mod.rs:64-72 and the
+ * par_iter sites crop.rs:112, extend.rs:114, convert.rs:60).  Images are independent; they are
+ * dealt to `n_devices` GPUs x `streams_per_device` in-flight slots through pinned staging
+ * buffers.  Per-image failures are isolated like ErrorCollector (mod.rs:113-145):
+ * statuses[i] carries image i's status and the call returns the number of failed images. ---- */
+typedef struct {
+    int32_t n_devices;           /* 0 = all visible devices */
+    int32_t streams_per_device;  /* 0 = default (3) */
+    const int32_t *device_ids;   /* NULL = 0..n_devices-1 */
+} slimg_batch_config;
+
+int32_t slimg_b200_pipeline_batch_host(const slimg_image *in, uint32_t n,
+                                       const slimg_pipeline_options *opts, int order,
+                                       const slimg_batch_config *cfg,
+                                       slimg_image *out, slimg_status *statuses);
+
+/* ---- misc ---- */
+const char *slimg_b200_last_error(void);          /* thread-local, never NULL */
+int32_t     slimg_b200_abi_version(void);
+int32_t     slimg_b200_device_count(void);        /* 0 when no usable CUDA device */
+uint64_t    slimg_b200_kernel_launches(void);     /* kernels this library has launched, process-wide */
+/* pinned host allocations for callers that want zero-copy staging (e2e bench) */
+void       *slimg_b200_host_alloc(size_t bytes);
+void        slimg_b200_host_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SLIMG_B200_H */

@@ -1,0 +1,508 @@
+// api.cu -- the C ABI of libslimg_b200.so (include/slimg_b200.h): argument validation with the
+// reference's error categories, per-device plan cache (filter taps + tiling live in HBM once per
+// geometry), launch glue, and the multi-GPU batch scheduler that stands where the reference's
+// rayon `par_iter` over files does (cli/src/commands/mod.rs:64-72, crop.rs:112, extend.rs:114,
+// convert.rs:60).
+#include <atomic>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#include "host.h"
+#include "kernels.cuh"
+
+namespace slimg {
+
+static std::atomic<uint64_t> g_launches{0};
+void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+static slimg_status cuda_fail(cudaError_t e, const char *what) {
+    return fail(SLIMG_ERR_IMAGE, std::string("CUDA: ") + what + ": " + cudaGetErrorString(e));
+}
+#define CU(call)                                                     \
+    do {                                                             \
+        cudaError_t e__ = (call);                                    \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call);        \
+    } while (0)
+
+static uint32_t pack_fill(const uint8_t f[4]) {
+    return uint32_t(f[0]) | (uint32_t(f[1]) << 8) | (uint32_t(f[2]) << 16) | (uint32_t(f[3]) << 24);
+}
+
+// ---- resize plans: device-resident tap tables + tiling, cached per (device, geometry) -------
+
+struct DevArray {
+    void *p = nullptr;
+    ~DevArray() { if (p) cudaFree(p); }
+    template <class T> cudaError_t upload(const std::vector<T> &v) {
+        size_t bytes = (v.empty() ? 1 : v.size()) * sizeof(T);
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e != cudaSuccess) return e;
+        if (!v.empty()) e = cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+        return e;
+    }
+};
+
+struct ResizePlan {
+    DevArray xl, xc, xw, xf, yl, yc, yw, yf, tx0, tspan;
+    ResizeParams params{};   // src/dst/strides filled per launch
+};
+
+struct GeomKey {
+    uint32_t v[24];
+    bool operator<(const GeomKey &o) const { return std::memcmp(v, o.v, sizeof v) < 0; }
+};
+
+static GeomKey make_key(const PipeGeom &g) {
+    GeomKey k{};
+    const uint32_t vals[] = {g.sw, g.sh, g.rx, g.ry, g.rw, g.rh, g.vw, g.vh, g.vox, g.voy, pack_fill(g.fill_pre),
+                             uint32_t(g.has_resize), g.Rw, g.Rh, g.px, g.py, g.pw, g.ph, g.fw, g.fh, g.fox, g.foy,
+                             pack_fill(g.fill_post)};
+    for (size_t i = 0; i < sizeof(vals) / sizeof(vals[0]); i++) k.v[i] = vals[i];
+    return k;
+}
+
+struct DeviceCtx {
+    std::mutex mu;
+    std::map<GeomKey, std::shared_ptr<ResizePlan>> plans;
+};
+
+static DeviceCtx &device_ctx(int dev) {
+    static std::mutex mu;
+    static std::map<int, std::unique_ptr<DeviceCtx>> ctxs;
+    std::lock_guard<std::mutex> lk(mu);
+    auto &c = ctxs[dev];
+    if (!c) c.reset(new DeviceCtx());
+    return *c;
+}
+
+static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizePlan> &out) {
+    auto plan = std::make_shared<ResizePlan>();
+    AxisTaps tx, ty;
+    build_axis_taps(g.vw, g.Rw, g.vox, g.rw, tx);
+    build_axis_taps(g.vh, g.Rh, g.voy, g.rh, ty);
+
+    // tiling of the final canvas for the generic kernel
+    int tile_w = g.vw >= g.Rw ? 32 : 64;
+    int tile_h = g.vh >= g.Rh ? 8 : 16;
+    std::vector<int32_t> tile_x0, tile_span;
+    int span_max = 0;
+    for (;;) {
+        const int tiles_x = int((g.fw + tile_w - 1) / tile_w);
+        tile_x0.assign(tiles_x, 0);
+        tile_span.assign(tiles_x, 0);
+        span_max = 0;
+        for (int t = 0; t < tiles_x; t++) {
+            const int64_t fx0 = int64_t(t) * tile_w, fx1 = std::min<int64_t>(fx0 + tile_w, g.fw);
+            const int64_t ix0 = std::max<int64_t>(fx0, g.fox), ix1 = std::min<int64_t>(fx1, int64_t(g.fox) + g.pw);
+            int lo = INT32_MAX, hi = 0;
+            for (int64_t fx = ix0; fx < ix1; fx++) {
+                const int64_t ox = fx - g.fox + g.px;
+                if (tx.count[ox] == 0) continue;
+                lo = std::min(lo, tx.left[ox]);
+                hi = std::max(hi, tx.left[ox] + tx.count[ox]);
+            }
+            if (lo < hi) { tile_x0[t] = lo; tile_span[t] = hi - lo; span_max = std::max(span_max, hi - lo); }
+        }
+        if (size_t(tile_h) * size_t(std::max(span_max, 1)) * 16 <= 192 * 1024) break;
+        if (tile_h > 1) tile_h /= 2;
+        else if (tile_w > 1) tile_w /= 2;
+        else return fail(SLIMG_ERR_RESIZE, "filter footprint of this resize exceeds shared memory");
+    }
+
+    cudaError_t e;
+    if ((e = plan->xl.upload(tx.left)) || (e = plan->xc.upload(tx.count)) || (e = plan->xw.upload(tx.w)) ||
+        (e = plan->xf.upload(tx.fillw)) || (e = plan->yl.upload(ty.left)) || (e = plan->yc.upload(ty.count)) ||
+        (e = plan->yw.upload(ty.w)) || (e = plan->yf.upload(ty.fillw)) || (e = plan->tx0.upload(tile_x0)) ||
+        (e = plan->tspan.upload(tile_span)))
+        return cuda_fail(e, "uploading resize plan");
+
+    ResizeParams &p = plan->params;
+    p.sw = g.sw;
+    p.rx = g.rx; p.ry = g.ry; p.rw = g.rw; p.rh = g.rh;
+    p.ax = AxisDev{(const int32_t *)plan->xl.p, (const int32_t *)plan->xc.p, (const float *)plan->xw.p,
+                   (const float *)plan->xf.p, tx.max_taps};
+    p.ay = AxisDev{(const int32_t *)plan->yl.p, (const int32_t *)plan->yc.p, (const float *)plan->yw.p,
+                   (const float *)plan->yf.p, ty.max_taps};
+    for (int c = 0; c < 4; c++) p.fill_pre[c] = float(g.fill_pre[c]);
+    p.px = g.px; p.py = g.py; p.pw = g.pw; p.ph = g.ph;
+    p.fw = g.fw; p.fh = g.fh; p.fox = g.fox; p.foy = g.foy;
+    p.fill_post = pack_fill(g.fill_post);
+    p.tile_w = tile_w; p.tile_h = tile_h; p.span_max = span_max;
+    p.tile_x0 = (const int32_t *)plan->tx0.p;
+    p.tile_span = (const int32_t *)plan->tspan.p;
+    out = plan;
+    return SLIMG_OK;
+}
+
+static slimg_status get_resize_plan(const PipeGeom &g, std::shared_ptr<ResizePlan> &out) {
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    DeviceCtx &ctx = device_ctx(dev);
+    const GeomKey key = make_key(g);
+    std::lock_guard<std::mutex> lk(ctx.mu);
+    auto it = ctx.plans.find(key);
+    if (it != ctx.plans.end()) { out = it->second; return SLIMG_OK; }
+    if (ctx.plans.size() > 256) ctx.plans.clear();   // bounded; in-flight launches hold shared_ptrs... see below
+    slimg_status st = build_resize_plan(g, out);
+    if (st == SLIMG_OK) ctx.plans[key] = out;
+    return st;
+}
+
+// Enqueue the whole pixel pipeline for n same-geometry images that are resident on the current
+// device.  One kernel launch per 65535 images.
+static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, uint32_t n, uint8_t *dst,
+                                        cudaStream_t stream) {
+    const size_t src_bytes = size_t(g.sw) * g.sh * 4, dst_bytes = size_t(g.fw) * g.fh * 4;
+    if (!g.has_resize) {
+        RemapParams p{};
+        p.src = src; p.dst = dst; p.src_img_bytes = src_bytes; p.dst_img_bytes = dst_bytes;
+        p.sw = g.sw; p.fw = g.fw; p.fh = g.fh;
+        // F(x,y) -> V(x - fox + px, y - foy + py) -> S(.. - vox + rx, .. - voy + ry)
+        const int64_t shift_x = int64_t(g.px) - g.fox, shift_y = int64_t(g.py) - g.foy;
+        p.bx0 = int32_t(g.fox); p.by0 = int32_t(g.foy);
+        p.bx1 = int32_t(g.fox + g.pw); p.by1 = int32_t(g.foy + g.ph);
+        p.ax0 = int32_t(std::max<int64_t>(p.bx0, int64_t(g.vox) - shift_x));
+        p.ay0 = int32_t(std::max<int64_t>(p.by0, int64_t(g.voy) - shift_y));
+        p.ax1 = int32_t(std::min<int64_t>(p.bx1, int64_t(g.vox) + g.rw - shift_x));
+        p.ay1 = int32_t(std::min<int64_t>(p.by1, int64_t(g.voy) + g.rh - shift_y));
+        p.dx = int32_t(shift_x - int64_t(g.vox) + g.rx);
+        p.dy = int32_t(shift_y - int64_t(g.voy) + g.ry);
+        p.fill_in = pack_fill(g.fill_pre); p.fill_out = pack_fill(g.fill_post);
+        CU(launch_remap(p, n, stream));
+        return SLIMG_OK;
+    }
+    std::shared_ptr<ResizePlan> plan;
+    slimg_status st = get_resize_plan(g, plan);
+    if (st != SLIMG_OK) return st;
+    ResizeParams p = plan->params;
+    p.src = src; p.dst = dst; p.src_img_bytes = src_bytes; p.dst_img_bytes = dst_bytes;
+    CU(launch_resize_generic(p, n, stream));
+    return SLIMG_OK;
+}
+
+static slimg_status check_device() {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(SLIMG_ERR_IMAGE, "no CUDA device: libslimg_b200 has no CPU fallback");
+    }
+    return SLIMG_OK;
+}
+
+// first stage of the pipeline decides which error category a malformed input buffer reports
+static slimg_status bad_buffer_status(const slimg_pipeline_options &o, int order) {
+    if (order == SLIMG_ORDER_CONVERT) {
+        if (o.has_crop) return SLIMG_ERR_CROP;
+        if (o.has_extend) return SLIMG_ERR_EXTEND;
+        if (o.has_resize) return SLIMG_ERR_RESIZE;
+    } else {
+        if (o.has_resize) return SLIMG_ERR_RESIZE;
+        if (o.has_crop) return SLIMG_ERR_CROP;
+        if (o.has_extend) return SLIMG_ERR_EXTEND;
+    }
+    return SLIMG_ERR_IMAGE;
+}
+
+static slimg_status validate_image(const slimg_image *in, const slimg_pipeline_options &o, int order) {
+    if (!in) return fail(SLIMG_ERR_IMAGE, "null image");
+    const size_t expected = size_t(in->width) * in->height * 4;
+    // extend.rs:98-104 demands len == w*h*4; crop/resize index the buffer and need at least that much
+    const bool exact = (order == SLIMG_ORDER_CONVERT && !o.has_crop && o.has_extend) ||
+                       (order == SLIMG_ORDER_CHAIN && !o.has_resize && !o.has_crop && o.has_extend);
+    if ((exact && in->len != expected) || in->len < expected || (expected > 0 && !in->data)) {
+        char buf[160];
+        std::snprintf(buf, sizeof buf, "invalid image data: expected %zu bytes (%ux%ux4), got %zu", expected,
+                      in->width, in->height, in->len);
+        return fail(bad_buffer_status(o, order), buf);
+    }
+    if (in->width == 0 || in->height == 0) return fail(bad_buffer_status(o, order), "image has a zero dimension");
+    return SLIMG_OK;
+}
+
+// one image, host in / host out, on the current device
+static slimg_status pipeline_one(const slimg_image *in, const slimg_pipeline_options &o, int order, slimg_image *out,
+                                 cudaStream_t stream, bool caller_buffer) {
+    slimg_status st = validate_image(in, o, order);
+    if (st != SLIMG_OK) return st;
+    PipeGeom g;
+    if ((st = build_geometry(in->width, in->height, o, order, g)) != SLIMG_OK) return st;
+    const size_t src_bytes = size_t(g.sw) * g.sh * 4, dst_bytes = size_t(g.fw) * g.fh * 4;
+
+    uint8_t *host_out = nullptr;
+    if (caller_buffer && out->data && out->len >= dst_bytes) host_out = out->data;
+    else {
+        host_out = static_cast<uint8_t *>(std::malloc(dst_bytes ? dst_bytes : 1));
+        if (!host_out) return fail(SLIMG_ERR_IMAGE, "out of host memory");
+    }
+    uint8_t *d_src = nullptr, *d_dst = nullptr;
+    auto cleanup = [&](slimg_status s) {
+        if (d_src) cudaFreeAsync(d_src, stream);
+        if (d_dst) cudaFreeAsync(d_dst, stream);
+        if (s != SLIMG_OK && host_out != out->data) std::free(host_out);
+        return s;
+    };
+    cudaError_t e;
+    if ((e = cudaMallocAsync((void **)&d_src, src_bytes, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    if ((e = cudaMallocAsync((void **)&d_dst, dst_bytes ? dst_bytes : 1, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    if ((e = cudaMemcpyAsync(d_src, in->data, src_bytes, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "H2D"));
+    if ((st = run_pipeline_device(g, d_src, 1, d_dst, stream)) != SLIMG_OK) return cleanup(st);
+    if ((e = cudaMemcpyAsync(host_out, d_dst, dst_bytes, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "D2H"));
+    if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return cleanup(cuda_fail(e, "pipeline kernels"));
+    cleanup(SLIMG_OK);
+    out->width = g.fw; out->height = g.fh; out->data = host_out; out->len = dst_bytes;
+    return SLIMG_OK;
+}
+
+// compute_reciprocal (jcdctmgr.c:173-221), DCTELEM = int, divisor = quantval << 3 (:245-251)
+static void build_quant(const uint16_t ql[64], const uint16_t qc[64], QuantDev &q) {
+    const uint16_t *t[2] = {ql, qc};
+    for (int k = 0; k < 2; k++)
+        for (int i = 0; i < 64; i++) {
+            const uint32_t divisor = uint32_t(t[k][i] ? t[k][i] : 1) << 3;
+            int b = 31 - __builtin_clz(divisor);
+            int r = 32 + b;
+            uint64_t fq = (uint64_t(1) << r) / divisor, fr = (uint64_t(1) << r) % divisor;
+            uint32_t c = divisor / 2;
+            if (fr == 0) { fq >>= 1; r--; }
+            else if (fr <= divisor / 2u) c++;
+            else fq++;
+            q.recip[k][i] = uint32_t(fq); q.corr[k][i] = c; q.shift[k][i] = uint8_t(r);
+        }
+}
+
+static void jpeg_geometry(uint32_t w, uint32_t h, slimg_jpeg_geometry &g) {
+    auto cdiv = [](uint32_t a, uint32_t b) { return uint32_t((uint64_t(a) + b - 1) / b); };
+    g.width = w; g.height = h;
+    g.y_wb = cdiv(w, 8); g.y_hb = cdiv(h, 8);
+    g.c_wb = cdiv(w, 16); g.c_hb = cdiv(h, 16);
+    g.y_WB = g.c_wb * 2; g.y_HB = g.c_hb * 2;
+    g.c_WB = g.c_wb; g.c_HB = g.c_hb;
+}
+
+static slimg_status run_jpeg_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h, const uint16_t ql[64],
+                                    const uint16_t qc[64], int16_t *y, int16_t *cb, int16_t *cr, cudaStream_t stream) {
+    slimg_jpeg_geometry g;
+    jpeg_geometry(w, h, g);
+    JpegParams p{};
+    p.src = src; p.y = y; p.cb = cb; p.cr = cr;
+    p.src_img_bytes = size_t(w) * h * 4;
+    p.y_img_elems = size_t(g.y_HB) * g.y_WB * 64;
+    p.c_img_elems = size_t(g.c_HB) * g.c_WB * 64;
+    p.w = w; p.h = h;
+    p.y_wb = g.y_wb; p.y_hb = g.y_hb; p.y_WB = g.y_WB; p.y_HB = g.y_HB; p.c_wb = g.c_wb; p.c_hb = g.c_hb;
+    build_quant(ql, qc, p.q);
+    CU(launch_jpeg_frontend(p, n, stream));
+    return SLIMG_OK;
+}
+
+}  // namespace slimg
+
+using namespace slimg;
+
+extern "C" {
+
+const char *slimg_b200_last_error(void) { return last_error_string().c_str(); }
+int32_t slimg_b200_abi_version(void) { return SLIMG_B200_ABI_VERSION; }
+uint64_t slimg_b200_kernel_launches(void) { return g_launches.load(); }
+
+int32_t slimg_b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+void *slimg_b200_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void slimg_b200_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+void slimg_b200_image_free(slimg_image *img) {
+    if (img && img->data) { std::free(img->data); img->data = nullptr; img->len = 0; }
+}
+
+slimg_status slimg_b200_pipeline(const slimg_image *in, const slimg_pipeline_options *opts, int order, slimg_image *out) {
+    if (!opts || !out) return fail(SLIMG_ERR_IMAGE, "null argument");
+    // geometry errors are reported before the device is touched, as the reference reports them
+    // before allocating (crop.rs:71, extend.rs:95-96, resize.rs:65)
+    slimg_status st = validate_image(in, *opts, order);
+    if (st != SLIMG_OK) return st;
+    PipeGeom g;
+    if ((st = build_geometry(in->width, in->height, *opts, order, g)) != SLIMG_OK) return st;
+    if ((st = check_device()) != SLIMG_OK) return st;
+    out->data = nullptr; out->len = 0;
+    return pipeline_one(in, *opts, order, out, cudaStreamPerThread, false);
+}
+
+slimg_status slimg_b200_crop(const slimg_image *in, const slimg_crop_mode *mode, slimg_image *out) {
+    if (!mode) return fail(SLIMG_ERR_IMAGE, "null argument");
+    slimg_pipeline_options o{};
+    o.has_crop = 1; o.crop = *mode;
+    return slimg_b200_pipeline(in, &o, SLIMG_ORDER_CONVERT, out);
+}
+
+slimg_status slimg_b200_extend(const slimg_image *in, const slimg_extend_mode *mode, const slimg_fill_color *fill,
+                               slimg_image *out) {
+    if (!mode || !fill) return fail(SLIMG_ERR_IMAGE, "null argument");
+    slimg_pipeline_options o{};
+    o.has_extend = 1; o.extend = *mode; o.has_fill = 1; o.fill = *fill;
+    return slimg_b200_pipeline(in, &o, SLIMG_ORDER_CONVERT, out);
+}
+
+slimg_status slimg_b200_resize(const slimg_image *in, const slimg_resize_mode *mode, slimg_image *out) {
+    if (!mode) return fail(SLIMG_ERR_IMAGE, "null argument");
+    slimg_pipeline_options o{};
+    o.has_resize = 1; o.resize = *mode;
+    return slimg_b200_pipeline(in, &o, SLIMG_ORDER_CONVERT, out);
+}
+
+slimg_status slimg_b200_pipeline_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
+                                              const slimg_pipeline_options *opts, int order, uint8_t *dst,
+                                              size_t dst_capacity, void *stream) {
+    if (!opts || (n && (!src || !dst))) return fail(SLIMG_ERR_IMAGE, "null argument");
+    if (w == 0 || h == 0) return fail(bad_buffer_status(*opts, order), "image has a zero dimension");
+    PipeGeom g;
+    slimg_status st = build_geometry(w, h, *opts, order, g);
+    if (st != SLIMG_OK) return st;
+    if (size_t(g.fw) * g.fh * 4 * n > dst_capacity) return fail(SLIMG_ERR_IMAGE, "destination buffer too small");
+    if ((st = check_device()) != SLIMG_OK) return st;
+    return run_pipeline_device(g, src, n, dst, static_cast<cudaStream_t>(stream));
+}
+
+void slimg_b200_jpeg_geometry(uint32_t w, uint32_t h, slimg_jpeg_geometry *g) { if (g) jpeg_geometry(w, h, *g); }
+
+// jcparam.c:130-152 jpeg_quality_scaling, :28-65 jpeg_add_quant_table (force_baseline = FALSE)
+void slimg_b200_jpeg_quant_table(int quality, int which, int base, uint16_t out[64]) {
+    static const uint16_t annexk_luma[64] = {16, 11, 10, 16, 24, 40, 51, 61, 12, 12, 14, 19, 26, 58, 60, 55,
+                                             14, 13, 16, 24, 40, 57, 69, 56, 14, 17, 22, 29, 51, 87, 80, 62,
+                                             18, 22, 37, 56, 68, 109, 103, 77, 24, 35, 55, 64, 81, 104, 113, 92,
+                                             49, 64, 78, 87, 103, 121, 120, 101, 72, 92, 95, 98, 112, 100, 103, 99};
+    static const uint16_t annexk_chroma[64] = {17, 18, 24, 47, 99, 99, 99, 99, 18, 21, 26, 66, 99, 99, 99, 99,
+                                               24, 26, 56, 99, 99, 99, 99, 99, 47, 66, 99, 99, 99, 99, 99, 99,
+                                               99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99,
+                                               99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99};
+    // MozJPEG quant_tbl_master_idx 3 (ImageMagick / N. Robidoux), used for luma and chroma alike.
+    // mozjpeg-sys is not in the reference tree: restated, parity unpinned.
+    static const uint16_t mozjpeg3[64] = {16, 16, 16, 18, 25, 37, 56, 85, 16, 17, 20, 27, 34, 40, 53, 75,
+                                          16, 20, 24, 31, 43, 62, 91, 135, 18, 27, 31, 40, 53, 74, 106, 156,
+                                          25, 34, 43, 53, 69, 94, 131, 189, 37, 40, 62, 74, 94, 124, 169, 238,
+                                          56, 53, 91, 106, 131, 169, 226, 311, 85, 75, 135, 156, 189, 238, 311, 418};
+    if (quality <= 0) quality = 1;
+    if (quality > 100) quality = 100;
+    const int scale = quality < 50 ? 5000 / quality : 200 - quality * 2;
+    const uint16_t *tbl = base == SLIMG_QT_MOZJPEG ? mozjpeg3 : (which == 0 ? annexk_luma : annexk_chroma);
+    for (int i = 0; i < 64; i++) {
+        long t = (long(tbl[i]) * scale + 50L) / 100L;
+        if (t <= 0) t = 1;
+        if (t > 32767) t = 32767;
+        out[i] = uint16_t(t);
+    }
+}
+
+slimg_status slimg_b200_jpeg_frontend_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
+                                                   const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                                                   int16_t *y, int16_t *cb, int16_t *cr, void *stream) {
+    if (!qt_luma || !qt_chroma || (n && (!src || !y || !cb || !cr))) return fail(SLIMG_ERR_IMAGE, "null argument");
+    if (w == 0 || h == 0) return fail(SLIMG_ERR_ENCODE, "image has a zero dimension");
+    slimg_status st = check_device();
+    if (st != SLIMG_OK) return st;
+    return run_jpeg_device(src, n, w, h, qt_luma, qt_chroma, y, cb, cr, static_cast<cudaStream_t>(stream));
+}
+
+slimg_status slimg_b200_jpeg_frontend(const slimg_image *in, const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                                      slimg_jpeg_coefs *out) {
+    if (!in || !qt_luma || !qt_chroma || !out) return fail(SLIMG_ERR_IMAGE, "null argument");
+    const size_t expected = size_t(in->width) * in->height * 4;
+    if (in->width == 0 || in->height == 0 || in->len < expected || !in->data)
+        return fail(SLIMG_ERR_ENCODE, "invalid image data for the JPEG front end");
+    slimg_status st = check_device();
+    if (st != SLIMG_OK) return st;
+    std::memset(out, 0, sizeof *out);
+    jpeg_geometry(in->width, in->height, out->geom);
+    std::memcpy(out->qt_luma, qt_luma, 128);
+    std::memcpy(out->qt_chroma, qt_chroma, 128);
+    const size_t ye = size_t(out->geom.y_HB) * out->geom.y_WB * 64, ce = size_t(out->geom.c_HB) * out->geom.c_WB * 64;
+    cudaStream_t stream = cudaStreamPerThread;
+    uint8_t *d_src = nullptr;
+    int16_t *d_coef = nullptr;
+    int16_t *h_coef = static_cast<int16_t *>(std::malloc((ye + 2 * ce) * 2));
+    if (!h_coef) return fail(SLIMG_ERR_IMAGE, "out of host memory");
+    auto cleanup = [&](slimg_status s) {
+        if (d_src) cudaFreeAsync(d_src, stream);
+        if (d_coef) cudaFreeAsync(d_coef, stream);
+        if (s != SLIMG_OK) std::free(h_coef);
+        return s;
+    };
+    cudaError_t e;
+    if ((e = cudaMallocAsync((void **)&d_src, expected, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    if ((e = cudaMallocAsync((void **)&d_coef, (ye + 2 * ce) * 2, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    if ((e = cudaMemcpyAsync(d_src, in->data, expected, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "H2D"));
+    if ((st = run_jpeg_device(d_src, 1, in->width, in->height, qt_luma, qt_chroma, d_coef, d_coef + ye, d_coef + ye + ce, stream)) != SLIMG_OK)
+        return cleanup(st);
+    if ((e = cudaMemcpyAsync(h_coef, d_coef, (ye + 2 * ce) * 2, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "D2H"));
+    if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return cleanup(cuda_fail(e, "jpeg front end kernel"));
+    cleanup(SLIMG_OK);
+    out->y = h_coef; out->cb = h_coef + ye; out->cr = h_coef + ye + ce;
+    return SLIMG_OK;
+}
+
+void slimg_b200_jpeg_coefs_free(slimg_jpeg_coefs *c) {
+    if (c && c->y) { std::free(c->y); c->y = c->cb = c->cr = nullptr; }
+}
+
+int32_t slimg_b200_pipeline_batch_host(const slimg_image *in, uint32_t n, const slimg_pipeline_options *opts, int order,
+                                       const slimg_batch_config *cfg, slimg_image *out, slimg_status *statuses) {
+    if (!opts || (n && (!in || !out))) { fail(SLIMG_ERR_IMAGE, "null argument"); return -1; }
+    if (check_device() != SLIMG_OK) {
+        for (uint32_t i = 0; statuses && i < n; i++) statuses[i] = SLIMG_ERR_IMAGE;
+        return int32_t(n);
+    }
+    int visible = slimg_b200_device_count();
+    int n_dev = cfg && cfg->n_devices > 0 ? cfg->n_devices : visible;
+    if (n_dev > visible && !(cfg && cfg->device_ids)) n_dev = visible;
+    const int streams = cfg && cfg->streams_per_device > 0 ? cfg->streams_per_device : 3;
+
+    std::atomic<uint32_t> next{0};
+    std::mutex err_mu;
+    std::string first_error;
+    // every image starts as "not processed"; a worker overwrites the entry it takes
+    std::vector<slimg_status> local_status;
+    if (!statuses) { local_status.resize(n); statuses = local_status.data(); }
+    for (uint32_t i = 0; i < n; i++) statuses[i] = SLIMG_ERR_IMAGE;
+    auto worker = [&](int device) {
+        if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return; }
+        cudaStream_t s = nullptr;
+        if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return; }
+        for (;;) {
+            const uint32_t i = next.fetch_add(1);
+            if (i >= n) break;
+            slimg_status st = pipeline_one(&in[i], *opts, order, &out[i], s, true);
+            statuses[i] = st;
+            if (st != SLIMG_OK) {
+                std::lock_guard<std::mutex> lk(err_mu);
+                if (first_error.empty()) first_error = "image " + std::to_string(i) + ": " + last_error_string();
+            }
+        }
+        cudaStreamSynchronize(s);
+        cudaStreamDestroy(s);
+    };
+    std::vector<std::thread> threads;
+    for (int d = 0; d < n_dev; d++)
+        for (int k = 0; k < streams; k++)
+            threads.emplace_back(worker, cfg && cfg->device_ids ? cfg->device_ids[d] : d);
+    for (auto &t : threads) t.join();
+    int32_t failed = 0;
+    for (uint32_t i = 0; i < n; i++) failed += statuses[i] != SLIMG_OK;
+    if (failed && first_error.empty()) first_error = "no worker could initialise its CUDA device";
+    if (!first_error.empty()) set_error(first_error);
+    return failed;
+}
+
+}  // extern "C"

@@ -1,0 +1,63 @@
+// host.h -- host-side internals of libslimg_b200: geometry, filter-tap plans, launch glue.
+// Not part of the ABI (that is include/slimg_b200.h).
+#pragma once
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/slimg_b200.h"
+
+namespace slimg {
+
+// ---- errors ------------------------------------------------------------------------------
+void set_error(const std::string &msg);
+slimg_status fail(slimg_status st, const std::string &msg);
+const std::string &last_error_string();
+
+// ---- geometry (geometry.cpp) -------------------------------------------------------------
+// Mirrors of crates/slimg-core/src/{resize,crop,extend}.rs region arithmetic.
+slimg_status calculate_dimensions(uint32_t ow, uint32_t oh, const slimg_resize_mode &m, uint32_t &w, uint32_t &h);
+slimg_status resize_output_dims(uint32_t w, uint32_t h, const slimg_resize_mode &m, uint32_t &ow, uint32_t &oh);
+slimg_status calculate_crop_region(uint32_t iw, uint32_t ih, const slimg_crop_mode &m,
+                                   uint32_t &x, uint32_t &y, uint32_t &w, uint32_t &h);
+slimg_status calculate_extend_region(uint32_t iw, uint32_t ih, const slimg_extend_mode &m,
+                                     uint32_t &cw, uint32_t &ch, uint32_t &ox, uint32_t &oy);
+
+// ---- pipeline geometry -------------------------------------------------------------------
+// Every pipeline this library runs is  S --(pre remap)--> V --(resize)--> R --(post remap)--> F :
+//   S  source image                         (sw x sh)
+//   V  virtual resize input: the rectangle (rx,ry,rw,rh) of S placed at (vox,voy) on a vw x vh
+//      canvas whose other pixels are `fill_pre`          (crop + extend before the resize)
+//   R  resize output (Rw x Rh); has_resize == false means R == V
+//   F  final image: the rectangle (px,py,pw,ph) of R placed at (fox,foy) on an fw x fh canvas
+//      whose other pixels are `fill_post`                (crop + extend after the resize)
+struct PipeGeom {
+    uint32_t sw = 0, sh = 0;
+    uint32_t rx = 0, ry = 0, rw = 0, rh = 0;
+    uint32_t vw = 0, vh = 0, vox = 0, voy = 0;
+    uint8_t fill_pre[4] = {0, 0, 0, 0};
+    bool has_resize = false;
+    uint32_t Rw = 0, Rh = 0;
+    uint32_t px = 0, py = 0, pw = 0, ph = 0;
+    uint32_t fw = 0, fh = 0, fox = 0, foy = 0;
+    uint8_t fill_post[4] = {0, 0, 0, 0};
+};
+
+slimg_status build_geometry(uint32_t w, uint32_t h, const slimg_pipeline_options &o, int order, PipeGeom &g);
+
+// ---- Lanczos3 taps of one axis (taps.cpp) ------------------------------------------------
+// image 0.25.9 imageops/sample.rs sampling bounds and weights, in strict f32, for the virtual
+// axis of length `in_len` resampled to `out_len`; then clipped to the part of the axis that is
+// backed by source pixels ([rect_off, rect_off+rect_len) in V coordinates).  Taps that fall on
+// fill are summed into fillw.
+struct AxisTaps {
+    int out_len = 0, max_taps = 0;
+    std::vector<int32_t> left;    // first source index IN RECT COORDINATES
+    std::vector<int32_t> count;   // taps inside the rect (may be 0)
+    std::vector<float> w;         // [out_len][max_taps], zero padded
+    std::vector<float> fillw;     // [out_len] sum of the weights that land on fill
+};
+void build_axis_taps(uint32_t in_len, uint32_t out_len, uint32_t rect_off, uint32_t rect_len, AxisTaps &t);
+
+}  // namespace slimg

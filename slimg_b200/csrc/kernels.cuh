@@ -1,0 +1,75 @@
+// kernels.cuh -- device-side parameter blocks and launch entry points of the sm_100a kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cstddef>
+#include <cstdint>
+
+namespace slimg {
+
+// ---- K1: crop / extend as one remapped copy (k1_remap.cu) -----------------------------------
+// dst pixel (x,y) of an fw x fh canvas takes
+//   src(x + dx, y + dy)  if (x,y) is inside rect A = [ax0,ax1) x [ay0,ay1)   (source backed)
+//   fill_in              if inside rect B = [bx0,bx1) x [by0,by1)            (B contains A)
+//   fill_out             otherwise
+// which is crop.rs:70-87 and extend.rs:94-133 (and their composition) with no intermediate.
+struct RemapParams {
+    const uint8_t *src;
+    uint8_t *dst;
+    size_t src_img_bytes, dst_img_bytes;
+    uint32_t sw;           // source row pitch in pixels
+    uint32_t fw, fh;
+    int32_t ax0, ay0, ax1, ay1, dx, dy;
+    int32_t bx0, by0, bx1, by1;
+    uint32_t fill_in, fill_out;   // packed RGBA, little endian (R in the low byte)
+};
+cudaError_t launch_remap(const RemapParams &p, uint32_t n_images, cudaStream_t stream);
+
+// ---- K2: Lanczos3 separable resize with fused pre / post remap (k2_resize.cu) ---------------
+struct AxisDev {
+    const int32_t *left;    // [out_len] first tap, in source-rect coordinates
+    const int32_t *count;   // [out_len] taps that land on source pixels
+    const float *w;         // [out_len][max_taps]
+    const float *fillw;     // [out_len] total weight of the taps that land on fill
+    int32_t max_taps;
+};
+
+struct ResizeParams {
+    const uint8_t *src;
+    uint8_t *dst;
+    size_t src_img_bytes, dst_img_bytes;
+    uint32_t sw;                       // source row pitch in pixels
+    uint32_t rx, ry, rw, rh;           // source rectangle the taps index into
+    AxisDev ax, ay;
+    float fill_pre[4];                 // colour of the virtual pixels outside the rectangle
+    uint32_t px, py, pw, ph;           // rectangle of the resize output R that is kept ...
+    uint32_t fw, fh, fox, foy;         // ... and where it lands on the final fw x fh canvas
+    uint32_t fill_post;                // packed RGBA of the rest of the canvas
+    // tiling (generic kernel)
+    int32_t tile_w, tile_h, span_max;
+    const int32_t *tile_x0;            // [tiles_x] first source-rect column a tile column needs
+    const int32_t *tile_span;          // [tiles_x] number of source-rect columns it needs
+};
+cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cudaStream_t stream);
+
+// ---- K3+K4: JPEG pre-entropy front end (k3_jpeg.cu) ------------------------------------------
+struct QuantDev {                      // jcdctmgr.c:173-221 compute_reciprocal, per table entry
+    uint32_t recip[2][64];
+    uint32_t corr[2][64];
+    uint8_t shift[2][64];              // total right shift (r in compute_reciprocal)
+};
+struct JpegParams {
+    const uint8_t *src;
+    int16_t *y, *cb, *cr;
+    size_t src_img_bytes;
+    size_t y_img_elems, c_img_elems;   // int16 elements per image in each plane
+    uint32_t w, h;
+    uint32_t y_wb, y_hb, y_WB, y_HB, c_wb, c_hb;
+    QuantDev q;
+};
+cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStream_t stream);
+
+// process-wide count of kernels launched by this library (slimg_b200_kernel_launches)
+void count_launch(uint64_t n = 1);
+
+}  // namespace slimg
