@@ -50,6 +50,10 @@ struct DevArray {
 struct ResizePlan {
     DevArray xl, xc, xw, xf, yl, yc, yw, yf, tx0, tspan;
     ResizeParams params{};   // src/dst/strides filled per launch
+    // fast path (k2_fast.cu), when the geometry qualifies
+    bool fast = false;
+    DevArray f_a0, f_nch, f_boff, f_bfrag, f_fillx, f_vrow, f_vleft, f_vright, f_filly, f_rowc;
+    FastResizeParams fparams{};
 };
 
 struct GeomKey {
@@ -135,6 +139,34 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
     p.tile_w = tile_w; p.tile_h = tile_h; p.span_max = span_max;
     p.tile_x0 = (const int32_t *)plan->tx0.p;
     p.tile_span = (const int32_t *)plan->tspan.p;
+    // tensor-core fast path
+    FastPlanHost fp;
+    build_fast_plan(g, tx, ty, fp);
+    if (fp.ok && std::getenv("SLIMG_B200_FORCE_GENERIC") == nullptr) {
+        std::vector<VRow> vrows(fp.vrow_w.size() / 8);
+        for (size_t y = 0; y < vrows.size(); y++)
+            for (int s = 0; s < 8; s++) { vrows[y].w[s] = fp.vrow_w[y * 8 + s]; vrows[y].out[s] = fp.vrow_out[y * 8 + s]; }
+        if ((e = plan->f_a0.upload(fp.tile_a0)) || (e = plan->f_nch.upload(fp.tile_nchunks)) ||
+            (e = plan->f_boff.upload(fp.tile_boff)) || (e = plan->f_bfrag.upload(fp.bfrag)) ||
+            (e = plan->f_fillx.upload(fp.fillw_x)) || (e = plan->f_vrow.upload(vrows)) ||
+            (e = plan->f_vleft.upload(fp.vleft)) || (e = plan->f_vright.upload(fp.vright)) ||
+            (e = plan->f_filly.upload(fp.fillw_y)) || (e = plan->f_rowc.upload(fp.row_computed)))
+            return cuda_fail(e, "uploading fast resize plan");
+        FastResizeParams &f = plan->fparams;
+        f.sw = g.sw; f.sh = g.sh; f.ry = g.ry; f.rh = g.rh; f.pw = g.pw; f.ph = g.ph;
+        f.n_tiles = fp.n_tiles; f.n_strips = fp.n_strips;
+        f.tile_a0 = (const int32_t *)plan->f_a0.p; f.tile_nchunks = (const int32_t *)plan->f_nch.p;
+        f.tile_boff = (const int32_t *)plan->f_boff.p; f.bfrag = (const uint32_t *)plan->f_bfrag.p;
+        f.fillw_x = (const float *)plan->f_fillx.p; f.hscale = fp.hscale;
+        f.vrow = (const VRow *)plan->f_vrow.p;
+        f.vleft = (const int32_t *)plan->f_vleft.p; f.vright = (const int32_t *)plan->f_vright.p;
+        f.fillw_y = (const float *)plan->f_filly.p; f.row_computed = (const uint8_t *)plan->f_rowc.p;
+        for (int c = 0; c < 4; c++) f.fill_pre[c] = float(g.fill_pre[c]);
+        f.fw = g.fw; f.fh = g.fh; f.fox = g.fox; f.foy = g.foy;
+        f.fill_post = pack_fill(g.fill_post); f.fill_pre_packed = pack_fill(g.fill_pre);
+        f.n_bands = 1; f.n_fill_blocks = fp.need_fill ? (g.fh + 31) / 32 : 0;
+        plan->fast = true;
+    }
     out = plan;
     return SLIMG_OK;
 }
@@ -179,6 +211,18 @@ static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, u
     std::shared_ptr<ResizePlan> plan;
     slimg_status st = get_resize_plan(g, plan);
     if (st != SLIMG_OK) return st;
+    if (plan->fast && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        FastResizeParams f = plan->fparams;
+        f.src = src; f.dst = dst; f.src_img_bytes = src_bytes; f.dst_img_bytes = dst_bytes;
+        // bands of output rows: enough CTAs to fill the GPU when the batch is small, none of the
+        // (6*ratio rows) halo recomputation when the batch alone fills it
+        const uint64_t ctas_per_band = uint64_t(f.n_strips) * n;
+        uint32_t bands = uint32_t((2 * 148 * 2 + ctas_per_band - 1) / ctas_per_band);
+        bands = std::max<uint32_t>(1, std::min<uint32_t>(bands, std::max<uint32_t>(1, f.ph / 8)));
+        f.n_bands = bands;
+        CU(launch_resize_fast(f, n, stream));
+        return SLIMG_OK;
+    }
     ResizeParams p = plan->params;
     p.src = src; p.dst = dst; p.src_img_bytes = src_bytes; p.dst_img_bytes = dst_bytes;
     CU(launch_resize_generic(p, n, stream));

@@ -60,4 +60,22 @@ struct AxisTaps {
 };
 void build_axis_taps(uint32_t in_len, uint32_t out_len, uint32_t rect_off, uint32_t rect_len, AxisTaps &t);
 
+// ---- fast-path plan (fastplan.cpp): fixed-point weight fragments for the tensor-core horizontal
+// pass and the slot table of the streaming vertical pass ----------------------------------------
+struct FastPlanHost {
+    bool ok = false;                       // false: geometry outside the fast path, use the generic kernel
+    uint32_t n_tiles = 0, n_strips = 0;
+    std::vector<int32_t> tile_a0, tile_nchunks, tile_boff;
+    std::vector<uint32_t> bfrag;
+    std::vector<float> fillw_x;
+    float hscale = 1.0f;
+    std::vector<float> vrow_w;             // [rows][8]
+    std::vector<int16_t> vrow_out;         // [rows][8]
+    std::vector<int32_t> vleft, vright;
+    std::vector<float> fillw_y;
+    std::vector<uint8_t> row_computed;
+    bool need_fill = false;
+};
+void build_fast_plan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, FastPlanHost &out);
+
 }  // namespace slimg

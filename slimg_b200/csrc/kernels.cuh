@@ -52,6 +52,38 @@ struct ResizeParams {
 };
 cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cudaStream_t stream);
 
+// ---- K2 fast path: tensor-core horizontal pass + streaming vertical pass (k2_fast.cu) ----------
+// Downscale (ratio >= 1) on both axes.  See k2_fast.cu for the algorithm.
+struct VRow {                // one source-rectangle row of the vertical pass
+    float w[8];              // weight of this row for the output currently held in slot s (0 if none)
+    int16_t out[8];          // local output row that is complete after this row, per slot; -1 = none
+};
+struct FastResizeParams {
+    const uint8_t *src;
+    uint8_t *dst;
+    size_t src_img_bytes, dst_img_bytes;
+    uint32_t sw, sh;                 // source pitch (pixels) and height
+    uint32_t ry, rh;                 // first row / row count of the source rectangle
+    uint32_t pw, ph;                 // columns / rows of the resize output that are kept
+    uint32_t n_tiles, n_strips;      // 8-column output tiles, 64-column strips
+    const int32_t *tile_a0;          // [n_tiles] absolute source column of the tile's first k-chunk (multiple of 4)
+    const int32_t *tile_nchunks;     // [n_tiles] 32-pixel k-chunks the tile's taps span
+    const int32_t *tile_boff;        // [n_tiles] first chunk of the tile inside bfrag
+    const uint32_t *bfrag;           // [chunks][3 limbs][32 lanes][2] weight fragments (s8 x4 per word)
+    const float *fillw_x;            // [n_tiles*8] weight that lands on fill, per kept output column
+    float hscale;                    // 2^-S of the fixed-point weights
+    const VRow *vrow;                // [rh padded to 16 (+16)]
+    const int32_t *vleft, *vright;   // [ph] rectangle-row window [left,right) of each kept output row
+    const float *fillw_y;            // [ph]
+    const uint8_t *row_computed;     // [ph] 0 = every tap of the row is fill: the row is pure fill colour
+    float fill_pre[4];
+    uint32_t fw, fh, fox, foy;       // final canvas and where the kept rectangle lands on it
+    uint32_t fill_post;              // packed RGBA outside the kept rectangle
+    uint32_t fill_pre_packed;        // packed RGBA of kept rows / columns whose every tap is fill
+    uint32_t n_bands, n_fill_blocks;
+};
+cudaError_t launch_resize_fast(const FastResizeParams &p, uint32_t n_images, cudaStream_t stream);
+
 // ---- K3+K4: JPEG pre-entropy front end (k3_jpeg.cu) ------------------------------------------
 struct QuantDev {                      // jcdctmgr.c:173-221 compute_reciprocal, per table entry
     uint32_t recip[2][64];

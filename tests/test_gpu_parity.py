@@ -155,7 +155,18 @@ def test_convert_order_fill_takes_part_in_the_taps(w, h, resize, crop, extend, f
     _close(_np(ll.pipeline(_ll_img(img), l, ll.ORDER_CONVERT)), want)
 
 
-@pytest.mark.parametrize("w,h,resize,crop,extend,fill", PIPE_CASES)
+CHAIN_CASES = [
+    (600, 400, ("width", 80), ("aspect", 16, 9), ("aspect", 1, 1), WHITE),
+    (600, 400, ("width", 80), ("aspect", 16, 9), ("aspect", 1, 1), CLEAR),
+    (401, 299, ("scale", 0.25), ("region", 7, 9, 80, 50), ("size", 133, 57), (10, 200, 30, 128)),
+    (120, 90, ("scale", 3.0), ("aspect", 1, 1), ("aspect", 16, 9), (0, 0, 0, 255)),
+    (300, 200, ("fit", 100, 100), None, ("aspect", 1, 1), None),
+    (300, 200, ("height", 50), ("region", 10, 10, 60, 35), None, None),
+    (1203, 807, ("width", 301), ("region", 1, 2, 299, 198), ("size", 640, 480), (1, 2, 3, 255)),
+]
+
+
+@pytest.mark.parametrize("w,h,resize,crop,extend,fill", CHAIN_CASES)
 def test_chain_order_resize_crop_extend(w, h, resize, crop, extend, fill):
     img = noise_image(w, h, 6)
     o, l = _modes(resize, crop, extend, fill)
