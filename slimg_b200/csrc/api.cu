@@ -52,7 +52,7 @@ struct ResizePlan {
     ResizeParams params{};   // src/dst/strides filled per launch
     // fast path (k2_fast.cu), when the geometry qualifies
     bool fast = false;
-    DevArray f_a0, f_nch, f_boff, f_bfrag, f_fillx, f_vrow, f_vleft, f_vright, f_filly, f_rowc;
+    DevArray f_a0, f_nch, f_boff, f_bfrag, f_fillx, f_vrow, f_vleft, f_vright, f_filly, f_rowc, f_sa0, f_sbytes;
     FastResizeParams fparams{};
 };
 
@@ -144,13 +144,21 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
     build_fast_plan(g, tx, ty, fp);
     if (fp.ok && std::getenv("SLIMG_B200_FORCE_GENERIC") == nullptr) {
         std::vector<VRow> vrows(fp.vrow_w.size() / 8);
-        for (size_t y = 0; y < vrows.size(); y++)
-            for (int s = 0; s < 8; s++) { vrows[y].w[s] = fp.vrow_w[y * 8 + s]; vrows[y].out[s] = fp.vrow_out[y * 8 + s]; }
+        for (size_t y = 0; y < vrows.size(); y++) {
+            VRow &v = vrows[y];
+            std::memset(&v, 0, sizeof v);
+            for (int s = 0; s < 8; s++) {
+                v.w2[2 * s] = v.w2[2 * s + 1] = fp.vrow_w[y * 8 + s];
+                v.out[s] = fp.vrow_out[y * 8 + s];
+                if (v.out[s] >= 0) v.done_mask |= 1u << s;
+            }
+        }
         if ((e = plan->f_a0.upload(fp.tile_a0)) || (e = plan->f_nch.upload(fp.tile_nchunks)) ||
             (e = plan->f_boff.upload(fp.tile_boff)) || (e = plan->f_bfrag.upload(fp.bfrag)) ||
             (e = plan->f_fillx.upload(fp.fillw_x)) || (e = plan->f_vrow.upload(vrows)) ||
             (e = plan->f_vleft.upload(fp.vleft)) || (e = plan->f_vright.upload(fp.vright)) ||
-            (e = plan->f_filly.upload(fp.fillw_y)) || (e = plan->f_rowc.upload(fp.row_computed)))
+            (e = plan->f_filly.upload(fp.fillw_y)) || (e = plan->f_rowc.upload(fp.row_computed)) ||
+            (e = plan->f_sa0.upload(fp.strip_a0)) || (e = plan->f_sbytes.upload(fp.strip_bytes)))
             return cuda_fail(e, "uploading fast resize plan");
         FastResizeParams &f = plan->fparams;
         f.sw = g.sw; f.sh = g.sh; f.ry = g.ry; f.rh = g.rh; f.pw = g.pw; f.ph = g.ph;
@@ -164,7 +172,9 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
         for (int c = 0; c < 4; c++) f.fill_pre[c] = float(g.fill_pre[c]);
         f.fw = g.fw; f.fh = g.fh; f.fox = g.fox; f.foy = g.foy;
         f.fill_post = pack_fill(g.fill_post); f.fill_pre_packed = pack_fill(g.fill_pre);
-        f.n_bands = 1; f.n_fill_blocks = fp.need_fill ? (g.fh + 31) / 32 : 0;
+        f.strip_a0 = (const int32_t *)plan->f_sa0.p; f.strip_bytes = (const int32_t *)plan->f_sbytes.p;
+        f.pitch = fp.pitch;
+        f.n_bands = 1; f.n_fill_blocks = fp.need_fill ? 1 : 0;
         plan->fast = true;
     }
     out = plan;

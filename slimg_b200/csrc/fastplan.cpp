@@ -122,6 +122,27 @@ void build_fast_plan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, 
     }
     if (out.bfrag.empty()) out.bfrag.assign(64, 0u);
 
+    // ---- strips: the span of source columns one CTA stages in shared memory -----------------------
+    out.strip_a0.assign(out.n_strips, 0);
+    out.strip_bytes.assign(out.n_strips, 16);
+    int64_t span_max = 4;
+    for (uint32_t s = 0; s < out.n_strips; s++) {
+        int64_t lo = INT64_MAX, hi = -1;
+        for (uint32_t t = s * 8; t < std::min(out.n_tiles, s * 8 + 8); t++) {
+            if (out.tile_nchunks[t] == 0) continue;
+            lo = std::min<int64_t>(lo, out.tile_a0[t]);
+            hi = std::max<int64_t>(hi, int64_t(out.tile_a0[t]) + 32 * out.tile_nchunks[t]);
+        }
+        if (hi < 0) { lo = 0; hi = 4; }
+        span_max = std::max(span_max, hi - lo);
+        out.strip_a0[s] = int32_t(lo);
+        out.strip_bytes[s] = int32_t((std::min<int64_t>(hi, g.sw) - lo) * 4);   // never read past the row end
+        for (uint32_t t = s * 8; t < std::min(out.n_tiles, s * 8 + 8); t++)
+            out.tile_a0[t] = out.tile_nchunks[t] ? int32_t(out.tile_a0[t] - lo) : 0;
+    }
+    out.pitch = uint32_t((span_max * 4 + 127) / 128 * 128 + 64);
+    if (size_t(out.pitch) * 16 * 2 > 200 * 1024) return;   // two stages must fit in shared memory
+
     // ---- vertical slot table ----------------------------------------------------------------------
     const size_t rows_pad = (size_t(g.rh) + 15) / 16 * 16 + 16;
     out.vrow_w.assign(rows_pad * 8, 0.0f);

@@ -65,7 +65,9 @@ void build_axis_taps(uint32_t in_len, uint32_t out_len, uint32_t rect_off, uint3
 struct FastPlanHost {
     bool ok = false;                       // false: geometry outside the fast path, use the generic kernel
     uint32_t n_tiles = 0, n_strips = 0;
-    std::vector<int32_t> tile_a0, tile_nchunks, tile_boff;
+    std::vector<int32_t> tile_a0, tile_nchunks, tile_boff;   // tile_a0 relative to the strip's span
+    std::vector<int32_t> strip_a0, strip_bytes;
+    uint32_t pitch = 0;
     std::vector<uint32_t> bfrag;
     std::vector<float> fillw_x;
     float hscale = 1.0f;

@@ -13,6 +13,10 @@
 // reading the image from HBM, and u8 -> f32 conversion (I2F: 16/clk/SM) is slower still.
 // mma.sync.m16n8k32.u8.s8 runs at 2028 MAC/clk/SM (measured) and takes the bytes as they are.
 //
+// Staging: one producer warp streams the CTA's strip of source rows into a ring of shared-memory
+// stages with cp.async.bulk (the TMA engine's linear copy, UBLKCP in SASS) completing on
+// mbarriers; eight consumer warps never wait on global memory.
+//
 // Horizontal pass (one warp = one tile of 8 output columns x 16 source rows):
 //   D[16 rows x 8 outs] += A[16 rows x 32 px] * B[32 px x 8 outs]      per channel, per k-chunk
 //   A = source pixels of ONE channel: a 128-bit load brings 4 RGBA pixels, 8 PRMTs transpose
@@ -21,10 +25,10 @@
 //   s32 accumulation is exact; the three digit planes are recombined once per tile.
 // The f32 result rows go to shared memory.
 //
-// Vertical pass (one thread = one output column x one channel): source rows stream by; output
-// row i accumulates in slot i mod 8 while its window is open (at most 8 windows overlap when
-// ratio >= 1), and is clamped, rounded half away from zero, packed and stored the moment its last
-// row has passed.  Nothing but source pixels is read from HBM and nothing but final pixels is
+// Vertical pass (one thread = one output column x two slots, all four channels, packed f32x2
+// FMAs): source rows stream by; output row i accumulates in slot i mod 8 while its window is open
+// (at most 8 windows overlap when ratio >= 1), and is clamped, rounded half away from zero, packed
+// and stored the moment its last row has passed.  Nothing but source pixels is read from HBM and nothing but final pixels is
 // written: the f32 intermediate of the reference (38-51 MB per image) never exists.
 //
 // Grid: x = strips of 64 output columns, y = bands of output rows (+ blocks that write the fill
@@ -36,20 +40,44 @@ namespace slimg {
 
 namespace {
 
-constexpr int kThreads = 256;
-constexpr int kWarps = 8;
-constexpr int kRows = 16;                    // source rows per step
+constexpr int kConsumerWarps = 8;
+constexpr int kConsumerThreads = kConsumerWarps * 32;
+constexpr int kThreads = kConsumerThreads + 32;   // + one producer warp
+constexpr int kRows = 16;                    // source rows per stage
 constexpr int kStripCols = 64;               // output columns per CTA
 constexpr int kIStride = kStripCols * 4 + 4; // floats per intermediate row (+16 B: conflict-free STS.128)
-constexpr int kMaxFlush = 24;                // output rows that can complete within one 16-row step
-constexpr int kFillRows = 32;                // canvas rows per fill block
+constexpr int kMaxFlush = 24;                // output rows that can complete within one stage
+constexpr int kVRowBytes = 96;
+constexpr int kVTabBytes = kRows * kVRowBytes;
+constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
 
-__device__ __forceinline__ uint4 ldg_v4(const uint8_t *p) {
-    uint4 r;
-    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
+static_assert(sizeof(VRow) == kVRowBytes, "VRow layout");
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok = 0, spins = 0;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (!ok && ++spins > kSpinLimit) asm volatile("trap;");
+    } while (!ok);
+}
+// TMA engine, linear form: global -> shared, completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory"); }
 
 __device__ __forceinline__ void imma_16832(int (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -69,50 +97,70 @@ __device__ __forceinline__ void transpose4(const uint4 &q, uint32_t &r, uint32_t
     a = __byte_perm(t2, t3, 0x7632);
 }
 
+// two f32 lanes per instruction (FFMA2): d = a * b + d
+__device__ __forceinline__ void fma2(float2 &d, const float2 &a, const float2 &b) {
+    unsigned long long dd = *reinterpret_cast<unsigned long long *>(&d);
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(dd)
+        : "l"(*reinterpret_cast<const unsigned long long *>(&a)), "l"(*reinterpret_cast<const unsigned long long *>(&b)));
+    d = *reinterpret_cast<float2 *>(&dd);
+}
+
 __device__ __forceinline__ uint32_t quantize_channel(float t) {
     t = fminf(fmaxf(t, 0.0f), 255.0f);      // clamp, then f32::round (half away; value is >= 0)
     return uint32_t(floorf(t + 0.5f));
 }
 
-struct Smem {
+struct SmemFixed {                            // lives after the stages in dynamic shared memory
     float inter[kRows * kIStride];           // horizontal-pass results of the current 16 rows
-    uint8_t outbuf[kMaxFlush][kStripCols][4];
+    uint32_t outbuf[kMaxFlush][kStripCols];  // packed output rows completed in this stage
     int out_row[kMaxFlush];
     int ys, ye;
+    uint64_t full[4], empty[4];
 };
 
-// Blocks past the bands write what is not computed: canvas rows outside the kept rectangle
-// (fill_post), kept rows whose taps are all fill (fill_pre), and the left / right margins.
-__device__ void fill_block(const FastResizeParams &p, uint32_t *dst, int fb) {
-    const int r0 = fb * kFillRows, r1 = min(r0 + kFillRows, int(p.fh));
-    for (int fr = r0; fr < r1; fr++) {
+// What is not computed is written by the producer warp once its loads are issued: canvas rows
+// outside the kept rectangle (fill_post), kept rows whose taps are all fill (fill_pre), and the
+// margins left / right of the kept columns.  Each CTA owns the canvas rows of its band and the
+// canvas columns of its strip (edge bands / strips extend to the canvas border).
+__device__ void fill_region(const FastResizeParams &p, uint32_t *dst, int i0, int i1, int lane) {
+    const bool first_band = blockIdx.y == 0, last_band = blockIdx.y + 1 == p.n_bands;
+    const bool first_strip = blockIdx.x == 0, last_strip = blockIdx.x + 1 == p.n_strips;
+    const int fr0 = first_band ? 0 : int(p.foy) + i0, fr1 = last_band ? int(p.fh) : int(p.foy) + i1;
+    const int cx0 = first_strip ? 0 : int(p.fox) + int(blockIdx.x) * kStripCols;
+    const int cx1 = last_strip ? int(p.fw) : int(p.fox) + int(blockIdx.x + 1) * kStripCols;
+    const int kx0 = int(p.fox), kx1 = int(p.fox + p.pw);
+    for (int fr = fr0; fr < fr1; fr++) {
         const int i = fr - int(p.foy);
         const bool kept = i >= 0 && i < int(p.ph);
         const bool computed = kept && p.row_computed[i];
         uint32_t *row = dst + size_t(fr) * p.fw;
-        for (int x = threadIdx.x; x < int(p.fw); x += kThreads) {
-            const bool in_cols = x >= int(p.fox) && x < int(p.fox + p.pw);
-            if (computed && in_cols) continue;
-            row[x] = (kept && in_cols) ? p.fill_pre_packed : p.fill_post;
+        if (computed) {                        // only the margins
+            for (int x = cx0 + lane; x < min(cx1, kx0); x += 32) row[x] = p.fill_post;
+            for (int x = max(cx0, kx1) + lane; x < cx1; x += 32) row[x] = p.fill_post;
+        } else {
+            for (int x = cx0 + lane; x < cx1; x += 32)
+                row[x] = (kept && x >= kx0 && x < kx1) ? p.fill_pre_packed : p.fill_post;
         }
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResizeParams p) {
-    __shared__ __align__(16) Smem sm;
+__global__ void __maxnreg__(112) resize_fast_kernel(const FastResizeParams p) {
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    const uint32_t stage_bytes = kRows * p.pitch + kVTabBytes;     // pixel rows, then the VRow slice
+    SmemFixed &sm = *reinterpret_cast<SmemFixed *>(smem_raw + size_t(p.stages) * stage_bytes);
+
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint8_t *src = p.src + size_t(blockIdx.z) * p.src_img_bytes;
     uint32_t *dst = reinterpret_cast<uint32_t *>(p.dst + size_t(blockIdx.z) * p.dst_img_bytes);
 
-    if (blockIdx.y >= p.n_bands) {
-        if (blockIdx.x == 0) fill_block(p, dst, int(blockIdx.y - p.n_bands));
-        return;
-    }
-
     // ---- this CTA's band of kept output rows and the source rows it needs --------------------
     const int i0 = int((uint64_t(blockIdx.y) * p.ph) / p.n_bands);
     const int i1 = int((uint64_t(blockIdx.y + 1) * p.ph) / p.n_bands);
-    if (tid == 0) { sm.ys = 0x7fffffff; sm.ye = 0; }
+    if (tid == 0) {
+        sm.ys = 0x7fffffff; sm.ye = 0;
+        for (uint32_t s = 0; s < p.stages; s++) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], kConsumerWarps); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
     {
         int lo = 0x7fffffff, hi = 0;
@@ -121,36 +169,57 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
         if (lo < hi) { atomicMin(&sm.ys, lo); atomicMax(&sm.ye, hi); }
     }
     __syncthreads();
-    const int ys = sm.ys, ye = sm.ye;
-    if (ys >= ye) return;                      // every row of the band is pure fill
+    const int ys = sm.ys, ye = max(sm.ye, sm.ys == 0x7fffffff ? 0 : sm.ys);
+    const int n_iter = sm.ys == 0x7fffffff ? 0 : (ye - ys + kRows - 1) / kRows;
 
-    // ---- horizontal-pass role: warp -> tile of 8 output columns ----------------------------------
+    if (warp == kConsumerWarps) {
+        // =========================== producer warp ===============================================
+        const int a0 = p.strip_a0[blockIdx.x];
+        const uint32_t row_bytes = uint32_t(p.strip_bytes[blockIdx.x]);
+        const uint8_t *col = src + size_t(a0) * 4;
+        const size_t pitch_src = size_t(p.sw) * 4;
+        for (int it = 0; it < n_iter; it++) {
+            const int s = it % int(p.stages);
+            const uint32_t parity = uint32_t(it / int(p.stages)) & 1u;
+            mbar_wait(&sm.empty[s], parity ^ 1u);              // passes at once on the first lap
+            uint8_t *stage = smem_raw + size_t(s) * stage_bytes;
+            const int y0 = ys + it * kRows;
+            if (lane == 0) mbar_arrive_expect_tx(&sm.full[s], kRows * row_bytes + kVTabBytes);
+            __syncwarp();
+            if (lane < kRows) {
+                const int row = min(int(p.ry) + y0 + lane, int(p.sh) - 1);   // rows past the end carry zero weights
+                bulk_g2s(stage + size_t(lane) * p.pitch, col + size_t(row) * pitch_src, row_bytes, &sm.full[s]);
+            } else if (lane == kRows) {
+                bulk_g2s(stage + size_t(kRows) * p.pitch, p.vrow + y0, kVTabBytes, &sm.full[s]);
+            }
+        }
+        if (p.n_fill_blocks) fill_region(p, dst, i0, i1, lane);
+        return;
+    }
+
+    // =============================== consumer warps ================================================
+    // horizontal-pass role: warp -> tile of 8 output columns
     const int g = lane >> 2, t = lane & 3;
-    const int tile = blockIdx.x * kWarps + warp;
+    const int tile = blockIdx.x * kConsumerWarps + warp;
     const bool has_tile = tile < int(p.n_tiles);
-    const int a0 = has_tile ? p.tile_a0[tile] : 0;
+    const int tile_off = has_tile ? p.tile_a0[tile] : 0;
     const int nchunks = has_tile ? p.tile_nchunks[tile] : 0;
     const uint2 *bfrag = reinterpret_cast<const uint2 *>(p.bfrag) + (has_tile ? size_t(p.tile_boff[tile]) * 96 : 0) + lane;
-    float hfill[2][4];                         // fill colour x weight-on-fill for this lane's two columns
-#pragma unroll
-    for (int j = 0; j < 2; j++) {
-        const float fw = has_tile ? p.fillw_x[tile * 8 + 2 * t + j] : 0.0f;
-#pragma unroll
-        for (int c = 0; c < 4; c++) hfill[j][c] = p.fill_pre[c] * fw;
-    }
-    const int max_px = int(p.sw) - 4;
-    const size_t pitch = size_t(p.sw) * 4;
+    const float fwx0 = has_tile ? p.fillw_x[tile * 8 + 2 * t] : 0.0f, fwx1 = has_tile ? p.fillw_x[tile * 8 + 2 * t + 1] : 0.0f;
+    const uint32_t frag_off = uint32_t(g) * p.pitch + uint32_t(tile_off + 4 * t) * 4;
 
-    // ---- vertical-pass role: thread -> (output column, channel) -----------------------------------
-    const int vcol = tid >> 2, vch = tid & 3;
-    const float vfill = p.fill_pre[vch];
-    float vacc[8];
-#pragma unroll
-    for (int s = 0; s < 8; s++) vacc[s] = 0.0f;
-    const int col0 = blockIdx.x * kStripCols;     // first kept output column of this strip
+    // vertical-pass role: thread -> (output column, slot pair); all four channels
+    const int vcol = tid >> 2, sp = tid & 3;
+    float2 va01 = {0.f, 0.f}, va23 = {0.f, 0.f}, vb01 = {0.f, 0.f}, vb23 = {0.f, 0.f};   // slots 2sp, 2sp+1
+    const int col0 = blockIdx.x * kStripCols;
 
-    for (int y0 = ys; y0 < ye; y0 += kRows) {
-        // ================= horizontal pass: 16 source rows -> sm.inter ==========================
+    for (int it = 0; it < n_iter; it++) {
+        const int s = it % int(p.stages);
+        const uint32_t parity = uint32_t(it / int(p.stages)) & 1u;
+        const uint8_t *stage = smem_raw + size_t(s) * stage_bytes;
+        mbar_wait(&sm.full[s], parity);
+
+        // ================= horizontal pass: 16 staged rows -> sm.inter ===========================
         if (has_tile) {
             int acc[3][4][4];
 #pragma unroll
@@ -160,15 +229,13 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
 #pragma unroll
                     for (int r = 0; r < 4; r++) acc[l][c][r] = 0;
 
-            const int row_a = min(int(p.ry) + y0 + g, int(p.sh) - 1);
-            const int row_b = min(int(p.ry) + y0 + g + 8, int(p.sh) - 1);
-            const uint8_t *pa = src + size_t(row_a) * pitch, *pb = src + size_t(row_b) * pitch;
-
+            const uint8_t *pa = stage + frag_off, *pb = pa + 8 * p.pitch;
 #pragma unroll 2
             for (int c = 0; c < nchunks; c++) {
-                const int x0 = min(a0 + 32 * c + 4 * t, max_px), x1 = min(a0 + 32 * c + 16 + 4 * t, max_px);
-                const uint4 q0 = ldg_v4(pa + size_t(x0) * 4), q1 = ldg_v4(pb + size_t(x0) * 4);
-                const uint4 q2 = ldg_v4(pa + size_t(x1) * 4), q3 = ldg_v4(pb + size_t(x1) * 4);
+                const uint4 q0 = *reinterpret_cast<const uint4 *>(pa + 128 * c);
+                const uint4 q1 = *reinterpret_cast<const uint4 *>(pb + 128 * c);
+                const uint4 q2 = *reinterpret_cast<const uint4 *>(pa + 128 * c + 64);
+                const uint4 q3 = *reinterpret_cast<const uint4 *>(pb + 128 * c + 64);
                 uint32_t A[4][4];              // [channel][fragment register]
                 transpose4(q0, A[0][0], A[1][0], A[2][0], A[3][0]);
                 transpose4(q1, A[0][1], A[1][1], A[2][1], A[3][1]);
@@ -186,62 +253,68 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
             for (int half = 0; half < 2; half++) {        // rows g, g+8
 #pragma unroll
                 for (int j = 0; j < 2; j++) {             // columns 2t, 2t+1
+                    const float fw = j ? fwx1 : fwx0;
                     float4 v;
                     float *pv = reinterpret_cast<float *>(&v);
 #pragma unroll
                     for (int ch = 0; ch < 4; ch++) {
                         const int r = half * 2 + j;
                         const int x = acc[0][ch][r] + (acc[1][ch][r] << 7) + (acc[2][ch][r] << 14);
-                        pv[ch] = fmaf(float(x), p.hscale, hfill[j][ch]);
+                        pv[ch] = fmaf(float(x), p.hscale, p.fill_pre[ch] * fw);
                     }
                     *reinterpret_cast<float4 *>(&sm.inter[(g + 8 * half) * kIStride + (warp * 8 + 2 * t + j) * 4]) = v;
                 }
             }
         }
-        __syncthreads();
+        consumer_sync();
 
         // ================= vertical pass: stream the 16 rows through the slots ======================
+        const uint8_t *vtab = stage + size_t(kRows) * p.pitch;
         int n_flush = 0;
 #pragma unroll 4
         for (int r = 0; r < kRows; r++) {
-            const VRow *vr = p.vrow + (y0 + r);
-            const float4 w0 = __ldg(reinterpret_cast<const float4 *>(vr->w));
-            const float4 w1 = __ldg(reinterpret_cast<const float4 *>(vr->w) + 1);
-            const uint4 ev = __ldg(reinterpret_cast<const uint4 *>(vr->out));
-            const float v = sm.inter[r * kIStride + vcol * 4 + vch];
-            vacc[0] = fmaf(v, w0.x, vacc[0]); vacc[1] = fmaf(v, w0.y, vacc[1]);
-            vacc[2] = fmaf(v, w0.z, vacc[2]); vacc[3] = fmaf(v, w0.w, vacc[3]);
-            vacc[4] = fmaf(v, w1.x, vacc[4]); vacc[5] = fmaf(v, w1.y, vacc[5]);
-            vacc[6] = fmaf(v, w1.z, vacc[6]); vacc[7] = fmaf(v, w1.w, vacc[7]);
-            if ((ev.x & ev.y & ev.z & ev.w) != 0xffffffffu) {       // some slot completes on this row (uniform)
-                const uint32_t e[4] = {ev.x, ev.y, ev.z, ev.w};
+            const uint8_t *vr = vtab + r * kVRowBytes;
+            const float4 v = *reinterpret_cast<const float4 *>(&sm.inter[r * kIStride + vcol * 4]);
+            const float4 w = *reinterpret_cast<const float4 *>(vr + sp * 16);     // wa wa wb wb
+            const uint32_t done = *reinterpret_cast<const uint32_t *>(vr + 64);
+            const float2 v01 = {v.x, v.y}, v23 = {v.z, v.w}, wa = {w.x, w.y}, wb = {w.z, w.w};
+            fma2(va01, v01, wa); fma2(va23, v23, wa);
+            fma2(vb01, v01, wb); fma2(vb23, v23, wb);
+            if (done) {                                   // some slot completes on this row (uniform)
 #pragma unroll
-                for (int s = 0; s < 8; s++) {
-                    const int i = int(int16_t((e[s >> 1] >> (16 * (s & 1))) & 0xffffu));
-                    if (i >= 0) {
-                        if (i >= i0 && i < i1 && n_flush < kMaxFlush) {
-                            const float val = fmaf(vfill, p.fillw_y[i], vacc[s]);
-                            sm.outbuf[n_flush][vcol][vch] = uint8_t(quantize_channel(val));
-                            if (tid == 0) sm.out_row[n_flush] = i;
-                            n_flush++;
+                for (int h = 0; h < 2; h++) {
+                    const int slot = 2 * sp + h;
+                    if (done & (1u << slot)) {
+                        const int i = *reinterpret_cast<const int16_t *>(vr + 80 + 2 * slot);
+                        const int k = n_flush + __popc(done & ((1u << slot) - 1u));
+                        const bool mine = i >= i0 && i < i1 && k < kMaxFlush;
+                        if (mine) {
+                            const float fy = p.fillw_y[i];
+                            const float2 a = h ? vb01 : va01, b = h ? vb23 : va23;
+                            sm.outbuf[k][vcol] = quantize_channel(fmaf(p.fill_pre[0], fy, a.x)) |
+                                                 (quantize_channel(fmaf(p.fill_pre[1], fy, a.y)) << 8) |
+                                                 (quantize_channel(fmaf(p.fill_pre[2], fy, b.x)) << 16) |
+                                                 (quantize_channel(fmaf(p.fill_pre[3], fy, b.y)) << 24);
                         }
-                        vacc[s] = 0.0f;
+                        if (vcol == 0 && k < kMaxFlush) sm.out_row[k] = mine ? i : -1;
+                        if (h) { vb01 = {0.f, 0.f}; vb23 = {0.f, 0.f}; } else { va01 = {0.f, 0.f}; va23 = {0.f, 0.f}; }
                     }
                 }
+                n_flush += __popc(done);
             }
         }
-        __syncthreads();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[s]);        // stage (pixels + VRow slice) may be refilled
+        consumer_sync();
 
-        // ================= store the output rows completed in this step ============================
-        for (int idx = tid; idx < n_flush * kStripCols; idx += kThreads) {
+        // ================= store the output rows completed in this stage ============================
+        n_flush = min(n_flush, kMaxFlush);
+        for (int idx = tid; idx < n_flush * kStripCols; idx += kConsumerThreads) {
             const int k = idx >> 6, c = idx & 63;
-            if (col0 + c < int(p.pw)) {
-                const uint32_t px = *reinterpret_cast<const uint32_t *>(&sm.outbuf[k][c][0]);
-                dst[size_t(p.foy + sm.out_row[k]) * p.fw + p.fox + col0 + c] = px;
-            }
+            const int i = sm.out_row[k];
+            if (i >= 0 && col0 + c < int(p.pw)) dst[size_t(p.foy + i) * p.fw + p.fox + col0 + c] = sm.outbuf[k][c];
         }
-        // (the next step's first __syncthreads orders these reads before outbuf is rewritten;
-        //  sm.inter is rewritten only after it as well)
+        // the next stage's first consumer_sync orders these reads before outbuf / inter are rewritten
     }
 }
 
@@ -249,14 +322,29 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
 
 cudaError_t launch_resize_fast(const FastResizeParams &p, uint32_t n_images, cudaStream_t stream) {
     if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
-    const unsigned gy = p.n_bands + p.n_fill_blocks;
-    if (gy > 65535 || p.n_strips == 0) return cudaErrorInvalidValue;
+    if (p.n_bands > 65535 || p.n_strips == 0) return cudaErrorInvalidValue;
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (configured_dev != dev) {
+        cudaError_t e = cudaFuncSetAttribute(resize_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        if (e != cudaSuccess) return e;
+        configured_dev = dev;
+    }
+    FastResizeParams q = p;
+    // ring depth: as many stages as fit in half an SM's shared memory (two CTAs per SM), at least two
+    const size_t stage_bytes = size_t(kRows) * p.pitch + kVTabBytes;
+    size_t stages = (110 * 1024 - sizeof(SmemFixed)) / stage_bytes;
+    if (stages < 2) stages = 2;
+    if (stages > 4) stages = 4;
+    q.stages = uint32_t(stages);
+    q.smem_bytes = uint32_t(stages * stage_bytes + sizeof(SmemFixed));
+    if (q.smem_bytes > 220 * 1024) return cudaErrorInvalidValue;
     for (uint32_t first = 0; first < n_images; first += 65535) {
-        FastResizeParams q = p;
-        q.src += size_t(first) * p.src_img_bytes;
-        q.dst += size_t(first) * p.dst_img_bytes;
+        q.src = p.src + size_t(first) * p.src_img_bytes;
+        q.dst = p.dst + size_t(first) * p.dst_img_bytes;
         const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
-        resize_fast_kernel<<<dim3(p.n_strips, gy, nz), kThreads, 0, stream>>>(q);
+        resize_fast_kernel<<<dim3(p.n_strips, p.n_bands, nz), kThreads, q.smem_bytes, stream>>>(q);
         count_launch();
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;

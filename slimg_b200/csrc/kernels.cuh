@@ -54,9 +54,11 @@ cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cuda
 
 // ---- K2 fast path: tensor-core horizontal pass + streaming vertical pass (k2_fast.cu) ----------
 // Downscale (ratio >= 1) on both axes.  See k2_fast.cu for the algorithm.
-struct VRow {                // one source-rectangle row of the vertical pass
-    float w[8];              // weight of this row for the output currently held in slot s (0 if none)
-    int16_t out[8];          // local output row that is complete after this row, per slot; -1 = none
+struct VRow {                // one source-rectangle row of the vertical pass (96 bytes)
+    float w2[16];            // weight of this row for the output held in slot s, duplicated (w,w) for f32x2 FMAs
+    uint32_t done_mask;      // bit s: the output in slot s is complete after this row
+    uint32_t pad[3];
+    int16_t out[8];          // local output row completing in slot s (valid where done_mask has the bit)
 };
 struct FastResizeParams {
     const uint8_t *src;
@@ -66,8 +68,13 @@ struct FastResizeParams {
     uint32_t ry, rh;                 // first row / row count of the source rectangle
     uint32_t pw, ph;                 // columns / rows of the resize output that are kept
     uint32_t n_tiles, n_strips;      // 8-column output tiles, 64-column strips
-    const int32_t *tile_a0;          // [n_tiles] absolute source column of the tile's first k-chunk (multiple of 4)
+    const int32_t *tile_a0;          // [n_tiles] column of the tile's first k-chunk RELATIVE to its strip's staged span (multiple of 4)
     const int32_t *tile_nchunks;     // [n_tiles] 32-pixel k-chunks the tile's taps span
+    const int32_t *strip_a0;         // [n_strips] absolute source column where the strip's staged span starts (multiple of 4)
+    const int32_t *strip_bytes;      // [n_strips] bytes of each source row staged for the strip (multiple of 16)
+    uint32_t pitch;                  // bytes between staged rows in shared memory (== 64 mod 128)
+    uint32_t stages;                 // depth of the staging ring
+    uint32_t smem_bytes;             // dynamic shared memory of the launch
     const int32_t *tile_boff;        // [n_tiles] first chunk of the tile inside bfrag
     const uint32_t *bfrag;           // [chunks][3 limbs][32 lanes][2] weight fragments (s8 x4 per word)
     const float *fillw_x;            // [n_tiles*8] weight that lands on fill, per kept output column
