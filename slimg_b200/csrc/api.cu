@@ -143,19 +143,20 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
     FastPlanHost fp;
     build_fast_plan(g, tx, ty, fp);
     if (fp.ok && std::getenv("SLIMG_B200_FORCE_GENERIC") == nullptr) {
-        std::vector<VRow> vrows(fp.vrow_w.size() / 8);
-        for (size_t y = 0; y < vrows.size(); y++) {
-            VRow &v = vrows[y];
-            std::memset(&v, 0, sizeof v);
+        std::vector<VQuad> vquads(fp.vrow_w.size() / 32);
+        for (size_t y = 0; y < vquads.size() * 4; y++) {
+            VQuad &v = vquads[y / 4];
+            const int r = int(y % 4);
+            v.done[r] = 0;
             for (int s = 0; s < 8; s++) {
-                v.w2[2 * s] = v.w2[2 * s + 1] = fp.vrow_w[y * 8 + s];
-                v.out[s] = fp.vrow_out[y * 8 + s];
-                if (v.out[s] >= 0) v.done_mask |= 1u << s;
+                v.w2[r][2 * s] = v.w2[r][2 * s + 1] = fp.vrow_w[y * 8 + s];
+                v.out[r][s] = fp.vrow_out[y * 8 + s];
+                if (v.out[r][s] >= 0) v.done[r] |= 1u << s;
             }
         }
         if ((e = plan->f_a0.upload(fp.tile_a0)) || (e = plan->f_nch.upload(fp.tile_nchunks)) ||
             (e = plan->f_boff.upload(fp.tile_boff)) || (e = plan->f_bfrag.upload(fp.bfrag)) ||
-            (e = plan->f_fillx.upload(fp.fillw_x)) || (e = plan->f_vrow.upload(vrows)) ||
+            (e = plan->f_fillx.upload(fp.fillw_x)) || (e = plan->f_vrow.upload(vquads)) ||
             (e = plan->f_vleft.upload(fp.vleft)) || (e = plan->f_vright.upload(fp.vright)) ||
             (e = plan->f_filly.upload(fp.fillw_y)) || (e = plan->f_rowc.upload(fp.row_computed)) ||
             (e = plan->f_sa0.upload(fp.strip_a0)) || (e = plan->f_sbytes.upload(fp.strip_bytes)))
@@ -166,7 +167,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
         f.tile_a0 = (const int32_t *)plan->f_a0.p; f.tile_nchunks = (const int32_t *)plan->f_nch.p;
         f.tile_boff = (const int32_t *)plan->f_boff.p; f.bfrag = (const uint32_t *)plan->f_bfrag.p;
         f.fillw_x = (const float *)plan->f_fillx.p; f.hscale = fp.hscale;
-        f.vrow = (const VRow *)plan->f_vrow.p;
+        f.vquad = (const VQuad *)plan->f_vrow.p;
         f.vleft = (const int32_t *)plan->f_vleft.p; f.vright = (const int32_t *)plan->f_vright.p;
         f.fillw_y = (const float *)plan->f_filly.p; f.row_computed = (const uint8_t *)plan->f_rowc.p;
         for (int c = 0; c < 4; c++) f.fill_pre[c] = float(g.fill_pre[c]);

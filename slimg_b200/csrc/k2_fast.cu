@@ -40,18 +40,16 @@ namespace slimg {
 
 namespace {
 
-constexpr int kConsumerWarps = 8;
-constexpr int kConsumerThreads = kConsumerWarps * 32;
-constexpr int kThreads = kConsumerThreads + 32;   // + one producer warp
+constexpr int kWarps = 8;
+constexpr int kThreads = kWarps * 32;
 constexpr int kRows = 16;                    // source rows per stage
 constexpr int kStripCols = 64;               // output columns per CTA
 constexpr int kIStride = kStripCols * 4 + 4; // floats per intermediate row (+16 B: conflict-free STS.128)
 constexpr int kMaxFlush = 24;                // output rows that can complete within one stage
-constexpr int kVRowBytes = 96;
-constexpr int kVTabBytes = kRows * kVRowBytes;
+constexpr int kVTabBytes = (kRows / 4) * int(sizeof(VQuad));
 constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
 
-static_assert(sizeof(VRow) == kVRowBytes, "VRow layout");
+static_assert(sizeof(VQuad) == 336 && kVTabBytes % 16 == 0, "VQuad layout");
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
 
@@ -77,7 +75,6 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory"); }
 
 __device__ __forceinline__ void imma_16832(int (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -115,21 +112,22 @@ struct SmemFixed {                            // lives after the stages in dynam
     uint32_t outbuf[kMaxFlush][kStripCols];  // packed output rows completed in this stage
     int out_row[kMaxFlush];
     int ys, ye;
-    uint64_t full[4], empty[4];
+    uint64_t full[4];
 };
 
-// What is not computed is written by the producer warp once its loads are issued: canvas rows
-// outside the kept rectangle (fill_post), kept rows whose taps are all fill (fill_pre), and the
-// margins left / right of the kept columns.  Each CTA owns the canvas rows of its band and the
-// canvas columns of its strip (edge bands / strips extend to the canvas border).
-__device__ void fill_region(const FastResizeParams &p, uint32_t *dst, int i0, int i1, int lane) {
+// What is not computed: canvas rows outside the kept rectangle (fill_post), kept rows whose taps
+// are all fill (fill_pre), and the margins left / right of the kept columns.  Each CTA owns the
+// canvas rows of its band and the canvas columns of its strip (edge bands / strips extend to the
+// canvas border).
+__device__ void fill_region(const FastResizeParams &p, uint32_t *dst, int i0, int i1, int tid) {
     const bool first_band = blockIdx.y == 0, last_band = blockIdx.y + 1 == p.n_bands;
     const bool first_strip = blockIdx.x == 0, last_strip = blockIdx.x + 1 == p.n_strips;
     const int fr0 = first_band ? 0 : int(p.foy) + i0, fr1 = last_band ? int(p.fh) : int(p.foy) + i1;
     const int cx0 = first_strip ? 0 : int(p.fox) + int(blockIdx.x) * kStripCols;
     const int cx1 = last_strip ? int(p.fw) : int(p.fox) + int(blockIdx.x + 1) * kStripCols;
     const int kx0 = int(p.fox), kx1 = int(p.fox + p.pw);
-    for (int fr = fr0; fr < fr1; fr++) {
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int fr = fr0 + warp; fr < fr1; fr += kWarps) {
         const int i = fr - int(p.foy);
         const bool kept = i >= 0 && i < int(p.ph);
         const bool computed = kept && p.row_computed[i];
@@ -144,9 +142,9 @@ __device__ void fill_region(const FastResizeParams &p, uint32_t *dst, int i0, in
     }
 }
 
-__global__ void __maxnreg__(112) resize_fast_kernel(const FastResizeParams p) {
+__global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResizeParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    const uint32_t stage_bytes = kRows * p.pitch + kVTabBytes;     // pixel rows, then the VRow slice
+    const uint32_t stage_bytes = kRows * p.pitch + kVTabBytes;     // pixel rows, then the VQuad slice
     SmemFixed &sm = *reinterpret_cast<SmemFixed *>(smem_raw + size_t(p.stages) * stage_bytes);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -158,7 +156,7 @@ __global__ void __maxnreg__(112) resize_fast_kernel(const FastResizeParams p) {
     const int i1 = int((uint64_t(blockIdx.y + 1) * p.ph) / p.n_bands);
     if (tid == 0) {
         sm.ys = 0x7fffffff; sm.ye = 0;
-        for (uint32_t s = 0; s < p.stages; s++) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], kConsumerWarps); }
+        for (uint32_t s = 0; s < p.stages; s++) mbar_init(&sm.full[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -169,38 +167,31 @@ __global__ void __maxnreg__(112) resize_fast_kernel(const FastResizeParams p) {
         if (lo < hi) { atomicMin(&sm.ys, lo); atomicMax(&sm.ye, hi); }
     }
     __syncthreads();
-    const int ys = sm.ys, ye = max(sm.ye, sm.ys == 0x7fffffff ? 0 : sm.ys);
-    const int n_iter = sm.ys == 0x7fffffff ? 0 : (ye - ys + kRows - 1) / kRows;
+    const bool any_rows = sm.ys != 0x7fffffff;
+    const int ys = any_rows ? (sm.ys & ~3) : 0;          // VQuad slices start on a multiple of 4 rows
+    const int n_iter = any_rows ? (sm.ye - ys + kRows - 1) / kRows : 0;
 
-    if (warp == kConsumerWarps) {
-        // =========================== producer warp ===============================================
-        const int a0 = p.strip_a0[blockIdx.x];
-        const uint32_t row_bytes = uint32_t(p.strip_bytes[blockIdx.x]);
-        const uint8_t *col = src + size_t(a0) * 4;
-        const size_t pitch_src = size_t(p.sw) * 4;
-        for (int it = 0; it < n_iter; it++) {
-            const int s = it % int(p.stages);
-            const uint32_t parity = uint32_t(it / int(p.stages)) & 1u;
-            mbar_wait(&sm.empty[s], parity ^ 1u);              // passes at once on the first lap
-            uint8_t *stage = smem_raw + size_t(s) * stage_bytes;
-            const int y0 = ys + it * kRows;
-            if (lane == 0) mbar_arrive_expect_tx(&sm.full[s], kRows * row_bytes + kVTabBytes);
-            __syncwarp();
-            if (lane < kRows) {
-                const int row = min(int(p.ry) + y0 + lane, int(p.sh) - 1);   // rows past the end carry zero weights
-                bulk_g2s(stage + size_t(lane) * p.pitch, col + size_t(row) * pitch_src, row_bytes, &sm.full[s]);
-            } else if (lane == kRows) {
-                bulk_g2s(stage + size_t(kRows) * p.pitch, p.vrow + y0, kVTabBytes, &sm.full[s]);
-            }
+    // ---- staging: threads 0..16 of the CTA drive the TMA engine ------------------------------------
+    const int strip_col = p.strip_a0[blockIdx.x];
+    const uint32_t row_bytes = uint32_t(p.strip_bytes[blockIdx.x]);
+    auto issue_stage = [&](int it) {
+        const int s = it % int(p.stages);
+        uint8_t *stage = smem_raw + size_t(s) * stage_bytes;
+        const int y0 = ys + it * kRows;
+        if (tid == 0) mbar_arrive_expect_tx(&sm.full[s], kRows * row_bytes + kVTabBytes);
+        if (tid < kRows) {
+            const int row = min(int(p.ry) + y0 + tid, int(p.sh) - 1);     // rows past the end carry zero weights
+            bulk_g2s(stage + size_t(tid) * p.pitch, src + (size_t(row) * p.sw + strip_col) * 4, row_bytes, &sm.full[s]);
+        } else if (tid == kRows) {
+            bulk_g2s(stage + size_t(kRows) * p.pitch, p.vquad + (y0 >> 2), kVTabBytes, &sm.full[s]);
         }
-        if (p.n_fill_blocks) fill_region(p, dst, i0, i1, lane);
-        return;
-    }
+    };
+    if (warp == 0)
+        for (int it = 0; it < min(n_iter, int(p.stages)); it++) issue_stage(it);
 
-    // =============================== consumer warps ================================================
-    // horizontal-pass role: warp -> tile of 8 output columns
+    // ---- horizontal-pass role: warp -> tile of 8 output columns ----------------------------------
     const int g = lane >> 2, t = lane & 3;
-    const int tile = blockIdx.x * kConsumerWarps + warp;
+    const int tile = blockIdx.x * kWarps + warp;
     const bool has_tile = tile < int(p.n_tiles);
     const int tile_off = has_tile ? p.tile_a0[tile] : 0;
     const int nchunks = has_tile ? p.tile_nchunks[tile] : 0;
@@ -208,7 +199,7 @@ __global__ void __maxnreg__(112) resize_fast_kernel(const FastResizeParams p) {
     const float fwx0 = has_tile ? p.fillw_x[tile * 8 + 2 * t] : 0.0f, fwx1 = has_tile ? p.fillw_x[tile * 8 + 2 * t + 1] : 0.0f;
     const uint32_t frag_off = uint32_t(g) * p.pitch + uint32_t(tile_off + 4 * t) * 4;
 
-    // vertical-pass role: thread -> (output column, slot pair); all four channels
+    // ---- vertical-pass role: thread -> (output column, slot pair); all four channels -------------
     const int vcol = tid >> 2, sp = tid & 3;
     float2 va01 = {0.f, 0.f}, va23 = {0.f, 0.f}, vb01 = {0.f, 0.f}, vb23 = {0.f, 0.f};   // slots 2sp, 2sp+1
     const int col0 = blockIdx.x * kStripCols;
@@ -266,56 +257,63 @@ __global__ void __maxnreg__(112) resize_fast_kernel(const FastResizeParams p) {
                 }
             }
         }
-        consumer_sync();
+        __syncthreads();
 
         // ================= vertical pass: stream the 16 rows through the slots ======================
-        const uint8_t *vtab = stage + size_t(kRows) * p.pitch;
+        const VQuad *vq = reinterpret_cast<const VQuad *>(stage + size_t(kRows) * p.pitch);
         int n_flush = 0;
-#pragma unroll 4
-        for (int r = 0; r < kRows; r++) {
-            const uint8_t *vr = vtab + r * kVRowBytes;
-            const float4 v = *reinterpret_cast<const float4 *>(&sm.inter[r * kIStride + vcol * 4]);
-            const float4 w = *reinterpret_cast<const float4 *>(vr + sp * 16);     // wa wa wb wb
-            const uint32_t done = *reinterpret_cast<const uint32_t *>(vr + 64);
-            const float2 v01 = {v.x, v.y}, v23 = {v.z, v.w}, wa = {w.x, w.y}, wb = {w.z, w.w};
-            fma2(va01, v01, wa); fma2(va23, v23, wa);
-            fma2(vb01, v01, wb); fma2(vb23, v23, wb);
-            if (done) {                                   // some slot completes on this row (uniform)
 #pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const int slot = 2 * sp + h;
-                    if (done & (1u << slot)) {
-                        const int i = *reinterpret_cast<const int16_t *>(vr + 80 + 2 * slot);
-                        const int k = n_flush + __popc(done & ((1u << slot) - 1u));
-                        const bool mine = i >= i0 && i < i1 && k < kMaxFlush;
-                        if (mine) {
-                            const float fy = p.fillw_y[i];
-                            const float2 a = h ? vb01 : va01, b = h ? vb23 : va23;
-                            sm.outbuf[k][vcol] = quantize_channel(fmaf(p.fill_pre[0], fy, a.x)) |
-                                                 (quantize_channel(fmaf(p.fill_pre[1], fy, a.y)) << 8) |
-                                                 (quantize_channel(fmaf(p.fill_pre[2], fy, b.x)) << 16) |
-                                                 (quantize_channel(fmaf(p.fill_pre[3], fy, b.y)) << 24);
+        for (int q = 0; q < kRows / 4; q++) {
+            const uint4 done4 = *reinterpret_cast<const uint4 *>(vq[q].done);
+            const uint32_t done[4] = {done4.x, done4.y, done4.z, done4.w};
+            const bool any_done = (done4.x | done4.y | done4.z | done4.w) != 0;   // uniform
+#pragma unroll
+            for (int rr = 0; rr < 4; rr++) {
+                const int r = q * 4 + rr;
+                const float4 v = *reinterpret_cast<const float4 *>(&sm.inter[r * kIStride + vcol * 4]);
+                const float4 w = *reinterpret_cast<const float4 *>(&vq[q].w2[rr][sp * 4]);     // wa wa wb wb
+                const float2 v01 = {v.x, v.y}, v23 = {v.z, v.w}, wa = {w.x, w.y}, wb = {w.z, w.w};
+                fma2(va01, v01, wa); fma2(va23, v23, wa);
+                fma2(vb01, v01, wb); fma2(vb23, v23, wb);
+                if (any_done && done[rr]) {               // some slot completes on this row (uniform)
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const int slot = 2 * sp + h;
+                        if (done[rr] & (1u << slot)) {
+                            const int i = vq[q].out[rr][slot];
+                            const int k = n_flush + __popc(done[rr] & ((1u << slot) - 1u));
+                            const bool mine = i >= i0 && i < i1 && k < kMaxFlush;
+                            if (mine) {
+                                const float fy = p.fillw_y[i];
+                                const float2 a = h ? vb01 : va01, b = h ? vb23 : va23;
+                                sm.outbuf[k][vcol] = quantize_channel(fmaf(p.fill_pre[0], fy, a.x)) |
+                                                     (quantize_channel(fmaf(p.fill_pre[1], fy, a.y)) << 8) |
+                                                     (quantize_channel(fmaf(p.fill_pre[2], fy, b.x)) << 16) |
+                                                     (quantize_channel(fmaf(p.fill_pre[3], fy, b.y)) << 24);
+                            }
+                            if (vcol == 0 && k < kMaxFlush) sm.out_row[k] = mine ? i : -1;
+                            if (h) { vb01 = {0.f, 0.f}; vb23 = {0.f, 0.f}; } else { va01 = {0.f, 0.f}; va23 = {0.f, 0.f}; }
                         }
-                        if (vcol == 0 && k < kMaxFlush) sm.out_row[k] = mine ? i : -1;
-                        if (h) { vb01 = {0.f, 0.f}; vb23 = {0.f, 0.f}; } else { va01 = {0.f, 0.f}; va23 = {0.f, 0.f}; }
                     }
+                    n_flush += __popc(done[rr]);
                 }
-                n_flush += __popc(done);
             }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.empty[s]);        // stage (pixels + VRow slice) may be refilled
-        consumer_sync();
+        __syncthreads();                                  // everyone is done with the stage, inter and outbuf are final
+
+        if (warp == 0 && it + int(p.stages) < n_iter) issue_stage(it + int(p.stages));   // refill this stage
 
         // ================= store the output rows completed in this stage ============================
         n_flush = min(n_flush, kMaxFlush);
-        for (int idx = tid; idx < n_flush * kStripCols; idx += kConsumerThreads) {
+        for (int idx = tid; idx < n_flush * kStripCols; idx += kThreads) {
             const int k = idx >> 6, c = idx & 63;
             const int i = sm.out_row[k];
             if (i >= 0 && col0 + c < int(p.pw)) dst[size_t(p.foy + i) * p.fw + p.fox + col0 + c] = sm.outbuf[k][c];
         }
-        // the next stage's first consumer_sync orders these reads before outbuf / inter are rewritten
+        // the next iteration's first __syncthreads orders these reads before outbuf / inter are rewritten
     }
+
+    if (p.n_fill_blocks) fill_region(p, dst, i0, i1, tid);
 }
 
 }  // namespace
@@ -329,12 +327,14 @@ cudaError_t launch_resize_fast(const FastResizeParams &p, uint32_t n_images, cud
     if (configured_dev != dev) {
         cudaError_t e = cudaFuncSetAttribute(resize_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
         if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(resize_fast_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        if (e != cudaSuccess) return e;
         configured_dev = dev;
     }
     FastResizeParams q = p;
     // ring depth: as many stages as fit in half an SM's shared memory (two CTAs per SM), at least two
     const size_t stage_bytes = size_t(kRows) * p.pitch + kVTabBytes;
-    size_t stages = (110 * 1024 - sizeof(SmemFixed)) / stage_bytes;
+    size_t stages = (112 * 1024 - sizeof(SmemFixed)) / stage_bytes;
     if (stages < 2) stages = 2;
     if (stages > 4) stages = 4;
     q.stages = uint32_t(stages);

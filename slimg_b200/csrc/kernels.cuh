@@ -54,11 +54,10 @@ cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cuda
 
 // ---- K2 fast path: tensor-core horizontal pass + streaming vertical pass (k2_fast.cu) ----------
 // Downscale (ratio >= 1) on both axes.  See k2_fast.cu for the algorithm.
-struct VRow {                // one source-rectangle row of the vertical pass (96 bytes)
-    float w2[16];            // weight of this row for the output held in slot s, duplicated (w,w) for f32x2 FMAs
-    uint32_t done_mask;      // bit s: the output in slot s is complete after this row
-    uint32_t pad[3];
-    int16_t out[8];          // local output row completing in slot s (valid where done_mask has the bit)
+struct VQuad {               // four consecutive source-rectangle rows of the vertical pass (336 bytes)
+    uint32_t done[4];        // per row: bit s set = the output in slot s is complete after this row
+    int16_t out[4][8];       // per row, per slot: local output row completing there (valid where the bit is set)
+    float w2[4][16];         // per row: weight for the output held in slot s, duplicated (w,w) for f32x2 FMAs
 };
 struct FastResizeParams {
     const uint8_t *src;
@@ -79,7 +78,7 @@ struct FastResizeParams {
     const uint32_t *bfrag;           // [chunks][3 limbs][32 lanes][2] weight fragments (s8 x4 per word)
     const float *fillw_x;            // [n_tiles*8] weight that lands on fill, per kept output column
     float hscale;                    // 2^-S of the fixed-point weights
-    const VRow *vrow;                // [rh padded to 16 (+16)]
+    const VQuad *vquad;              // [(rh padded to 16, +16) / 4]
     const int32_t *vleft, *vright;   // [ph] rectangle-row window [left,right) of each kept output row
     const float *fillw_y;            // [ph]
     const uint8_t *row_computed;     // [ph] 0 = every tap of the row is fill: the row is pure fill colour
