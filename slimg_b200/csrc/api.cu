@@ -175,6 +175,8 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
         f.fill_post = pack_fill(g.fill_post); f.fill_pre_packed = pack_fill(g.fill_pre);
         f.strip_a0 = (const int32_t *)plan->f_sa0.p; f.strip_bytes = (const int32_t *)plan->f_sbytes.p;
         f.pitch = fp.pitch;
+        f.max_chunks = 0;
+        for (int32_t c : fp.tile_nchunks) f.max_chunks = std::max<uint32_t>(f.max_chunks, uint32_t(c));
         f.n_bands = 1; f.n_fill_blocks = fp.need_fill ? 1 : 0;
         plan->fast = true;
     }

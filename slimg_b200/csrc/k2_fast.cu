@@ -82,6 +82,13 @@ __device__ __forceinline__ void imma_16832(int (&d)[4], const uint32_t (&a)[4], 
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+// first k-chunk: C = 0 comes from the zero register, no accumulator clearing
+__device__ __forceinline__ void imma_16832_z(int (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "r"(0));
+}
+
 // 4 RGBA pixels -> the same 4 pixels of R, of G, of B, of A (one register each)
 __device__ __forceinline__ void transpose4(const uint4 &q, uint32_t &r, uint32_t &g, uint32_t &b, uint32_t &a) {
     const uint32_t t0 = __byte_perm(q.x, q.y, 0x5140);   // R0 R1 G0 G1
@@ -108,10 +115,11 @@ __device__ __forceinline__ uint32_t quantize_channel(float t) {
 }
 
 struct SmemFixed {                            // lives after the stages in dynamic shared memory
-    float inter[kRows * kIStride];           // horizontal-pass results of the current 16 rows
+    float inter[kRows * kIStride];           // horizontal-pass results of the current 16 rows (8 columns per warp)
     uint32_t outbuf[kMaxFlush][kStripCols];  // packed output rows completed in this stage
-    int out_row[kMaxFlush];
+    int out_row[kWarps][kMaxFlush];
     int ys, ye;
+    int done_cnt[4];                         // warps finished with each stage
     uint64_t full[4];
 };
 
@@ -119,29 +127,34 @@ struct SmemFixed {                            // lives after the stages in dynam
 // are all fill (fill_pre), and the margins left / right of the kept columns.  Each CTA owns the
 // canvas rows of its band and the canvas columns of its strip (edge bands / strips extend to the
 // canvas border).
-__device__ void fill_region(const FastResizeParams &p, uint32_t *dst, int i0, int i1, int tid) {
+__device__ __noinline__ void fill_region(const FastResizeParams &p, uint32_t *dst, int i0, int i1, int tid) {
     const bool first_band = blockIdx.y == 0, last_band = blockIdx.y + 1 == p.n_bands;
     const bool first_strip = blockIdx.x == 0, last_strip = blockIdx.x + 1 == p.n_strips;
     const int fr0 = first_band ? 0 : int(p.foy) + i0, fr1 = last_band ? int(p.fh) : int(p.foy) + i1;
     const int cx0 = first_strip ? 0 : int(p.fox) + int(blockIdx.x) * kStripCols;
     const int cx1 = last_strip ? int(p.fw) : int(p.fox) + int(blockIdx.x + 1) * kStripCols;
     const int kx0 = int(p.fox), kx1 = int(p.fox + p.pw);
+    const bool margins = cx0 < kx0 || kx1 < cx1;
     const int warp = tid >> 5, lane = tid & 31;
+#pragma unroll 1
     for (int fr = fr0 + warp; fr < fr1; fr += kWarps) {
         const int i = fr - int(p.foy);
         const bool kept = i >= 0 && i < int(p.ph);
         const bool computed = kept && p.row_computed[i];
+        if (computed && !margins) continue;
         uint32_t *row = dst + size_t(fr) * p.fw;
-        if (computed) {                        // only the margins
-            for (int x = cx0 + lane; x < min(cx1, kx0); x += 32) row[x] = p.fill_post;
-            for (int x = max(cx0, kx1) + lane; x < cx1; x += 32) row[x] = p.fill_post;
-        } else {
-            for (int x = cx0 + lane; x < cx1; x += 32)
-                row[x] = (kept && x >= kx0 && x < kx1) ? p.fill_pre_packed : p.fill_post;
+#pragma unroll 1
+        for (int x = cx0 + lane; x < cx1; x += 32) {
+            const bool in_cols = x >= kx0 && x < kx1;
+            if (computed && in_cols) continue;
+            row[x] = (kept && in_cols) ? p.fill_pre_packed : p.fill_post;
         }
     }
 }
 
+// NCH > 0: every tile of the launch spans at most NCH k-chunks and its weight fragments stay in
+// registers for the whole band; NCH == 0: any chunk count, fragments are re-read (L1/L2) per stage.
+template <int NCH>
 __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResizeParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     const uint32_t stage_bytes = kRows * p.pitch + kVTabBytes;     // pixel rows, then the VQuad slice
@@ -156,7 +169,7 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
     const int i1 = int((uint64_t(blockIdx.y + 1) * p.ph) / p.n_bands);
     if (tid == 0) {
         sm.ys = 0x7fffffff; sm.ye = 0;
-        for (uint32_t s = 0; s < p.stages; s++) mbar_init(&sm.full[s], 1);
+        for (uint32_t s = 0; s < p.stages; s++) { mbar_init(&sm.full[s], 1); sm.done_cnt[s] = 0; }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -171,18 +184,19 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
     const int ys = any_rows ? (sm.ys & ~3) : 0;          // VQuad slices start on a multiple of 4 rows
     const int n_iter = any_rows ? (sm.ye - ys + kRows - 1) / kRows : 0;
 
-    // ---- staging: threads 0..16 of the CTA drive the TMA engine ------------------------------------
+    // ---- staging: warp 0 drives the TMA engine, one linear bulk copy per lane (16 rows + table) ----
     const int strip_col = p.strip_a0[blockIdx.x];
     const uint32_t row_bytes = uint32_t(p.strip_bytes[blockIdx.x]);
-    auto issue_stage = [&](int it) {
+    auto issue_stage = [&](int it) {               // called by all lanes of warp 0
         const int s = it % int(p.stages);
         uint8_t *stage = smem_raw + size_t(s) * stage_bytes;
         const int y0 = ys + it * kRows;
-        if (tid == 0) mbar_arrive_expect_tx(&sm.full[s], kRows * row_bytes + kVTabBytes);
-        if (tid < kRows) {
-            const int row = min(int(p.ry) + y0 + tid, int(p.sh) - 1);     // rows past the end carry zero weights
-            bulk_g2s(stage + size_t(tid) * p.pitch, src + (size_t(row) * p.sw + strip_col) * 4, row_bytes, &sm.full[s]);
-        } else if (tid == kRows) {
+        if (lane == 0) mbar_arrive_expect_tx(&sm.full[s], kRows * row_bytes + kVTabBytes);
+        __syncwarp();
+        if (lane < kRows) {
+            const int row = min(int(p.ry) + y0 + lane, int(p.sh) - 1);    // rows past the end carry zero weights
+            bulk_g2s(stage + size_t(lane) * p.pitch, src + (size_t(row) * p.sw + strip_col) * 4, row_bytes, &sm.full[s]);
+        } else if (lane == kRows) {
             bulk_g2s(stage + size_t(kRows) * p.pitch, p.vquad + (y0 >> 2), kVTabBytes, &sm.full[s]);
         }
     };
@@ -198,11 +212,19 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
     const uint2 *bfrag = reinterpret_cast<const uint2 *>(p.bfrag) + (has_tile ? size_t(p.tile_boff[tile]) * 96 : 0) + lane;
     const float fwx0 = has_tile ? p.fillw_x[tile * 8 + 2 * t] : 0.0f, fwx1 = has_tile ? p.fillw_x[tile * 8 + 2 * t + 1] : 0.0f;
     const uint32_t frag_off = uint32_t(g) * p.pitch + uint32_t(tile_off + 4 * t) * 4;
+    uint2 bw[NCH > 0 ? NCH : 1][3];
+    if (NCH > 0) {
+#pragma unroll
+        for (int c = 0; c < NCH; c++)
+#pragma unroll
+            for (int l = 0; l < 3; l++) bw[c][l] = c < nchunks ? __ldg(bfrag + (c * 3 + l) * 32) : make_uint2(0u, 0u);
+    }
 
-    // ---- vertical-pass role: thread -> (output column, slot pair); all four channels -------------
+    // ---- vertical-pass role: thread -> (output column of the warp's own tile, slot pair) ----------
     const int vcol = tid >> 2, sp = tid & 3;
     float2 va01 = {0.f, 0.f}, va23 = {0.f, 0.f}, vb01 = {0.f, 0.f}, vb23 = {0.f, 0.f};   // slots 2sp, 2sp+1
     const int col0 = blockIdx.x * kStripCols;
+    int *my_out_row = sm.out_row[warp];
 
     for (int it = 0; it < n_iter; it++) {
         const int s = it % int(p.stages);
@@ -213,16 +235,8 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
         // ================= horizontal pass: 16 staged rows -> sm.inter ===========================
         if (has_tile) {
             int acc[3][4][4];
-#pragma unroll
-            for (int l = 0; l < 3; l++)
-#pragma unroll
-                for (int c = 0; c < 4; c++)
-#pragma unroll
-                    for (int r = 0; r < 4; r++) acc[l][c][r] = 0;
-
             const uint8_t *pa = stage + frag_off, *pb = pa + 8 * p.pitch;
-#pragma unroll 2
-            for (int c = 0; c < nchunks; c++) {
+            auto chunk = [&](int c, const uint2 (&b)[3], bool first) {
                 const uint4 q0 = *reinterpret_cast<const uint4 *>(pa + 128 * c);
                 const uint4 q1 = *reinterpret_cast<const uint4 *>(pb + 128 * c);
                 const uint4 q2 = *reinterpret_cast<const uint4 *>(pa + 128 * c + 64);
@@ -233,10 +247,27 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
                 transpose4(q2, A[0][2], A[1][2], A[2][2], A[3][2]);
                 transpose4(q3, A[0][3], A[1][3], A[2][3], A[3][3]);
 #pragma unroll
-                for (int l = 0; l < 3; l++) {
-                    const uint2 b = __ldg(bfrag + (size_t(c) * 3 + l) * 32);
+                for (int l = 0; l < 3; l++)
 #pragma unroll
-                    for (int ch = 0; ch < 4; ch++) imma_16832(acc[l][ch], A[ch], b.x, b.y);
+                    for (int ch = 0; ch < 4; ch++) {
+                        if (first) imma_16832_z(acc[l][ch], A[ch], b[l].x, b[l].y);
+                        else imma_16832(acc[l][ch], A[ch], b[l].x, b[l].y);
+                    }
+            };
+            if (NCH > 0) {
+#pragma unroll
+                for (int c = 0; c < NCH; c++)
+                    if (c == 0 || c < nchunks) chunk(c, bw[c], c == 0);
+            } else {
+                uint2 b[3];
+#pragma unroll
+                for (int l = 0; l < 3; l++) b[l] = nchunks > 0 ? __ldg(bfrag + l * 32) : make_uint2(0u, 0u);
+                chunk(0, b, true);
+#pragma unroll 1
+                for (int c = 1; c < nchunks; c++) {
+#pragma unroll
+                    for (int l = 0; l < 3; l++) b[l] = __ldg(bfrag + (size_t(c) * 3 + l) * 32);
+                    chunk(c, b, false);
                 }
             }
             // recombine the three digit planes, scale, add the fill constant, store f32
@@ -257,7 +288,7 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
                 }
             }
         }
-        __syncthreads();
+        __syncwarp();        // the warp's vertical pass reads only the 8 columns the warp itself produced
 
         // ================= vertical pass: stream the 16 rows through the slots ======================
         const VQuad *vq = reinterpret_cast<const VQuad *>(stage + size_t(kRows) * p.pitch);
@@ -291,7 +322,7 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
                                                      (quantize_channel(fmaf(p.fill_pre[2], fy, b.x)) << 16) |
                                                      (quantize_channel(fmaf(p.fill_pre[3], fy, b.y)) << 24);
                             }
-                            if (vcol == 0 && k < kMaxFlush) sm.out_row[k] = mine ? i : -1;
+                            if ((lane >> 2) == 0 && k < kMaxFlush) my_out_row[k] = mine ? i : -1;
                             if (h) { vb01 = {0.f, 0.f}; vb23 = {0.f, 0.f}; } else { va01 = {0.f, 0.f}; va23 = {0.f, 0.f}; }
                         }
                     }
@@ -299,18 +330,19 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
                 }
             }
         }
-        __syncthreads();                                  // everyone is done with the stage, inter and outbuf are final
+        __syncwarp();
 
-        if (warp == 0 && it + int(p.stages) < n_iter) issue_stage(it + int(p.stages));   // refill this stage
-
-        // ================= store the output rows completed in this stage ============================
+        // ================= store the output rows this warp completed in this stage ==================
         n_flush = min(n_flush, kMaxFlush);
-        for (int idx = tid; idx < n_flush * kStripCols; idx += kThreads) {
-            const int k = idx >> 6, c = idx & 63;
-            const int i = sm.out_row[k];
+        for (int idx = lane; idx < n_flush * 8; idx += 32) {
+            const int k = idx >> 3, c = warp * 8 + (idx & 7);
+            const int i = my_out_row[k];
             if (i >= 0 && col0 + c < int(p.pw)) dst[size_t(p.foy + i) * p.fw + p.fox + col0 + c] = sm.outbuf[k][c];
         }
-        // the next iteration's first __syncthreads orders these reads before outbuf / inter are rewritten
+        // every warp is done with the stage: refill it for iteration it + stages.  (The barrier also
+        // orders this warp's reads of inter / outbuf before the next stage rewrites them.)
+        __syncthreads();
+        if (warp == 0 && it + int(p.stages) < n_iter) issue_stage(it + int(p.stages));
     }
 
     if (p.n_fill_blocks) fill_region(p, dst, i0, i1, tid);
@@ -318,16 +350,15 @@ __global__ void __launch_bounds__(kThreads, 2) resize_fast_kernel(const FastResi
 
 }  // namespace
 
-cudaError_t launch_resize_fast(const FastResizeParams &p, uint32_t n_images, cudaStream_t stream) {
-    if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
-    if (p.n_bands > 65535 || p.n_strips == 0) return cudaErrorInvalidValue;
+template <int NCH>
+static cudaError_t launch_fast_t(const FastResizeParams &p, uint32_t n_images, cudaStream_t stream) {
     static thread_local int configured_dev = -1;
     int dev = 0;
     cudaGetDevice(&dev);
     if (configured_dev != dev) {
-        cudaError_t e = cudaFuncSetAttribute(resize_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(resize_fast_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(resize_fast_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        e = cudaFuncSetAttribute(resize_fast_kernel<NCH>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         if (e != cudaSuccess) return e;
         configured_dev = dev;
     }
@@ -344,12 +375,20 @@ cudaError_t launch_resize_fast(const FastResizeParams &p, uint32_t n_images, cud
         q.src = p.src + size_t(first) * p.src_img_bytes;
         q.dst = p.dst + size_t(first) * p.dst_img_bytes;
         const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
-        resize_fast_kernel<<<dim3(p.n_strips, p.n_bands, nz), kThreads, q.smem_bytes, stream>>>(q);
+        resize_fast_kernel<NCH><<<dim3(p.n_strips, p.n_bands, nz), kThreads, q.smem_bytes, stream>>>(q);
         count_launch();
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
     return cudaSuccess;
+}
+
+cudaError_t launch_resize_fast(const FastResizeParams &p, uint32_t n_images, cudaStream_t stream) {
+    if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
+    if (p.n_bands > 65535 || p.n_strips == 0) return cudaErrorInvalidValue;
+    if (p.max_chunks <= 2) return launch_fast_t<2>(p, n_images, stream);
+    if (p.max_chunks <= 4) return launch_fast_t<4>(p, n_images, stream);
+    return launch_fast_t<0>(p, n_images, stream);
 }
 
 }  // namespace slimg

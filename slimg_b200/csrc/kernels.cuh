@@ -71,6 +71,7 @@ struct FastResizeParams {
     const int32_t *tile_nchunks;     // [n_tiles] 32-pixel k-chunks the tile's taps span
     const int32_t *strip_a0;         // [n_strips] absolute source column where the strip's staged span starts (multiple of 4)
     const int32_t *strip_bytes;      // [n_strips] bytes of each source row staged for the strip (multiple of 16)
+    uint32_t max_chunks;             // largest tile_nchunks of the plan
     uint32_t pitch;                  // bytes between staged rows in shared memory (== 64 mod 128)
     uint32_t stages;                 // depth of the staging ring
     uint32_t smem_bytes;             // dynamic shared memory of the launch
