@@ -54,6 +54,10 @@ struct ResizePlan {
     bool fast = false;
     DevArray f_a0, f_nch, f_boff, f_bfrag, f_fillx, f_vrow, f_vleft, f_vright, f_filly, f_rowc, f_sa0, f_sbytes;
     FastResizeParams fparams{};
+    // V-first integer tensor pipeline (k2_vfirst.cu), preferred when the geometry qualifies
+    bool vfirst = false;
+    DevArray v_a0, v_need, v_nch, v_b1, v_bias, v_rowc, v_col0, v_src0, v_nblk, v_bytes, v_kb0, v_tnch, v_b2, v_cx;
+    VfParams vparams{};
 };
 
 struct GeomKey {
@@ -139,10 +143,48 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
     p.tile_w = tile_w; p.tile_h = tile_h; p.span_max = span_max;
     p.tile_x0 = (const int32_t *)plan->tx0.p;
     p.tile_span = (const int32_t *)plan->tspan.p;
-    // tensor-core fast path
+    // which resize kernel: SLIMG_B200_RESIZE_PATH = vfirst (default) | hfirst | generic
+    const char *path_env = std::getenv("SLIMG_B200_RESIZE_PATH");
+    const std::string path = path_env ? path_env : "vfirst";
+    if (path == "vfirst") {
+        const char *dig_env = std::getenv("SLIMG_B200_DIGITS");
+        const int ndig = dig_env && dig_env[0] == '2' ? 2 : 3;
+        VPlanHost vp;
+        build_vplan(g, tx, ty, ndig, vp);
+        if (vp.ok) {
+            if ((e = plan->v_a0.upload(vp.grp_a0)) || (e = plan->v_need.upload(vp.grp_need)) ||
+                (e = plan->v_nch.upload(vp.grp_nch)) || (e = plan->v_b1.upload(vp.b1)) || (e = plan->v_bias.upload(vp.bias)) ||
+                (e = plan->v_rowc.upload(vp.row_computed)) || (e = plan->v_col0.upload(vp.strip_col0)) ||
+                (e = plan->v_src0.upload(vp.strip_src0)) || (e = plan->v_nblk.upload(vp.strip_nblk)) ||
+                (e = plan->v_bytes.upload(vp.strip_bytes)) || (e = plan->v_kb0.upload(vp.tile_kb0)) ||
+                (e = plan->v_tnch.upload(vp.tile_nch)) || (e = plan->v_b2.upload(vp.b2)) || (e = plan->v_cx.upload(vp.cx)))
+                return cuda_fail(e, "uploading V-first resize plan");
+            VfParams &v = plan->vparams;
+            v.sw = g.sw; v.sh = g.sh; v.ry = g.ry; v.pw = g.pw; v.ph = g.ph;
+            v.ndig = vp.ndig; v.nch1 = vp.nch1; v.nch2 = vp.nch2;
+            v.n_groups = vp.n_groups;
+            v.grp_a0 = (const int32_t *)plan->v_a0.p; v.grp_need = (const int32_t *)plan->v_need.p;
+            v.grp_nch = (const int32_t *)plan->v_nch.p; v.b1 = (const uint32_t *)plan->v_b1.p;
+            v.bias = (const int32_t *)plan->v_bias.p; v.row_computed = (const uint8_t *)plan->v_rowc.p;
+            v.sh1 = vp.sh1;
+            v.n_strips = vp.n_strips;
+            v.strip_col0 = (const int32_t *)plan->v_col0.p; v.strip_src0 = (const int32_t *)plan->v_src0.p;
+            v.strip_nblk = (const int32_t *)plan->v_nblk.p; v.strip_bytes = (const int32_t *)plan->v_bytes.p;
+            v.tile_kb0 = (const int32_t *)plan->v_kb0.p; v.tile_nch = (const int32_t *)plan->v_tnch.p;
+            v.b2 = (const uint32_t *)plan->v_b2.p; v.cx = (const float *)plan->v_cx.p;
+            for (int l = 0; l < 2; l++)
+                for (int d = 0; d < 3; d++) v.s2[l][d] = vp.s2[l][d];
+            v.ring_rows = vp.ring_rows; v.pitch = vp.pitch; v.pitch_v = vp.pitch_v; v.smem_bytes = vp.smem_bytes;
+            v.fw = g.fw; v.fh = g.fh; v.fox = g.fox; v.foy = g.foy;
+            v.fill_post = pack_fill(g.fill_post); v.fill_pre_packed = pack_fill(g.fill_pre);
+            v.n_bands = 1; v.need_fill = vp.need_fill ? 1 : 0;
+            plan->vfirst = true;
+        }
+    }
+    // H-first tensor-core path (kept for A/B comparison)
     FastPlanHost fp;
     build_fast_plan(g, tx, ty, fp);
-    if (fp.ok && std::getenv("SLIMG_B200_FORCE_GENERIC") == nullptr) {
+    if (fp.ok && path != "generic" && std::getenv("SLIMG_B200_FORCE_GENERIC") == nullptr) {
         std::vector<VQuad> vquads(fp.vrow_w.size() / 32);
         for (size_t y = 0; y < vquads.size() * 4; y++) {
             VQuad &v = vquads[y / 4];
@@ -224,6 +266,18 @@ static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, u
     std::shared_ptr<ResizePlan> plan;
     slimg_status st = get_resize_plan(g, plan);
     if (st != SLIMG_OK) return st;
+    if (plan->vfirst && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        VfParams v = plan->vparams;
+        v.src = src; v.dst = dst; v.src_img_bytes = src_bytes; v.dst_img_bytes = dst_bytes;
+        // bands of output-row groups: enough CTAs to fill the GPU when the batch is small, no halo
+        // recomputation (one band's worth of source rows per extra band) when the batch alone fills it
+        const uint64_t ctas_per_band = uint64_t(v.n_strips) * n;
+        uint32_t bands = uint32_t((2 * 148 + ctas_per_band - 1) / ctas_per_band);
+        bands = std::max<uint32_t>(1, std::min<uint32_t>(bands, std::max<uint32_t>(1, v.n_groups / 4)));
+        v.n_bands = bands;
+        CU(launch_resize_vfirst(v, n, stream));
+        return SLIMG_OK;
+    }
     if (plan->fast && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
         FastResizeParams f = plan->fparams;
         f.src = src; f.dst = dst; f.src_img_bytes = src_bytes; f.dst_img_bytes = dst_bytes;

@@ -80,4 +80,33 @@ struct FastPlanHost {
 };
 void build_fast_plan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, FastPlanHost &out);
 
+// ---- V-first integer tensor pipeline plan (vplan.cpp, k2_vfirst.cu) ------------------------------
+// Pass 1 (vertical) and pass 2 (horizontal) both run as u8 x s8 integer MMAs; the weights of taps.cpp
+// are quantised to fixed point and split into NDIG signed base-256 digits.
+struct VPlanHost {
+    bool ok = false;
+    int ndig = 3;
+    // vertical: groups of 8 kept output rows
+    uint32_t n_groups = 0;
+    int nch1 = 0;                          // max 32-row chunks a group's band spans
+    std::vector<int32_t> grp_a0, grp_need, grp_nch;
+    std::vector<uint32_t> b1;              // [n_groups][nch1][ndig][32 lanes][2]
+    std::vector<int32_t> bias;             // [n_groups*8][4]
+    std::vector<uint8_t> row_computed;     // [ph]
+    int sh1 = 0;                           // V16 = (x + bias) >> sh1
+    // horizontal: strips of <= 64 kept output columns, tiles of 8
+    uint32_t n_strips = 0;
+    int nch2 = 0;                          // max 32-pixel chunks a tile's band spans
+    std::vector<int32_t> strip_col0;       // [n_strips + 1]
+    std::vector<int32_t> strip_src0, strip_nblk, strip_bytes;   // [n_strips]
+    std::vector<int32_t> tile_kb0, tile_nch;                    // [n_strips][8]
+    std::vector<uint32_t> b2;              // [n_strips][8][nch2][ndig][32][2]
+    std::vector<float> cx;                 // [pw][4]
+    float s2[2][3] = {{0, 0, 0}, {0, 0, 0}};
+    // shared-memory geometry
+    uint32_t ring_rows = 0, pitch = 0, pitch_v = 0, smem_bytes = 0;
+    bool need_fill = false;
+};
+void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int ndig, VPlanHost &out);
+
 }  // namespace slimg

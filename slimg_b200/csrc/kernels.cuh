@@ -91,6 +91,45 @@ struct FastResizeParams {
 };
 cudaError_t launch_resize_fast(const FastResizeParams &p, uint32_t n_images, cudaStream_t stream);
 
+// ---- K2 V-first integer tensor pipeline (k2_vfirst.cu, plan in vplan.cpp) ---------------------------
+struct VfParams {
+    const uint8_t *src;
+    uint8_t *dst;
+    size_t src_img_bytes, dst_img_bytes;
+    uint32_t sw, sh;                 // source pitch (pixels) and height
+    uint32_t ry;                     // first row of the source rectangle
+    uint32_t pw, ph;                 // columns / rows of the resize output that are kept
+    int32_t ndig, nch1, nch2;        // weight digits; max chunks per group (pass 1) / tile (pass 2)
+    // vertical pass: groups of 8 kept output rows
+    uint32_t n_groups;
+    const int32_t *grp_a0;           // [n_groups] first rectangle row of the group's band
+    const int32_t *grp_need;         // [n_groups] end (exclusive) of the rows the group reads with non-zero weight
+    const int32_t *grp_nch;          // [n_groups] 32-row chunks of the band (0: nothing to compute)
+    const uint32_t *b1;              // [n_groups][4][ndig][32 lanes][2] weight fragments (s8 x4 per word)
+    const int32_t *bias;             // [n_groups*8][4] fill term + offset + rounding half, per row and channel
+    const uint8_t *row_computed;     // [ph]
+    int32_t sh1;                     // right shift that turns the s32 sum into the u16 intermediate
+    // horizontal pass: strips of <= 64 kept output columns, tiles of 8
+    uint32_t n_strips;
+    const int32_t *strip_col0;       // [n_strips+1] first kept column of each strip
+    const int32_t *strip_src0;       // [n_strips] absolute source column where the staged span starts (multiple of 4)
+    const int32_t *strip_nblk;       // [n_strips] 16-byte blocks of each staged row
+    const int32_t *strip_bytes;      // [n_strips] bytes staged per source row
+    const int32_t *tile_kb0;         // [n_strips][8] first block of the tile's k range
+    const int32_t *tile_nch;         // [n_strips][8] 32-pixel chunks of the tile's k range
+    const uint32_t *b2;              // [n_strips][8][4][ndig][32 lanes][2]
+    const float *cx;                 // [pw][4] constant term per kept column and channel
+    float s2[2][3];                  // scale of accumulator [limb][digit]
+    // shared memory geometry
+    uint32_t ring_rows, pitch, pitch_v, smem_bytes;
+    // canvas
+    uint32_t fw, fh, fox, foy;
+    uint32_t fill_post, fill_pre_packed;
+    uint32_t n_bands, need_fill;
+};
+cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStream_t stream);
+size_t vfirst_smem_tail_bytes();
+
 // ---- K3+K4: JPEG pre-entropy front end (k3_jpeg.cu) ------------------------------------------
 struct QuantDev {                      // jcdctmgr.c:173-221 compute_reciprocal, per table entry
     uint32_t recip[2][64];

@@ -1,0 +1,287 @@
+// vplan.cpp -- host-side plan of the V-first integer tensor pipeline (k2_vfirst.cu).
+//
+// Both passes of the Lanczos3 downscale are integer GEMMs on the tensor cores (u8 x s8 -> s32):
+//   pass 1 (vertical)   D1[byte of the row][8 output rows]      = sum over source rows
+//   pass 2 (horizontal) D2[(channel,row)][8 output columns]     = sum over source pixels
+// The f32 weights of taps.cpp are turned into fixed point (S fractional bits) and split into NDIG
+// balanced base-256 digits (s8).  The pass-1 result is re-quantised to 16 bits (7 fractional bits,
+// offset so it is never negative) and enters pass 2 as two u8 limbs.  All arithmetic up to the final
+// float recombination is exact integer arithmetic, so the only errors are the weight quantisation
+// (<= 2^-(S+1) per tap) and the 2^-8 rounding of the intermediate.
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+
+#include "host.h"
+
+namespace slimg {
+
+namespace {
+
+constexpr int kFrac = 7;        // fractional bits of the 16-bit intermediate
+constexpr int kOffset = 64;     // added to the intermediate so Lanczos undershoot stays >= 0
+constexpr int kPrefetchRows = 48;
+constexpr int kMaxCh = 4;          // chunk stride of the fragment tables (the kernel's NCH1 / NCH2)
+constexpr size_t kSmemBudget = 227 * 1024 - 2048;
+const int kPerm[4] = {0, 2, 1, 3};   // k-slot -> pixel inside a 4-pixel block (k2_vfirst.cu, pass-1 epilogue)
+
+// quantise one output's taps so that they sum to round(sum(w) * 2^S) exactly
+void quantise(const float *w, int cnt, int S, std::vector<int64_t> &q) {
+    q.assign(cnt, 0);
+    double sum_w = 0.0;
+    int64_t sum_q = 0;
+    int big = 0;
+    for (int i = 0; i < cnt; i++) {
+        sum_w += double(w[i]);
+        q[i] = std::llround(double(w[i]) * std::ldexp(1.0, S));
+        sum_q += q[i];
+        if (std::fabs(w[i]) > std::fabs(w[big])) big = i;
+    }
+    if (cnt) q[big] += std::llround(sum_w * std::ldexp(1.0, S)) - sum_q;
+}
+
+bool split_digits(int64_t x, int ndig, int8_t d[3]) {
+    d[0] = d[1] = d[2] = 0;
+    for (int l = 0; l < ndig; l++) {
+        const int64_t dl = ((x + 128) & 255) - 128;
+        d[l] = int8_t(dl);
+        x = (x - dl) / 256;
+    }
+    return x == 0;
+}
+
+int pick_scale(float maxw, int ndig) {
+    // largest S with maxw * 2^S inside the digit range (with a little room for the sum fix-up)
+    const double range = ndig == 2 ? 32000.0 : 8.0e6;
+    int S = int(std::floor(std::log2(range / double(maxw))));
+    return std::min(S, 22);
+}
+
+// B fragment of mma.m16n8k32 (col-major K x N): lane = n*4 + (k%16)/4, register = k/16, byte = k%4
+inline void put_b(uint32_t *frag, int k, int n, int8_t v) {
+    const int lane = n * 4 + (k % 16) / 4, reg = k / 16, byte = k % 4;
+    frag[lane * 2 + reg] |= uint32_t(uint8_t(v)) << (8 * byte);
+}
+
+}  // namespace
+
+void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int ndig, VPlanHost &out) {
+    out = VPlanHost();
+    out.ndig = ndig;
+    if (!g.has_resize) return;
+    if (g.vw < g.Rw || g.vh < g.Rh) return;          // downscale (ratio >= 1) on both axes
+    if (g.sw % 4 != 0 || g.sw < 4) return;           // 16-byte aligned rows
+    if (g.pw == 0 || g.ph == 0 || g.rw == 0 || g.rh == 0) return;
+
+    // ---------------- vertical pass ----------------
+    float maxw_y = 0.0f;
+    for (uint32_t i = 0; i < g.ph; i++) {
+        const uint32_t o = g.py + i;
+        for (int k = 0; k < ty.count[o]; k++) maxw_y = std::max(maxw_y, std::fabs(ty.w[size_t(o) * ty.max_taps + k]));
+    }
+    if (!(maxw_y > 0.0f)) return;
+    const int Sy = pick_scale(maxw_y, ndig);
+    if (Sy < kFrac + 2) return;
+    out.sh1 = Sy - kFrac;
+
+    out.n_groups = (g.ph + 7) / 8;
+    out.grp_a0.assign(out.n_groups, 0);
+    out.grp_need.assign(out.n_groups, 0);
+    out.grp_nch.assign(out.n_groups, 0);
+    out.row_computed.assign(g.ph, 0);
+    out.bias.assign(size_t(out.n_groups) * 8 * 4, 0);
+    int max_need = 0;
+    for (uint32_t j = 0; j < out.n_groups; j++) {
+        int lo = INT32_MAX, hi = -1;
+        for (uint32_t n = 0; n < 8 && j * 8 + n < g.ph; n++) {
+            const uint32_t o = g.py + j * 8 + n;
+            if (ty.count[o] == 0) continue;
+            lo = std::min(lo, ty.left[o]);
+            hi = std::max(hi, ty.left[o] + ty.count[o]);
+        }
+        if (hi < 0) continue;
+        out.grp_a0[j] = lo;
+        out.grp_need[j] = hi;
+        out.grp_nch[j] = (hi - lo + 31) / 32;
+        out.nch1 = std::max(out.nch1, out.grp_nch[j]);
+        max_need = std::max(max_need, hi - lo);
+    }
+    if (out.nch1 == 0 || out.nch1 > kMaxCh) return;       // bands of more than 128 source rows: other kernels
+    // bands must move down monotonically (ring buffer)
+    {
+        int prev = -1;
+        for (uint32_t j = 0; j < out.n_groups; j++) {
+            if (out.grp_nch[j] == 0) continue;
+            if (out.grp_a0[j] < prev) return;
+            prev = out.grp_a0[j];
+        }
+    }
+    out.b1.assign(size_t(out.n_groups) * kMaxCh * ndig * 64, 0u);
+    std::vector<int64_t> q;
+    for (uint32_t j = 0; j < out.n_groups; j++) {
+        for (uint32_t n = 0; n < 8; n++) {
+            const uint32_t i = j * 8 + n;
+            if (i >= g.ph) break;
+            const uint32_t o = g.py + i;
+            const int cnt = ty.count[o];
+            const float *w = &ty.w[size_t(o) * ty.max_taps];
+            quantise(w, cnt, Sy, q);
+            int64_t pos = 0, neg = 0;
+            for (int k = 0; k < cnt; k++) {
+                (q[k] > 0 ? pos : neg) += q[k];
+                int8_t d[3];
+                if (!split_digits(q[k], ndig, d)) return;
+                const int row = ty.left[o] + k - out.grp_a0[j];     // row inside the group's band
+                for (int l = 0; l < ndig; l++)
+                    put_b(&out.b1[((size_t(j) * kMaxCh + row / 32) * ndig + l) * 64], row % 32, int(n), d[l]);
+            }
+            out.row_computed[i] = cnt > 0;
+            // bias = fill term + offset + rounding half; the 16-bit intermediate must stay in range
+            for (int c = 0; c < 4; c++) {
+                const int64_t fillterm = std::llround(double(g.fill_pre[c]) * double(ty.fillw[o]) * std::ldexp(1.0, Sy));
+                const int64_t bias = fillterm + (int64_t(kOffset) << Sy) + (int64_t(1) << (out.sh1 - 1));
+                const int64_t lo_x = 255 * neg + bias, hi_x = 255 * pos + bias;
+                if (lo_x < 0 || (hi_x >> out.sh1) > 65535 || hi_x > INT32_MAX || bias > INT32_MAX) return;
+                out.bias[size_t(i) * 4 + c] = int32_t(bias);
+            }
+        }
+    }
+
+    // ---------------- horizontal pass ----------------
+    float maxw_x = 0.0f;
+    for (uint32_t j = 0; j < g.pw; j++) {
+        const uint32_t o = g.px + j;
+        for (int k = 0; k < tx.count[o]; k++) maxw_x = std::max(maxw_x, std::fabs(tx.w[size_t(o) * tx.max_taps + k]));
+    }
+    if (!(maxw_x > 0.0f)) return;
+    const int Sx = pick_scale(maxw_x, ndig);
+    if (Sx < 8) return;
+    for (int l = 0; l < 2; l++)
+        for (int d = 0; d < 3; d++) out.s2[l][d] = d < ndig ? float(std::ldexp(1.0, 8 * l + 8 * d - Sx - kFrac)) : 0.0f;
+
+    // ring depth: the rows a group needs plus what should be in flight, in 16-row steps
+    const uint32_t ring_rows = uint32_t((std::max(32 * out.nch1, max_need + kPrefetchRows) + 15) / 16 * 16);
+    out.ring_rows = ring_rows;
+    const size_t fixed_bytes = 2 * 8 * 64 * 4 /* output staging */ + 1024 /* barriers, bookkeeping */;
+
+    // span of source pixels (absolute columns) a range of kept output columns needs
+    auto span_of = [&](uint32_t c0, uint32_t c1, int64_t &lo, int64_t &hi) {
+        lo = INT64_MAX; hi = -1;
+        for (uint32_t j = c0; j < c1; j++) {
+            const uint32_t o = g.px + j;
+            if (tx.count[o] == 0) continue;
+            lo = std::min<int64_t>(lo, int64_t(g.rx) + tx.left[o]);
+            hi = std::max<int64_t>(hi, int64_t(g.rx) + tx.left[o] + tx.count[o]);
+        }
+    };
+    auto smem_for = [&](int64_t nblk, uint32_t &pitch, uint32_t &pitch_v) {
+        int64_t units = nblk | 1;                                  // odd multiple of 16 bytes
+        pitch = uint32_t(units * 16);
+        int64_t qv = (nblk + 3 + 3) / 4;                           // words per V row = 4 * odd >= nblk + 3
+        if (qv % 2 == 0) qv++;
+        pitch_v = uint32_t(qv * 16);
+        return size_t(ring_rows) * pitch + size_t(4) * 32 * pitch_v + fixed_bytes;
+    };
+    // widest strips (multiple of 8 columns, at most 64) whose staging fits in shared memory
+    uint32_t cols = 0;
+    for (uint32_t cand = 64; cand >= 8; cand -= 8) {
+        bool fits = true;
+        for (uint32_t c0 = 0; c0 < g.pw && fits; c0 += cand) {
+            int64_t lo, hi;
+            span_of(c0, std::min(g.pw, c0 + cand), lo, hi);
+            if (hi < 0) continue;
+            const int64_t nblk = (hi - (lo & ~int64_t(3)) + 3) / 4;
+            uint32_t p, pv;
+            if (smem_for(nblk, p, pv) > kSmemBudget) fits = false;
+        }
+        if (fits) { cols = cand; break; }
+    }
+    if (cols == 0) return;
+    out.n_strips = (g.pw + cols - 1) / cols;
+    // even the strips out (keeps the multiple of 8)
+    cols = std::min<uint32_t>(cols, ((g.pw + out.n_strips - 1) / out.n_strips + 7) / 8 * 8);
+    out.n_strips = (g.pw + cols - 1) / cols;
+
+    out.strip_col0.assign(out.n_strips + 1, 0);
+    out.strip_src0.assign(out.n_strips, 0);
+    out.strip_nblk.assign(out.n_strips, 1);
+    out.strip_bytes.assign(out.n_strips, 16);
+    out.tile_kb0.assign(size_t(out.n_strips) * 8, 0);
+    out.tile_nch.assign(size_t(out.n_strips) * 8, 0);
+    out.cx.assign(size_t(g.pw) * 4, 0.0f);
+    int64_t max_nblk = 1;
+    struct TileQ { std::vector<std::vector<int64_t>> q; };
+    // first sweep: geometry and the chunk count
+    for (uint32_t s = 0; s < out.n_strips; s++) {
+        const uint32_t c0 = s * cols, c1 = std::min(g.pw, c0 + cols);
+        out.strip_col0[s] = int32_t(c0);
+        out.strip_col0[s + 1] = int32_t(c1);
+        int64_t lo, hi;
+        span_of(c0, c1, lo, hi);
+        if (hi < 0) continue;                        // every tap of the strip lands on fill
+        const int64_t s0 = lo & ~int64_t(3);
+        const int64_t nblk = (hi - s0 + 3) / 4;
+        out.strip_src0[s] = int32_t(s0);
+        out.strip_nblk[s] = int32_t(nblk);
+        out.strip_bytes[s] = int32_t((std::min<int64_t>(s0 + nblk * 4, g.sw) - s0) * 4);
+        max_nblk = std::max(max_nblk, nblk);
+        for (uint32_t t = 0; t * 8 < c1 - c0; t++) {
+            int64_t tlo, thi;
+            span_of(c0 + t * 8, std::min(c1, c0 + t * 8 + 8), tlo, thi);
+            if (thi < 0) continue;
+            int64_t kb0 = (tlo - s0) / 4;
+            int64_t nch = (thi - s0 - kb0 * 4 + 31) / 32;
+            if (kb0 + 8 * nch > nblk && nblk >= 8 * nch) {      // keep the chunks inside the staged span
+                kb0 = nblk - 8 * nch;
+            }
+            out.tile_kb0[s * 8 + t] = int32_t(kb0);
+            out.tile_nch[s * 8 + t] = int32_t(nch);
+            out.nch2 = std::max(out.nch2, int(nch));
+        }
+    }
+    if (out.nch2 == 0 || out.nch2 > kMaxCh) return;
+    out.smem_bytes = uint32_t(smem_for(max_nblk, out.pitch, out.pitch_v));
+    if (out.smem_bytes > kSmemBudget) return;
+    // the V rows must also hold chunks that run past the staged span (narrow strips)
+    for (uint32_t s = 0; s < out.n_strips; s++)
+        for (int t = 0; t < 8; t++)
+            if (size_t(out.tile_kb0[s * 8 + t] + 8 * out.tile_nch[s * 8 + t] + 3) * 4 > out.pitch_v) return;
+
+    // second sweep: weights
+    out.b2.assign(size_t(out.n_strips) * 8 * kMaxCh * ndig * 64, 0u);
+    for (uint32_t s = 0; s < out.n_strips; s++) {
+        const uint32_t c0 = uint32_t(out.strip_col0[s]), c1 = uint32_t(out.strip_col0[s + 1]);
+        const int64_t s0 = out.strip_src0[s];
+        for (uint32_t j = c0; j < c1; j++) {
+            const uint32_t o = g.px + j, t = (j - c0) / 8, n = (j - c0) % 8;
+            const int cnt = tx.count[o];
+            quantise(&tx.w[size_t(o) * tx.max_taps], cnt, Sx, q);
+            int64_t sum_q = 0;
+            const int64_t kb0 = out.tile_kb0[s * 8 + t];
+            for (int k = 0; k < cnt; k++) {
+                sum_q += q[k];
+                int8_t d[3];
+                if (!split_digits(q[k], ndig, d)) return;
+                const int64_t rel = int64_t(g.rx) + tx.left[o] + k - s0;      // pixel inside the staged span
+                const int64_t blk = rel / 4 - kb0;
+                int slot = 0;
+                for (int z = 0; z < 4; z++) if (kPerm[z] == int(rel % 4)) slot = z;
+                const int64_t kk = blk * 4 + slot;                            // k index inside the tile's chunks
+                if (kk < 0 || kk >= 32 * out.tile_nch[s * 8 + t]) return;
+                for (int l = 0; l < ndig; l++)
+                    put_b(&out.b2[(((size_t(s) * 8 + t) * kMaxCh + size_t(kk / 32)) * ndig + l) * 64], int(kk % 32), int(n), d[l]);
+            }
+            // constant term: fill taps of the horizontal pass minus the intermediate's offset
+            const double off = -double(kOffset) * double(sum_q) * std::ldexp(1.0, -Sx);
+            for (int c = 0; c < 4; c++)
+                out.cx[size_t(j) * 4 + c] = float(off + double(g.fill_pre[c]) * double(tx.fillw[o]));
+        }
+    }
+
+    for (uint32_t i = 0; i < g.ph; i++)
+        if (!out.row_computed[i]) out.need_fill = true;
+    if (g.pw != g.fw || g.ph != g.fh) out.need_fill = true;
+    out.ok = true;
+}
+
+}  // namespace slimg
