@@ -56,7 +56,7 @@ struct ResizePlan {
     FastResizeParams fparams{};
     // V-first integer tensor pipeline (k2_vfirst.cu), preferred when the geometry qualifies
     bool vfirst = false;
-    DevArray v_a0, v_need, v_nch, v_b1, v_bias, v_rowc, v_col0, v_src0, v_nblk, v_bytes, v_kb0, v_tnch, v_b2, v_cx;
+    DevArray v_recs, v_rowc, v_col0, v_src0, v_nblk, v_bytes, v_kb0, v_tnch, v_b2, v_cx;
     VfParams vparams{};
 };
 
@@ -152,9 +152,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
         VPlanHost vp;
         build_vplan(g, tx, ty, ndig, vp);
         if (vp.ok) {
-            if ((e = plan->v_a0.upload(vp.grp_a0)) || (e = plan->v_need.upload(vp.grp_need)) ||
-                (e = plan->v_nch.upload(vp.grp_nch)) || (e = plan->v_b1.upload(vp.b1)) || (e = plan->v_bias.upload(vp.bias)) ||
-                (e = plan->v_rowc.upload(vp.row_computed)) || (e = plan->v_col0.upload(vp.strip_col0)) ||
+            if ((e = plan->v_recs.upload(vp.recs)) || (e = plan->v_rowc.upload(vp.row_computed)) || (e = plan->v_col0.upload(vp.strip_col0)) ||
                 (e = plan->v_src0.upload(vp.strip_src0)) || (e = plan->v_nblk.upload(vp.strip_nblk)) ||
                 (e = plan->v_bytes.upload(vp.strip_bytes)) || (e = plan->v_kb0.upload(vp.tile_kb0)) ||
                 (e = plan->v_tnch.upload(vp.tile_nch)) || (e = plan->v_b2.upload(vp.b2)) || (e = plan->v_cx.upload(vp.cx)))
@@ -162,10 +160,8 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
             VfParams &v = plan->vparams;
             v.sw = g.sw; v.sh = g.sh; v.ry = g.ry; v.pw = g.pw; v.ph = g.ph;
             v.ndig = vp.ndig; v.nch1 = vp.nch1; v.nch2 = vp.nch2;
-            v.n_groups = vp.n_groups;
-            v.grp_a0 = (const int32_t *)plan->v_a0.p; v.grp_need = (const int32_t *)plan->v_need.p;
-            v.grp_nch = (const int32_t *)plan->v_nch.p; v.b1 = (const uint32_t *)plan->v_b1.p;
-            v.bias = (const int32_t *)plan->v_bias.p; v.row_computed = (const uint8_t *)plan->v_rowc.p;
+            v.n_recs = vp.n_recs; v.rec_words = vp.rec_words; v.recs = (const uint32_t *)plan->v_recs.p;
+            v.row_computed = (const uint8_t *)plan->v_rowc.p;
             v.sh1 = vp.sh1;
             v.n_strips = vp.n_strips;
             v.strip_col0 = (const int32_t *)plan->v_col0.p; v.strip_src0 = (const int32_t *)plan->v_src0.p;
@@ -273,7 +269,7 @@ static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, u
         // recomputation (one band's worth of source rows per extra band) when the batch alone fills it
         const uint64_t ctas_per_band = uint64_t(v.n_strips) * n;
         uint32_t bands = uint32_t((2 * 148 + ctas_per_band - 1) / ctas_per_band);
-        bands = std::max<uint32_t>(1, std::min<uint32_t>(bands, std::max<uint32_t>(1, v.n_groups / 4)));
+        bands = std::max<uint32_t>(1, std::min<uint32_t>(bands, std::max<uint32_t>(1, v.n_recs / 4)));
         v.n_bands = bands;
         CU(launch_resize_vfirst(v, n, stream));
         return SLIMG_OK;

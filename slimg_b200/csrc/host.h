@@ -90,7 +90,9 @@ struct VPlanHost {
     uint32_t n_groups = 0;
     int nch1 = 0;                          // max 32-row chunks a group's band spans
     std::vector<int32_t> grp_a0, grp_need, grp_nch;
-    std::vector<uint32_t> b1;              // [n_groups][nch1][ndig][32 lanes][2]
+    std::vector<uint32_t> b1;              // [n_groups][4][ndig][32 lanes][2]
+    std::vector<uint32_t> recs;            // [n_recs][rec_words]: header + fragments of each non-empty group
+    uint32_t n_recs = 0, rec_words = 0;
     std::vector<int32_t> bias;             // [n_groups*8][4]
     std::vector<uint8_t> row_computed;     // [ph]
     int sh1 = 0;                           // V16 = (x + bias) >> sh1

@@ -36,7 +36,7 @@ namespace {
 
 constexpr int kWarps = 16;
 constexpr int kThreads = kWarps * 32;
-constexpr int kStepRows = 16;                // source rows per ring step (one mbarrier each)
+constexpr int kStepRows = 16;                // source rows per ring step (one mbarrier each) == kWarps
 constexpr int kMaxSteps = 16;                // ring of at most 256 rows
 constexpr int kStageCols = 64;
 constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
@@ -73,6 +73,12 @@ __device__ __forceinline__ void imma(int (&d)[4], const uint32_t (&a)[4], const 
                  : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
 }
+// first k-chunk: C = 0 comes from the zero register, no accumulator clearing
+__device__ __forceinline__ void imma_z(int (&d)[4], const uint32_t (&a)[4], const uint2 &b) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "r"(0));
+}
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
     uint32_t v;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
@@ -93,9 +99,10 @@ __device__ __forceinline__ uint32_t quantize_channel(float t) {
     return uint32_t(floorf(t + 0.5f));
 }
 
-struct SmemTail {                             // after the ring and the V planes
+struct SmemTail {                             // after the ring, the V planes and the two group records
     uint32_t stage[2][8][kStageCols];        // packed output rows of the last two groups
     uint64_t full[kMaxSteps];
+    int counter[2];                          // pass-1 work queue (pairs of 16-byte blocks), one per V buffer
 };
 
 // What is not computed: canvas rows outside the kept rectangle (fill_post), kept rows whose taps
@@ -132,72 +139,94 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     const uint32_t ring = smem_u32(smem_raw);
     const uint32_t vbase = ring + p.ring_rows * p.pitch;
     const uint32_t vplane = 32u * p.pitch_v;                   // one limb of one buffer
-    SmemTail &tail = *reinterpret_cast<SmemTail *>(smem_raw + size_t(p.ring_rows) * p.pitch + 4u * vplane);
+    const size_t rec_off = size_t(p.ring_rows) * p.pitch + 4u * vplane;
+    const uint32_t *recbuf = reinterpret_cast<const uint32_t *>(smem_raw + rec_off);
+    SmemTail &tail = *reinterpret_cast<SmemTail *>(smem_raw + rec_off + 2u * p.rec_words * 4u);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     const uint8_t *src = p.src + size_t(blockIdx.z) * p.src_img_bytes;
     uint32_t *dst = reinterpret_cast<uint32_t *>(p.dst + size_t(blockIdx.z) * p.dst_img_bytes);
 
-    // ---- this CTA's strip and band ---------------------------------------------------------------
+    // ---- this CTA's strip and band (a range of group records) -----------------------------------------
     const int strip = blockIdx.x;
     const int col0 = p.strip_col0[strip], col1 = p.strip_col0[strip + 1];
     const int nblk = p.strip_nblk[strip];
     const uint32_t row_bytes = uint32_t(p.strip_bytes[strip]);
     const uint8_t *src_col = src + size_t(p.strip_src0[strip]) * 4;
-    const int j0 = int((uint64_t(blockIdx.y) * p.n_groups) / gridDim.y);
-    const int j1 = int((uint64_t(blockIdx.y + 1) * p.n_groups) / gridDim.y);
-    const int i0 = j0 * 8, i1 = min(j1 * 8, int(p.ph));
-
-    // first / last source row of the band (uniform; a handful of loads from L2)
-    int ys = 0, ye = 0;
-    {
-        bool any = false;
-        for (int j = j0; j < j1; j++) {
-            if (p.grp_nch[j] == 0) continue;
-            if (!any) { ys = p.grp_a0[j] & ~(kStepRows - 1); any = true; }
-            ye = p.grp_need[j];
-        }
-    }
+    const int rec0 = int((uint64_t(blockIdx.y) * p.n_recs) / gridDim.y);
+    const int rec1 = int((uint64_t(blockIdx.y + 1) * p.n_recs) / gridDim.y);
+    const int n_iter = rec1 - rec0;
+    // kept rows this band owns on the canvas (for the fill): from its first group to the next band's first group
+    const int i0 = rec0 == 0 ? 0 : int(p.recs[size_t(rec0) * p.rec_words]) * 8;
+    const int i1 = rec1 == int(p.n_recs) ? int(p.ph) : int(p.recs[size_t(rec1) * p.rec_words]) * 8;
+    const int ys = n_iter > 0 ? int(p.recs[size_t(rec0) * p.rec_words + 1]) & ~(kStepRows - 1) : 0;
+    const int ye = n_iter > 0 ? int(p.recs[size_t(rec1 - 1) * p.rec_words + 2]) : 0;
     const int n_steps = (ye - ys + kStepRows - 1) / kStepRows;
     const int nst = int(p.ring_rows) / kStepRows;
 
+    auto prefetch_rec = [&](int r, uint32_t buf) {           // group record r -> shared memory, 16 bytes per thread
+        if (tid < int(p.rec_words / 4)) {
+            const uint32_t d = smem_u32(recbuf) + (buf * p.rec_words + uint32_t(tid) * 4u) * 4u;
+            const uint32_t *s = p.recs + size_t(r) * p.rec_words + size_t(tid) * 4;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(s) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
     if (tid == 0) {
         for (int s = 0; s < nst; s++) mbar_init(&tail.full[s], 1);
+        tail.counter[0] = 0; tail.counter[1] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if (n_iter > 0) prefetch_rec(rec0, 0);
+    asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
 
-    // ---- producer: warp 0 drives the TMA engine, one linear bulk copy per source row ----------------
-    int next_issue = 0;                       // warp 0 only
-    auto issue_step = [&](int s) {            // all lanes of warp 0
-        const int slot = s % nst;
-        if (lane == 0) mbar_arrive_expect_tx(&tail.full[slot], kStepRows * row_bytes);
-        __syncwarp();
-        if (lane < kStepRows) {
-            const int y = ys + s * kStepRows + lane;
-            const int row = min(int(p.ry) + y, int(p.sh) - 1);           // rows past the end carry zero weights
-            bulk_g2s(ring + uint32_t(slot * kStepRows + lane) * p.pitch, src_col + size_t(row) * p.sw * 4, row_bytes,
-                     &tail.full[slot]);
+    // ---- producer: every warp owns one of the 16 source rows of a ring step and issues its linear bulk
+    //      copy (TMA engine) from lane 0; thread 0 arms the step's mbarrier before the CTA barrier that
+    //      precedes the copies.  (One warp issuing all 16 copies serialises them: the instruction takes
+    //      uniform operands.)  The bookkeeping is uniform across the CTA. ---------------------------------
+    int next_issue = 0, issue_slot = 0;
+    auto arm_steps = [&](int upto) {          // thread 0
+        int slot = issue_slot;
+        for (int s = next_issue; s < upto; s++) {
+            mbar_arrive_expect_tx(&tail.full[slot], kStepRows * row_bytes);
+            if (++slot == nst) slot = 0;
         }
     };
-    if (warp == 0)
-        for (; next_issue < min(n_steps, nst); next_issue++) issue_step(next_issue);
+    auto issue_steps = [&](int upto) {        // all threads; lane 0 of warp w copies row w of each step
+        for (; next_issue < upto; next_issue++) {
+            if (lane == 0) {
+                const int y = ys + next_issue * kStepRows + warp;
+                const int row = min(int(p.ry) + y, int(p.sh) - 1);       // rows past the end carry zero weights
+                bulk_g2s(ring + uint32_t(issue_slot * kStepRows + warp) * p.pitch, src_col + size_t(row) * p.sw * 4,
+                         row_bytes, &tail.full[issue_slot]);
+            }
+            if (++issue_slot == nst) issue_slot = 0;
+        }
+    };
+    {
+        const int upto = min(n_steps, nst);
+        if (tid == 0) arm_steps(upto);
+        __syncthreads();
+        issue_steps(upto);
+    }
 
-    // ---- pass-2 role: warp -> (channel pair, tile of 8 output columns); weights stay in registers ------
-    const int mt = warp >> 3, tile = warp & 7;
+    // ---- pass-2 role: the first 2*ntile warps each own (channel pair, tile of 8 output columns);
+    //      their weights stay in registers for the whole band ------------------------------------------
     const int ntile = (col1 - col0 + 7) >> 3;
-    const bool p2_active = tile < ntile;
-    const int nch2 = p2_active ? p.tile_nch[strip * 8 + tile] : 0;
+    const bool p2_active = warp < 2 * ntile;
+    const int mt = p2_active ? warp / ntile : 0, tile = p2_active ? warp - mt * ntile : 0;
     const int kb0 = p2_active ? p.tile_kb0[strip * 8 + tile] : 0;
     uint2 bw2[NCH2][NDIG];
 #pragma unroll
     for (int c = 0; c < NCH2; c++)
 #pragma unroll
         for (int d = 0; d < NDIG; d++)
-            bw2[c][d] = c < nch2 ? __ldg(reinterpret_cast<const uint2 *>(p.b2) +
-                                         ((size_t(strip * 8 + tile) * NCH2 + c) * NDIG + d) * 32 + lane)
-                                 : make_uint2(0u, 0u);
+            bw2[c][d] = p2_active ? __ldg(reinterpret_cast<const uint2 *>(p.b2) +
+                                          ((size_t(strip * 8 + tile) * NCH2 + c) * NDIG + d) * 32 + lane)
+                                  : make_uint2(0u, 0u);
     float cxr[2][2];                           // [column 2t+e][channel 2mt+h]
 #pragma unroll
     for (int e = 0; e < 2; e++)
@@ -207,8 +236,15 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             cxr[e][h] = (p2_active && col < col1) ? p.cx[size_t(col) * 4 + 2 * mt + h] : 0.0f;
         }
 
-    int jprev = -1;                            // previous non-empty group (its output rows are still staged)
-    uint32_t it = 0;                           // non-empty groups processed so far: parity picks the V / stage buffers
+    // ring bookkeeping without divisions: the step / slot / phase this warp waits on next, and the ring
+    // position of the current band start
+    int w_step = 0, w_slot = 0;
+    uint32_t w_par = 0;
+    int pos = 0, prev_a0 = ys;
+    int jprev = -1;                            // previous group (its output rows are still staged)
+    const int npair = (nblk + 1) >> 1;
+    const int sh1 = p.sh1;
+    const int ch = g & 3, hh = g >> 2;
 
     auto copy_out = [&](int j, uint32_t buf) { // staged rows of group j -> global, whole rows
         const int r = warp & 7, i = j * 8 + r;
@@ -220,16 +256,25 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     };
 
 #pragma unroll 1
-    for (int j = j0; j < j1; j++) {
-        const int nch1 = p.grp_nch[j];
-        if (nch1 == 0) continue;               // uniform: every tap of these rows is fill
-        const int a0 = p.grp_a0[j];
-        const uint32_t vbuf = vbase + (it & 1u) * 2u * vplane;
+    for (int it = 0; it < n_iter; it++) {
+        const uint32_t buf = uint32_t(it) & 1u;
+        const uint32_t *rec = recbuf + buf * p.rec_words;
+        if (it + 1 < n_iter) prefetch_rec(rec0 + it + 1, buf ^ 1u);
+        const int j = int(rec[0]), a0 = int(rec[1]), need = int(rec[2]);
+        const uint32_t vbuf = vbase + buf * 2u * vplane;
+        if (tid == 0) tail.counter[buf ^ 1u] = 0;     // next group's queue; its last users passed the previous barrier
 
         // ---- wait for the source rows of this group (step s lives in slot s % nst, phase s / nst) ----
         {
-            const int need = (p.grp_need[j] - ys + kStepRows - 1) / kStepRows;
-            for (int s = (a0 - ys) / kStepRows; s < need; s++) mbar_wait(&tail.full[s % nst], uint32_t(s / nst) & 1u);
+            const int first = (a0 - ys) / kStepRows, last = (need - ys + kStepRows - 1) / kStepRows;
+            while (w_step < last) {
+                if (w_step >= first) mbar_wait(&tail.full[w_slot], w_par);
+                w_step++;
+                if (++w_slot == nst) { w_slot = 0; w_par ^= 1u; }
+            }
+            pos += a0 - prev_a0;
+            prev_a0 = a0;
+            while (pos >= int(p.ring_rows)) pos -= int(p.ring_rows);
         }
 
         // ================= pass 1: vertical taps of 8 output rows over the strip =======================
@@ -240,83 +285,88 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             for (int c = 0; c < NCH1; c++) {
 #pragma unroll
                 for (int d = 0; d < NDIG; d++)
-                    bw1[c][d] = c < nch1 ? __ldg(reinterpret_cast<const uint2 *>(p.b1) +
-                                                 ((size_t(j) * NCH1 + c) * NDIG + d) * 32 + lane)
-                                         : make_uint2(0u, 0u);
-                rowoff[c] = ring + uint32_t((a0 - ys + 32 * c + lane) % int(p.ring_rows)) * p.pitch;
+                    bw1[c][d] = *reinterpret_cast<const uint2 *>(rec + 64 + ((c * NDIG + d) * 32 + lane) * 2);
+                int rr = pos + 32 * c + lane;
+                if (rr >= int(p.ring_rows)) rr -= int(p.ring_rows);
+                if (rr >= int(p.ring_rows)) rr -= int(p.ring_rows);
+                rowoff[c] = ring + uint32_t(rr) * p.pitch;
             }
-            const int ch = g & 3, hh = g >> 2;
-            const int bias0 = p.bias[(size_t(j) * 8 + 2 * t) * 4 + ch], bias1 = p.bias[(size_t(j) * 8 + 2 * t + 1) * 4 + ch];
+            const int bias0 = int(rec[8 + (2 * t) * 4 + ch]), bias1 = int(rec[8 + (2 * t + 1) * 4 + ch]);
             // V word address of (row 8*ch + 2t + hh, block 0): rows are pitch_v apart, channel planes skewed by one word
             const uint32_t vrow = vbuf + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u;
 
+            int *counter = &tail.counter[buf];
+            int pr = 0;
+            if (lane == 0) pr = atomicAdd(counter, 1);
+            pr = __shfl_sync(0xffffffffu, pr, 0);
 #pragma unroll 1
-            for (int blk = warp; blk < nblk; blk += kWarps) {
-                int acc[NDIG][4];
+            while (pr < npair) {
+                int nxt = 0;
+                if (lane == 0) nxt = atomicAdd(counter, 1);      // next pair: the answer arrives while this one computes
+                const int blk = pr * 2;
+                int acc[2][NDIG][4];
 #pragma unroll
-                for (int d = 0; d < NDIG; d++)
+                for (int c = 0; c < NCH1; c++) {       // groups with shorter bands carry zero weights in the rest
+                    uint32_t a[2][4];
+                    ldsm_t(a[0], rowoff[c] + uint32_t(blk) * 16u);
+                    ldsm_t(a[1], rowoff[c] + uint32_t(blk) * 16u + 16u);
 #pragma unroll
-                    for (int i = 0; i < 4; i++) acc[d][i] = 0;
-#pragma unroll
-                for (int c = 0; c < NCH1; c++) {
-                    if (c < nch1) {
-                        uint32_t a[4];
-                        ldsm_t(a, rowoff[c] + uint32_t(blk) * 16u);
-#pragma unroll
-                        for (int d = 0; d < NDIG; d++) imma(acc[d], a, bw1[c][d]);
+                    for (int d = 0; d < NDIG; d++) {
+                        if (c == 0) { imma_z(acc[0][d], a[0], bw1[c][d]); imma_z(acc[1][d], a[1], bw1[c][d]); }
+                        else { imma(acc[0][d], a[0], bw1[c][d]); imma(acc[1][d], a[1], bw1[c][d]); }
                     }
                 }
                 // recombine the digit planes (exact), re-quantise to u16, split into limbs
-                int v[4];
 #pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    int x = acc[0][i] + (acc[1][i] << 8);
-                    if (NDIG == 3) x += acc[NDIG - 1][i] << 16;
-                    v[i] = (x + ((i & 1) ? bias1 : bias0)) >> p.sh1;
+                for (int u = 0; u < 2; u++) {
+                    int v[4];
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        int x = acc[u][0][i] + (acc[u][1][i] << 8);
+                        if (NDIG == 3) x += acc[u][NDIG - 1][i] << 16;
+                        v[i] = (x + ((i & 1) ? bias1 : bias0)) >> sh1;
+                    }
+                    // v[0],v[2]: pixel hh / hh+2 of output row 2t; v[1],v[3]: same pixels of row 2t+1
+                    const uint32_t w0 = __byte_perm(uint32_t(v[0]), uint32_t(v[2]), 0x5140);   // lo lo hi hi of row 2t
+                    const uint32_t w1 = __byte_perm(uint32_t(v[1]), uint32_t(v[3]), 0x5140);   // ... of row 2t+1
+                    const uint32_t send = hh ? w0 : w1, mine = hh ? w1 : w0;
+                    const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 16);
+                    const uint32_t pa = hh ? recv : mine, pb = hh ? mine : recv;              // pixels (0,2) and (1,3)
+                    if (blk + u < nblk) {
+                        sts32(vrow + uint32_t(blk + u) * 4u, __byte_perm(pa, pb, 0x5410));             // low limbs
+                        sts32(vrow + vplane + uint32_t(blk + u) * 4u, __byte_perm(pa, pb, 0x7632));    // high limbs
+                    }
                 }
-                // v[0],v[2]: pixel hh / hh+2 of output row 2t; v[1],v[3]: same pixels of row 2t+1
-                const uint32_t w0 = __byte_perm(uint32_t(v[0]), uint32_t(v[2]), 0x5140);   // lo lo hi hi of row 2t
-                const uint32_t w1 = __byte_perm(uint32_t(v[1]), uint32_t(v[3]), 0x5140);   // ... of row 2t+1
-                const uint32_t send = hh ? w0 : w1, mine = hh ? w1 : w0;
-                const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 16);
-                const uint32_t pa = hh ? recv : mine, pb = hh ? mine : recv;              // pixels (0,2) and (1,3)
-                sts32(vrow + uint32_t(blk) * 4u, __byte_perm(pa, pb, 0x5410));             // low limbs
-                sts32(vrow + vplane + uint32_t(blk) * 4u, __byte_perm(pa, pb, 0x7632));    // high limbs
+                pr = __shfl_sync(0xffffffffu, nxt, 0);
             }
         }
-        __syncthreads();      // V[j&1] complete; every warp is done with the ring rows below the next band
-                              // and with pass 2 of the previous group (its staged rows can be written out)
-
-        // ---- producer: refill the ring steps no later group needs ------------------------------------
-        if (warp == 0) {
-            int a_next = ye;
-            for (int jj = j + 1; jj < j1; jj++)
-                if (p.grp_nch[jj]) { a_next = p.grp_a0[jj]; break; }
-            while (next_issue < n_steps && ys + (next_issue - nst + 1) * kStepRows <= a_next) issue_step(next_issue++);
-        }
-        if (jprev >= 0) copy_out(jprev, (it & 1u) ^ 1u);
+        // ring steps no later group needs: step s may replace step s - nst once every row of that one lies
+        // above the next band
+        const int a_next = it + 1 < n_iter ? int(rec[4]) : ye;
+        const int refill_upto = min(n_steps, (a_next - ys) / kStepRows + nst);
+        if (tid == 0) arm_steps(refill_upto);
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncthreads();      // V[buf] and the next record are complete; every warp is done with the ring rows
+                              // below the next band and with pass 2 of the previous group
+        issue_steps(refill_upto);
+        if (jprev >= 0) copy_out(jprev, buf ^ 1u);
 
         // ================= pass 2: horizontal taps, 2 channels x 8 rows x 8 output columns per warp =======
         if (p2_active) {
             int acc[2][NDIG][4];
-#pragma unroll
-            for (int l = 0; l < 2; l++)
-#pragma unroll
-                for (int d = 0; d < NDIG; d++)
-#pragma unroll
-                    for (int i = 0; i < 4; i++) acc[l][d][i] = 0;
             const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
             const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
 #pragma unroll
             for (int c = 0; c < NCH2; c++) {
-                if (c < nch2) {
 #pragma unroll
-                    for (int l = 0; l < 2; l++) {
-                        uint32_t a[4];
-                        const uint32_t o = uint32_t(l) * vplane + uint32_t(c) * 32u;
-                        a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
+                for (int l = 0; l < 2; l++) {
+                    uint32_t a[4];
+                    const uint32_t o = uint32_t(l) * vplane + uint32_t(c) * 32u;
+                    a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
 #pragma unroll
-                        for (int d = 0; d < NDIG; d++) imma(acc[l][d], a, bw2[c][d]);
+                    for (int d = 0; d < NDIG; d++) {
+                        if (c == 0) imma_z(acc[l][d], a, bw2[c][d]);
+                        else imma(acc[l][d], a, bw2[c][d]);
                     }
                 }
             }
@@ -331,15 +381,14 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                     for (int d = 0; d < NDIG; d++) f = fmaf(int_to_float(acc[l][d][i]), p.s2[l][d], f);
                 q[i] = quantize_channel(f);
             }
-            uint8_t *st = reinterpret_cast<uint8_t *>(&tail.stage[it & 1u][g][tile * 8 + 2 * t]) + 2 * mt;
+            uint8_t *st = reinterpret_cast<uint8_t *>(&tail.stage[buf][g][tile * 8 + 2 * t]) + 2 * mt;
             sts16(smem_u32(st), q[0] | (q[2] << 8));
             sts16(smem_u32(st + 4), q[1] | (q[3] << 8));
         }
         jprev = j;
-        it++;
     }
     __syncthreads();
-    if (jprev >= 0) copy_out(jprev, (it & 1u) ^ 1u);
+    if (jprev >= 0) copy_out(jprev, uint32_t(n_iter - 1) & 1u);
 
     if (p.need_fill) fill_region(p, dst, i0, i1, col0, col1, tid);
 }
@@ -376,8 +425,12 @@ cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStrea
     if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
     if (p.n_bands == 0 || p.n_bands > 65535 || p.n_strips == 0 || p.nch1 > 4 || p.nch2 > 4) return cudaErrorInvalidValue;
     if (p.ring_rows % kStepRows != 0 || p.ring_rows / kStepRows > kMaxSteps) return cudaErrorInvalidValue;
-    if (p.ndig == 2) return launch_vf_t<2, 4, 4>(p, n_images, stream);
-    return launch_vf_t<3, 4, 4>(p, n_images, stream);
+#define SLIMG_VF_CASE(D, A, B) if (p.ndig == D && p.nch1 == A && p.nch2 == B) return launch_vf_t<D, A, B>(p, n_images, stream);
+#define SLIMG_VF_ROW(D, A) SLIMG_VF_CASE(D, A, 1) SLIMG_VF_CASE(D, A, 2) SLIMG_VF_CASE(D, A, 3) SLIMG_VF_CASE(D, A, 4)
+#define SLIMG_VF_ALL(D) SLIMG_VF_ROW(D, 1) SLIMG_VF_ROW(D, 2) SLIMG_VF_ROW(D, 3) SLIMG_VF_ROW(D, 4)
+    SLIMG_VF_ALL(2)
+    SLIMG_VF_ALL(3)
+    return cudaErrorInvalidValue;
 }
 
 }  // namespace slimg

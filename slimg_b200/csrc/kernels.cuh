@@ -101,12 +101,10 @@ struct VfParams {
     uint32_t pw, ph;                 // columns / rows of the resize output that are kept
     int32_t ndig, nch1, nch2;        // weight digits; max chunks per group (pass 1) / tile (pass 2)
     // vertical pass: groups of 8 kept output rows
-    uint32_t n_groups;
-    const int32_t *grp_a0;           // [n_groups] first rectangle row of the group's band
-    const int32_t *grp_need;         // [n_groups] end (exclusive) of the rows the group reads with non-zero weight
-    const int32_t *grp_nch;          // [n_groups] 32-row chunks of the band (0: nothing to compute)
-    const uint32_t *b1;              // [n_groups][4][ndig][32 lanes][2] weight fragments (s8 x4 per word)
-    const int32_t *bias;             // [n_groups*8][4] fill term + offset + rounding half, per row and channel
+    // one record per non-empty group (vplan.cpp): 64 header words {group, band start, end of needed rows,
+    // chunks, next band start, -, -, -, bias[8][4]} then [4][ndig][32 lanes][2] weight fragments (s8 x4 per word)
+    uint32_t n_recs, rec_words;
+    const uint32_t *recs;
     const uint8_t *row_computed;     // [ph]
     int32_t sh1;                     // right shift that turns the s32 sum into the u16 intermediate
     // horizontal pass: strips of <= 64 kept output columns, tiles of 8

@@ -20,7 +20,7 @@ namespace {
 
 constexpr int kFrac = 7;        // fractional bits of the 16-bit intermediate
 constexpr int kOffset = 64;     // added to the intermediate so Lanczos undershoot stays >= 0
-constexpr int kPrefetchRows = 48;
+constexpr int kPrefetchRows = 64;   // a whole group's worth of new rows must be in flight while the previous group computes
 constexpr int kMaxCh = 4;          // chunk stride of the fragment tables (the kernel's NCH1 / NCH2)
 constexpr size_t kSmemBudget = 227 * 1024 - 2048;
 const int kPerm[4] = {0, 2, 1, 3};   // k-slot -> pixel inside a 4-pixel block (k2_vfirst.cu, pass-1 epilogue)
@@ -109,14 +109,16 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     if (out.nch1 == 0 || out.nch1 > kMaxCh) return;       // bands of more than 128 source rows: other kernels
     // bands must move down monotonically (ring buffer)
     {
-        int prev = -1;
+        int prev = -1, prev_need = 0;
         for (uint32_t j = 0; j < out.n_groups; j++) {
             if (out.grp_nch[j] == 0) continue;
             if (out.grp_a0[j] < prev) return;
+            if (prev >= 0 && out.grp_a0[j] > prev_need) return;   // no unread rows between bands: every ring step gets waited on
             prev = out.grp_a0[j];
+            prev_need = out.grp_need[j];
         }
     }
-    out.b1.assign(size_t(out.n_groups) * kMaxCh * ndig * 64, 0u);
+    out.b1.assign(size_t(out.n_groups) * out.nch1 * ndig * 64, 0u);
     std::vector<int64_t> q;
     for (uint32_t j = 0; j < out.n_groups; j++) {
         for (uint32_t n = 0; n < 8; n++) {
@@ -133,7 +135,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
                 if (!split_digits(q[k], ndig, d)) return;
                 const int row = ty.left[o] + k - out.grp_a0[j];     // row inside the group's band
                 for (int l = 0; l < ndig; l++)
-                    put_b(&out.b1[((size_t(j) * kMaxCh + row / 32) * ndig + l) * 64], row % 32, int(n), d[l]);
+                    put_b(&out.b1[((size_t(j) * out.nch1 + row / 32) * ndig + l) * 64], row % 32, int(n), d[l]);
             }
             out.row_computed[i] = cnt > 0;
             // bias = fill term + offset + rounding half; the 16-bit intermediate must stay in range
@@ -146,6 +148,24 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
             }
         }
     }
+
+    // one contiguous record per non-empty group, in band order: what the kernel prefetches into shared
+    // memory one group ahead.  Header (64 words): group index, band start, end of the needed rows,
+    // chunk count, band start of the next record; bias[8][4] from word 8.  Then the weight fragments.
+    out.rec_words = 64 + uint32_t(out.nch1) * ndig * 64;
+    for (uint32_t j = 0; j < out.n_groups; j++) {
+        if (out.grp_nch[j] == 0) continue;
+        const size_t base = out.recs.size();
+        out.recs.resize(base + out.rec_words, 0u);
+        uint32_t *r = &out.recs[base];
+        r[0] = j; r[1] = uint32_t(out.grp_a0[j]); r[2] = uint32_t(out.grp_need[j]); r[3] = uint32_t(out.grp_nch[j]);
+        r[4] = uint32_t(out.grp_need[j]);                       // patched below when a next record exists
+        for (int k = 0; k < 32; k++) r[8 + k] = uint32_t(out.bias[size_t(j) * 32 + k]);
+        std::copy(out.b1.begin() + size_t(j) * out.nch1 * ndig * 64, out.b1.begin() + size_t(j + 1) * out.nch1 * ndig * 64, r + 64);
+        if (base) out.recs[base - out.rec_words + 4] = uint32_t(out.grp_a0[j]);
+        out.n_recs++;
+    }
+    if (out.n_recs == 0) return;
 
     // ---------------- horizontal pass ----------------
     float maxw_x = 0.0f;
@@ -162,7 +182,8 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     // ring depth: the rows a group needs plus what should be in flight, in 16-row steps
     const uint32_t ring_rows = uint32_t((std::max(32 * out.nch1, max_need + kPrefetchRows) + 15) / 16 * 16);
     out.ring_rows = ring_rows;
-    const size_t fixed_bytes = 2 * 8 * 64 * 4 /* output staging */ + 1024 /* barriers, bookkeeping */;
+    const size_t fixed_bytes = 2 * 8 * 64 * 4 /* output staging */ + 2 * size_t(out.rec_words) * 4 /* group records */ +
+                               1024 /* barriers, bookkeeping */;
 
     // span of source pixels (absolute columns) a range of kept output columns needs
     auto span_of = [&](uint32_t c0, uint32_t c1, int64_t &lo, int64_t &hi) {
@@ -210,7 +231,6 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     out.tile_nch.assign(size_t(out.n_strips) * 8, 0);
     out.cx.assign(size_t(g.pw) * 4, 0.0f);
     int64_t max_nblk = 1;
-    struct TileQ { std::vector<std::vector<int64_t>> q; };
     // first sweep: geometry and the chunk count
     for (uint32_t s = 0; s < out.n_strips; s++) {
         const uint32_t c0 = s * cols, c1 = std::min(g.pw, c0 + cols);
@@ -240,15 +260,16 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         }
     }
     if (out.nch2 == 0 || out.nch2 > kMaxCh) return;
-    out.smem_bytes = uint32_t(smem_for(max_nblk, out.pitch, out.pitch_v));
-    if (out.smem_bytes > kSmemBudget) return;
-    // the V rows must also hold chunks that run past the staged span (narrow strips)
+    // every tile runs the plan's nch2 chunks: pull the k ranges inside the staged span where it is wide enough
     for (uint32_t s = 0; s < out.n_strips; s++)
-        for (int t = 0; t < 8; t++)
-            if (size_t(out.tile_kb0[s * 8 + t] + 8 * out.tile_nch[s * 8 + t] + 3) * 4 > out.pitch_v) return;
-
+        for (int t = 0; t < 8; t++) {
+            int32_t &kb0 = out.tile_kb0[s * 8 + t];
+            kb0 = std::max<int32_t>(0, std::min<int32_t>(kb0, out.strip_nblk[s] - 8 * out.nch2));
+        }
+    out.smem_bytes = uint32_t(smem_for(std::max<int64_t>(max_nblk, 8 * out.nch2), out.pitch, out.pitch_v));
+    if (out.smem_bytes > kSmemBudget) return;
     // second sweep: weights
-    out.b2.assign(size_t(out.n_strips) * 8 * kMaxCh * ndig * 64, 0u);
+    out.b2.assign(size_t(out.n_strips) * 8 * out.nch2 * ndig * 64, 0u);
     for (uint32_t s = 0; s < out.n_strips; s++) {
         const uint32_t c0 = uint32_t(out.strip_col0[s]), c1 = uint32_t(out.strip_col0[s + 1]);
         const int64_t s0 = out.strip_src0[s];
@@ -267,9 +288,9 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
                 int slot = 0;
                 for (int z = 0; z < 4; z++) if (kPerm[z] == int(rel % 4)) slot = z;
                 const int64_t kk = blk * 4 + slot;                            // k index inside the tile's chunks
-                if (kk < 0 || kk >= 32 * out.tile_nch[s * 8 + t]) return;
+                if (kk < 0 || kk >= 32 * out.nch2) return;
                 for (int l = 0; l < ndig; l++)
-                    put_b(&out.b2[(((size_t(s) * 8 + t) * kMaxCh + size_t(kk / 32)) * ndig + l) * 64], int(kk % 32), int(n), d[l]);
+                    put_b(&out.b2[(((size_t(s) * 8 + t) * out.nch2 + size_t(kk / 32)) * ndig + l) * 64], int(kk % 32), int(n), d[l]);
             }
             // constant term: fill taps of the horizontal pass minus the intermediate's offset
             const double off = -double(kOffset) * double(sum_q) * std::ldexp(1.0, -Sx);
