@@ -148,7 +148,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
     const std::string path = path_env ? path_env : "vfirst";
     if (path == "vfirst") {
         const char *dig_env = std::getenv("SLIMG_B200_DIGITS");
-        const int ndig = dig_env && dig_env[0] == '2' ? 2 : 3;
+        const int ndig = dig_env && dig_env[0] == '3' ? 3 : 2;
         VPlanHost vp;
         build_vplan(g, tx, ty, ndig, vp);
         if (vp.ok) {

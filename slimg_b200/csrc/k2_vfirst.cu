@@ -27,7 +27,8 @@
 // Nothing but source pixels is read from HBM and nothing but final pixels is written: the f32
 // intermediate of the reference (38-51 MB per image) never exists.
 //
-// Grid: x = strips, y = bands of output-row groups, z = image.  512 threads, one CTA per SM.
+// Grid: x = strips, y = bands of output-row groups, z = image.  512 threads, one CTA per SM: the first
+// (strip columns / 8) warps run pass 2, the others pass 1; one CTA barrier per group.
 #include "kernels.cuh"
 
 namespace slimg {
@@ -188,7 +189,13 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     //      precedes the copies.  (One warp issuing all 16 copies serialises them: the instruction takes
     //      uniform operands.)  The bookkeeping is uniform across the CTA. ---------------------------------
     int next_issue = 0, issue_slot = 0;
-    auto arm_steps = [&](int upto) {          // thread 0
+    int my_row = int(p.ry) + ys + warp;                        // source row of this warp's next copy
+    const uint8_t *my_src = src_col + size_t(my_row) * p.sw * 4;
+    const size_t step_stride = size_t(kStepRows) * p.sw * 4;
+    const uint8_t *last_src = src_col + size_t(p.sh - 1) * p.sw * 4;
+    uint32_t my_dst = ring + uint32_t(warp) * p.pitch;
+    const uint32_t step_bytes = kStepRows * p.pitch;
+    auto arm_steps = [&](int upto) {          // one thread
         int slot = issue_slot;
         for (int s = next_issue; s < upto; s++) {
             mbar_arrive_expect_tx(&tail.full[slot], kStepRows * row_bytes);
@@ -197,13 +204,10 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     };
     auto issue_steps = [&](int upto) {        // all threads; lane 0 of warp w copies row w of each step
         for (; next_issue < upto; next_issue++) {
-            if (lane == 0) {
-                const int y = ys + next_issue * kStepRows + warp;
-                const int row = min(int(p.ry) + y, int(p.sh) - 1);       // rows past the end carry zero weights
-                bulk_g2s(ring + uint32_t(issue_slot * kStepRows + warp) * p.pitch, src_col + size_t(row) * p.sw * 4,
-                         row_bytes, &tail.full[issue_slot]);
-            }
-            if (++issue_slot == nst) issue_slot = 0;
+            if (lane == 0)                    // rows past the end of the image carry zero weights: any row will do
+                bulk_g2s(my_dst, my_row < int(p.sh) ? my_src : last_src, row_bytes, &tail.full[issue_slot]);
+            my_row += kStepRows; my_src += step_stride; my_dst += step_bytes;
+            if (++issue_slot == nst) { issue_slot = 0; my_dst = ring + uint32_t(warp) * p.pitch; }
         }
     };
     {
@@ -213,38 +217,11 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         issue_steps(upto);
     }
 
-    // ---- pass-2 role: the first 2*ntile warps each own (channel pair, tile of 8 output columns);
-    //      their weights stay in registers for the whole band ------------------------------------------
+    // ---- roles: the first ntile warps run pass 2 (one tile of 8 output columns each, all four channels);
+    //      the others run pass 1 (pairs of 16-byte blocks from a shared queue) ---------------------------
     const int ntile = (col1 - col0 + 7) >> 3;
-    const bool p2_active = warp < 2 * ntile;
-    const int mt = p2_active ? warp / ntile : 0, tile = p2_active ? warp - mt * ntile : 0;
-    const int kb0 = p2_active ? p.tile_kb0[strip * 8 + tile] : 0;
-    uint2 bw2[NCH2][NDIG];
-#pragma unroll
-    for (int c = 0; c < NCH2; c++)
-#pragma unroll
-        for (int d = 0; d < NDIG; d++)
-            bw2[c][d] = p2_active ? __ldg(reinterpret_cast<const uint2 *>(p.b2) +
-                                          ((size_t(strip * 8 + tile) * NCH2 + c) * NDIG + d) * 32 + lane)
-                                  : make_uint2(0u, 0u);
-    float cxr[2][2];                           // [column 2t+e][channel 2mt+h]
-#pragma unroll
-    for (int e = 0; e < 2; e++)
-#pragma unroll
-        for (int h = 0; h < 2; h++) {
-            const int col = col0 + tile * 8 + 2 * t + e;
-            cxr[e][h] = (p2_active && col < col1) ? p.cx[size_t(col) * 4 + 2 * mt + h] : 0.0f;
-        }
-
-    // ring bookkeeping without divisions: the step / slot / phase this warp waits on next, and the ring
-    // position of the current band start
-    int w_step = 0, w_slot = 0;
-    uint32_t w_par = 0;
-    int pos = 0, prev_a0 = ys;
+    const bool pass2_warp = warp < ntile;
     int jprev = -1;                            // previous group (its output rows are still staged)
-    const int npair = (nblk + 1) >> 1;
-    const int sh1 = p.sh1;
-    const int ch = g & 3, hh = g >> 2;
 
     auto copy_out = [&](int j, uint32_t buf) { // staged rows of group j -> global, whole rows
         const int r = warp & 7, i = j * 8 + r;
@@ -254,138 +231,187 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             for (int c = lane + 32 * (warp >> 3); c < col1 - col0; c += 64) row[c] = st[c];
         }
     };
-
-#pragma unroll 1
-    for (int it = 0; it < n_iter; it++) {
-        const uint32_t buf = uint32_t(it) & 1u;
-        const uint32_t *rec = recbuf + buf * p.rec_words;
-        if (it + 1 < n_iter) prefetch_rec(rec0 + it + 1, buf ^ 1u);
-        const int j = int(rec[0]), a0 = int(rec[1]), need = int(rec[2]);
-        const uint32_t vbuf = vbase + buf * 2u * vplane;
-        if (tid == 0) tail.counter[buf ^ 1u] = 0;     // next group's queue; its last users passed the previous barrier
-
-        // ---- wait for the source rows of this group (step s lives in slot s % nst, phase s / nst) ----
-        {
-            const int first = (a0 - ys) / kStepRows, last = (need - ys + kStepRows - 1) / kStepRows;
-            while (w_step < last) {
-                if (w_step >= first) mbar_wait(&tail.full[w_slot], w_par);
-                w_step++;
-                if (++w_slot == nst) { w_slot = 0; w_par ^= 1u; }
-            }
-            pos += a0 - prev_a0;
-            prev_a0 = a0;
-            while (pos >= int(p.ring_rows)) pos -= int(p.ring_rows);
-        }
-
-        // ================= pass 1: vertical taps of 8 output rows over the strip =======================
-        {
-            uint2 bw1[NCH1][NDIG];
-            uint32_t rowoff[NCH1];
-#pragma unroll
-            for (int c = 0; c < NCH1; c++) {
-#pragma unroll
-                for (int d = 0; d < NDIG; d++)
-                    bw1[c][d] = *reinterpret_cast<const uint2 *>(rec + 64 + ((c * NDIG + d) * 32 + lane) * 2);
-                int rr = pos + 32 * c + lane;
-                if (rr >= int(p.ring_rows)) rr -= int(p.ring_rows);
-                if (rr >= int(p.ring_rows)) rr -= int(p.ring_rows);
-                rowoff[c] = ring + uint32_t(rr) * p.pitch;
-            }
-            const int bias0 = int(rec[8 + (2 * t) * 4 + ch]), bias1 = int(rec[8 + (2 * t + 1) * 4 + ch]);
-            // V word address of (row 8*ch + 2t + hh, block 0): rows are pitch_v apart, channel planes skewed by one word
-            const uint32_t vrow = vbuf + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u;
-
-            int *counter = &tail.counter[buf];
-            int pr = 0;
-            if (lane == 0) pr = atomicAdd(counter, 1);
-            pr = __shfl_sync(0xffffffffu, pr, 0);
-#pragma unroll 1
-            while (pr < npair) {
-                int nxt = 0;
-                if (lane == 0) nxt = atomicAdd(counter, 1);      // next pair: the answer arrives while this one computes
-                const int blk = pr * 2;
-                int acc[2][NDIG][4];
-#pragma unroll
-                for (int c = 0; c < NCH1; c++) {       // groups with shorter bands carry zero weights in the rest
-                    uint32_t a[2][4];
-                    ldsm_t(a[0], rowoff[c] + uint32_t(blk) * 16u);
-                    ldsm_t(a[1], rowoff[c] + uint32_t(blk) * 16u + 16u);
-#pragma unroll
-                    for (int d = 0; d < NDIG; d++) {
-                        if (c == 0) { imma_z(acc[0][d], a[0], bw1[c][d]); imma_z(acc[1][d], a[1], bw1[c][d]); }
-                        else { imma(acc[0][d], a[0], bw1[c][d]); imma(acc[1][d], a[1], bw1[c][d]); }
-                    }
-                }
-                // recombine the digit planes (exact), re-quantise to u16, split into limbs
-#pragma unroll
-                for (int u = 0; u < 2; u++) {
-                    int v[4];
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        int x = acc[u][0][i] + (acc[u][1][i] << 8);
-                        if (NDIG == 3) x += acc[u][NDIG - 1][i] << 16;
-                        v[i] = (x + ((i & 1) ? bias1 : bias0)) >> sh1;
-                    }
-                    // v[0],v[2]: pixel hh / hh+2 of output row 2t; v[1],v[3]: same pixels of row 2t+1
-                    const uint32_t w0 = __byte_perm(uint32_t(v[0]), uint32_t(v[2]), 0x5140);   // lo lo hi hi of row 2t
-                    const uint32_t w1 = __byte_perm(uint32_t(v[1]), uint32_t(v[3]), 0x5140);   // ... of row 2t+1
-                    const uint32_t send = hh ? w0 : w1, mine = hh ? w1 : w0;
-                    const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 16);
-                    const uint32_t pa = hh ? recv : mine, pb = hh ? mine : recv;              // pixels (0,2) and (1,3)
-                    if (blk + u < nblk) {
-                        sts32(vrow + uint32_t(blk + u) * 4u, __byte_perm(pa, pb, 0x5410));             // low limbs
-                        sts32(vrow + vplane + uint32_t(blk + u) * 4u, __byte_perm(pa, pb, 0x7632));    // high limbs
-                    }
-                }
-                pr = __shfl_sync(0xffffffffu, nxt, 0);
-            }
-        }
+    // the part of an iteration every warp runs between its two role-specific halves
+    auto turn = [&](int it, const uint32_t *rec, uint32_t buf) {
         // ring steps no later group needs: step s may replace step s - nst once every row of that one lies
         // above the next band
         const int a_next = it + 1 < n_iter ? int(rec[4]) : ye;
         const int refill_upto = min(n_steps, (a_next - ys) / kStepRows + nst);
-        if (tid == 0) arm_steps(refill_upto);
+        // armed by a pass-1 thread: it has waited on every step that is being replaced, so their phases are over
+        if (tid == kThreads - 32) {
+            arm_steps(refill_upto);
+            tail.counter[buf ^ 1u] = 0;       // next group's queue; its last users passed the previous barrier
+        }
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();      // V[buf] and the next record are complete; every warp is done with the ring rows
                               // below the next band and with pass 2 of the previous group
         issue_steps(refill_upto);
         if (jprev >= 0) copy_out(jprev, buf ^ 1u);
+    };
 
-        // ================= pass 2: horizontal taps, 2 channels x 8 rows x 8 output columns per warp =======
-        if (p2_active) {
-            int acc[2][NDIG][4];
-            const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
-            const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
+    if (pass2_warp) {
+        // ================= pass 2: horizontal taps, 4 channels x 8 rows x 8 output columns per warp =======
+        const int tile = warp;
+        const int kb0 = p.tile_kb0[strip * 8 + tile];
+        uint2 bw2[NCH2][NDIG];
 #pragma unroll
-            for (int c = 0; c < NCH2; c++) {
+        for (int c = 0; c < NCH2; c++)
 #pragma unroll
-                for (int l = 0; l < 2; l++) {
-                    uint32_t a[4];
-                    const uint32_t o = uint32_t(l) * vplane + uint32_t(c) * 32u;
-                    a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
+            for (int d = 0; d < NDIG; d++)
+                bw2[c][d] = __ldg(reinterpret_cast<const uint2 *>(p.b2) + ((size_t(strip * 8 + tile) * NCH2 + c) * NDIG + d) * 32 + lane);
+        float cxr[2][4];                       // [column 2t+e][channel]
 #pragma unroll
-                    for (int d = 0; d < NDIG; d++) {
-                        if (c == 0) imma_z(acc[l][d], a, bw2[c][d]);
-                        else imma(acc[l][d], a, bw2[c][d]);
+        for (int e = 0; e < 2; e++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const int col = col0 + tile * 8 + 2 * t + e;
+                cxr[e][c] = col < col1 ? p.cx[size_t(col) * 4 + c] : 0.0f;
+            }
+        float s2[2][NDIG];
+#pragma unroll
+        for (int l = 0; l < 2; l++)
+#pragma unroll
+            for (int d = 0; d < NDIG; d++) s2[l][d] = p.s2[l][d];
+
+#pragma unroll 1
+        for (int it = 0; it < n_iter; it++) {
+            const uint32_t buf = uint32_t(it) & 1u;
+            const uint32_t *rec = recbuf + buf * p.rec_words;
+            if (it + 1 < n_iter) prefetch_rec(rec0 + it + 1, buf ^ 1u);
+            const int j = int(rec[0]);
+            turn(it, rec, buf);
+
+            const uint32_t vbuf = vbase + buf * 2u * vplane;
+            uint32_t px[2] = {0u, 0u};         // packed RGBA of columns 2t, 2t+1 of output row g
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) {   // channel pairs (0,1) and (2,3)
+                int acc[2][NDIG][4];
+                const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
+                const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
+#pragma unroll
+                for (int c = 0; c < NCH2; c++) {
+#pragma unroll
+                    for (int l = 0; l < 2; l++) {
+                        uint32_t a[4];
+                        const uint32_t o = uint32_t(l) * vplane + uint32_t(c) * 32u;
+                        a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
+#pragma unroll
+                        for (int d = 0; d < NDIG; d++) {
+                            if (c == 0) imma_z(acc[l][d], a, bw2[c][d]);
+                            else imma(acc[l][d], a, bw2[c][d]);
+                        }
                     }
                 }
+                // i = 0,1: channel 2mt, columns 2t, 2t+1; i = 2,3: channel 2mt+1
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    float f = cxr[i & 1][2 * mt + (i >> 1)];
+#pragma unroll
+                    for (int l = 0; l < 2; l++)
+#pragma unroll
+                        for (int d = 0; d < NDIG; d++) f = fmaf(int_to_float(acc[l][d][i]), s2[l][d], f);
+                    px[i & 1] |= quantize_channel(f) << (8 * (2 * mt + (i >> 1)));
+                }
             }
-            // i = 0,1: channel 2mt, columns 2t, 2t+1; i = 2,3: channel 2mt+1
-            uint32_t q[4];
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                float f = cxr[i & 1][i >> 1];
-#pragma unroll
-                for (int l = 0; l < 2; l++)
-#pragma unroll
-                    for (int d = 0; d < NDIG; d++) f = fmaf(int_to_float(acc[l][d][i]), p.s2[l][d], f);
-                q[i] = quantize_channel(f);
-            }
-            uint8_t *st = reinterpret_cast<uint8_t *>(&tail.stage[buf][g][tile * 8 + 2 * t]) + 2 * mt;
-            sts16(smem_u32(st), q[0] | (q[2] << 8));
-            sts16(smem_u32(st + 4), q[1] | (q[3] << 8));
+            *reinterpret_cast<uint2 *>(&tail.stage[buf][g][tile * 8 + 2 * t]) = make_uint2(px[0], px[1]);
+            jprev = j;
         }
-        jprev = j;
+    } else {
+        // ================= pass 1: vertical taps of 8 output rows over the strip =======================
+        // ring bookkeeping without divisions: the step / slot / phase this warp waits on next, and the ring
+        // position of the current band start
+        int w_step = 0, w_slot = 0;
+        uint32_t w_par = 0;
+        int pos = 0, prev_a0 = ys;
+        const int npair = (nblk + 1) >> 1;
+        const int sh1 = p.sh1;
+        const int ch = g & 3, hh = g >> 2;
+        const int ring_rows = int(p.ring_rows);
+
+#pragma unroll 1
+        for (int it = 0; it < n_iter; it++) {
+            const uint32_t buf = uint32_t(it) & 1u;
+            const uint32_t *rec = recbuf + buf * p.rec_words;
+            if (it + 1 < n_iter) prefetch_rec(rec0 + it + 1, buf ^ 1u);
+            const int j = int(rec[0]), a0 = int(rec[1]), need = int(rec[2]);
+
+            // ---- wait for the source rows of this group (step s lives in slot s % nst, phase s / nst) ----
+            {
+                const int first = (a0 - ys) / kStepRows, last = (need - ys + kStepRows - 1) / kStepRows;
+                while (w_step < last) {
+                    if (w_step >= first) mbar_wait(&tail.full[w_slot], w_par);
+                    w_step++;
+                    if (++w_slot == nst) { w_slot = 0; w_par ^= 1u; }
+                }
+                pos += a0 - prev_a0;
+                prev_a0 = a0;
+                while (pos >= ring_rows) pos -= ring_rows;
+            }
+            {
+                uint2 bw1[NCH1][NDIG];
+                uint32_t rowoff[NCH1];
+#pragma unroll
+                for (int c = 0; c < NCH1; c++) {
+#pragma unroll
+                    for (int d = 0; d < NDIG; d++)
+                        bw1[c][d] = *reinterpret_cast<const uint2 *>(rec + 64 + ((c * NDIG + d) * 32 + lane) * 2);
+                    int rr = pos + 32 * c + lane;
+                    if (rr >= ring_rows) rr -= ring_rows;
+                    if (rr >= ring_rows) rr -= ring_rows;
+                    rowoff[c] = ring + uint32_t(rr) * p.pitch;
+                }
+                const int bias0 = int(rec[8 + (2 * t) * 4 + ch]), bias1 = int(rec[8 + (2 * t + 1) * 4 + ch]);
+                // V word address of (row 8*ch + 2t + hh, block 0): rows are pitch_v apart, channel planes skewed by one word
+                const uint32_t vrow = vbase + buf * 2u * vplane + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u;
+
+                int *counter = &tail.counter[buf];
+                int pr = 0;
+                if (lane == 0) pr = atomicAdd(counter, 1);
+                pr = __shfl_sync(0xffffffffu, pr, 0);
+#pragma unroll 1
+                while (pr < npair) {
+                    int nxt = 0;
+                    if (lane == 0) nxt = atomicAdd(counter, 1);      // next pair: the answer arrives while this one computes
+                    const int blk = pr * 2;
+                    int acc[2][NDIG][4];
+#pragma unroll
+                    for (int c = 0; c < NCH1; c++) {       // groups with shorter bands carry zero weights in the rest
+                        uint32_t a[2][4];
+                        ldsm_t(a[0], rowoff[c] + uint32_t(blk) * 16u);
+                        ldsm_t(a[1], rowoff[c] + uint32_t(blk) * 16u + 16u);
+#pragma unroll
+                        for (int d = 0; d < NDIG; d++) {
+                            if (c == 0) { imma_z(acc[0][d], a[0], bw1[c][d]); imma_z(acc[1][d], a[1], bw1[c][d]); }
+                            else { imma(acc[0][d], a[0], bw1[c][d]); imma(acc[1][d], a[1], bw1[c][d]); }
+                        }
+                    }
+                    // recombine the digit planes (exact), re-quantise to u16, split into limbs
+#pragma unroll
+                    for (int u = 0; u < 2; u++) {
+                        int v[4];
+#pragma unroll
+                        for (int i = 0; i < 4; i++) {
+                            int x = acc[u][0][i] + (acc[u][1][i] << 8);
+                            if (NDIG == 3) x += acc[u][NDIG - 1][i] << 16;
+                            v[i] = (x + ((i & 1) ? bias1 : bias0)) >> sh1;
+                        }
+                        // v[0],v[2]: pixel hh / hh+2 of output row 2t; v[1],v[3]: same pixels of row 2t+1
+                        const uint32_t w0 = __byte_perm(uint32_t(v[0]), uint32_t(v[2]), 0x5140);   // lo lo hi hi of row 2t
+                        const uint32_t w1 = __byte_perm(uint32_t(v[1]), uint32_t(v[3]), 0x5140);   // ... of row 2t+1
+                        const uint32_t send = hh ? w0 : w1, mine = hh ? w1 : w0;
+                        const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 16);
+                        const uint32_t pa = hh ? recv : mine, pb = hh ? mine : recv;              // pixels (0,2) and (1,3)
+                        if (blk + u < nblk) {
+                            sts32(vrow + uint32_t(blk + u) * 4u, __byte_perm(pa, pb, 0x5410));             // low limbs
+                            sts32(vrow + vplane + uint32_t(blk + u) * 4u, __byte_perm(pa, pb, 0x7632));    // high limbs
+                        }
+                    }
+                    pr = __shfl_sync(0xffffffffu, nxt, 0);
+                }
+            }
+            turn(it, rec, buf);
+            jprev = j;
+        }
     }
     __syncthreads();
     if (jprev >= 0) copy_out(jprev, uint32_t(n_iter - 1) & 1u);
