@@ -40,6 +40,7 @@ constexpr int kThreads = kWarps * 32;
 constexpr int kStepRows = 16;                // source rows per ring step (one mbarrier each) == kWarps
 constexpr int kMaxSteps = 16;                // ring of at most 256 rows
 constexpr int kStageCols = 64;
+constexpr int kUnit = 4;                     // 16-byte blocks a pass-1 warp takes from the queue at a time (vplan.cpp pads to it)
 constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
@@ -79,6 +80,12 @@ __device__ __forceinline__ void imma_z(int (&d)[4], const uint32_t (&a)[4], cons
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
                  : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "r"(0));
+}
+// first k-chunk of the first digit: the accumulator starts at the bias of its output row (columns n = 2t, 2t+1)
+__device__ __forceinline__ void imma_c(int (&d)[4], const uint32_t (&a)[4], const uint2 &b, int c0, int c1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%10,%11};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "r"(c0), "r"(c1));
 }
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
     uint32_t v;
@@ -323,7 +330,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         int w_step = 0, w_slot = 0;
         uint32_t w_par = 0;
         int pos = 0, prev_a0 = ys;
-        const int npair = (nblk + 1) >> 1;
+        const int nquad = nblk / kUnit;           // the plan pads the strip to a whole number of units
         const int sh1 = p.sh1;
         const int ch = g & 3, hh = g >> 2;
         const int ring_rows = int(p.ring_rows);
@@ -359,41 +366,47 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                     if (rr >= ring_rows) rr -= ring_rows;
                     if (rr >= ring_rows) rr -= ring_rows;
                     rowoff[c] = ring + uint32_t(rr) * p.pitch;
+                    asm volatile("" : "+r"(rowoff[c]));       // keep it in a register: cheaper than recomputing per block
                 }
                 const int bias0 = int(rec[8 + (2 * t) * 4 + ch]), bias1 = int(rec[8 + (2 * t + 1) * 4 + ch]);
                 // V word address of (row 8*ch + 2t + hh, block 0): rows are pitch_v apart, channel planes skewed by one word
-                const uint32_t vrow = vbase + buf * 2u * vplane + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u;
+                uint32_t vrow = vbase + buf * 2u * vplane + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u;
+                uint32_t vrow_hi = vrow + vplane;
+                asm volatile("" : "+r"(vrow), "+r"(vrow_hi));
 
                 int *counter = &tail.counter[buf];
-                int pr = 0;
-                if (lane == 0) pr = atomicAdd(counter, 1);
-                pr = __shfl_sync(0xffffffffu, pr, 0);
+                int qd = 0;
+                if (lane == 0) qd = atomicAdd(counter, 1);
+                qd = __shfl_sync(0xffffffffu, qd, 0);
 #pragma unroll 1
-                while (pr < npair) {
+                while (qd < nquad) {
                     int nxt = 0;
-                    if (lane == 0) nxt = atomicAdd(counter, 1);      // next pair: the answer arrives while this one computes
-                    const int blk = pr * 2;
-                    int acc[2][NDIG][4];
+                    if (lane == 0) nxt = atomicAdd(counter, 1);      // next unit: the answer arrives while this one computes
+                    const uint32_t boff = uint32_t(qd) * (kUnit * 16u);
+                    int acc[kUnit][NDIG][4];
 #pragma unroll
                     for (int c = 0; c < NCH1; c++) {       // groups with shorter bands carry zero weights in the rest
-                        uint32_t a[2][4];
-                        ldsm_t(a[0], rowoff[c] + uint32_t(blk) * 16u);
-                        ldsm_t(a[1], rowoff[c] + uint32_t(blk) * 16u + 16u);
+                        uint32_t a[kUnit][4];
 #pragma unroll
-                        for (int d = 0; d < NDIG; d++) {
-                            if (c == 0) { imma_z(acc[0][d], a[0], bw1[c][d]); imma_z(acc[1][d], a[1], bw1[c][d]); }
-                            else { imma(acc[0][d], a[0], bw1[c][d]); imma(acc[1][d], a[1], bw1[c][d]); }
-                        }
+                        for (int u = 0; u < kUnit; u++) ldsm_t(a[u], rowoff[c] + boff + uint32_t(u) * 16u);
+#pragma unroll
+                        for (int d = 0; d < NDIG; d++)
+#pragma unroll
+                            for (int u = 0; u < kUnit; u++) {
+                                if (c == 0 && d == 0) imma_c(acc[u][d], a[u], bw1[c][d], bias0, bias1);   // the sum starts at the bias
+                                else if (c == 0) imma_z(acc[u][d], a[u], bw1[c][d]);
+                                else imma(acc[u][d], a[u], bw1[c][d]);
+                            }
                     }
                     // recombine the digit planes (exact), re-quantise to u16, split into limbs
 #pragma unroll
-                    for (int u = 0; u < 2; u++) {
+                    for (int u = 0; u < kUnit; u++) {
                         int v[4];
 #pragma unroll
                         for (int i = 0; i < 4; i++) {
                             int x = acc[u][0][i] + (acc[u][1][i] << 8);
                             if (NDIG == 3) x += acc[u][NDIG - 1][i] << 16;
-                            v[i] = (x + ((i & 1) ? bias1 : bias0)) >> sh1;
+                            v[i] = x >> sh1;
                         }
                         // v[0],v[2]: pixel hh / hh+2 of output row 2t; v[1],v[3]: same pixels of row 2t+1
                         const uint32_t w0 = __byte_perm(uint32_t(v[0]), uint32_t(v[2]), 0x5140);   // lo lo hi hi of row 2t
@@ -401,12 +414,11 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                         const uint32_t send = hh ? w0 : w1, mine = hh ? w1 : w0;
                         const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 16);
                         const uint32_t pa = hh ? recv : mine, pb = hh ? mine : recv;              // pixels (0,2) and (1,3)
-                        if (blk + u < nblk) {
-                            sts32(vrow + uint32_t(blk + u) * 4u, __byte_perm(pa, pb, 0x5410));             // low limbs
-                            sts32(vrow + vplane + uint32_t(blk + u) * 4u, __byte_perm(pa, pb, 0x7632));    // high limbs
-                        }
+                        // (the plan pads the strip to a whole number of units)
+                        sts32(vrow + boff / 4u + uint32_t(u) * 4u, __byte_perm(pa, pb, 0x5410));       // low limbs
+                        sts32(vrow_hi + boff / 4u + uint32_t(u) * 4u, __byte_perm(pa, pb, 0x7632));    // high limbs
                     }
-                    pr = __shfl_sync(0xffffffffu, nxt, 0);
+                    qd = __shfl_sync(0xffffffffu, nxt, 0);
                 }
             }
             turn(it, rec, buf);

@@ -21,6 +21,7 @@ namespace {
 constexpr int kFrac = 7;        // fractional bits of the 16-bit intermediate
 constexpr int kOffset = 64;     // added to the intermediate so Lanczos undershoot stays >= 0
 constexpr int kPrefetchRows = 64;   // a whole group's worth of new rows must be in flight while the previous group computes
+constexpr int kUnit = 4;           // k2_vfirst.cu kUnit
 constexpr int kMaxCh = 4;          // chunk stride of the fragment tables (the kernel's NCH1 / NCH2)
 constexpr size_t kSmemBudget = 227 * 1024 - 2048;
 const int kPerm[4] = {0, 2, 1, 3};   // k-slot -> pixel inside a 4-pixel block (k2_vfirst.cu, pass-1 epilogue)
@@ -196,7 +197,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         }
     };
     auto smem_for = [&](int64_t nblk, uint32_t &pitch, uint32_t &pitch_v) {
-        int64_t units = nblk | 1;                                  // odd multiple of 16 bytes
+        int64_t units = nblk | 1;                                  // odd multiple of 16 bytes (nblk is even)
         pitch = uint32_t(units * 16);
         int64_t qv = (nblk + 3 + 3) / 4;                           // words per V row = 4 * odd >= nblk + 3
         if (qv % 2 == 0) qv++;
@@ -211,7 +212,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
             int64_t lo, hi;
             span_of(c0, std::min(g.pw, c0 + cand), lo, hi);
             if (hi < 0) continue;
-            const int64_t nblk = (hi - (lo & ~int64_t(3)) + 3) / 4;
+            const int64_t nblk = ((hi - (lo & ~int64_t(3)) + 3) / 4 + kUnit - 1) / kUnit * kUnit;
             uint32_t p, pv;
             if (smem_for(nblk, p, pv) > kSmemBudget) fits = false;
         }
@@ -240,10 +241,12 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         span_of(c0, c1, lo, hi);
         if (hi < 0) continue;                        // every tap of the strip lands on fill
         const int64_t s0 = lo & ~int64_t(3);
-        const int64_t nblk = (hi - s0 + 3) / 4;
+        // pass 1 works on units of kUnit 16-byte blocks: pad to a whole number (the extra blocks read whatever
+        // lies beyond the staged bytes of the row and meet zero weights in pass 2)
+        const int64_t nblk = ((hi - s0 + 3) / 4 + kUnit - 1) / kUnit * kUnit;
         out.strip_src0[s] = int32_t(s0);
         out.strip_nblk[s] = int32_t(nblk);
-        out.strip_bytes[s] = int32_t((std::min<int64_t>(s0 + nblk * 4, g.sw) - s0) * 4);
+        out.strip_bytes[s] = int32_t((std::min<int64_t>(s0 + (hi - s0 + 3) / 4 * 4, g.sw) - s0) * 4);
         max_nblk = std::max(max_nblk, nblk);
         for (uint32_t t = 0; t * 8 < c1 - c0; t++) {
             int64_t tlo, thi;
