@@ -48,6 +48,9 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
@@ -108,9 +111,11 @@ __device__ __forceinline__ uint32_t quantize_channel(float t) {
 }
 
 struct SmemTail {                             // after the ring, the V planes and the two group records
-    uint32_t stage[2][8][kStageCols];        // packed output rows of the last two groups
-    uint64_t full[kMaxSteps];
-    int counter[2];                          // pass-1 work queue (pairs of 16-byte blocks), one per V buffer
+    uint64_t full[kMaxSteps];                // ring step landed (tx bytes)
+    uint64_t rec_full[2];                    // group record landed (tx bytes)
+    uint64_t v_full[2];                      // every pass-1 warp is done with the group: V complete, band rows released
+    uint64_t v_empty[2];                     // every pass-2 warp has read V
+    int counter[2];                          // pass-1 work queues (units of kUnit blocks), one per V buffer, never reset
 };
 
 // What is not computed: canvas rows outside the kept rectangle (fill_post), kept rows whose taps
@@ -173,90 +178,62 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     const int n_steps = (ye - ys + kStepRows - 1) / kStepRows;
     const int nst = int(p.ring_rows) / kStepRows;
 
-    auto prefetch_rec = [&](int r, uint32_t buf) {           // group record r -> shared memory, 16 bytes per thread
-        if (tid < int(p.rec_words / 4)) {
-            const uint32_t d = smem_u32(recbuf) + (buf * p.rec_words + uint32_t(tid) * 4u) * 4u;
-            const uint32_t *s = p.recs + size_t(r) * p.rec_words + size_t(tid) * 4;
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(s) : "memory");
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-
+    // ---- roles ---------------------------------------------------------------------------------------
+    //   warps [0, ntile)        pass 2: one tile of 8 output columns each, all four channels
+    //   warps [ntile, 15)       pass 1: units of kUnit 16-byte blocks from a shared queue
+    //   warp 15                 producer: ring refills and group records through the TMA engine
+    // They meet only on mbarriers: no CTA-wide barrier inside the band loop.
+    const int ntile = (col1 - col0 + 7) >> 3;
+    const int n_p1 = kWarps - 1 - ntile;
+    const uint32_t rec_bytes = p.rec_words * 4u;
     if (tid == 0) {
         for (int s = 0; s < nst; s++) mbar_init(&tail.full[s], 1);
-        tail.counter[0] = 0; tail.counter[1] = 0;
+        for (int b = 0; b < 2; b++) {
+            mbar_init(&tail.rec_full[b], 1);
+            mbar_init(&tail.v_full[b], uint32_t(n_p1));
+            mbar_init(&tail.v_empty[b], uint32_t(ntile));
+            tail.counter[b] = 0;
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (n_iter > 0) prefetch_rec(rec0, 0);
-    asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
 
-    // ---- producer: every warp owns one of the 16 source rows of a ring step and issues its linear bulk
-    //      copy (TMA engine) from lane 0; thread 0 arms the step's mbarrier before the CTA barrier that
-    //      precedes the copies.  (One warp issuing all 16 copies serialises them: the instruction takes
-    //      uniform operands.)  The bookkeeping is uniform across the CTA. ---------------------------------
-    int next_issue = 0, issue_slot = 0;
-    int my_row = int(p.ry) + ys + warp;                        // source row of this warp's next copy
-    const uint8_t *my_src = src_col + size_t(my_row) * p.sw * 4;
-    const size_t step_stride = size_t(kStepRows) * p.sw * 4;
-    const uint8_t *last_src = src_col + size_t(p.sh - 1) * p.sw * 4;
-    uint32_t my_dst = ring + uint32_t(warp) * p.pitch;
-    const uint32_t step_bytes = kStepRows * p.pitch;
-    auto arm_steps = [&](int upto) {          // one thread
-        int slot = issue_slot;
-        for (int s = next_issue; s < upto; s++) {
-            mbar_arrive_expect_tx(&tail.full[slot], kStepRows * row_bytes);
-            if (++slot == nst) slot = 0;
+    if (warp == kWarps - 1) {
+        // ================= producer ====================================================================
+        // One linear bulk copy per source row (lanes 0..15 own the rows of a step), one per group record.
+        int next_issue = 0, issue_slot = 0;
+        auto issue_steps = [&](int upto) {
+            for (; next_issue < upto; next_issue++) {
+                if (lane == 0) mbar_arrive_expect_tx(&tail.full[issue_slot], kStepRows * row_bytes);
+                __syncwarp();
+                if (lane < kStepRows) {
+                    const int y = int(p.ry) + ys + next_issue * kStepRows + lane;
+                    const int row = min(y, int(p.sh) - 1);               // rows past the end carry zero weights
+                    bulk_g2s(ring + uint32_t(issue_slot * kStepRows + lane) * p.pitch, src_col + size_t(row) * p.sw * 4,
+                             row_bytes, &tail.full[issue_slot]);
+                }
+                if (++issue_slot == nst) issue_slot = 0;
+            }
+        };
+        auto issue_rec = [&](int it) {
+            if (lane == 0) {
+                uint64_t *bar = &tail.rec_full[it & 1];
+                mbar_arrive_expect_tx(bar, rec_bytes);
+                bulk_g2s(smem_u32(recbuf) + uint32_t(it & 1) * rec_bytes, p.recs + size_t(rec0 + it) * p.rec_words, rec_bytes, bar);
+            }
+        };
+        if (n_iter > 0) issue_rec(0);
+        if (n_iter > 1) issue_rec(1);
+        issue_steps(min(n_steps, nst));
+#pragma unroll 1
+        for (int it = 0; it < n_iter; it++) {
+            // band start of the next group: ring steps entirely above it are free once this group is done
+            const int a_next = it + 1 < n_iter ? int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words + 1)) : ye;
+            mbar_wait(&tail.v_full[it & 1], uint32_t(it >> 1) & 1u);
+            issue_steps(min(n_steps, (a_next - ys) / kStepRows + nst));
+            if (it + 2 < n_iter) issue_rec(it + 2);          // the record buffer of this group is free as well
         }
-    };
-    auto issue_steps = [&](int upto) {        // all threads; lane 0 of warp w copies row w of each step
-        for (; next_issue < upto; next_issue++) {
-            if (lane == 0)                    // rows past the end of the image carry zero weights: any row will do
-                bulk_g2s(my_dst, my_row < int(p.sh) ? my_src : last_src, row_bytes, &tail.full[issue_slot]);
-            my_row += kStepRows; my_src += step_stride; my_dst += step_bytes;
-            if (++issue_slot == nst) { issue_slot = 0; my_dst = ring + uint32_t(warp) * p.pitch; }
-        }
-    };
-    {
-        const int upto = min(n_steps, nst);
-        if (tid == 0) arm_steps(upto);
-        __syncthreads();
-        issue_steps(upto);
-    }
-
-    // ---- roles: the first ntile warps run pass 2 (one tile of 8 output columns each, all four channels);
-    //      the others run pass 1 (pairs of 16-byte blocks from a shared queue) ---------------------------
-    const int ntile = (col1 - col0 + 7) >> 3;
-    const bool pass2_warp = warp < ntile;
-    int jprev = -1;                            // previous group (its output rows are still staged)
-
-    auto copy_out = [&](int j, uint32_t buf) { // staged rows of group j -> global, whole rows
-        const int r = warp & 7, i = j * 8 + r;
-        if (i < int(p.ph) && p.row_computed[i]) {
-            uint32_t *row = dst + size_t(p.foy + i) * p.fw + p.fox + col0;
-            const uint32_t *st = tail.stage[buf][r];
-            for (int c = lane + 32 * (warp >> 3); c < col1 - col0; c += 64) row[c] = st[c];
-        }
-    };
-    // the part of an iteration every warp runs between its two role-specific halves
-    auto turn = [&](int it, const uint32_t *rec, uint32_t buf) {
-        // ring steps no later group needs: step s may replace step s - nst once every row of that one lies
-        // above the next band
-        const int a_next = it + 1 < n_iter ? int(rec[4]) : ye;
-        const int refill_upto = min(n_steps, (a_next - ys) / kStepRows + nst);
-        // armed by a pass-1 thread: it has waited on every step that is being replaced, so their phases are over
-        if (tid == kThreads - 32) {
-            arm_steps(refill_upto);
-            tail.counter[buf ^ 1u] = 0;       // next group's queue; its last users passed the previous barrier
-        }
-        asm volatile("cp.async.wait_all;" ::: "memory");
-        __syncthreads();      // V[buf] and the next record are complete; every warp is done with the ring rows
-                              // below the next band and with pass 2 of the previous group
-        issue_steps(refill_upto);
-        if (jprev >= 0) copy_out(jprev, buf ^ 1u);
-    };
-
-    if (pass2_warp) {
+    } else if (warp < ntile) {
         // ================= pass 2: horizontal taps, 4 channels x 8 rows x 8 output columns per warp =======
         const int tile = warp;
         const int kb0 = p.tile_kb0[strip * 8 + tile];
@@ -266,33 +243,30 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
 #pragma unroll
             for (int d = 0; d < NDIG; d++)
                 bw2[c][d] = __ldg(reinterpret_cast<const uint2 *>(p.b2) + ((size_t(strip * 8 + tile) * NCH2 + c) * NDIG + d) * 32 + lane);
-        float cxr[2][4];                       // [column 2t+e][channel]
+        const int ocol = col0 + tile * 8 + 2 * t;          // this lane's two kept output columns
+        float cxr[2][4];                                   // [column ocol+e][channel]
 #pragma unroll
         for (int e = 0; e < 2; e++)
 #pragma unroll
-            for (int c = 0; c < 4; c++) {
-                const int col = col0 + tile * 8 + 2 * t + e;
-                cxr[e][c] = col < col1 ? p.cx[size_t(col) * 4 + c] : 0.0f;
-            }
+            for (int c = 0; c < 4; c++) cxr[e][c] = ocol + e < col1 ? p.cx[size_t(ocol + e) * 4 + c] : 0.0f;
         float s2[2][NDIG];
 #pragma unroll
         for (int l = 0; l < 2; l++)
 #pragma unroll
             for (int d = 0; d < NDIG; d++) s2[l][d] = p.s2[l][d];
+        int j_next = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words)) : 0;
 
 #pragma unroll 1
         for (int it = 0; it < n_iter; it++) {
             const uint32_t buf = uint32_t(it) & 1u;
-            const uint32_t *rec = recbuf + buf * p.rec_words;
-            if (it + 1 < n_iter) prefetch_rec(rec0 + it + 1, buf ^ 1u);
-            const int j = int(rec[0]);
-            turn(it, rec, buf);
-
+            const int j = j_next;
+            if (it + 1 < n_iter) j_next = int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words));
             const uint32_t vbuf = vbase + buf * 2u * vplane;
-            uint32_t px[2] = {0u, 0u};         // packed RGBA of columns 2t, 2t+1 of output row g
+            mbar_wait(&tail.v_full[buf], uint32_t(it >> 1) & 1u);
+
+            int acc[2][2][NDIG][4];            // [channel pair][limb][digit]
 #pragma unroll
             for (int mt = 0; mt < 2; mt++) {   // channel pairs (0,1) and (2,3)
-                int acc[2][NDIG][4];
                 const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
                 const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
 #pragma unroll
@@ -304,24 +278,33 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                         a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
 #pragma unroll
                         for (int d = 0; d < NDIG; d++) {
-                            if (c == 0) imma_z(acc[l][d], a, bw2[c][d]);
-                            else imma(acc[l][d], a, bw2[c][d]);
+                            if (c == 0) imma_z(acc[mt][l][d], a, bw2[c][d]);
+                            else imma(acc[mt][l][d], a, bw2[c][d]);
                         }
                     }
                 }
-                // i = 0,1: channel 2mt, columns 2t, 2t+1; i = 2,3: channel 2mt+1
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tail.v_empty[buf]);       // V[buf] may be overwritten (two groups on)
+
+            uint32_t px[2] = {0u, 0u};         // packed RGBA of columns ocol, ocol+1 of output row g
 #pragma unroll
-                for (int i = 0; i < 4; i++) {
+            for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                for (int i = 0; i < 4; i++) {  // i = 0,1: channel 2mt, columns +0, +1; i = 2,3: channel 2mt+1
                     float f = cxr[i & 1][2 * mt + (i >> 1)];
 #pragma unroll
                     for (int l = 0; l < 2; l++)
 #pragma unroll
-                        for (int d = 0; d < NDIG; d++) f = fmaf(int_to_float(acc[l][d][i]), s2[l][d], f);
+                        for (int d = 0; d < NDIG; d++) f = fmaf(int_to_float(acc[mt][l][d][i]), s2[l][d], f);
                     px[i & 1] |= quantize_channel(f) << (8 * (2 * mt + (i >> 1)));
                 }
+            const int i_row = j * 8 + g;
+            if (i_row < int(p.ph) && p.row_computed[i_row]) {
+                uint32_t *o = dst + size_t(p.foy + i_row) * p.fw + p.fox + ocol;
+                if (ocol < col1) o[0] = px[0];
+                if (ocol + 1 < col1) o[1] = px[1];
             }
-            *reinterpret_cast<uint2 *>(&tail.stage[buf][g][tile * 8 + 2 * t]) = make_uint2(px[0], px[1]);
-            jprev = j;
         }
     } else {
         // ================= pass 1: vertical taps of 8 output rows over the strip =======================
@@ -331,6 +314,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         uint32_t w_par = 0;
         int pos = 0, prev_a0 = ys;
         const int nquad = nblk / kUnit;           // the plan pads the strip to a whole number of units
+        const int per_group = nquad + n_p1;       // queue tickets a group consumes: every warp draws one blank
         const int sh1 = p.sh1;
         const int ch = g & 3, hh = g >> 2;
         const int ring_rows = int(p.ring_rows);
@@ -339,8 +323,18 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         for (int it = 0; it < n_iter; it++) {
             const uint32_t buf = uint32_t(it) & 1u;
             const uint32_t *rec = recbuf + buf * p.rec_words;
-            if (it + 1 < n_iter) prefetch_rec(rec0 + it + 1, buf ^ 1u);
-            const int j = int(rec[0]), a0 = int(rec[1]), need = int(rec[2]);
+            mbar_wait(&tail.rec_full[buf], uint32_t(it >> 1) & 1u);
+            const int a0 = int(rec[1]), need = int(rec[2]);
+            uint2 bw1[NCH1][NDIG];
+#pragma unroll
+            for (int c = 0; c < NCH1; c++)
+#pragma unroll
+                for (int d = 0; d < NDIG; d++)
+                    bw1[c][d] = *reinterpret_cast<const uint2 *>(rec + 64 + ((c * NDIG + d) * 32 + lane) * 2);
+            const int bias0 = int(rec[8 + (2 * t) * 4 + ch]), bias1 = int(rec[8 + (2 * t + 1) * 4 + ch]);
+
+            int *counter = &tail.counter[buf];
+            const int base = (it >> 1) * per_group;
 
             // ---- wait for the source rows of this group (step s lives in slot s % nst, phase s / nst) ----
             {
@@ -354,79 +348,72 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                 prev_a0 = a0;
                 while (pos >= ring_rows) pos -= ring_rows;
             }
-            {
-                uint2 bw1[NCH1][NDIG];
-                uint32_t rowoff[NCH1];
+            uint32_t rowoff[NCH1];
 #pragma unroll
-                for (int c = 0; c < NCH1; c++) {
+            for (int c = 0; c < NCH1; c++) {
+                int rr = pos + 32 * c + lane;
+                if (rr >= ring_rows) rr -= ring_rows;
+                if (rr >= ring_rows) rr -= ring_rows;
+                rowoff[c] = ring + uint32_t(rr) * p.pitch;
+                asm volatile("" : "+r"(rowoff[c]));       // keep it in a register: cheaper than recomputing per block
+            }
+            // V word address of (row 8*ch + 2t + hh, block 0): rows are pitch_v apart, channel planes skewed by one word
+            uint32_t vrow = vbase + buf * 2u * vplane + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u;
+            uint32_t vrow_hi = vrow + vplane;
+            asm volatile("" : "+r"(vrow), "+r"(vrow_hi));
+            // V[buf] was last read by pass 2 two groups ago
+            // (which also means every pass-1 warp has drawn its last ticket of that group from this queue)
+            mbar_wait(&tail.v_empty[buf], (uint32_t(it >> 1) & 1u) ^ 1u);
+
+            int qd = 0;
+            if (lane == 0) qd = atomicAdd(counter, 1);
+            qd = __shfl_sync(0xffffffffu, qd, 0) - base;
+#pragma unroll 1
+            while (qd < nquad) {
+                int nxt = 0;
+                if (lane == 0) nxt = atomicAdd(counter, 1);      // next unit: the answer arrives while this one computes
+                const uint32_t boff = uint32_t(qd) * (kUnit * 16u);
+                int acc[kUnit][NDIG][4];
+#pragma unroll
+                for (int c = 0; c < NCH1; c++) {       // groups with shorter bands carry zero weights in the rest
+                    uint32_t a[kUnit][4];
+#pragma unroll
+                    for (int u = 0; u < kUnit; u++) ldsm_t(a[u], rowoff[c] + boff + uint32_t(u) * 16u);
 #pragma unroll
                     for (int d = 0; d < NDIG; d++)
-                        bw1[c][d] = *reinterpret_cast<const uint2 *>(rec + 64 + ((c * NDIG + d) * 32 + lane) * 2);
-                    int rr = pos + 32 * c + lane;
-                    if (rr >= ring_rows) rr -= ring_rows;
-                    if (rr >= ring_rows) rr -= ring_rows;
-                    rowoff[c] = ring + uint32_t(rr) * p.pitch;
-                    asm volatile("" : "+r"(rowoff[c]));       // keep it in a register: cheaper than recomputing per block
-                }
-                const int bias0 = int(rec[8 + (2 * t) * 4 + ch]), bias1 = int(rec[8 + (2 * t + 1) * 4 + ch]);
-                // V word address of (row 8*ch + 2t + hh, block 0): rows are pitch_v apart, channel planes skewed by one word
-                uint32_t vrow = vbase + buf * 2u * vplane + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u;
-                uint32_t vrow_hi = vrow + vplane;
-                asm volatile("" : "+r"(vrow), "+r"(vrow_hi));
-
-                int *counter = &tail.counter[buf];
-                int qd = 0;
-                if (lane == 0) qd = atomicAdd(counter, 1);
-                qd = __shfl_sync(0xffffffffu, qd, 0);
-#pragma unroll 1
-                while (qd < nquad) {
-                    int nxt = 0;
-                    if (lane == 0) nxt = atomicAdd(counter, 1);      // next unit: the answer arrives while this one computes
-                    const uint32_t boff = uint32_t(qd) * (kUnit * 16u);
-                    int acc[kUnit][NDIG][4];
 #pragma unroll
-                    for (int c = 0; c < NCH1; c++) {       // groups with shorter bands carry zero weights in the rest
-                        uint32_t a[kUnit][4];
-#pragma unroll
-                        for (int u = 0; u < kUnit; u++) ldsm_t(a[u], rowoff[c] + boff + uint32_t(u) * 16u);
-#pragma unroll
-                        for (int d = 0; d < NDIG; d++)
-#pragma unroll
-                            for (int u = 0; u < kUnit; u++) {
-                                if (c == 0 && d == 0) imma_c(acc[u][d], a[u], bw1[c][d], bias0, bias1);   // the sum starts at the bias
-                                else if (c == 0) imma_z(acc[u][d], a[u], bw1[c][d]);
-                                else imma(acc[u][d], a[u], bw1[c][d]);
-                            }
-                    }
-                    // recombine the digit planes (exact), re-quantise to u16, split into limbs
-#pragma unroll
-                    for (int u = 0; u < kUnit; u++) {
-                        int v[4];
-#pragma unroll
-                        for (int i = 0; i < 4; i++) {
-                            int x = acc[u][0][i] + (acc[u][1][i] << 8);
-                            if (NDIG == 3) x += acc[u][NDIG - 1][i] << 16;
-                            v[i] = x >> sh1;
+                        for (int u = 0; u < kUnit; u++) {
+                            if (c == 0 && d == 0) imma_c(acc[u][d], a[u], bw1[c][d], bias0, bias1);   // the sum starts at the bias
+                            else if (c == 0) imma_z(acc[u][d], a[u], bw1[c][d]);
+                            else imma(acc[u][d], a[u], bw1[c][d]);
                         }
-                        // v[0],v[2]: pixel hh / hh+2 of output row 2t; v[1],v[3]: same pixels of row 2t+1
-                        const uint32_t w0 = __byte_perm(uint32_t(v[0]), uint32_t(v[2]), 0x5140);   // lo lo hi hi of row 2t
-                        const uint32_t w1 = __byte_perm(uint32_t(v[1]), uint32_t(v[3]), 0x5140);   // ... of row 2t+1
-                        const uint32_t send = hh ? w0 : w1, mine = hh ? w1 : w0;
-                        const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 16);
-                        const uint32_t pa = hh ? recv : mine, pb = hh ? mine : recv;              // pixels (0,2) and (1,3)
-                        // (the plan pads the strip to a whole number of units)
-                        sts32(vrow + boff / 4u + uint32_t(u) * 4u, __byte_perm(pa, pb, 0x5410));       // low limbs
-                        sts32(vrow_hi + boff / 4u + uint32_t(u) * 4u, __byte_perm(pa, pb, 0x7632));    // high limbs
-                    }
-                    qd = __shfl_sync(0xffffffffu, nxt, 0);
                 }
+                // recombine the digit planes (exact), re-quantise to u16, split into limbs
+#pragma unroll
+                for (int u = 0; u < kUnit; u++) {
+                    int v[4];
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        int x = acc[u][0][i] + (acc[u][1][i] << 8);
+                        if (NDIG == 3) x += acc[u][NDIG - 1][i] << 16;
+                        v[i] = x >> sh1;
+                    }
+                    // v[0],v[2]: pixel hh / hh+2 of output row 2t; v[1],v[3]: same pixels of row 2t+1
+                    const uint32_t w0 = __byte_perm(uint32_t(v[0]), uint32_t(v[2]), 0x5140);   // lo lo hi hi of row 2t
+                    const uint32_t w1 = __byte_perm(uint32_t(v[1]), uint32_t(v[3]), 0x5140);   // ... of row 2t+1
+                    const uint32_t send = hh ? w0 : w1, mine = hh ? w1 : w0;
+                    const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 16);
+                    const uint32_t pa = hh ? recv : mine, pb = hh ? mine : recv;              // pixels (0,2) and (1,3)
+                    sts32(vrow + boff / 4u + uint32_t(u) * 4u, __byte_perm(pa, pb, 0x5410));       // low limbs
+                    sts32(vrow_hi + boff / 4u + uint32_t(u) * 4u, __byte_perm(pa, pb, 0x7632));    // high limbs
+                }
+                qd = __shfl_sync(0xffffffffu, nxt, 0) - base;
             }
-            turn(it, rec, buf);
-            jprev = j;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tail.v_full[buf]);        // this warp's share of V[buf] is written
         }
     }
     __syncthreads();
-    if (jprev >= 0) copy_out(jprev, uint32_t(n_iter - 1) & 1u);
 
     if (p.need_fill) fill_region(p, dst, i0, i1, col0, col1, tid);
 }
