@@ -29,6 +29,8 @@
 //
 // Grid: x = strips, y = bands of output-row groups, z = image.  512 threads, one CTA per SM: the first
 // (strip columns / 8) warps run pass 2, the others pass 1; one CTA barrier per group.
+#include <cuda.h>
+
 #include "kernels.cuh"
 
 namespace slimg {
@@ -39,7 +41,6 @@ constexpr int kWarps = 16;
 constexpr int kThreads = kWarps * 32;
 constexpr int kStepRows = 16;                // source rows per ring step (one mbarrier each) == kWarps
 constexpr int kMaxSteps = 16;                // ring of at most 256 rows
-constexpr int kStageCols = 64;
 constexpr int kUnit = 4;                     // 16-byte blocks a pass-1 warp takes from the queue at a time (vplan.cpp pads to it)
 constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
 
@@ -66,6 +67,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// TMA engine, tiled form: one box of kStepRows source rows (pitch bytes each) per instruction
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
 }
 
 // 32 source rows x 16 bytes, transposed: lane (g,t) gets rows 4t..4t+3 (+16) of byte columns g, g+8
@@ -98,10 +105,6 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
 __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
     asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
-__device__ __forceinline__ void sts16(uint32_t addr, uint32_t v) {
-    asm volatile("st.shared.b16 [%0], %1;" ::"r"(addr), "h"(uint16_t(v)) : "memory");
-}
-
 // exact s32 -> f32 for |x| < 2^22 without the quarter-rate I2F
 __device__ __forceinline__ float int_to_float(int x) { return __int_as_float(x + 0x4B400000) - 12582912.0f; }
 
@@ -147,7 +150,7 @@ __device__ __noinline__ void fill_region(const VfParams &p, uint32_t *dst, int i
 }
 
 template <int NDIG, int NCH1, int NCH2>
-__global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfParams p) {
+__global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfParams p, const __grid_constant__ CUtensorMap tmap) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     const uint32_t ring = smem_u32(smem_raw);
     const uint32_t vbase = ring + p.ring_rows * p.pitch;
@@ -165,8 +168,6 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     const int strip = blockIdx.x;
     const int col0 = p.strip_col0[strip], col1 = p.strip_col0[strip + 1];
     const int nblk = p.strip_nblk[strip];
-    const uint32_t row_bytes = uint32_t(p.strip_bytes[strip]);
-    const uint8_t *src_col = src + size_t(p.strip_src0[strip]) * 4;
     const int rec0 = int((uint64_t(blockIdx.y) * p.n_recs) / gridDim.y);
     const int rec1 = int((uint64_t(blockIdx.y + 1) * p.n_recs) / gridDim.y);
     const int n_iter = rec1 - rec0;
@@ -200,17 +201,18 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
 
     if (warp == kWarps - 1) {
         // ================= producer ====================================================================
-        // One linear bulk copy per source row (lanes 0..15 own the rows of a step), one per group record.
+        // One tiled TMA copy per ring step (a box of 16 source rows of the strip; the source batch is one tall
+        // 2-D tensor of 8-byte elements, rows past its end and columns past the row end read as zero), one
+        // linear bulk copy per group record.
         int next_issue = 0, issue_slot = 0;
+        const int tc0 = p.strip_src0[strip] >> 1;                                   // 8-byte elements
+        const int tr0 = int(blockIdx.z) * int(p.sh) + int(p.ry) + ys;
         auto issue_steps = [&](int upto) {
             for (; next_issue < upto; next_issue++) {
-                if (lane == 0) mbar_arrive_expect_tx(&tail.full[issue_slot], kStepRows * row_bytes);
-                __syncwarp();
-                if (lane < kStepRows) {
-                    const int y = int(p.ry) + ys + next_issue * kStepRows + lane;
-                    const int row = min(y, int(p.sh) - 1);               // rows past the end carry zero weights
-                    bulk_g2s(ring + uint32_t(issue_slot * kStepRows + lane) * p.pitch, src_col + size_t(row) * p.sw * 4,
-                             row_bytes, &tail.full[issue_slot]);
+                if (lane == 0) {
+                    mbar_arrive_expect_tx(&tail.full[issue_slot], kStepRows * p.pitch);
+                    tma_load_2d(ring + uint32_t(issue_slot * kStepRows) * p.pitch, &tmap, tc0, tr0 + next_issue * kStepRows,
+                                &tail.full[issue_slot]);
                 }
                 if (++issue_slot == nst) issue_slot = 0;
             }
@@ -230,8 +232,8 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             // band start of the next group: ring steps entirely above it are free once this group is done
             const int a_next = it + 1 < n_iter ? int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words + 1)) : ye;
             mbar_wait(&tail.v_full[it & 1], uint32_t(it >> 1) & 1u);
+            if (it + 2 < n_iter) issue_rec(it + 2);          // the record buffer of this group is free
             issue_steps(min(n_steps, (a_next - ys) / kStepRows + nst));
-            if (it + 2 < n_iter) issue_rec(it + 2);          // the record buffer of this group is free as well
         }
     } else if (warp < ntile) {
         // ================= pass 2: horizontal taps, 4 channels x 8 rows x 8 output columns per warp =======
@@ -420,6 +422,36 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
 
 }  // namespace
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (the library does not link libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(f);
+    }();
+    return fn;
+}
+
+// the source batch as one tall 2-D tensor of 8-byte elements; box = one ring step (pitch bytes x 16 rows)
+static cudaError_t make_source_map(const VfParams &p, const uint8_t *src, uint32_t n_images, CUtensorMap &map) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return cudaErrorNotSupported;
+    const cuuint64_t dims[2] = {cuuint64_t(p.sw) / 2, cuuint64_t(p.sh) * n_images};
+    const cuuint64_t strides[1] = {cuuint64_t(p.sw) * 4};
+    const cuuint32_t box[2] = {p.pitch / 8, cuuint32_t(kStepRows)};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<uint8_t *>(src), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
 template <int NDIG, int NCH1, int NCH2>
 static cudaError_t launch_vf_t(const VfParams &p, uint32_t n_images, cudaStream_t stream) {
     static thread_local int configured_dev = -1;
@@ -436,9 +468,12 @@ static cudaError_t launch_vf_t(const VfParams &p, uint32_t n_images, cudaStream_
         q.src = p.src + size_t(first) * p.src_img_bytes;
         q.dst = p.dst + size_t(first) * p.dst_img_bytes;
         const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
-        resize_vfirst_kernel<NDIG, NCH1, NCH2><<<dim3(p.n_strips, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q);
+        CUtensorMap map;
+        cudaError_t e = make_source_map(q, q.src, nz, map);
+        if (e != cudaSuccess) return e;
+        resize_vfirst_kernel<NDIG, NCH1, NCH2><<<dim3(p.n_strips, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q, map);
         count_launch();
-        cudaError_t e = cudaGetLastError();
+        e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
     return cudaSuccess;
