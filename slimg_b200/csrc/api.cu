@@ -173,7 +173,10 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
             v.ring_rows = vp.ring_rows; v.pitch = vp.pitch; v.pitch_v = vp.pitch_v; v.smem_bytes = vp.smem_bytes;
             v.fw = g.fw; v.fh = g.fh; v.fox = g.fox; v.foy = g.foy;
             v.fill_post = pack_fill(g.fill_post); v.fill_pre_packed = pack_fill(g.fill_pre);
-            v.n_bands = 1; v.need_fill = vp.need_fill ? 1 : 0;
+            v.n_bands = 1; v.need_fill = (vp.need_fill ? 1u : 0u) | (vp.rows_pure_fill ? 2u : 0u);
+            if (vp.need_fill && !std::getenv("SLIMG_B200_FILL_EARLY")) v.need_fill |= 4u;   // fill after the band loop (measured faster)
+            const char *pf_env = std::getenv("SLIMG_B200_PREFETCH_STEPS");
+            v.pf_steps = pf_env ? uint32_t(std::atoi(pf_env)) : 0u;   // measured: no gain, the ring is not DRAM-latency bound
             plan->vfirst = true;
         }
     }

@@ -75,6 +75,11 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
                  ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
 }
 
+// same box, only as far as L2: hides the DRAM part of the latency from the (small) ring
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *map, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
+}
+
 // 32 source rows x 16 bytes, transposed: lane (g,t) gets rows 4t..4t+3 (+16) of byte columns g, g+8
 __device__ __forceinline__ void ldsm_t(uint32_t (&a)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m16n16.x2.trans.shared.b8 {%0,%1,%2,%3}, [%4];"
@@ -125,19 +130,21 @@ struct SmemTail {                             // after the ring, the V planes an
 // are all fill (fill_pre), and the margins left / right of the kept columns.  Each CTA owns the
 // canvas rows of its band and the canvas columns of its strip (edge bands / strips extend to the
 // canvas border).
-__device__ __noinline__ void fill_region(const VfParams &p, uint32_t *dst, int i0, int i1, int c0, int c1, int tid) {
+// Run by the pass-2 warps before their first group: they would otherwise idle while the ring fills.
+__device__ __noinline__ void fill_region(const VfParams &p, uint32_t *dst, int i0, int i1, int c0, int c1, int warp, int nwarps) {
     const bool first_band = blockIdx.y == 0, last_band = blockIdx.y + 1 == gridDim.y;
     const bool first_strip = blockIdx.x == 0, last_strip = blockIdx.x + 1 == gridDim.x;
     const int fr0 = first_band ? 0 : int(p.foy) + i0, fr1 = last_band ? int(p.fh) : int(p.foy) + i1;
     const int cx0 = first_strip ? 0 : int(p.fox) + c0, cx1 = last_strip ? int(p.fw) : int(p.fox) + c1;
     const int kx0 = int(p.fox), kx1 = int(p.fox + p.pw);
     const bool margins = cx0 < kx0 || kx1 < cx1;
-    const int warp = tid >> 5, lane = tid & 31;
+    const int lane = threadIdx.x & 31;
+    const bool all_computed = (p.need_fill & 2u) == 0;        // no kept row is pure fill: skip the table
 #pragma unroll 1
-    for (int fr = fr0 + warp; fr < fr1; fr += kWarps) {
+    for (int fr = fr0 + warp; fr < fr1; fr += nwarps) {
         const int i = fr - int(p.foy);
         const bool kept = i >= 0 && i < int(p.ph);
-        const bool computed = kept && p.row_computed[i];
+        const bool computed = kept && (all_computed || p.row_computed[i]);
         if (computed && !margins) continue;
         uint32_t *row = dst + size_t(fr) * p.fw;
 #pragma unroll 1
@@ -207,7 +214,14 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         int next_issue = 0, issue_slot = 0;
         const int tc0 = p.strip_src0[strip] >> 1;                                   // 8-byte elements
         const int tr0 = int(blockIdx.z) * int(p.sh) + int(p.ry) + ys;
+        int next_pf = 0;
+        const int pf_steps = int(p.pf_steps);
         auto issue_steps = [&](int upto) {
+            // steps further down the strip are pulled into L2 while the ring is still busy with earlier ones
+            const int pf_upto = pf_steps > 0 ? min(n_steps, upto + pf_steps) : 0;
+            if (next_pf < upto) next_pf = upto;
+            for (; next_pf < pf_upto; next_pf++)
+                if (lane == 0) tma_prefetch_2d(&tmap, tc0, tr0 + next_pf * kStepRows);
             for (; next_issue < upto; next_issue++) {
                 if (lane == 0) {
                     mbar_arrive_expect_tx(&tail.full[issue_slot], kStepRows * p.pitch);
@@ -257,6 +271,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
 #pragma unroll
             for (int d = 0; d < NDIG; d++) s2[l][d] = p.s2[l][d];
         int j_next = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words)) : 0;
+        if (p.need_fill && !(p.need_fill & 4u)) fill_region(p, dst, i0, i1, col0, col1, warp, ntile);
 
 #pragma unroll 1
         for (int it = 0; it < n_iter; it++) {
@@ -415,9 +430,10 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             if (lane == 0) mbar_arrive(&tail.v_full[buf]);        // this warp's share of V[buf] is written
         }
     }
-    __syncthreads();
-
-    if (p.need_fill) fill_region(p, dst, i0, i1, col0, col1, tid);
+    if (p.need_fill & 4u) {
+        __syncthreads();
+        fill_region(p, dst, i0, i1, col0, col1, warp, kWarps);
+    }
 }
 
 }  // namespace

@@ -123,7 +123,9 @@ struct VfParams {
     // canvas
     uint32_t fw, fh, fox, foy;
     uint32_t fill_post, fill_pre_packed;
-    uint32_t n_bands, need_fill;
+    uint32_t n_bands;
+    uint32_t need_fill;              // bit 0: some canvas pixels are not computed; bit 1: some kept rows are pure fill
+    uint32_t pf_steps;               // ring steps prefetched into L2 ahead of the ring (0 = off)
 };
 cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStream_t stream);
 size_t vfirst_smem_tail_bytes();

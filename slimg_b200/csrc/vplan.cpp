@@ -303,7 +303,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     }
 
     for (uint32_t i = 0; i < g.ph; i++)
-        if (!out.row_computed[i]) out.need_fill = true;
+        if (!out.row_computed[i]) out.need_fill = out.rows_pure_fill = true;
     if (g.pw != g.fw || g.ph != g.fh) out.need_fill = true;
     out.ok = true;
 }
