@@ -4,6 +4,7 @@
 // rayon `par_iter` over files does (cli/src/commands/mod.rs:64-72, crop.rs:112, extend.rs:114,
 // convert.rs:60).
 #include <atomic>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -56,7 +57,7 @@ struct ResizePlan {
     FastResizeParams fparams{};
     // V-first integer tensor pipeline (k2_vfirst.cu), preferred when the geometry qualifies
     bool vfirst = false;
-    DevArray v_recs, v_rowc, v_col0, v_src0, v_nblk, v_bytes, v_kb0, v_tnch, v_b2, v_cx;
+    DevArray v_recs, v_rowc, v_col0, v_src0, v_nblk, v_bytes, v_upw, v_nunits, v_kb0, v_tnch, v_b2, v_cx;
     VfParams vparams{};
 };
 
@@ -151,10 +152,15 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
         const int ndig = dig_env && dig_env[0] == '3' ? 3 : 2;
         VPlanHost vp;
         build_vplan(g, tx, ty, ndig, vp);
+        if (std::getenv("SLIMG_B200_DEBUG"))
+            std::fprintf(stderr, "[slimg_b200] vplan ok=%d strips=%u cols=%d unit=%d upw=%d nunits=%d early=%d ring=%u pitch=%u pitch_v=%u smem=%u nch1=%d nch2=%d recs=%u\n",
+                         int(vp.ok), vp.n_strips, vp.ok ? vp.strip_col0[1] : 0, vp.unit, vp.ok ? vp.strip_upw[0] : 0,
+                         vp.ok ? vp.strip_nunits[0] : 0, int(vp.early_go), vp.ring_rows, vp.pitch, vp.pitch_v, vp.smem_bytes,
+                         vp.nch1, vp.nch2, vp.n_recs);
         if (vp.ok) {
             if ((e = plan->v_recs.upload(vp.recs)) || (e = plan->v_rowc.upload(vp.row_computed)) || (e = plan->v_col0.upload(vp.strip_col0)) ||
                 (e = plan->v_src0.upload(vp.strip_src0)) || (e = plan->v_nblk.upload(vp.strip_nblk)) ||
-                (e = plan->v_bytes.upload(vp.strip_bytes)) || (e = plan->v_kb0.upload(vp.tile_kb0)) ||
+                (e = plan->v_bytes.upload(vp.strip_bytes)) || (e = plan->v_upw.upload(vp.strip_upw)) || (e = plan->v_nunits.upload(vp.strip_nunits)) || (e = plan->v_kb0.upload(vp.tile_kb0)) ||
                 (e = plan->v_tnch.upload(vp.tile_nch)) || (e = plan->v_b2.upload(vp.b2)) || (e = plan->v_cx.upload(vp.cx)))
                 return cuda_fail(e, "uploading V-first resize plan");
             VfParams &v = plan->vparams;
@@ -166,6 +172,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
             v.n_strips = vp.n_strips;
             v.strip_col0 = (const int32_t *)plan->v_col0.p; v.strip_src0 = (const int32_t *)plan->v_src0.p;
             v.strip_nblk = (const int32_t *)plan->v_nblk.p; v.strip_bytes = (const int32_t *)plan->v_bytes.p;
+            v.strip_upw = (const int32_t *)plan->v_upw.p; v.strip_nunits = (const int32_t *)plan->v_nunits.p; v.unit = vp.unit; v.early_go = vp.early_go ? 1u : 0u;
             v.tile_kb0 = (const int32_t *)plan->v_kb0.p; v.tile_nch = (const int32_t *)plan->v_tnch.p;
             v.b2 = (const uint32_t *)plan->v_b2.p; v.cx = (const float *)plan->v_cx.p;
             for (int l = 0; l < 2; l++)
@@ -175,6 +182,8 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
             v.fill_post = pack_fill(g.fill_post); v.fill_pre_packed = pack_fill(g.fill_pre);
             v.n_bands = 1; v.need_fill = (vp.need_fill ? 1u : 0u) | (vp.rows_pure_fill ? 2u : 0u);
             if (vp.need_fill && !std::getenv("SLIMG_B200_FILL_EARLY")) v.need_fill |= 4u;   // fill after the band loop (measured faster)
+            const char *dbg_env = std::getenv("SLIMG_B200_VF_DEBUG");
+            v.debug = dbg_env ? uint32_t(std::atoi(dbg_env)) : 0u;
             const char *pf_env = std::getenv("SLIMG_B200_PREFETCH_STEPS");
             v.pf_steps = pf_env ? uint32_t(std::atoi(pf_env)) : 0u;   // measured: no gain, the ring is not DRAM-latency bound
             plan->vfirst = true;

@@ -100,7 +100,9 @@ struct VPlanHost {
     uint32_t n_strips = 0;
     int nch2 = 0;                          // max 32-pixel chunks a tile's band spans
     std::vector<int32_t> strip_col0;       // [n_strips + 1]
-    std::vector<int32_t> strip_src0, strip_nblk, strip_bytes;   // [n_strips]
+    std::vector<int32_t> strip_src0, strip_nblk, strip_bytes, strip_upw, strip_nunits;   // [n_strips]
+    int unit = 4;                          // 16-byte blocks per pass-1 unit
+    bool early_go = false;
     std::vector<int32_t> tile_kb0, tile_nch;                    // [n_strips][8]
     std::vector<uint32_t> b2;              // [n_strips][8][nch2][ndig][32][2]
     std::vector<float> cx;                 // [pw][4]

@@ -41,7 +41,7 @@ constexpr int kWarps = 16;
 constexpr int kThreads = kWarps * 32;
 constexpr int kStepRows = 16;                // source rows per ring step (one mbarrier each) == kWarps
 constexpr int kMaxSteps = 16;                // ring of at most 256 rows
-constexpr int kUnit = 4;                     // 16-byte blocks a pass-1 warp takes from the queue at a time (vplan.cpp pads to it)
+constexpr int kRecBufs = 4;                  // group records in flight: fetched three groups ahead (vplan.cpp sizes for it)
 constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
@@ -120,10 +120,11 @@ __device__ __forceinline__ uint32_t quantize_channel(float t) {
 
 struct SmemTail {                             // after the ring, the V planes and the two group records
     uint64_t full[kMaxSteps];                // ring step landed (tx bytes)
-    uint64_t rec_full[2];                    // group record landed (tx bytes)
+    uint64_t rec_full[kRecBufs];                  // group record landed (tx bytes)
+    uint64_t go[2];                          // producer: record + source rows of the group are in, V[buf] is free
     uint64_t v_full[2];                      // every pass-1 warp is done with the group: V complete, band rows released
     uint64_t v_empty[2];                     // every pass-2 warp has read V
-    int counter[2];                          // pass-1 work queues (units of kUnit blocks), one per V buffer, never reset
+    int pos[2];                              // ring row of the group's band start (written by the producer before `go`)
 };
 
 // What is not computed: canvas rows outside the kept rectangle (fill_post), kept rows whose taps
@@ -156,7 +157,7 @@ __device__ __noinline__ void fill_region(const VfParams &p, uint32_t *dst, int i
     }
 }
 
-template <int NDIG, int NCH1, int NCH2>
+template <int NDIG, int NCH1, int NCH2, int UNIT>
 __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfParams p, const __grid_constant__ CUtensorMap tmap) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     const uint32_t ring = smem_u32(smem_raw);
@@ -164,17 +165,15 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     const uint32_t vplane = 32u * p.pitch_v;                   // one limb of one buffer
     const size_t rec_off = size_t(p.ring_rows) * p.pitch + 4u * vplane;
     const uint32_t *recbuf = reinterpret_cast<const uint32_t *>(smem_raw + rec_off);
-    SmemTail &tail = *reinterpret_cast<SmemTail *>(smem_raw + rec_off + 2u * p.rec_words * 4u);
+    SmemTail &tail = *reinterpret_cast<SmemTail *>(smem_raw + rec_off + uint32_t(kRecBufs) * p.rec_words * 4u);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
-    const uint8_t *src = p.src + size_t(blockIdx.z) * p.src_img_bytes;
     uint32_t *dst = reinterpret_cast<uint32_t *>(p.dst + size_t(blockIdx.z) * p.dst_img_bytes);
 
     // ---- this CTA's strip and band (a range of group records) -----------------------------------------
     const int strip = blockIdx.x;
     const int col0 = p.strip_col0[strip], col1 = p.strip_col0[strip + 1];
-    const int nblk = p.strip_nblk[strip];
     const int rec0 = int((uint64_t(blockIdx.y) * p.n_recs) / gridDim.y);
     const int rec1 = int((uint64_t(blockIdx.y + 1) * p.n_recs) / gridDim.y);
     const int n_iter = rec1 - rec0;
@@ -188,19 +187,22 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
 
     // ---- roles ---------------------------------------------------------------------------------------
     //   warps [0, ntile)        pass 2: one tile of 8 output columns each, all four channels
-    //   warps [ntile, 15)       pass 1: units of kUnit 16-byte blocks from a shared queue
+    //   warps [ntile, 14)       pass 1: each warp owns `upw` units of UNIT 16-byte blocks of the strip, for every group
+    //   warp 14                 signaller: waits for a group's record, source rows and free V buffer, then hands
+    //                           pass 1 ONE barrier per group
     //   warp 15                 producer: ring refills and group records through the TMA engine
     // They meet only on mbarriers: no CTA-wide barrier inside the band loop.
     const int ntile = (col1 - col0 + 7) >> 3;
-    const int n_p1 = kWarps - 1 - ntile;
+    const int n_p1 = kWarps - 2 - ntile;
     const uint32_t rec_bytes = p.rec_words * 4u;
     if (tid == 0) {
         for (int s = 0; s < nst; s++) mbar_init(&tail.full[s], 1);
+        for (int b = 0; b < kRecBufs; b++) mbar_init(&tail.rec_full[b], 1);
         for (int b = 0; b < 2; b++) {
-            mbar_init(&tail.rec_full[b], 1);
+            mbar_init(&tail.go[b], 1);
             mbar_init(&tail.v_full[b], uint32_t(n_p1));
             mbar_init(&tail.v_empty[b], uint32_t(ntile));
-            tail.counter[b] = 0;
+            tail.pos[b] = 0;
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -210,44 +212,66 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         // ================= producer ====================================================================
         // One tiled TMA copy per ring step (a box of 16 source rows of the strip; the source batch is one tall
         // 2-D tensor of 8-byte elements, rows past its end and columns past the row end read as zero), one
-        // linear bulk copy per group record.
-        int next_issue = 0, issue_slot = 0;
+        // linear bulk copy per group record.  Lane l issues step next_issue + l: a refill is one pass of the warp.
+        int next_issue = 0;
         const int tc0 = p.strip_src0[strip] >> 1;                                   // 8-byte elements
         const int tr0 = int(blockIdx.z) * int(p.sh) + int(p.ry) + ys;
-        int next_pf = 0;
-        const int pf_steps = int(p.pf_steps);
+        const uint32_t step_bytes = kStepRows * p.pitch;
         auto issue_steps = [&](int upto) {
-            // steps further down the strip are pulled into L2 while the ring is still busy with earlier ones
-            const int pf_upto = pf_steps > 0 ? min(n_steps, upto + pf_steps) : 0;
-            if (next_pf < upto) next_pf = upto;
-            for (; next_pf < pf_upto; next_pf++)
-                if (lane == 0) tma_prefetch_2d(&tmap, tc0, tr0 + next_pf * kStepRows);
-            for (; next_issue < upto; next_issue++) {
-                if (lane == 0) {
-                    mbar_arrive_expect_tx(&tail.full[issue_slot], kStepRows * p.pitch);
-                    tma_load_2d(ring + uint32_t(issue_slot * kStepRows) * p.pitch, &tmap, tc0, tr0 + next_issue * kStepRows,
-                                &tail.full[issue_slot]);
-                }
-                if (++issue_slot == nst) issue_slot = 0;
+            const int step = next_issue + lane;                 // at most nst <= 16 steps are ever issued at once
+            if (step < upto) {
+                const int slot = step % nst;
+                mbar_arrive_expect_tx(&tail.full[slot], step_bytes);
+                tma_load_2d(ring + uint32_t(slot) * step_bytes, &tmap, tc0, tr0 + ((p.debug & 4u) ? (step & 7) : step) * kStepRows, &tail.full[slot]);
             }
+            next_issue = max(next_issue, upto);
         };
         auto issue_rec = [&](int it) {
             if (lane == 0) {
-                uint64_t *bar = &tail.rec_full[it & 1];
+                uint64_t *bar = &tail.rec_full[it & (kRecBufs - 1)];
                 mbar_arrive_expect_tx(bar, rec_bytes);
-                bulk_g2s(smem_u32(recbuf) + uint32_t(it & 1) * rec_bytes, p.recs + size_t(rec0 + it) * p.rec_words, rec_bytes, bar);
+                bulk_g2s(smem_u32(recbuf) + uint32_t(it & (kRecBufs - 1)) * rec_bytes, p.recs + size_t(rec0 + it) * p.rec_words, rec_bytes, bar);
             }
         };
-        if (n_iter > 0) issue_rec(0);
-        if (n_iter > 1) issue_rec(1);
         issue_steps(min(n_steps, nst));
+        for (int r = 0; r < kRecBufs; r++)
+            if (r < n_iter) issue_rec(r);
+        // band start of the group after next, fetched a group early: ring steps entirely above a group's successor's
+        // band start are free once the group is done
+        int a_next = n_iter > 1 ? int(__ldg(p.recs + size_t(rec0 + 1) * p.rec_words + 1)) : ye;
 #pragma unroll 1
         for (int it = 0; it < n_iter; it++) {
-            // band start of the next group: ring steps entirely above it are free once this group is done
-            const int a_next = it + 1 < n_iter ? int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words + 1)) : ye;
+            const int a_cur = a_next;
+            a_next = it + 2 < n_iter ? int(__ldg(p.recs + size_t(rec0 + it + 2) * p.rec_words + 1)) : ye;
             mbar_wait(&tail.v_full[it & 1], uint32_t(it >> 1) & 1u);
-            if (it + 2 < n_iter) issue_rec(it + 2);          // the record buffer of this group is free
-            issue_steps(min(n_steps, (a_next - ys) / kStepRows + nst));
+            issue_steps(min(n_steps, (a_cur - ys) / kStepRows + nst));
+            if (it + kRecBufs < n_iter) issue_rec(it + kRecBufs);   // the record buffer of this group is free
+        }
+    } else if (warp == kWarps - 2) {
+        // ================= signaller: does the waiting for pass 1 =======================================
+        // Group `it` may start when its record and source rows have landed and pass 2 has drained V[it & 1].
+        // Lane l waits for ring step first + l; then one arrive on go[]: pass-1 warps wait on a single barrier.
+        const int ring_rows = int(p.ring_rows);
+        int a0 = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words + 1)) : 0;
+        int need = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words + 2)) : 0;
+#pragma unroll 1
+        for (int it = 0; it < n_iter; it++) {
+            const uint32_t buf = uint32_t(it) & 1u, par = uint32_t(it >> 1) & 1u;
+            const int a0_cur = a0, need_cur = need;
+            if (it + 1 < n_iter) {                           // next group's header, in flight while this one is waited for
+                a0 = int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words + 1));
+                need = int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words + 2));
+            }
+            const int first = (a0_cur - ys) / kStepRows, last = (need_cur - ys + kStepRows - 1) / kStepRows;
+            const int step = first + lane;                   // a band spans at most 128 rows + alignment: <= 9 steps
+            if (step < last) mbar_wait(&tail.full[step % nst], uint32_t(step / nst) & 1u);
+            mbar_wait(&tail.rec_full[it & (kRecBufs - 1)], uint32_t(it / kRecBufs) & 1u);
+            mbar_wait(&tail.v_empty[buf], par ^ 1u);        // V[buf] was last read by pass 2 two groups ago
+            __syncwarp();
+            if (lane == 0) {
+                tail.pos[buf] = (a0_cur - ys) % ring_rows;
+                mbar_arrive(&tail.go[buf]);                  // release: pos is visible to the waiters
+            }
         }
     } else if (warp < ntile) {
         // ================= pass 2: horizontal taps, 4 channels x 8 rows x 8 output columns per warp =======
@@ -281,6 +305,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             const uint32_t vbuf = vbase + buf * 2u * vplane;
             mbar_wait(&tail.v_full[buf], uint32_t(it >> 1) & 1u);
 
+            if (p.debug & 2u) { __syncwarp(); if (lane == 0) mbar_arrive(&tail.v_empty[buf]); continue; }
             int acc[2][2][NDIG][4];            // [channel pair][limb][digit]
 #pragma unroll
             for (int mt = 0; mt < 2; mt++) {   // channel pairs (0,1) and (2,3)
@@ -325,23 +350,23 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         }
     } else {
         // ================= pass 1: vertical taps of 8 output rows over the strip =======================
-        // ring bookkeeping without divisions: the step / slot / phase this warp waits on next, and the ring
-        // position of the current band start
-        int w_step = 0, w_slot = 0;
-        uint32_t w_par = 0;
-        int pos = 0, prev_a0 = ys;
-        const int nquad = nblk / kUnit;           // the plan pads the strip to a whole number of units
-        const int per_group = nquad + n_p1;       // queue tickets a group consumes: every warp draws one blank
+        // Static ownership: warp w1 of the n_p1 pass-1 warps computes units [w1*upw, (w1+1)*upw) of UNIT blocks in
+        // every group (the plan pads the staged span to n_p1*upw*UNIT blocks), so there is no queue and one
+        // barrier wait per group.
+        const int w1 = warp - ntile;
+        const int upw_all = p.strip_upw[strip];
+        const int upw = max(0, min(upw_all, p.strip_nunits[strip] - w1 * upw_all));     // this warp's units
         const int sh1 = p.sh1;
         const int ch = g & 3, hh = g >> 2;
         const int ring_rows = int(p.ring_rows);
+        const uint32_t boff0 = uint32_t(w1 * upw_all) * (UNIT * 16u);
 
 #pragma unroll 1
         for (int it = 0; it < n_iter; it++) {
             const uint32_t buf = uint32_t(it) & 1u;
-            const uint32_t *rec = recbuf + buf * p.rec_words;
-            mbar_wait(&tail.rec_full[buf], uint32_t(it >> 1) & 1u);
-            const int a0 = int(rec[1]), need = int(rec[2]);
+            const uint32_t *rec = recbuf + uint32_t(it & (kRecBufs - 1)) * p.rec_words;
+            mbar_wait(&tail.go[buf], uint32_t(it >> 1) & 1u);
+            const int pos = tail.pos[buf];
             uint2 bw1[NCH1][NDIG];
 #pragma unroll
             for (int c = 0; c < NCH1; c++)
@@ -350,56 +375,33 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                     bw1[c][d] = *reinterpret_cast<const uint2 *>(rec + 64 + ((c * NDIG + d) * 32 + lane) * 2);
             const int bias0 = int(rec[8 + (2 * t) * 4 + ch]), bias1 = int(rec[8 + (2 * t + 1) * 4 + ch]);
 
-            int *counter = &tail.counter[buf];
-            const int base = (it >> 1) * per_group;
-
-            // ---- wait for the source rows of this group (step s lives in slot s % nst, phase s / nst) ----
-            {
-                const int first = (a0 - ys) / kStepRows, last = (need - ys + kStepRows - 1) / kStepRows;
-                while (w_step < last) {
-                    if (w_step >= first) mbar_wait(&tail.full[w_slot], w_par);
-                    w_step++;
-                    if (++w_slot == nst) { w_slot = 0; w_par ^= 1u; }
-                }
-                pos += a0 - prev_a0;
-                prev_a0 = a0;
-                while (pos >= ring_rows) pos -= ring_rows;
-            }
             uint32_t rowoff[NCH1];
 #pragma unroll
             for (int c = 0; c < NCH1; c++) {
                 int rr = pos + 32 * c + lane;
                 if (rr >= ring_rows) rr -= ring_rows;
                 if (rr >= ring_rows) rr -= ring_rows;
-                rowoff[c] = ring + uint32_t(rr) * p.pitch;
+                rowoff[c] = ring + uint32_t(rr) * p.pitch + boff0;
                 asm volatile("" : "+r"(rowoff[c]));       // keep it in a register: cheaper than recomputing per block
             }
             // V word address of (row 8*ch + 2t + hh, block 0): rows are pitch_v apart, channel planes skewed by one word
-            uint32_t vrow = vbase + buf * 2u * vplane + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u;
+            uint32_t vrow = vbase + buf * 2u * vplane + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u + boff0 / 4u;
             uint32_t vrow_hi = vrow + vplane;
             asm volatile("" : "+r"(vrow), "+r"(vrow_hi));
-            // V[buf] was last read by pass 2 two groups ago
-            // (which also means every pass-1 warp has drawn its last ticket of that group from this queue)
-            mbar_wait(&tail.v_empty[buf], (uint32_t(it >> 1) & 1u) ^ 1u);
 
-            int qd = 0;
-            if (lane == 0) qd = atomicAdd(counter, 1);
-            qd = __shfl_sync(0xffffffffu, qd, 0) - base;
 #pragma unroll 1
-            while (qd < nquad) {
-                int nxt = 0;
-                if (lane == 0) nxt = atomicAdd(counter, 1);      // next unit: the answer arrives while this one computes
-                const uint32_t boff = uint32_t(qd) * (kUnit * 16u);
-                int acc[kUnit][NDIG][4];
+            for (int q = 0; q < ((p.debug & 1u) ? 0 : upw); q++) {
+                const uint32_t boff = uint32_t(q) * (UNIT * 16u);
+                int acc[UNIT][NDIG][4];
 #pragma unroll
                 for (int c = 0; c < NCH1; c++) {       // groups with shorter bands carry zero weights in the rest
-                    uint32_t a[kUnit][4];
+                    uint32_t a[UNIT][4];
 #pragma unroll
-                    for (int u = 0; u < kUnit; u++) ldsm_t(a[u], rowoff[c] + boff + uint32_t(u) * 16u);
+                    for (int u = 0; u < UNIT; u++) ldsm_t(a[u], rowoff[c] + boff + uint32_t(u) * 16u);
 #pragma unroll
                     for (int d = 0; d < NDIG; d++)
 #pragma unroll
-                        for (int u = 0; u < kUnit; u++) {
+                        for (int u = 0; u < UNIT; u++) {
                             if (c == 0 && d == 0) imma_c(acc[u][d], a[u], bw1[c][d], bias0, bias1);   // the sum starts at the bias
                             else if (c == 0) imma_z(acc[u][d], a[u], bw1[c][d]);
                             else imma(acc[u][d], a[u], bw1[c][d]);
@@ -407,7 +409,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                 }
                 // recombine the digit planes (exact), re-quantise to u16, split into limbs
 #pragma unroll
-                for (int u = 0; u < kUnit; u++) {
+                for (int u = 0; u < UNIT; u++) {
                     int v[4];
 #pragma unroll
                     for (int i = 0; i < 4; i++) {
@@ -417,14 +419,13 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                     }
                     // v[0],v[2]: pixel hh / hh+2 of output row 2t; v[1],v[3]: same pixels of row 2t+1
                     const uint32_t w0 = __byte_perm(uint32_t(v[0]), uint32_t(v[2]), 0x5140);   // lo lo hi hi of row 2t
-                    const uint32_t w1 = __byte_perm(uint32_t(v[1]), uint32_t(v[3]), 0x5140);   // ... of row 2t+1
-                    const uint32_t send = hh ? w0 : w1, mine = hh ? w1 : w0;
+                    const uint32_t w1r = __byte_perm(uint32_t(v[1]), uint32_t(v[3]), 0x5140);  // ... of row 2t+1
+                    const uint32_t send = hh ? w0 : w1r, mine = hh ? w1r : w0;
                     const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 16);
                     const uint32_t pa = hh ? recv : mine, pb = hh ? mine : recv;              // pixels (0,2) and (1,3)
                     sts32(vrow + boff / 4u + uint32_t(u) * 4u, __byte_perm(pa, pb, 0x5410));       // low limbs
                     sts32(vrow_hi + boff / 4u + uint32_t(u) * 4u, __byte_perm(pa, pb, 0x7632));    // high limbs
                 }
-                qd = __shfl_sync(0xffffffffu, nxt, 0) - base;
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&tail.v_full[buf]);        // this warp's share of V[buf] is written
@@ -468,13 +469,13 @@ static cudaError_t make_source_map(const VfParams &p, const uint8_t *src, uint32
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
-template <int NDIG, int NCH1, int NCH2>
+template <int NDIG, int NCH1, int NCH2, int UNIT>
 static cudaError_t launch_vf_t(const VfParams &p, uint32_t n_images, cudaStream_t stream) {
     static thread_local int configured_dev = -1;
     int dev = 0;
     cudaGetDevice(&dev);
     if (configured_dev != dev) {
-        cudaError_t e = cudaFuncSetAttribute(resize_vfirst_kernel<NDIG, NCH1, NCH2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(resize_vfirst_kernel<NDIG, NCH1, NCH2, UNIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              227 * 1024);
         if (e != cudaSuccess) return e;
         configured_dev = dev;
@@ -487,7 +488,7 @@ static cudaError_t launch_vf_t(const VfParams &p, uint32_t n_images, cudaStream_
         CUtensorMap map;
         cudaError_t e = make_source_map(q, q.src, nz, map);
         if (e != cudaSuccess) return e;
-        resize_vfirst_kernel<NDIG, NCH1, NCH2><<<dim3(p.n_strips, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q, map);
+        resize_vfirst_kernel<NDIG, NCH1, NCH2, UNIT><<<dim3(p.n_strips, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q, map);
         count_launch();
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
@@ -501,11 +502,13 @@ cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStrea
     if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
     if (p.n_bands == 0 || p.n_bands > 65535 || p.n_strips == 0 || p.nch1 > 4 || p.nch2 > 4) return cudaErrorInvalidValue;
     if (p.ring_rows % kStepRows != 0 || p.ring_rows / kStepRows > kMaxSteps) return cudaErrorInvalidValue;
-#define SLIMG_VF_CASE(D, A, B) if (p.ndig == D && p.nch1 == A && p.nch2 == B) return launch_vf_t<D, A, B>(p, n_images, stream);
-#define SLIMG_VF_ROW(D, A) SLIMG_VF_CASE(D, A, 1) SLIMG_VF_CASE(D, A, 2) SLIMG_VF_CASE(D, A, 3) SLIMG_VF_CASE(D, A, 4)
-#define SLIMG_VF_ALL(D) SLIMG_VF_ROW(D, 1) SLIMG_VF_ROW(D, 2) SLIMG_VF_ROW(D, 3) SLIMG_VF_ROW(D, 4)
-    SLIMG_VF_ALL(2)
+#define SLIMG_VF_CASE(A, B, U) if (p.nch1 == A && p.nch2 == B && p.unit == U) return launch_vf_t<2, A, B, U>(p, n_images, stream);
+#define SLIMG_VF_ROW(A, U) SLIMG_VF_CASE(A, 1, U) SLIMG_VF_CASE(A, 2, U) SLIMG_VF_CASE(A, 3, U) SLIMG_VF_CASE(A, 4, U)
+#define SLIMG_VF_ALL(U) SLIMG_VF_ROW(1, U) SLIMG_VF_ROW(2, U) SLIMG_VF_ROW(3, U) SLIMG_VF_ROW(4, U)
+    if (p.ndig != 2) return cudaErrorInvalidValue;
     SLIMG_VF_ALL(3)
+    SLIMG_VF_ALL(4)
+    SLIMG_VF_ALL(5)
     return cudaErrorInvalidValue;
 }
 

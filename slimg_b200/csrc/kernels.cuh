@@ -113,6 +113,10 @@ struct VfParams {
     const int32_t *strip_src0;       // [n_strips] absolute source column where the staged span starts (multiple of 4)
     const int32_t *strip_nblk;       // [n_strips] 16-byte blocks of each staged row
     const int32_t *strip_bytes;      // [n_strips] bytes staged per source row
+    const int32_t *strip_upw;        // [n_strips] consecutive units of `unit` blocks each pass-1 warp of the strip owns
+    const int32_t *strip_nunits;     // [n_strips] units of the strip (the last warps may own fewer than upw, or none)
+    int32_t unit;                    // 16-byte blocks per pass-1 unit (kernel template UNIT)
+    uint32_t early_go;               // 1: the ring always holds the next group's rows, `go` is signalled a group ahead
     const int32_t *tile_kb0;         // [n_strips][8] first block of the tile's k range
     const int32_t *tile_nch;         // [n_strips][8] 32-pixel chunks of the tile's k range
     const uint32_t *b2;              // [n_strips][8][4][ndig][32 lanes][2]
@@ -125,6 +129,7 @@ struct VfParams {
     uint32_t fill_post, fill_pre_packed;
     uint32_t n_bands;
     uint32_t need_fill;              // bit 0: some canvas pixels are not computed; bit 1: some kept rows are pure fill
+    uint32_t debug;                  // experiment switches (SLIMG_B200_VF_DEBUG), 0 in production
     uint32_t pf_steps;               // ring steps prefetched into L2 ahead of the ring (0 = off)
 };
 cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStream_t stream);

@@ -21,7 +21,6 @@ namespace {
 constexpr int kFrac = 7;        // fractional bits of the 16-bit intermediate
 constexpr int kOffset = 64;     // added to the intermediate so Lanczos undershoot stays >= 0
 constexpr int kPrefetchRows = 64;   // a whole group's worth of new rows must be in flight while the previous group computes
-constexpr int kUnit = 4;           // k2_vfirst.cu kUnit
 constexpr int kMaxCh = 4;          // chunk stride of the fragment tables (the kernel's NCH1 / NCH2)
 constexpr size_t kSmemBudget = 227 * 1024 - 2048;
 const int kPerm[4] = {0, 2, 1, 3};   // k-slot -> pixel inside a 4-pixel block (k2_vfirst.cu, pass-1 epilogue)
@@ -180,11 +179,21 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     for (int l = 0; l < 2; l++)
         for (int d = 0; d < 3; d++) out.s2[l][d] = d < ndig ? float(std::ldexp(1.0, 8 * l + 8 * d - Sx - kFrac)) : 0.0f;
 
-    // ring depth: the rows a group needs plus what should be in flight, in 16-row steps
-    const uint32_t ring_rows = uint32_t((std::max(32 * out.nch1, max_need + kPrefetchRows) + 15) / 16 * 16);
-    out.ring_rows = ring_rows;
-    const size_t fixed_bytes = 2 * 8 * 64 * 4 /* output staging */ + 2 * size_t(out.rec_words) * 4 /* group records */ +
-                               1024 /* barriers, bookkeeping */;
+    // ring depth, in 16-row steps: the rows a group needs plus a group's worth in flight.  When the ring can also
+    // hold everything the NEXT group needs before the current one is released (band start rounded down to a step),
+    // the producer signals groups one ahead (early_go) and pass 1 never waits on a freshly issued copy.
+    int max_look = 0;
+    {
+        int prev = -1;
+        for (uint32_t j = 0; j < out.n_groups; j++) {
+            if (out.grp_nch[j] == 0) continue;
+            if (prev >= 0) max_look = std::max(max_look, out.grp_need[j] - out.grp_a0[prev]);
+            prev = int(j);
+        }
+    }
+    const uint32_t ring_min = uint32_t((std::max(32 * out.nch1, max_need + kPrefetchRows) + 15) / 16 * 16);
+    const uint32_t ring_early = std::max(ring_min, uint32_t((max_look + 15 + 15) / 16 * 16));
+    const size_t fixed_bytes = 4 * size_t(out.rec_words) * 4 /* group records, k2_vfirst.cu kRecBufs */ + 1024 /* barriers, bookkeeping */;
 
     // span of source pixels (absolute columns) a range of kept output columns needs
     auto span_of = [&](uint32_t c0, uint32_t c1, int64_t &lo, int64_t &hi) {
@@ -196,38 +205,85 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
             hi = std::max<int64_t>(hi, int64_t(g.rx) + tx.left[o] + tx.count[o]);
         }
     };
-    auto smem_for = [&](int64_t nblk, uint32_t &pitch, uint32_t &pitch_v) {
-        int64_t units = nblk | 1;                                  // odd multiple of 16 bytes (nblk is even)
+    // pass 1 splits a strip's 16-byte blocks statically: units of `unit` blocks, upw consecutive units per warp
+    // over the (14 - tiles) pass-1 warps (the last warps may own fewer, or none)
+    auto pad_blocks = [&](int64_t raw, uint32_t ncols, int unit, int &upw) {
+        const int64_t n_p1 = 14 - int64_t((ncols + 7) / 8);   // k2_vfirst.cu: 16 warps - producer - signaller - tiles
+        const int64_t nunits = (raw + unit - 1) / unit;
+        upw = int((nunits + n_p1 - 1) / n_p1);
+        return nunits * unit;
+    };
+    auto smem_for = [&](int64_t nblk, uint32_t ring_rows, uint32_t &pitch, uint32_t &pitch_v) {
+        int64_t units = nblk | 1;                                  // odd multiple of 16 bytes: conflict-free ldmatrix rows
         pitch = uint32_t(units * 16);
         int64_t qv = (nblk + 3 + 3) / 4;                           // words per V row = 4 * odd >= nblk + 3
         if (qv % 2 == 0) qv++;
         pitch_v = uint32_t(qv * 16);
         return size_t(ring_rows) * pitch + size_t(4) * 32 * pitch_v + fixed_bytes;
     };
-    // widest strips (multiple of 8 columns, at most 64) whose staging fits in shared memory
+    // widest strips (multiple of 8 columns, at most 64) whose staging fits in shared memory; per width the unit
+    // size with the least padding; early_go when the deeper ring still fits
+    const char *cols_env = std::getenv("SLIMG_B200_STRIP_COLS");
+    const char *early_env = std::getenv("SLIMG_B200_EARLY_GO");
+    const char *unit_env = std::getenv("SLIMG_B200_UNIT");
     uint32_t cols = 0;
-    for (uint32_t cand = 64; cand >= 8; cand -= 8) {
-        bool fits = true;
-        for (uint32_t c0 = 0; c0 < g.pw && fits; c0 += cand) {
+    int unit = 0;
+    bool early = false;
+    auto max_padded = [&](uint32_t cand, int u, int &crit) {
+        int64_t worst = 0;
+        crit = 0;
+        for (uint32_t c0 = 0; c0 < g.pw; c0 += cand) {
+            const uint32_t c1 = std::min(g.pw, c0 + cand);
             int64_t lo, hi;
-            span_of(c0, std::min(g.pw, c0 + cand), lo, hi);
+            span_of(c0, c1, lo, hi);
             if (hi < 0) continue;
-            const int64_t nblk = ((hi - (lo & ~int64_t(3)) + 3) / 4 + kUnit - 1) / kUnit * kUnit;
-            uint32_t p, pv;
-            if (smem_for(nblk, p, pv) > kSmemBudget) fits = false;
+            int upw;
+            worst = std::max(worst, pad_blocks((hi - (lo & ~int64_t(3)) + 3) / 4, c1 - c0, u, upw));
+            crit = std::max(crit, upw * u);                       // blocks of the busiest warp
         }
-        if (fits) { cols = cand; break; }
+        return std::max<int64_t>(worst, 8 * kMaxCh);
+    };
+    for (uint32_t cand = 64; cand >= 8 && cols == 0; cand -= 8) {
+        if (cols_env && uint32_t(std::atoi(cols_env)) != cand) continue;
+        // even the strips out first (keeps the multiple of 8)
+        const uint32_t ns = (g.pw + cand - 1) / cand;
+        const uint32_t even = std::min<uint32_t>(cand, ((g.pw + ns - 1) / ns + 7) / 8 * 8);
+        int best_u = 0, best_crit = INT32_MAX;
+        int64_t best_blk = INT64_MAX;
+        for (int u = 5; u >= 3; u--) {
+            if (unit_env && std::atoi(unit_env) != u) continue;
+            int crit;
+            const int64_t blk = max_padded(even, u, crit);
+            if (crit < best_crit || (crit == best_crit && blk < best_blk)) { best_blk = blk; best_u = u; best_crit = crit; }
+        }
+        if (!best_u) continue;
+        uint32_t pch, pv;
+        const bool want_early = !(early_env && early_env[0] == '0');
+        if (want_early && smem_for(best_blk, ring_early, pch, pv) <= kSmemBudget) { cols = even; unit = best_u; early = true; }
+        else if (smem_for(best_blk, ring_min, pch, pv) <= kSmemBudget) { cols = even; unit = best_u; early = false; }
     }
     if (cols == 0) return;
-    out.n_strips = (g.pw + cols - 1) / cols;
-    // even the strips out (keeps the multiple of 8)
-    cols = std::min<uint32_t>(cols, ((g.pw + out.n_strips - 1) / out.n_strips + 7) / 8 * 8);
+    out.unit = unit;
+    out.early_go = early;
+    out.ring_rows = early ? ring_early : ring_min;
+    if (out.ring_rows / 16 > 16) return;                          // k2_vfirst.cu kMaxSteps
+    {
+        // deepen the ring as far as shared memory allows: every extra step is 16 more rows in flight
+        int unused;
+        const int64_t blk = max_padded(cols, unit, unused);
+        const char *ring_env = std::getenv("SLIMG_B200_RING_STEPS");
+        const uint32_t cap = ring_env ? uint32_t(std::atoi(ring_env)) * 16 : 256u;
+        uint32_t pch, pv;
+        while (out.ring_rows + 16 <= std::min(cap, 256u) && smem_for(blk, out.ring_rows + 16, pch, pv) <= kSmemBudget) out.ring_rows += 16;
+    }
     out.n_strips = (g.pw + cols - 1) / cols;
 
     out.strip_col0.assign(out.n_strips + 1, 0);
     out.strip_src0.assign(out.n_strips, 0);
     out.strip_nblk.assign(out.n_strips, 1);
     out.strip_bytes.assign(out.n_strips, 16);
+    out.strip_upw.assign(out.n_strips, 0);
+    out.strip_nunits.assign(out.n_strips, 0);
     out.tile_kb0.assign(size_t(out.n_strips) * 8, 0);
     out.tile_nch.assign(size_t(out.n_strips) * 8, 0);
     out.cx.assign(size_t(g.pw) * 4, 0.0f);
@@ -241,11 +297,13 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         span_of(c0, c1, lo, hi);
         if (hi < 0) continue;                        // every tap of the strip lands on fill
         const int64_t s0 = lo & ~int64_t(3);
-        // pass 1 works on units of kUnit 16-byte blocks: pad to a whole number (the extra blocks read whatever
-        // lies beyond the staged bytes of the row and meet zero weights in pass 2)
-        const int64_t nblk = ((hi - s0 + 3) / 4 + kUnit - 1) / kUnit * kUnit;
+        // the padding blocks read whatever lies beyond the staged bytes of the row and meet zero weights in pass 2
+        int upw = 0;
+        const int64_t nblk = pad_blocks((hi - s0 + 3) / 4, c1 - c0, unit, upw);
         out.strip_src0[s] = int32_t(s0);
         out.strip_nblk[s] = int32_t(nblk);
+        out.strip_upw[s] = upw;
+        out.strip_nunits[s] = int32_t(nblk / unit);
         out.strip_bytes[s] = int32_t((std::min<int64_t>(s0 + (hi - s0 + 3) / 4 * 4, g.sw) - s0) * 4);
         max_nblk = std::max(max_nblk, nblk);
         for (uint32_t t = 0; t * 8 < c1 - c0; t++) {
@@ -269,7 +327,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
             int32_t &kb0 = out.tile_kb0[s * 8 + t];
             kb0 = std::max<int32_t>(0, std::min<int32_t>(kb0, out.strip_nblk[s] - 8 * out.nch2));
         }
-    out.smem_bytes = uint32_t(smem_for(std::max<int64_t>(max_nblk, 8 * out.nch2), out.pitch, out.pitch_v));
+    out.smem_bytes = uint32_t(smem_for(std::max<int64_t>(max_nblk, 8 * out.nch2), out.ring_rows, out.pitch, out.pitch_v));
     if (out.smem_bytes > kSmemBudget) return;
     // second sweep: weights
     out.b2.assign(size_t(out.n_strips) * 8 * out.nch2 * ndig * 64, 0u);
