@@ -59,6 +59,10 @@ struct ResizePlan {
     bool vfirst = false;
     DevArray v_recs, v_rowc, v_col0, v_src0, v_nblk, v_bytes, v_upw, v_nunits, v_kb0, v_tnch, v_b2, v_cx;
     VfParams vparams{};
+    // tcgen05 pipeline (k2_tc.cu), preferred over the mma.sync pipeline when the geometry qualifies
+    bool tc = false;
+    DevArray t_crecs, t_c0, t_c1, t_bias, t_col0, t_src0, t_kb0, t_b2, t_cx;
+    TcParams tparams{};
 };
 
 struct GeomKey {
@@ -147,7 +151,39 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
     // which resize kernel: SLIMG_B200_RESIZE_PATH = vfirst (default) | hfirst | generic
     const char *path_env = std::getenv("SLIMG_B200_RESIZE_PATH");
     const std::string path = path_env ? path_env : "vfirst";
-    if (path == "vfirst") {
+    if (path == "tc") {
+        TcPlanHost tp;
+        build_tcplan(g, tx, ty, tp);
+        if (std::getenv("SLIMG_B200_DEBUG"))
+            std::fprintf(stderr, "[slimg_b200] tcplan ok=%d strips=%u cols=%d panels=%u nbuf=%u slots=%u blocks=%u chunks=%u nb_max=%u nch2=%d smem=%u\n",
+                         int(tp.ok), tp.n_strips, tp.ok ? tp.strip_col0[1] : 0, tp.n_panels, tp.nbuf, tp.slots, tp.n_blocks, tp.n_chunks,
+                         tp.nb_max, tp.nch2, tp.smem_bytes);
+        if (tp.ok) {
+            if ((e = plan->t_crecs.upload(tp.crecs)) || (e = plan->t_c0.upload(tp.blk_c0)) || (e = plan->t_c1.upload(tp.blk_c1)) ||
+                (e = plan->t_bias.upload(tp.bias)) || (e = plan->t_col0.upload(tp.strip_col0)) || (e = plan->t_src0.upload(tp.strip_src0)) ||
+                (e = plan->t_kb0.upload(tp.tile_kb0)) || (e = plan->t_b2.upload(tp.b2)) || (e = plan->t_cx.upload(tp.cx)))
+                return cuda_fail(e, "uploading tcgen05 resize plan");
+            TcParams &t = plan->tparams;
+            t.sw = g.sw; t.sh = g.sh; t.ry = g.ry; t.pw = g.pw; t.ph = g.ph;
+            t.nch2 = tp.nch2; t.sh1 = tp.sh1;
+            t.n_blocks = tp.n_blocks; t.n_chunks = tp.n_chunks; t.crec_words = tp.crec_words;
+            t.crecs = (const uint32_t *)plan->t_crecs.p; t.blk_c0 = (const int32_t *)plan->t_c0.p; t.blk_c1 = (const int32_t *)plan->t_c1.p;
+            t.bias = (const int32_t *)plan->t_bias.p;
+            t.n_strips = tp.n_strips; t.n_panels = tp.n_panels;
+            t.strip_col0 = (const int32_t *)plan->t_col0.p; t.strip_src0 = (const int32_t *)plan->t_src0.p;
+            t.tile_kb0 = (const int32_t *)plan->t_kb0.p; t.b2 = (const uint32_t *)plan->t_b2.p; t.cx = (const float *)plan->t_cx.p;
+            for (int l = 0; l < 2; l++)
+                for (int d = 0; d < 3; d++) t.s2[l][d] = tp.s2[l][d];
+            t.slots = tp.slots; t.slot_bytes = tp.slot_bytes; t.pitch_v = tp.pitch_v; t.smem_bytes = tp.smem_bytes; t.nbuf = tp.nbuf;
+            t.fw = g.fw; t.fh = g.fh; t.fox = g.fox; t.foy = g.foy;
+            t.fill_post = pack_fill(g.fill_post); t.fill_pre_packed = pack_fill(g.fill_pre);
+            t.n_bands = 1; t.need_fill = tp.need_fill ? 1u : 0u;
+            const char *dbg_env = std::getenv("SLIMG_B200_VF_DEBUG");
+            t.debug = dbg_env ? uint32_t(std::atoi(dbg_env)) : 0u;
+            plan->tc = true;
+        }
+    }
+    if (path == "vfirst" || (path == "tc" && !plan->tc)) {
         const char *dig_env = std::getenv("SLIMG_B200_DIGITS");
         const int ndig = dig_env && dig_env[0] == '3' ? 3 : 2;
         VPlanHost vp;
@@ -274,6 +310,17 @@ static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, u
     std::shared_ptr<ResizePlan> plan;
     slimg_status st = get_resize_plan(g, plan);
     if (st != SLIMG_OK) return st;
+    if (plan->tc && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        TcParams t = plan->tparams;
+        t.src = src; t.dst = dst; t.src_img_bytes = src_bytes; t.dst_img_bytes = dst_bytes;
+        // bands of 16-row blocks: enough CTAs to fill the GPU when the batch is small
+        const uint64_t ctas_per_band = uint64_t(t.n_strips) * n;
+        uint32_t bands = uint32_t((2 * 148 + ctas_per_band - 1) / ctas_per_band);
+        bands = std::max<uint32_t>(1, std::min<uint32_t>(bands, std::max<uint32_t>(1, t.n_blocks / 2)));
+        t.n_bands = bands;
+        CU(launch_resize_tc(t, n, stream));
+        return SLIMG_OK;
+    }
     if (plan->vfirst && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
         VfParams v = plan->vparams;
         v.src = src; v.dst = dst; v.src_img_bytes = src_bytes; v.dst_img_bytes = dst_bytes;

@@ -112,5 +112,36 @@ struct VPlanHost {
     bool need_fill = false, rows_pure_fill = false;
 };
 void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int ndig, VPlanHost &out);
+// fixed-point helpers shared by the integer plans (vplan.cpp)
+void quantise(const float *w, int cnt, int S, std::vector<int64_t> &q);     // taps -> integers with the exact sum
+bool split_digits(int64_t x, int ndig, int8_t d[3]);                         // balanced base-256 digits
+int pick_scale(float maxw, int ndig);
+void put_b(uint32_t *frag, int k, int n, int8_t v);                          // mma.m16n8k32 B fragment slot
+
+// ---- tcgen05 pipeline plan (tcplan.cpp, k2_tc.cu) -------------------------------------------------------
+// Vertical pass on the 5th-generation tensor cores: source rows stream through a shared-memory ring in chunks of
+// 32 rows (the K of one tcgen05.mma.kind::i8), accumulators for blocks of 16 kept output rows live in TMEM.
+struct TcPlanHost {
+    bool ok = false;
+    int ndig = 2, sh1 = 0;
+    // vertical: blocks of 16 kept output rows, chunks of 32 source-rectangle rows
+    uint32_t n_blocks = 0, n_chunks = 0, nb_max = 0;
+    uint32_t crec_words = 0;               // words per chunk record: 16 header + nb_max * ndig * 128 (weight tiles)
+    std::vector<uint32_t> crecs;           // [n_chunks][crec_words]
+    std::vector<int32_t> blk_c0, blk_c1;   // [n_blocks] first / last chunk of each block
+    std::vector<int32_t> bias;             // [n_blocks*16][4]
+    // horizontal: strips of kept output columns, tiles of 8; staged span starts on a 128-byte boundary
+    uint32_t n_strips = 0, n_panels = 0;   // panels of 128 bytes (32 pixels) staged per strip (max over strips)
+    int nch2 = 0;
+    std::vector<int32_t> strip_col0;       // [n_strips + 1]
+    std::vector<int32_t> strip_src0;       // [n_strips] first staged source pixel (multiple of 4)
+    std::vector<int32_t> tile_kb0;         // [n_strips][8] first 4-pixel block of the tile's k range
+    std::vector<uint32_t> b2;              // [n_strips][8][nch2][ndig][32][2]
+    std::vector<float> cx;                 // [pw][4]
+    float s2[2][3] = {{0, 0, 0}, {0, 0, 0}};
+    uint32_t slots = 0, slot_bytes = 0, pitch_v = 0, smem_bytes = 0, nbuf = 0;
+    bool need_fill = false;
+};
+void build_tcplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, TcPlanHost &out);
 
 }  // namespace slimg

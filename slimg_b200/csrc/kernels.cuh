@@ -135,6 +135,37 @@ struct VfParams {
 cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStream_t stream);
 size_t vfirst_smem_tail_bytes();
 
+// ---- K2 tcgen05 pipeline (k2_tc.cu, plan in tcplan.cpp) ---------------------------------------------------
+struct TcParams {
+    const uint8_t *src;
+    uint8_t *dst;
+    size_t src_img_bytes, dst_img_bytes;
+    uint32_t sw, sh;                 // source pitch (pixels) and height
+    uint32_t ry;                     // first row of the source rectangle
+    uint32_t pw, ph;                 // columns / rows of the resize output that are kept
+    int32_t nch2, sh1;               // 32-pixel chunks per pass-2 tile; right shift to the u16 intermediate
+    // vertical pass: blocks of 16 kept rows, chunks of 32 source-rectangle rows
+    uint32_t n_blocks, n_chunks, crec_words;
+    const uint32_t *crecs;           // [n_chunks][crec_words]: {first block, blocks, flags, chunk, ...12} + [blocks][2 digits][512 B] tiles
+    const int32_t *blk_c0, *blk_c1;  // [n_blocks] first / last chunk of a block
+    const int32_t *bias;             // [n_blocks*16][4]
+    // horizontal pass
+    uint32_t n_strips, n_panels;
+    const int32_t *strip_col0;       // [n_strips+1] first kept column of each strip
+    const int32_t *strip_src0;       // [n_strips] first staged source pixel (multiple of 4)
+    const int32_t *tile_kb0;         // [n_strips][8] first 4-pixel block of the tile's k range
+    const uint32_t *b2;              // [n_strips][8][nch2][2][32 lanes][2]
+    const float *cx;                 // [pw][4] constant term per kept column and channel
+    float s2[2][3];                  // scale of accumulator [limb][digit]
+    // shared memory / TMEM geometry
+    uint32_t slots, slot_bytes, pitch_v, smem_bytes, nbuf;
+    // canvas
+    uint32_t fw, fh, fox, foy;
+    uint32_t fill_post, fill_pre_packed;
+    uint32_t n_bands, need_fill, debug;
+};
+cudaError_t launch_resize_tc(const TcParams &p, uint32_t n_images, cudaStream_t stream);
+
 // ---- K3+K4: JPEG pre-entropy front end (k3_jpeg.cu) ------------------------------------------
 struct QuantDev {                      // jcdctmgr.c:173-221 compute_reciprocal, per table entry
     uint32_t recip[2][64];

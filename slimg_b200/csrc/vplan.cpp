@@ -25,6 +25,8 @@ constexpr int kMaxCh = 4;          // chunk stride of the fragment tables (the k
 constexpr size_t kSmemBudget = 227 * 1024 - 2048;
 const int kPerm[4] = {0, 2, 1, 3};   // k-slot -> pixel inside a 4-pixel block (k2_vfirst.cu, pass-1 epilogue)
 
+}  // namespace
+
 // quantise one output's taps so that they sum to round(sum(w) * 2^S) exactly
 void quantise(const float *w, int cnt, int S, std::vector<int64_t> &q) {
     q.assign(cnt, 0);
@@ -58,12 +60,10 @@ int pick_scale(float maxw, int ndig) {
 }
 
 // B fragment of mma.m16n8k32 (col-major K x N): lane = n*4 + (k%16)/4, register = k/16, byte = k%4
-inline void put_b(uint32_t *frag, int k, int n, int8_t v) {
+void put_b(uint32_t *frag, int k, int n, int8_t v) {
     const int lane = n * 4 + (k % 16) / 4, reg = k / 16, byte = k % 4;
     frag[lane * 2 + reg] |= uint32_t(uint8_t(v)) << (8 * byte);
 }
-
-}  // namespace
 
 void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int ndig, VPlanHost &out) {
     out = VPlanHost();
