@@ -36,8 +36,9 @@ constexpr int kEpiWarp0 = 4, kEpiWarps = 8;  // warps 4..11: epilogue, two per T
 constexpr int kProducerWarp = 12, kMmaWarp = 13;
 constexpr int kMaxSlots = 12;
 constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
-// tcgen05 instruction descriptor: D = s32, A = u8 MN-major, B = s8 K-major, M = 128, N = 16
-constexpr uint32_t kIdesc = (2u << 4) | (0u << 7) | (1u << 10) | (1u << 15) | (0u << 16) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
+// tcgen05 instruction descriptor: D = s32, A = u8 MN-major, B = s8 K-major, M = 128, N = 32 (both weight digits of a
+// block's 16 rows in one instruction: the A panel is read from shared memory once)
+constexpr uint32_t kIdesc = (2u << 4) | (0u << 7) | (1u << 10) | (1u << 15) | (0u << 16) | ((32u >> 3) << 17) | ((128u >> 4) << 24);
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
@@ -75,6 +76,11 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
@@ -212,42 +218,47 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
         }
     } else if (warp == kMmaWarp) {
         // ================= MMA issue: every (block, panel, digit) of the chunk ============================
+        // One elected thread runs the whole loop (tcgen05.mma / commit are single-thread instructions; a loop that
+        // is uniform per construction keeps the compiler from wrapping every issue in an election).
+        if (elect_one()) {
 #pragma unroll 1
-        for (int s = 0; s < n_steps; s++) {
-            const int slot = s % slots;
-            mbar_wait(&tail.full[slot], uint32_t(s / slots) & 1u);
-            tc_fence_after();
-            const uint32_t *rec = reinterpret_cast<const uint32_t *>(smem_raw + size_t(slots) * p.slot_bytes + size_t(slot) * crec_bytes);
-            const int first = int(rec[0]), nb = int(rec[1]);
-            const uint32_t flags = rec[2];
-            const uint32_t a_base = ring + uint32_t(slot) * p.slot_bytes;
-            const uint32_t b_base = crec_base + uint32_t(slot) * crec_bytes + 64u;
+            for (int s = 0; s < n_steps; s++) {
+                const int slot = s % slots;
+                mbar_wait(&tail.full[slot], uint32_t(s / slots) & 1u);
+                tc_fence_after();
+                const uint32_t *rec = reinterpret_cast<const uint32_t *>(smem_raw + size_t(slots) * p.slot_bytes + size_t(slot) * crec_bytes);
+                const int first = int(rec[0]), nb = int(rec[1]);
+                const uint32_t flags = rec[2];
+                const uint64_t a_desc0 = desc_a(ring + uint32_t(slot) * p.slot_bytes);
+                const uint64_t b_desc0 = desc_b(crec_base + uint32_t(slot) * crec_bytes + 64u);
 #pragma unroll 1
-            for (int i = 0; i < nb; i++) {
-                const int b = first + i;
-                if (b < blk0 || b >= blk1) continue;
-                const int use = (b - blk0) / nbuf, abuf = (b - blk0) - use * nbuf;
-                const bool starts = (flags >> i) & 1u, ends = (flags >> (8 + i)) & 1u;
-                if (starts) {                                    // the buffer's previous block must have been drained
-                    mbar_wait(&tail.acc_empty[abuf], (uint32_t(use) & 1u) ^ 1u);
-                    tc_fence_after();
-                }
-                if (lane == 0) {
+                for (int i = 0; i < nb; i++) {
+                    const int b = first + i;
+                    if (b < blk0 || b >= blk1) continue;
+                    const int use = (b - blk0) / nbuf, abuf = (b - blk0) - use * nbuf;
+                    const bool starts = (flags >> i) & 1u, ends = (flags >> (8 + i)) & 1u;
+                    if (starts) {                                // the buffer's previous block must have been drained
+                        mbar_wait(&tail.acc_empty[abuf], (uint32_t(use) & 1u) ^ 1u);
+                        tc_fence_after();
+                    }
+                    const uint32_t acc = starts ? 0u : 1u;
+                    const uint64_t bd0 = b_desc0 + uint64_t(i) * (2u * 512u >> 4);     // digit tiles are contiguous: N = 32
+                    uint64_t ad = a_desc0;
+                    uint32_t dcol = tmem + uint32_t(abuf) * 32u;
+                    if (!(p.debug & 1u)) {
 #pragma unroll 1
-                    for (int pn = 0; pn < npan; pn++) {
-                        const uint64_t ad = desc_a(a_base + uint32_t(pn) * 4096u);
-#pragma unroll
-                        for (int d = 0; d < NDIG; d++)
-                            umma_i8(tmem + uint32_t((pn * nbuf + abuf) * 32 + d * 16), ad, desc_b(b_base + uint32_t(i * NDIG + d) * 512u),
-                                    starts ? 0u : 1u);
+                        for (int pn = 0; pn < npan; pn++) {
+                            umma_i8(dcol, ad, bd0, acc);
+                            ad += 4096u >> 4;
+                            dcol += uint32_t(nbuf) * 32u;
+                        }
                     }
                     if (ends) umma_commit(&tail.acc_full[abuf]);
                 }
-                __syncwarp();
+                umma_commit(&tail.empty[slot]);                  // the slot is free once everything issued so far retires
             }
-            if (lane == 0) umma_commit(&tail.empty[slot]);       // the slot is free once everything issued so far retires
-            __syncwarp();
         }
+        __syncwarp();
     } else if (warp >= kEpiWarp0 && warp < kEpiWarp0 + kEpiWarps) {
         // ================= epilogue: TMEM -> 16-bit intermediate -> V planes ==============================
         const int quarter = warp & 3, half = (warp - kEpiWarp0) >> 2;
@@ -274,7 +285,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
                 mbar_wait(&tail.v_empty[vb], (uint32_t(gi >> 1) & 1u) ^ 1u);
                 const uint32_t vrow = v0 + vb * 2u * vplane;
 #pragma unroll 1
-                for (int pn = pn0; pn < pn1; pn++) {
+                for (int pn = pn0; pn < ((p.debug & 8u) ? pn0 : pn1); pn++) {
                     int lo[8], hi[8];
                     const uint32_t taddr = tmem + lane_addr + uint32_t((pn * nbuf + abuf) * 32 + 8 * h);
                     tmem_ld8(taddr, lo);
@@ -324,6 +335,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
             const uint32_t buf = uint32_t(gi) & 1u;
             const uint32_t vbuf = vbase + buf * 2u * vplane;
             mbar_wait(&tail.v_full[buf], uint32_t(gi >> 1) & 1u);
+            if (p.debug & 2u) { __syncwarp(); if (lane == 0) mbar_arrive(&tail.v_empty[buf]); continue; }
 
             int acc[2][2][NDIG][4];            // [channel pair][limb][digit]
 #pragma unroll
