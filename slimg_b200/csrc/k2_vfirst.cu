@@ -31,6 +31,8 @@
 // (strip columns / 8) warps run pass 2, the others pass 1; one CTA barrier per group.
 #include <cuda.h>
 
+#include <algorithm>
+
 #include "kernels.cuh"
 
 namespace slimg {
@@ -41,6 +43,7 @@ constexpr int kWarps = 16;
 constexpr int kThreads = kWarps * 32;
 constexpr int kStepRows = 16;                // source rows per ring step (one mbarrier each) == kWarps
 constexpr int kMaxSteps = 16;                // ring of at most 256 rows
+constexpr int kVBufs = kVfVBufs;             // V (vertical-pass result) buffers: pass 1 may run this many groups ahead of pass 2
 constexpr int kRecBufs = 4;                  // group records in flight: fetched three groups ahead (vplan.cpp sizes for it)
 constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
 
@@ -121,39 +124,41 @@ __device__ __forceinline__ uint32_t quantize_channel(float t) {
 struct SmemTail {                             // after the ring, the V planes and the two group records
     uint64_t full[kMaxSteps];                // ring step landed (tx bytes)
     uint64_t rec_full[kRecBufs];                  // group record landed (tx bytes)
-    uint64_t go[2];                          // producer: record + source rows of the group are in, V[buf] is free
-    uint64_t v_full[2];                      // every pass-1 warp is done with the group: V complete, band rows released
-    uint64_t v_empty[2];                     // every pass-2 warp has read V
-    int pos[2];                              // ring row of the group's band start (written by the producer before `go`)
+    uint64_t go[kVBufs];                     // producer: record + source rows of the group are in, V[buf] is free
+    uint64_t v_full[kVBufs];                 // every pass-1 warp is done with the group: V complete, band rows released
+    uint64_t v_empty[kVBufs];                // every pass-2 warp has read V
+    int pos[kVBufs];                           // ring row of the group's band start (written by the producer before `go`)
 };
 
 // What is not computed: canvas rows outside the kept rectangle (fill_post), kept rows whose taps
-// are all fill (fill_pre), and the margins left / right of the kept columns.  Each CTA owns the
-// canvas rows of its band and the canvas columns of its strip (edge bands / strips extend to the
-// canvas border).
-// Run by the pass-2 warps before their first group: they would otherwise idle while the ring fills.
-__device__ __noinline__ void fill_region(const VfParams &p, uint32_t *dst, int i0, int i1, int c0, int c1, int warp, int nwarps) {
-    const bool first_band = blockIdx.y == 0, last_band = blockIdx.y + 1 == gridDim.y;
-    const bool first_strip = blockIdx.x == 0, last_strip = blockIdx.x + 1 == gridDim.x;
-    const int fr0 = first_band ? 0 : int(p.foy) + i0, fr1 = last_band ? int(p.fh) : int(p.foy) + i1;
-    const int cx0 = first_strip ? 0 : int(p.fox) + c0, cx1 = last_strip ? int(p.fw) : int(p.fox) + c1;
-    const int kx0 = int(p.fox), kx1 = int(p.fox + p.pw);
-    const bool margins = cx0 < kx0 || kx1 < cx1;
-    const int lane = threadIdx.x & 31;
-    const bool all_computed = (p.need_fill & 2u) == 0;        // no kept row is pure fill: skip the table
+// are all fill (fill_pre), and the margins left / right of the kept columns.  Dedicated fill CTAs
+// (blockIdx.x >= n_strips) write them with 16-byte stores, one canvas row per warp, while the strip
+// CTAs of the same image stream the source: the fill costs the strip pipeline nothing.
+__device__ __forceinline__ void fill_span(uint32_t *row, int x0, int x1, uint32_t v, int lane) {
+    if (x1 <= x0) return;
+    const int head = min(x1 - x0, int(((16u - (uint32_t(reinterpret_cast<uintptr_t>(row + x0)) & 15u)) & 15u) >> 2));
+    if (lane < head) row[x0 + lane] = v;
+    const int xb = x0 + head, nvec = (x1 - xb) >> 2;
+    const uint4 vv = make_uint4(v, v, v, v);
+    for (int i = lane; i < nvec; i += 32) reinterpret_cast<uint4 *>(row + xb)[i] = vv;
+    const int xt = xb + nvec * 4;
+    if (xt + lane < x1) row[xt + lane] = v;
+}
+
+__device__ __forceinline__ void fill_canvas(uint32_t *dst, int fw, int fh, int fox, int foy, int pw, int ph, const uint8_t *row_computed,
+                                            bool all_computed, uint32_t fill_pre, uint32_t fill_post, int part, int nparts) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int kx0 = fox, kx1 = fox + pw;
 #pragma unroll 1
-    for (int fr = fr0 + warp; fr < fr1; fr += nwarps) {
-        const int i = fr - int(p.foy);
-        const bool kept = i >= 0 && i < int(p.ph);
-        const bool computed = kept && (all_computed || p.row_computed[i]);
-        if (computed && !margins) continue;
-        uint32_t *row = dst + size_t(fr) * p.fw;
-#pragma unroll 1
-        for (int x = cx0 + lane; x < cx1; x += 32) {
-            const bool in_cols = x >= kx0 && x < kx1;
-            if (computed && in_cols) continue;
-            row[x] = (kept && in_cols) ? p.fill_pre_packed : p.fill_post;
-        }
+    for (int fr = part * kWarps + warp; fr < fh; fr += nparts * kWarps) {
+        const int i = fr - foy;
+        const bool kept = i >= 0 && i < ph;
+        const bool computed = kept && (all_computed || row_computed[i]);
+        uint32_t *row = dst + size_t(fr) * fw;
+        if (!kept) { fill_span(row, 0, fw, fill_post, lane); continue; }
+        fill_span(row, 0, kx0, fill_post, lane);
+        if (!computed) fill_span(row, kx0, kx1, fill_pre, lane);
+        fill_span(row, kx1, fw, fill_post, lane);
     }
 }
 
@@ -163,13 +168,18 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     const uint32_t ring = smem_u32(smem_raw);
     const uint32_t vbase = ring + p.ring_rows * p.pitch;
     const uint32_t vplane = 32u * p.pitch_v;                   // one limb of one buffer
-    const size_t rec_off = size_t(p.ring_rows) * p.pitch + 4u * vplane;
+    const size_t rec_off = size_t(p.ring_rows) * p.pitch + 2u * kVBufs * vplane;
     const uint32_t *recbuf = reinterpret_cast<const uint32_t *>(smem_raw + rec_off);
     SmemTail &tail = *reinterpret_cast<SmemTail *>(smem_raw + rec_off + uint32_t(kRecBufs) * p.rec_words * 4u);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     uint32_t *dst = reinterpret_cast<uint32_t *>(p.dst + size_t(blockIdx.z) * p.dst_img_bytes);
+    if (blockIdx.x >= p.n_strips) {              // fill CTA: no shared memory, no barriers
+        fill_canvas(dst, int(p.fw), int(p.fh), int(p.fox), int(p.foy), int(p.pw), int(p.ph), p.row_computed, (p.need_fill & 2u) == 0,
+                    p.fill_pre_packed, p.fill_post, int(blockIdx.x - p.n_strips), int(gridDim.x - p.n_strips));
+        return;
+    }
 
     // ---- this CTA's strip and band (a range of group records) -----------------------------------------
     const int strip = blockIdx.x;
@@ -177,9 +187,6 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     const int rec0 = int((uint64_t(blockIdx.y) * p.n_recs) / gridDim.y);
     const int rec1 = int((uint64_t(blockIdx.y + 1) * p.n_recs) / gridDim.y);
     const int n_iter = rec1 - rec0;
-    // kept rows this band owns on the canvas (for the fill): from its first group to the next band's first group
-    const int i0 = rec0 == 0 ? 0 : int(p.recs[size_t(rec0) * p.rec_words]) * 8;
-    const int i1 = rec1 == int(p.n_recs) ? int(p.ph) : int(p.recs[size_t(rec1) * p.rec_words]) * 8;
     const int ys = n_iter > 0 ? int(p.recs[size_t(rec0) * p.rec_words + 1]) & ~(kStepRows - 1) : 0;
     const int ye = n_iter > 0 ? int(p.recs[size_t(rec1 - 1) * p.rec_words + 2]) : 0;
     const int n_steps = (ye - ys + kStepRows - 1) / kStepRows;
@@ -198,7 +205,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     if (tid == 0) {
         for (int s = 0; s < nst; s++) mbar_init(&tail.full[s], 1);
         for (int b = 0; b < kRecBufs; b++) mbar_init(&tail.rec_full[b], 1);
-        for (int b = 0; b < 2; b++) {
+        for (int b = 0; b < kVBufs; b++) {
             mbar_init(&tail.go[b], 1);
             mbar_init(&tail.v_full[b], uint32_t(n_p1));
             mbar_init(&tail.v_empty[b], uint32_t(ntile));
@@ -240,10 +247,12 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         // band start are free once the group is done
         int a_next = n_iter > 1 ? int(__ldg(p.recs + size_t(rec0 + 1) * p.rec_words + 1)) : ye;
 #pragma unroll 1
+        uint32_t buf = 0, par = 0;
         for (int it = 0; it < n_iter; it++) {
             const int a_cur = a_next;
             a_next = it + 2 < n_iter ? int(__ldg(p.recs + size_t(rec0 + it + 2) * p.rec_words + 1)) : ye;
-            mbar_wait(&tail.v_full[it & 1], uint32_t(it >> 1) & 1u);
+            mbar_wait(&tail.v_full[buf], par);
+            if (++buf == kVBufs) { buf = 0; par ^= 1u; }
             issue_steps(min(n_steps, (a_cur - ys) / kStepRows + nst));
             if (it + kRecBufs < n_iter) issue_rec(it + kRecBufs);   // the record buffer of this group is free
         }
@@ -255,8 +264,8 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         int a0 = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words + 1)) : 0;
         int need = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words + 2)) : 0;
 #pragma unroll 1
+        uint32_t buf = 0, par = 0;
         for (int it = 0; it < n_iter; it++) {
-            const uint32_t buf = uint32_t(it) & 1u, par = uint32_t(it >> 1) & 1u;
             const int a0_cur = a0, need_cur = need;
             if (it + 1 < n_iter) {                           // next group's header, in flight while this one is waited for
                 a0 = int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words + 1));
@@ -266,12 +275,13 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             const int step = first + lane;                   // a band spans at most 128 rows + alignment: <= 9 steps
             if (step < last) mbar_wait(&tail.full[step % nst], uint32_t(step / nst) & 1u);
             mbar_wait(&tail.rec_full[it & (kRecBufs - 1)], uint32_t(it / kRecBufs) & 1u);
-            mbar_wait(&tail.v_empty[buf], par ^ 1u);        // V[buf] was last read by pass 2 two groups ago
+            mbar_wait(&tail.v_empty[buf], par ^ 1u);        // V[buf] was last read by pass 2 kVBufs groups ago
             __syncwarp();
             if (lane == 0) {
                 tail.pos[buf] = (a0_cur - ys) % ring_rows;
                 mbar_arrive(&tail.go[buf]);                  // release: pos is visible to the waiters
             }
+            if (++buf == kVBufs) { buf = 0; par ^= 1u; }
         }
     } else if (warp < ntile) {
         // ================= pass 2: horizontal taps, 4 channels x 8 rows x 8 output columns per warp =======
@@ -295,15 +305,14 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
 #pragma unroll
             for (int d = 0; d < NDIG; d++) s2[l][d] = p.s2[l][d];
         int j_next = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words)) : 0;
-        if (p.need_fill && !(p.need_fill & 4u)) fill_region(p, dst, i0, i1, col0, col1, warp, ntile);
 
 #pragma unroll 1
-        for (int it = 0; it < n_iter; it++) {
-            const uint32_t buf = uint32_t(it) & 1u;
+        uint32_t buf = 0, par = 0;
+        for (int it = 0; it < n_iter; it++, buf = buf + 1 == kVBufs ? 0 : buf + 1, par ^= buf == 0 ? 1u : 0u) {
             const int j = j_next;
             if (it + 1 < n_iter) j_next = int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words));
             const uint32_t vbuf = vbase + buf * 2u * vplane;
-            mbar_wait(&tail.v_full[buf], uint32_t(it >> 1) & 1u);
+            mbar_wait(&tail.v_full[buf], par);
 
             if (p.debug & 2u) { __syncwarp(); if (lane == 0) mbar_arrive(&tail.v_empty[buf]); continue; }
             int acc[2][2][NDIG][4];            // [channel pair][limb][digit]
@@ -327,7 +336,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tail.v_empty[buf]);       // V[buf] may be overwritten (two groups on)
+            if (lane == 0) mbar_arrive(&tail.v_empty[buf]);       // V[buf] may be overwritten (kVBufs groups on)
 
             uint32_t px[2] = {0u, 0u};         // packed RGBA of columns ocol, ocol+1 of output row g
 #pragma unroll
@@ -362,10 +371,10 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         const uint32_t boff0 = uint32_t(w1 * upw_all) * (UNIT * 16u);
 
 #pragma unroll 1
-        for (int it = 0; it < n_iter; it++) {
-            const uint32_t buf = uint32_t(it) & 1u;
+        uint32_t buf = 0, par = 0;
+        for (int it = 0; it < n_iter; it++, buf = buf + 1 == kVBufs ? 0 : buf + 1, par ^= buf == 0 ? 1u : 0u) {
             const uint32_t *rec = recbuf + uint32_t(it & (kRecBufs - 1)) * p.rec_words;
-            mbar_wait(&tail.go[buf], uint32_t(it >> 1) & 1u);
+            mbar_wait(&tail.go[buf], par);
             const int pos = tail.pos[buf];
             uint2 bw1[NCH1][NDIG];
 #pragma unroll
@@ -431,10 +440,6 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             if (lane == 0) mbar_arrive(&tail.v_full[buf]);        // this warp's share of V[buf] is written
         }
     }
-    if (p.need_fill & 4u) {
-        __syncthreads();
-        fill_region(p, dst, i0, i1, col0, col1, warp, kWarps);
-    }
 }
 
 }  // namespace
@@ -488,7 +493,13 @@ static cudaError_t launch_vf_t(const VfParams &p, uint32_t n_images, cudaStream_
         CUtensorMap map;
         cudaError_t e = make_source_map(q, q.src, nz, map);
         if (e != cudaSuccess) return e;
-        resize_vfirst_kernel<NDIG, NCH1, NCH2, UNIT><<<dim3(p.n_strips, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q, map);
+        // fill CTAs: one per ~2 MB of canvas that is not computed (at least one when anything is), after the strips of the image
+        unsigned nfill = 0;
+        if (p.need_fill) {
+            const uint64_t bytes = (uint64_t(p.fw) * p.fh - uint64_t(p.pw) * p.ph) * 4u;
+            nfill = unsigned(std::min<uint64_t>(32, 1 + bytes / (2u << 20)));
+        }
+        resize_vfirst_kernel<NDIG, NCH1, NCH2, UNIT><<<dim3(p.n_strips + nfill, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q, map);
         count_launch();
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;

@@ -132,6 +132,7 @@ struct VfParams {
     uint32_t debug;                  // experiment switches (SLIMG_B200_VF_DEBUG), 0 in production
     uint32_t pf_steps;               // ring steps prefetched into L2 ahead of the ring (0 = off)
 };
+constexpr int kVfVBufs = 3;         // V buffers of the kernel (vplan.cpp sizes shared memory for them)
 cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStream_t stream);
 size_t vfirst_smem_tail_bytes();
 

@@ -13,6 +13,7 @@
 #include <cstdlib>
 
 #include "host.h"
+#include "kernels.cuh"
 
 namespace slimg {
 
@@ -219,7 +220,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         int64_t qv = (nblk + 3 + 3) / 4;                           // words per V row = 4 * odd >= nblk + 3
         if (qv % 2 == 0) qv++;
         pitch_v = uint32_t(qv * 16);
-        return size_t(ring_rows) * pitch + size_t(4) * 32 * pitch_v + fixed_bytes;
+        return size_t(ring_rows) * pitch + size_t(2 * kVfVBufs) * 32 * pitch_v + fixed_bytes;
     };
     // widest strips (multiple of 8 columns, at most 64) whose staging fits in shared memory; per width the unit
     // size with the least padding; early_go when the deeper ring still fits
