@@ -189,9 +189,9 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
         VPlanHost vp;
         build_vplan(g, tx, ty, ndig, vp);
         if (std::getenv("SLIMG_B200_DEBUG"))
-            std::fprintf(stderr, "[slimg_b200] vplan ok=%d strips=%u cols=%d unit=%d upw=%d nunits=%d early=%d ring=%u pitch=%u pitch_v=%u smem=%u nch1=%d nch2=%d recs=%u\n",
+            std::fprintf(stderr, "[slimg_b200] vplan ok=%d strips=%u cols=%d unit=%d upw=%d nunits=%d early=%d vbufs=%u ring=%u pitch=%u pitch_v=%u smem=%u nch1=%d nch2=%d recs=%u\n",
                          int(vp.ok), vp.n_strips, vp.ok ? vp.strip_col0[1] : 0, vp.unit, vp.ok ? vp.strip_upw[0] : 0,
-                         vp.ok ? vp.strip_nunits[0] : 0, int(vp.early_go), vp.ring_rows, vp.pitch, vp.pitch_v, vp.smem_bytes,
+                         vp.ok ? vp.strip_nunits[0] : 0, int(vp.early_go), vp.vbufs, vp.ring_rows, vp.pitch, vp.pitch_v, vp.smem_bytes,
                          vp.nch1, vp.nch2, vp.n_recs);
         if (vp.ok) {
             if ((e = plan->v_recs.upload(vp.recs)) || (e = plan->v_rowc.upload(vp.row_computed)) || (e = plan->v_col0.upload(vp.strip_col0)) ||
@@ -213,7 +213,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
             v.b2 = (const uint32_t *)plan->v_b2.p; v.cx = (const float *)plan->v_cx.p;
             for (int l = 0; l < 2; l++)
                 for (int d = 0; d < 3; d++) v.s2[l][d] = vp.s2[l][d];
-            v.ring_rows = vp.ring_rows; v.pitch = vp.pitch; v.pitch_v = vp.pitch_v; v.smem_bytes = vp.smem_bytes;
+            v.vbufs = vp.vbufs; v.ring_rows = vp.ring_rows; v.pitch = vp.pitch; v.pitch_v = vp.pitch_v; v.smem_bytes = vp.smem_bytes;
             v.fw = g.fw; v.fh = g.fh; v.fox = g.fox; v.foy = g.foy;
             v.fill_post = pack_fill(g.fill_post); v.fill_pre_packed = pack_fill(g.fill_pre);
             v.n_bands = 1; v.need_fill = (vp.need_fill ? 1u : 0u) | (vp.rows_pure_fill ? 2u : 0u);

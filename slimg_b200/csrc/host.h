@@ -109,6 +109,7 @@ struct VPlanHost {
     float s2[2][3] = {{0, 0, 0}, {0, 0, 0}};
     // shared-memory geometry
     uint32_t ring_rows = 0, pitch = 0, pitch_v = 0, smem_bytes = 0;
+    uint32_t vbufs = 3;                    // V buffers (k2_vfirst.cu): 2..4
     bool need_fill = false, rows_pure_fill = false;
 };
 void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int ndig, VPlanHost &out);

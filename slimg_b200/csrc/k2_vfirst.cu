@@ -42,8 +42,8 @@ namespace {
 constexpr int kWarps = 16;
 constexpr int kThreads = kWarps * 32;
 constexpr int kStepRows = 16;                // source rows per ring step (one mbarrier each) == kWarps
-constexpr int kMaxSteps = 16;                // ring of at most 256 rows
-constexpr int kVBufs = kVfVBufs;             // V (vertical-pass result) buffers: pass 1 may run this many groups ahead of pass 2
+constexpr int kMaxSteps = 32;                // ring of at most 512 rows (one step per producer lane)
+constexpr int kMaxVBufs = kVfMaxVBufs;            // V (vertical-pass result) buffers: pass 1 may run this many groups ahead of pass 2
 constexpr int kRecBufs = 4;                  // group records in flight: fetched three groups ahead (vplan.cpp sizes for it)
 constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
 
@@ -124,10 +124,10 @@ __device__ __forceinline__ uint32_t quantize_channel(float t) {
 struct SmemTail {                             // after the ring, the V planes and the two group records
     uint64_t full[kMaxSteps];                // ring step landed (tx bytes)
     uint64_t rec_full[kRecBufs];                  // group record landed (tx bytes)
-    uint64_t go[kVBufs];                     // producer: record + source rows of the group are in, V[buf] is free
-    uint64_t v_full[kVBufs];                 // every pass-1 warp is done with the group: V complete, band rows released
-    uint64_t v_empty[kVBufs];                // every pass-2 warp has read V
-    int pos[kVBufs];                           // ring row of the group's band start (written by the producer before `go`)
+    uint64_t go[kMaxVBufs];                     // producer: record + source rows of the group are in, V[buf] is free
+    uint64_t v_full[kMaxVBufs];                 // every pass-1 warp is done with the group: V complete, band rows released
+    uint64_t v_empty[kMaxVBufs];                // every pass-2 warp has read V
+    int pos[kMaxVBufs];                           // ring row of the group's band start (written by the producer before `go`)
 };
 
 // What is not computed: canvas rows outside the kept rectangle (fill_post), kept rows whose taps
@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     const uint32_t ring = smem_u32(smem_raw);
     const uint32_t vbase = ring + p.ring_rows * p.pitch;
     const uint32_t vplane = 32u * p.pitch_v;                   // one limb of one buffer
-    const size_t rec_off = size_t(p.ring_rows) * p.pitch + 2u * kVBufs * vplane;
+    const size_t rec_off = size_t(p.ring_rows) * p.pitch + 2u * p.vbufs * vplane;
     const uint32_t *recbuf = reinterpret_cast<const uint32_t *>(smem_raw + rec_off);
     SmemTail &tail = *reinterpret_cast<SmemTail *>(smem_raw + rec_off + uint32_t(kRecBufs) * p.rec_words * 4u);
 
@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     if (tid == 0) {
         for (int s = 0; s < nst; s++) mbar_init(&tail.full[s], 1);
         for (int b = 0; b < kRecBufs; b++) mbar_init(&tail.rec_full[b], 1);
-        for (int b = 0; b < kVBufs; b++) {
+        for (int b = 0; b < int(p.vbufs); b++) {
             mbar_init(&tail.go[b], 1);
             mbar_init(&tail.v_full[b], uint32_t(n_p1));
             mbar_init(&tail.v_empty[b], uint32_t(ntile));
@@ -225,13 +225,19 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         const int tr0 = int(blockIdx.z) * int(p.sh) + int(p.ry) + ys;
         const uint32_t step_bytes = kStepRows * p.pitch;
         auto issue_steps = [&](int upto) {
-            const int step = next_issue + lane;                 // at most nst <= 16 steps are ever issued at once
+            const int step = next_issue + lane;                 // at most nst <= 32 steps are ever issued at once
             if (step < upto) {
                 const int slot = step % nst;
                 mbar_arrive_expect_tx(&tail.full[slot], step_bytes);
                 tma_load_2d(ring + uint32_t(slot) * step_bytes, &tmap, tc0, tr0 + ((p.debug & 4u) ? (step & 7) : step) * kStepRows, &tail.full[slot]);
             }
             next_issue = max(next_issue, upto);
+        };
+        // steps beyond the ring, as far as L2: the DRAM part of their latency is paid before they get a ring slot
+        int next_pf = 0;
+        auto prefetch_steps = [&](int upto) {
+            for (int s = max(next_pf, next_issue) + lane; s < upto; s += 32) tma_prefetch_2d(&tmap, tc0, tr0 + s * kStepRows);
+            next_pf = max(next_pf, upto);
         };
         auto issue_rec = [&](int it) {
             if (lane == 0) {
@@ -241,6 +247,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             }
         };
         issue_steps(min(n_steps, nst));
+        if (p.pf_steps) prefetch_steps(min(n_steps, next_issue + int(p.pf_steps)));
         for (int r = 0; r < kRecBufs; r++)
             if (r < n_iter) issue_rec(r);
         // band start of the group after next, fetched a group early: ring steps entirely above a group's successor's
@@ -252,8 +259,9 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             const int a_cur = a_next;
             a_next = it + 2 < n_iter ? int(__ldg(p.recs + size_t(rec0 + it + 2) * p.rec_words + 1)) : ye;
             mbar_wait(&tail.v_full[buf], par);
-            if (++buf == kVBufs) { buf = 0; par ^= 1u; }
+            if (++buf == p.vbufs) { buf = 0; par ^= 1u; }
             issue_steps(min(n_steps, (a_cur - ys) / kStepRows + nst));
+            if (p.pf_steps) prefetch_steps(min(n_steps, next_issue + int(p.pf_steps)));
             if (it + kRecBufs < n_iter) issue_rec(it + kRecBufs);   // the record buffer of this group is free
         }
     } else if (warp == kWarps - 2) {
@@ -275,13 +283,13 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             const int step = first + lane;                   // a band spans at most 128 rows + alignment: <= 9 steps
             if (step < last) mbar_wait(&tail.full[step % nst], uint32_t(step / nst) & 1u);
             mbar_wait(&tail.rec_full[it & (kRecBufs - 1)], uint32_t(it / kRecBufs) & 1u);
-            mbar_wait(&tail.v_empty[buf], par ^ 1u);        // V[buf] was last read by pass 2 kVBufs groups ago
+            mbar_wait(&tail.v_empty[buf], par ^ 1u);        // V[buf] was last read by pass 2 vbufs groups ago
             __syncwarp();
             if (lane == 0) {
                 tail.pos[buf] = (a0_cur - ys) % ring_rows;
                 mbar_arrive(&tail.go[buf]);                  // release: pos is visible to the waiters
             }
-            if (++buf == kVBufs) { buf = 0; par ^= 1u; }
+            if (++buf == p.vbufs) { buf = 0; par ^= 1u; }
         }
     } else if (warp < ntile) {
         // ================= pass 2: horizontal taps, 4 channels x 8 rows x 8 output columns per warp =======
@@ -308,7 +316,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
 
 #pragma unroll 1
         uint32_t buf = 0, par = 0;
-        for (int it = 0; it < n_iter; it++, buf = buf + 1 == kVBufs ? 0 : buf + 1, par ^= buf == 0 ? 1u : 0u) {
+        for (int it = 0; it < n_iter; it++, buf = buf + 1 == p.vbufs ? 0 : buf + 1, par ^= buf == 0 ? 1u : 0u) {
             const int j = j_next;
             if (it + 1 < n_iter) j_next = int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words));
             const uint32_t vbuf = vbase + buf * 2u * vplane;
@@ -336,7 +344,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tail.v_empty[buf]);       // V[buf] may be overwritten (kVBufs groups on)
+            if (lane == 0) mbar_arrive(&tail.v_empty[buf]);       // V[buf] may be overwritten (vbufs groups on)
 
             uint32_t px[2] = {0u, 0u};         // packed RGBA of columns ocol, ocol+1 of output row g
 #pragma unroll
@@ -372,7 +380,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
 
 #pragma unroll 1
         uint32_t buf = 0, par = 0;
-        for (int it = 0; it < n_iter; it++, buf = buf + 1 == kVBufs ? 0 : buf + 1, par ^= buf == 0 ? 1u : 0u) {
+        for (int it = 0; it < n_iter; it++, buf = buf + 1 == p.vbufs ? 0 : buf + 1, par ^= buf == 0 ? 1u : 0u) {
             const uint32_t *rec = recbuf + uint32_t(it & (kRecBufs - 1)) * p.rec_words;
             mbar_wait(&tail.go[buf], par);
             const int pos = tail.pos[buf];

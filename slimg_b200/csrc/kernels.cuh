@@ -124,6 +124,7 @@ struct VfParams {
     float s2[2][3];                  // scale of accumulator [limb][digit]
     // shared memory geometry
     uint32_t ring_rows, pitch, pitch_v, smem_bytes;
+    uint32_t vbufs;                  // V (vertical-pass result) buffers: pass 1 may run this many groups ahead of pass 2
     // canvas
     uint32_t fw, fh, fox, foy;
     uint32_t fill_post, fill_pre_packed;
@@ -132,7 +133,7 @@ struct VfParams {
     uint32_t debug;                  // experiment switches (SLIMG_B200_VF_DEBUG), 0 in production
     uint32_t pf_steps;               // ring steps prefetched into L2 ahead of the ring (0 = off)
 };
-constexpr int kVfVBufs = 3;         // V buffers of the kernel (vplan.cpp sizes shared memory for them)
+constexpr int kVfMaxVBufs = 4;      // most V buffers the kernel supports (VfParams::vbufs)
 cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStream_t stream);
 size_t vfirst_smem_tail_bytes();
 

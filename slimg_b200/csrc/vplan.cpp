@@ -220,13 +220,15 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         int64_t qv = (nblk + 3 + 3) / 4;                           // words per V row = 4 * odd >= nblk + 3
         if (qv % 2 == 0) qv++;
         pitch_v = uint32_t(qv * 16);
-        return size_t(ring_rows) * pitch + size_t(2 * kVfVBufs) * 32 * pitch_v + fixed_bytes;
+        return size_t(ring_rows) * pitch + size_t(2 * out.vbufs) * 32 * pitch_v + fixed_bytes;
     };
     // widest strips (multiple of 8 columns, at most 64) whose staging fits in shared memory; per width the unit
     // size with the least padding; early_go when the deeper ring still fits
     const char *cols_env = std::getenv("SLIMG_B200_STRIP_COLS");
     const char *early_env = std::getenv("SLIMG_B200_EARLY_GO");
     const char *unit_env = std::getenv("SLIMG_B200_UNIT");
+    const char *vbufs_env = std::getenv("SLIMG_B200_VBUFS");
+    out.vbufs = vbufs_env ? uint32_t(std::min(kVfMaxVBufs, std::max(2, std::atoi(vbufs_env)))) : 3u;
     uint32_t cols = 0;
     int unit = 0;
     bool early = false;
@@ -267,15 +269,15 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     out.unit = unit;
     out.early_go = early;
     out.ring_rows = early ? ring_early : ring_min;
-    if (out.ring_rows / 16 > 16) return;                          // k2_vfirst.cu kMaxSteps
+    if (out.ring_rows / 16 > 32) return;                          // k2_vfirst.cu kMaxSteps
     {
         // deepen the ring as far as shared memory allows: every extra step is 16 more rows in flight
         int unused;
         const int64_t blk = max_padded(cols, unit, unused);
         const char *ring_env = std::getenv("SLIMG_B200_RING_STEPS");
-        const uint32_t cap = ring_env ? uint32_t(std::atoi(ring_env)) * 16 : 256u;
+        const uint32_t cap = ring_env ? uint32_t(std::atoi(ring_env)) * 16 : 512u;
         uint32_t pch, pv;
-        while (out.ring_rows + 16 <= std::min(cap, 256u) && smem_for(blk, out.ring_rows + 16, pch, pv) <= kSmemBudget) out.ring_rows += 16;
+        while (out.ring_rows + 16 <= std::min(cap, 512u) && smem_for(blk, out.ring_rows + 16, pch, pv) <= kSmemBudget) out.ring_rows += 16;
     }
     out.n_strips = (g.pw + cols - 1) / cols;
 
