@@ -32,12 +32,15 @@ sys.path.insert(0, ROOT)
 
 SRC_W, SRC_H = 6000, 4000
 MPX_PER_IMAGE = SRC_W * SRC_H / 1e6
+# arithmetic of the CUDA path: u8 pixels x s8 weight digits -> s32 on the integer tensor pipe (fixed point, exact),
+# f32 only for the final recombination; the CPU reference arm computes in f32 like the image crate
+DTYPE = "u8*s8->s32 fixed point"
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=128, help="images per GPU per step (device-resident)")
@@ -80,6 +83,16 @@ def measured_peak_gbs():
     return 6650.0, "fallback"
 
 
+def measured_traffic(order: str, batch: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the K2 launch from the committed ncu --set full capture
+    (profiles/traffic.json: bytes per image of that capture), scaled to this launch's batch; None if absent."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[order]
+        return float(t["dram_bytes_per_image"]) * batch
+    except Exception:
+        return None
+
+
 # ---- clocks ------------------------------------------------------------------------------------------
 
 class ClockSampler:
@@ -95,7 +108,7 @@ class ClockSampler:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100",
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "20",
                  "-i", str(self.gpu)], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -270,7 +283,7 @@ def main():
     launch_ms = ms / max(1, launches)
     achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_kind": peak_kind, "kernel": "resize pipeline (K2)",
+                "traffic": measured_traffic(args.order, B), "peak_kind": peak_kind, "kernel": "resize pipeline (K2)",
                 "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": launch_ms}
 
     # end to end through the host-buffer C ABI
@@ -279,6 +292,9 @@ def main():
         lib = ll.library()
         nb = args.e2e_batch
         in_bytes, out_bytes = SRC_W * SRC_H * 4, ow * oh * 4
+        # the library uploads only the source window the pipeline reads (slimg_b200_pipeline_source_window)
+        wx, wy, ww, wh = ll.pipeline_source_window(SRC_W, SRC_H, opts, order)
+        h2d_bytes = ww * wh * 4 if ww * 10 < SRC_W * 9 else wh * SRC_W * 4
         pin_in = lib.slimg_b200_host_alloc(nb * in_bytes)
         pin_out = lib.slimg_b200_host_alloc(nb * out_bytes)
         if not pin_in or not pin_out:
@@ -315,7 +331,8 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_value = world * nb * e2e_steps * MPX_PER_IMAGE / float(t.item())
         checksum = int(np.ctypeslib.as_array(C.cast(pin_out, C.POINTER(C.c_uint8)), shape=(nb * out_bytes,))[::4097].sum())
-        e2e = {"value": e2e_value, "unit": "Mpx/s", "h2d_bytes_per_step": nb * in_bytes, "d2h_bytes_per_step": nb * out_bytes,
+        e2e = {"value": e2e_value, "unit": "Mpx/s", "h2d_bytes_per_step": nb * h2d_bytes, "d2h_bytes_per_step": nb * out_bytes,
+               "host_image_bytes_per_step": nb * in_bytes,
                "images_per_gpu_per_step": nb, "steps": e2e_steps, "timer": "host wall clock around the C-ABI calls, max over ranks",
                "result_checksum": checksum}
         lib.slimg_b200_host_free(pin_in); lib.slimg_b200_host_free(pin_out)
@@ -323,7 +340,7 @@ def main():
     cpu = None
     if rank == 0 and not args.no_cpu:
         threads = host_threads()
-        n_img = args.cpu_images or max(16, min(64, threads * 2))
+        n_img = args.cpu_images or max(32, min(256, threads * 8))
         dt, mpx = cpu_run(args.order, n_img, threads)
         cpu = {"value": mpx, "unit": "Mpx/s", "cores": threads, "kind": "port",
                "sample": f"{n_img} synthetic 24 MP images of the same workload, one image per thread, {dt:.1f} s wall"}
@@ -335,7 +352,7 @@ def main():
         print(json.dumps({
             "metric": "Mpx/s resize->crop->extend", "value": value, "unit": "Mpx/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
             "config": workload_config(args, B), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(launches), "clocks": clocks,
         }))

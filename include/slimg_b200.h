@@ -115,6 +115,12 @@ slimg_status slimg_b200_calculate_extend_region(uint32_t w, uint32_t h, const sl
 slimg_status slimg_b200_pipeline_output_dims(uint32_t w, uint32_t h, const slimg_pipeline_options *opts,
                                              int order, uint32_t *out_w, uint32_t *out_h);
 
+/* The rectangle of the source image the pipeline actually reads for these options (every filter tap with a
+ * non-zero weight behind the kept output pixels): host-fed calls upload only this window, and a caller that
+ * stages its own device buffers may do the same.  win_w == 0 means no source pixel is read. */
+slimg_status slimg_b200_pipeline_source_window(uint32_t w, uint32_t h, const slimg_pipeline_options *opts, int order,
+                                               uint32_t *x, uint32_t *y, uint32_t *win_w, uint32_t *win_h);
+
 /* ---- single-image operations, host buffers in / host buffers out ----
  * `out->data` is allocated by the library (release with slimg_b200_image_free). */
 

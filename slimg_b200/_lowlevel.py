@@ -75,6 +75,7 @@ ABI_SYMBOLS = (
     "slimg_b200_jpeg_coefs_free", "slimg_b200_pipeline_batch_device", "slimg_b200_jpeg_frontend_batch_device",
     "slimg_b200_pipeline_batch_host", "slimg_b200_last_error", "slimg_b200_abi_version",
     "slimg_b200_device_count", "slimg_b200_kernel_launches", "slimg_b200_host_alloc", "slimg_b200_host_free",
+    "slimg_b200_pipeline_source_window",
 )
 
 _lib: Optional[C.CDLL] = None
@@ -98,6 +99,7 @@ def library() -> C.CDLL:
         "slimg_b200_calculate_crop_region": (C.c_int, [C.c_uint32, C.c_uint32, C.POINTER(CCropMode), u32p, u32p, u32p, u32p]),
         "slimg_b200_calculate_extend_region": (C.c_int, [C.c_uint32, C.c_uint32, C.POINTER(CExtendMode), u32p, u32p, u32p, u32p]),
         "slimg_b200_pipeline_output_dims": (C.c_int, [C.c_uint32, C.c_uint32, C.POINTER(CPipelineOptions), C.c_int, u32p, u32p]),
+        "slimg_b200_pipeline_source_window": (C.c_int, [C.c_uint32, C.c_uint32, C.POINTER(CPipelineOptions), C.c_int, u32p, u32p, u32p, u32p]),
         "slimg_b200_crop": (C.c_int, [C.POINTER(CImage), C.POINTER(CCropMode), C.POINTER(CImage)]),
         "slimg_b200_extend": (C.c_int, [C.POINTER(CImage), C.POINTER(CExtendMode), C.POINTER(CFillColor), C.POINTER(CImage)]),
         "slimg_b200_resize": (C.c_int, [C.POINTER(CImage), C.POINTER(CResizeMode), C.POINTER(CImage)]),
@@ -356,6 +358,14 @@ def pipeline_output_dims(w, h, options: CPipelineOptions, order: int = ORDER_CON
     ow, oh = C.c_uint32(), C.c_uint32()
     _check(library().slimg_b200_pipeline_output_dims(w, h, C.byref(options), order, C.byref(ow), C.byref(oh)))
     return ow.value, oh.value
+
+
+def pipeline_source_window(w, h, options: CPipelineOptions, order: int = ORDER_CONVERT):
+    """(x, y, width, height) of the source rectangle the pipeline reads (what host-fed calls upload)."""
+    x, y, ww, hh = C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
+    _check(library().slimg_b200_pipeline_source_window(w, h, C.byref(options), order, C.byref(x), C.byref(y),
+                                                       C.byref(ww), C.byref(hh)))
+    return x.value, y.value, ww.value, hh.value
 
 
 def jpeg_geometry(w, h) -> CJpegGeometry:

@@ -51,6 +51,8 @@ struct DevArray {
 struct ResizePlan {
     DevArray xl, xc, xw, xf, yl, yc, yw, yf, tx0, tspan;
     ResizeParams params{};   // src/dst/strides filled per launch
+    // rows / columns of the source any kernel of this plan reads with a non-zero weight (what a host-fed call uploads)
+    uint32_t win_r0 = 0, win_r1 = 0, win_c0 = 0, win_c1 = 0;
     // fast path (k2_fast.cu), when the geometry qualifies
     bool fast = false;
     DevArray f_a0, f_nch, f_boff, f_bfrag, f_fillx, f_vrow, f_vleft, f_vright, f_filly, f_rowc, f_sa0, f_sbytes;
@@ -93,6 +95,27 @@ static DeviceCtx &device_ctx(int dev) {
     return *c;
 }
 
+// source rows / columns behind the kept output rectangle: every tap with a non-zero weight lies inside
+static void window_from_taps(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, uint32_t &wr0, uint32_t &wr1,
+                             uint32_t &wc0, uint32_t &wc1) {
+    int64_t r0 = INT64_MAX, r1 = -1, c0 = INT64_MAX, c1 = -1;
+    for (uint32_t i = 0; i < g.ph; i++) {
+        const uint32_t o = g.py + i;
+        if (ty.count[o] == 0) continue;
+        r0 = std::min<int64_t>(r0, ty.left[o]); r1 = std::max<int64_t>(r1, int64_t(ty.left[o]) + ty.count[o]);
+    }
+    for (uint32_t j = 0; j < g.pw; j++) {
+        const uint32_t o = g.px + j;
+        if (tx.count[o] == 0) continue;
+        c0 = std::min<int64_t>(c0, tx.left[o]); c1 = std::max<int64_t>(c1, int64_t(tx.left[o]) + tx.count[o]);
+    }
+    wr0 = wr1 = wc0 = wc1 = 0;
+    if (r1 > r0 && c1 > c0) {
+        wr0 = g.ry + uint32_t(r0); wr1 = g.ry + uint32_t(r1);
+        wc0 = g.rx + uint32_t(c0); wc1 = g.rx + uint32_t(c1);
+    }
+}
+
 static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizePlan> &out) {
     auto plan = std::make_shared<ResizePlan>();
     AxisTaps tx, ty;
@@ -127,6 +150,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
         else return fail(SLIMG_ERR_RESIZE, "filter footprint of this resize exceeds shared memory");
     }
 
+    window_from_taps(g, tx, ty, plan->win_r0, plan->win_r1, plan->win_c0, plan->win_c1);
     cudaError_t e;
     if ((e = plan->xl.upload(tx.left)) || (e = plan->xc.upload(tx.count)) || (e = plan->xw.upload(tx.w)) ||
         (e = plan->xf.upload(tx.fillw)) || (e = plan->yl.upload(ty.left)) || (e = plan->yc.upload(ty.count)) ||
@@ -221,7 +245,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
             const char *dbg_env = std::getenv("SLIMG_B200_VF_DEBUG");
             v.debug = dbg_env ? uint32_t(std::atoi(dbg_env)) : 0u;
             const char *pf_env = std::getenv("SLIMG_B200_PREFETCH_STEPS");
-            v.pf_steps = pf_env ? uint32_t(std::atoi(pf_env)) : 0u;   // measured: no gain, the ring is not DRAM-latency bound
+            v.pf_steps = pf_env ? uint32_t(std::atoi(pf_env)) : 16u;  // ring steps prefetched into L2 ahead of the ring (measured: 8-16 best, 32 worse)
             plan->vfirst = true;
         }
     }
@@ -282,6 +306,27 @@ static slimg_status get_resize_plan(const PipeGeom &g, std::shared_ptr<ResizePla
     slimg_status st = build_resize_plan(g, out);
     if (st == SLIMG_OK) ctx.plans[key] = out;
     return st;
+}
+
+// Rows [r0,r1) x columns [c0,c1) of the source that the pipeline reads for this geometry.
+static bool remap_window(const PipeGeom &g, uint32_t &r0, uint32_t &r1, uint32_t &c0, uint32_t &c1) {
+    if (!g.has_resize) {      // R == V: the kept rectangle of V, where it is backed by the source rectangle
+        const int64_t x0 = std::max<int64_t>(g.vox, g.px), x1 = std::min<int64_t>(int64_t(g.vox) + g.rw, int64_t(g.px) + g.pw);
+        const int64_t y0 = std::max<int64_t>(g.voy, g.py), y1 = std::min<int64_t>(int64_t(g.voy) + g.rh, int64_t(g.py) + g.ph);
+        if (x1 <= x0 || y1 <= y0) { r0 = r1 = c0 = c1 = 0; return true; }
+        c0 = uint32_t(x0 - g.vox + g.rx); c1 = uint32_t(x1 - g.vox + g.rx);
+        r0 = uint32_t(y0 - g.voy + g.ry); r1 = uint32_t(y1 - g.voy + g.ry);
+        return true;
+    }
+    return false;
+}
+static slimg_status source_window(const PipeGeom &g, uint32_t &r0, uint32_t &r1, uint32_t &c0, uint32_t &c1) {
+    if (remap_window(g, r0, r1, c0, c1)) return SLIMG_OK;
+    std::shared_ptr<ResizePlan> plan;
+    slimg_status st = get_resize_plan(g, plan);
+    if (st != SLIMG_OK) return st;
+    r0 = plan->win_r0; r1 = plan->win_r1; c0 = plan->win_c0; c1 = plan->win_c1;
+    return SLIMG_OK;
 }
 
 // Enqueue the whole pixel pipeline for n same-geometry images that are resident on the current
@@ -416,7 +461,22 @@ static slimg_status pipeline_one(const slimg_image *in, const slimg_pipeline_opt
     cudaError_t e;
     if ((e = cudaMallocAsync((void **)&d_src, src_bytes, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
     if ((e = cudaMallocAsync((void **)&d_dst, dst_bytes ? dst_bytes : 1, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
-    if ((e = cudaMemcpyAsync(d_src, in->data, src_bytes, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "H2D"));
+    // upload only what the kernels read: the rows (and, when the window is much narrower than the image, the columns)
+    // of the source behind the kept output rectangle; the rest of d_src stays unwritten and unread (staging that
+    // over-reads a ring step meets zero weights: integer 0 x anything = 0)
+    uint32_t r0 = 0, r1 = g.sh, c0 = 0, c1 = g.sw;
+    if ((st = source_window(g, r0, r1, c0, c1)) != SLIMG_OK) return cleanup(st);
+    if (r1 > r0 && c1 > c0) {
+        if (uint64_t(c1 - c0) * 10 < uint64_t(g.sw) * 9) {
+            const size_t off = (size_t(r0) * g.sw + c0) * 4;
+            e = cudaMemcpy2DAsync(d_src + off, size_t(g.sw) * 4, in->data + off, size_t(g.sw) * 4, size_t(c1 - c0) * 4, r1 - r0,
+                                  cudaMemcpyHostToDevice, stream);
+        } else {
+            const size_t off = size_t(r0) * g.sw * 4;
+            e = cudaMemcpyAsync(d_src + off, in->data + off, size_t(r1 - r0) * g.sw * 4, cudaMemcpyHostToDevice, stream);
+        }
+        if (e != cudaSuccess) return cleanup(cuda_fail(e, "H2D"));
+    }
     if ((st = run_pipeline_device(g, d_src, 1, d_dst, stream)) != SLIMG_OK) return cleanup(st);
     if ((e = cudaMemcpyAsync(host_out, d_dst, dst_bytes, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "D2H"));
     if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return cleanup(cuda_fail(e, "pipeline kernels"));
@@ -621,6 +681,23 @@ slimg_status slimg_b200_jpeg_frontend(const slimg_image *in, const uint16_t qt_l
 
 void slimg_b200_jpeg_coefs_free(slimg_jpeg_coefs *c) {
     if (c && c->y) { std::free(c->y); c->y = c->cb = c->cr = nullptr; }
+}
+
+slimg_status slimg_b200_pipeline_source_window(uint32_t w, uint32_t h, const slimg_pipeline_options *opts, int order,
+                                               uint32_t *x, uint32_t *y, uint32_t *win_w, uint32_t *win_h) {
+    if (!opts || !x || !y || !win_w || !win_h) return fail(SLIMG_ERR_IMAGE, "null argument");
+    PipeGeom g;
+    slimg_status st = build_geometry(w, h, *opts, order, g);
+    if (st != SLIMG_OK) return st;
+    uint32_t r0, r1, c0, c1;
+    if (!remap_window(g, r0, r1, c0, c1)) {
+        AxisTaps tx, ty;
+        build_axis_taps(g.vw, g.Rw, g.vox, g.rw, tx);
+        build_axis_taps(g.vh, g.Rh, g.voy, g.rh, ty);
+        window_from_taps(g, tx, ty, r0, r1, c0, c1);
+    }
+    *x = c0; *y = r0; *win_w = c1 - c0; *win_h = r1 - r0;
+    return SLIMG_OK;
 }
 
 int32_t slimg_b200_pipeline_batch_host(const slimg_image *in, uint32_t n, const slimg_pipeline_options *opts, int order,

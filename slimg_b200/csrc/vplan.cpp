@@ -23,6 +23,7 @@ constexpr int kFrac = 7;        // fractional bits of the 16-bit intermediate
 constexpr int kOffset = 64;     // added to the intermediate so Lanczos undershoot stays >= 0
 constexpr int kPrefetchRows = 64;   // a whole group's worth of new rows must be in flight while the previous group computes
 constexpr int kMaxCh = 4;          // chunk stride of the fragment tables (the kernel's NCH1 / NCH2)
+constexpr double kLookGroups = 2.0;  // ring depth wanted beyond the current band, in groups of 8 output rows
 constexpr size_t kSmemBudget = 227 * 1024 - 2048;
 const int kPerm[4] = {0, 2, 1, 3};   // k-slot -> pixel inside a 4-pixel block (k2_vfirst.cu, pass-1 epilogue)
 
@@ -228,7 +229,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     const char *early_env = std::getenv("SLIMG_B200_EARLY_GO");
     const char *unit_env = std::getenv("SLIMG_B200_UNIT");
     const char *vbufs_env = std::getenv("SLIMG_B200_VBUFS");
-    out.vbufs = vbufs_env ? uint32_t(std::min(kVfMaxVBufs, std::max(2, std::atoi(vbufs_env)))) : 3u;
+    out.vbufs = vbufs_env ? uint32_t(std::min(kVfMaxVBufs, std::max(2, std::atoi(vbufs_env)))) : 4u;
     uint32_t cols = 0;
     int unit = 0;
     bool early = false;
@@ -246,6 +247,14 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         }
         return std::max<int64_t>(worst, 8 * kMaxCh);
     };
+    // Widest strips whose ring still runs `kLookGroups` groups ahead of the band being filtered: the ring is refilled
+    // once per group, so a shallow ring leaves too few bytes in flight however wide the strip is (measured on B200:
+    // 7.5x downscale 16 columns beat 24, 5x 32 beat 40, 4x the widest won).  Falls back to the widest that fits.
+    const double rows_per_group = 8.0 * double(g.vh) / double(g.Rh);
+    const char *ring_env = std::getenv("SLIMG_B200_RING_STEPS");
+    const uint32_t ring_cap = std::min(512u, ring_env ? uint32_t(std::atoi(ring_env)) * 16 : 512u);
+    uint32_t fb_cols = 0, fb_ring = 0; int fb_unit = 0; bool fb_early = false;      // fallback: widest fitting candidate
+    uint32_t ring_rows = 0;
     for (uint32_t cand = 64; cand >= 8 && cols == 0; cand -= 8) {
         if (cols_env && uint32_t(std::atoi(cols_env)) != cand) continue;
         // even the strips out first (keeps the multiple of 8)
@@ -262,23 +271,23 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         if (!best_u) continue;
         uint32_t pch, pv;
         const bool want_early = !(early_env && early_env[0] == '0');
-        if (want_early && smem_for(best_blk, ring_early, pch, pv) <= kSmemBudget) { cols = even; unit = best_u; early = true; }
-        else if (smem_for(best_blk, ring_min, pch, pv) <= kSmemBudget) { cols = even; unit = best_u; early = false; }
+        bool fits = false, e = false;
+        if (want_early && smem_for(best_blk, ring_early, pch, pv) <= kSmemBudget) { fits = true; e = true; }
+        else if (smem_for(best_blk, ring_min, pch, pv) <= kSmemBudget) { fits = true; e = false; }
+        if (!fits) continue;
+        // deepen the ring as far as shared memory allows: every extra step is 16 more rows in flight
+        uint32_t rr = e ? ring_early : ring_min;
+        while (rr + 16 <= ring_cap && smem_for(best_blk, rr + 16, pch, pv) <= kSmemBudget) rr += 16;
+        if (!fb_cols) { fb_cols = even; fb_ring = rr; fb_unit = best_u; fb_early = e; }
+        const double look = (double(rr) - 32.0 * out.nch1) / rows_per_group;
+        if (look >= kLookGroups || cols_env) { cols = even; unit = best_u; early = e; ring_rows = rr; }
     }
+    if (cols == 0) { cols = fb_cols; unit = fb_unit; early = fb_early; ring_rows = fb_ring; }
     if (cols == 0) return;
     out.unit = unit;
     out.early_go = early;
-    out.ring_rows = early ? ring_early : ring_min;
+    out.ring_rows = ring_rows;
     if (out.ring_rows / 16 > 32) return;                          // k2_vfirst.cu kMaxSteps
-    {
-        // deepen the ring as far as shared memory allows: every extra step is 16 more rows in flight
-        int unused;
-        const int64_t blk = max_padded(cols, unit, unused);
-        const char *ring_env = std::getenv("SLIMG_B200_RING_STEPS");
-        const uint32_t cap = ring_env ? uint32_t(std::atoi(ring_env)) * 16 : 512u;
-        uint32_t pch, pv;
-        while (out.ring_rows + 16 <= std::min(cap, 512u) && smem_for(blk, out.ring_rows + 16, pch, pv) <= kSmemBudget) out.ring_rows += 16;
-    }
     out.n_strips = (g.pw + cols - 1) / cols;
 
     out.strip_col0.assign(out.n_strips + 1, 0);

@@ -72,3 +72,19 @@ def test_no_cpu_fallback():
     with pytest.raises(ll.SlimgError.Image, match="no CUDA device"):
         ll.crop(ll.ImageData(10, 8, bytes(320)), ll.CropMode.REGION(0, 0, 5, 4))
     assert ll.kernel_launches() == 0
+
+
+def test_source_window_is_what_the_taps_read():
+    """slimg_b200_pipeline_source_window: the rows / columns behind the kept output rectangle (host arithmetic)."""
+    # C3 chain order: Width(800) -> 800x533, crop 16:9 keeps rows 41..490, Lanczos3 window of those rows (bench.py)
+    o = ll.make_options(resize=ll.ResizeMode.WIDTH(800), crop=ll.CropMode.ASPECT_RATIO(16, 9),
+                        extend=ll.ExtendMode.ASPECT_RATIO(1, 1))
+    x, y, w, h = ll.pipeline_source_window(6000, 4000, o, ll.ORDER_CHAIN)
+    assert (x, w) == (0, 6000) and 3400 < h < 3440 and y > 250
+    # convert order: crop 16:9 of 6000x4000 is (0,312,6000,3375); the resize reads exactly that rectangle
+    assert ll.pipeline_source_window(6000, 4000, o, ll.ORDER_CONVERT) == (0, 312, 6000, 3375)
+    # crop only: the crop region itself (crop.rs:45-66)
+    o = ll.make_options(crop=ll.CropMode.REGION(10, 20, 30, 40))
+    assert ll.pipeline_source_window(100, 100, o, ll.ORDER_CONVERT) == (10, 20, 30, 40)
+    # no stage: the whole image
+    assert ll.pipeline_source_window(64, 48, ll.make_options(), ll.ORDER_CONVERT) == (0, 0, 64, 48)
