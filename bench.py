@@ -226,7 +226,7 @@ def main():
     import ctypes as C
     import torch
     import torch.distributed as dist
-    from slimg_b200 import _lowlevel as ll
+    from slimg_b200 import _lowlevel as ll, _shard
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py --impl b200 needs a CUDA device (no CPU fallback)")
@@ -270,12 +270,9 @@ def main():
     barrier()
     ms = ev0.elapsed_time(ev1)
     launches = ll.kernel_launches() - launches0
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
+    ms_max = _shard.max_over_ranks(ms, device="cuda")
     clocks = sampler.stop() if rank == 0 else None
-    value = world * B * args.steps * MPX_PER_IMAGE / (ms_max * 1e-3)
+    value = _shard.whole_job_throughput(B * args.steps * MPX_PER_IMAGE, world, ms_max * 1e-3)
 
     # roofline of the (single) kernel of the step, from this rank's own launches
     peak, peak_kind = measured_peak_gbs()
@@ -326,10 +323,7 @@ def main():
             e2e_step()
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
-        t = torch.tensor([dt], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_value = world * nb * e2e_steps * MPX_PER_IMAGE / float(t.item())
+        e2e_value = _shard.whole_job_throughput(nb * e2e_steps * MPX_PER_IMAGE, world, _shard.max_over_ranks(dt, device="cuda"))
         checksum = int(np.ctypeslib.as_array(C.cast(pin_out, C.POINTER(C.c_uint8)), shape=(nb * out_bytes,))[::4097].sum())
         e2e = {"value": e2e_value, "unit": "Mpx/s", "h2d_bytes_per_step": nb * h2d_bytes, "d2h_bytes_per_step": nb * out_bytes,
                "host_image_bytes_per_step": nb * in_bytes,

@@ -252,6 +252,49 @@ def ref_jpeg_frontend(img: np.ndarray, qt_luma: np.ndarray, qt_chroma: np.ndarra
     return y, cb, cr
 
 
+def ref_jpeg_encode(img: np.ndarray, qt_luma: np.ndarray, qt_chroma: np.ndarray) -> bytes:
+    """The JPEG byte stream the real libjpeg-turbo writes for this image (baseline, optimised Huffman tables)."""
+    r = ref_lib()
+    if r is None:
+        raise FileNotFoundError(_REF_PATH)
+    img = _as_rgba(img)
+    h, w = img.shape[:2]
+    ql = np.ascontiguousarray(qt_luma, np.uint16); qc = np.ascontiguousarray(qt_chroma, np.uint16)
+    out, size = C.POINTER(C.c_ubyte)(), C.c_ulong()
+    r.ljt_encode(_ptr(img, _u8p), C.c_uint32(w), C.c_uint32(h), _ptr(ql, _u16p), _ptr(qc, _u16p), C.byref(out), C.byref(size))
+    data = C.string_at(out, size.value)
+    r.ljt_free(out)
+    return data
+
+
+def ref_jpeg_write_coefficients(y, cb, cr, w: int, h: int, qt_luma, qt_chroma, progressive: bool = False) -> bytes:
+    """hand quantised coefficients (from the CUDA front end) to the reference family's entropy
+    coder with jpeg_write_coefficients (jctrans.c:43); returns the JPEG byte stream."""
+    r = ref_lib()
+    if r is None:
+        raise FileNotFoundError(_REF_PATH)
+    y = np.ascontiguousarray(y, np.int16); cb = np.ascontiguousarray(cb, np.int16); cr = np.ascontiguousarray(cr, np.int16)
+    ql = np.ascontiguousarray(qt_luma, np.uint16); qc = np.ascontiguousarray(qt_chroma, np.uint16)
+    out, size = C.POINTER(C.c_ubyte)(), C.c_ulong()
+    r.ljt_write_coefficients(_ptr(y, _i16p), _ptr(cb, _i16p), _ptr(cr, _i16p), C.c_uint32(w), C.c_uint32(h),
+                             _ptr(ql, _u16p), _ptr(qc, _u16p), C.c_int(1 if progressive else 0), C.byref(out), C.byref(size))
+    data = C.string_at(out, size.value)
+    r.ljt_free(out)
+    return data
+
+
+def ref_jpeg_decode(jpg: bytes, w: int, h: int) -> np.ndarray:
+    r = ref_lib()
+    if r is None:
+        raise FileNotFoundError(_REF_PATH)
+    out = np.empty((h, w, 4), np.uint8)
+    ow, oh = C.c_uint32(), C.c_uint32()
+    rc = r.ljt_decode_rgba(jpg, C.c_ulong(len(jpg)), C.byref(ow), C.byref(oh), _ptr(out, _u8p), C.c_size_t(out.nbytes))
+    if rc or (ow.value, oh.value) != (w, h):
+        raise ValueError(f"decoded {ow.value}x{oh.value}, expected {w}x{h}")
+    return out
+
+
 def ref_jpeg_quant_table(quality: int, which: int) -> np.ndarray:
     r = ref_lib()
     if r is None:

@@ -107,3 +107,72 @@ int ljt_frontend(const uint8_t *rgba, uint32_t w, uint32_t h,
     free(buf);
     return 0;
 }
+
+/* The hand-off SURVEY.md 8(f1) names: quantised coefficients computed elsewhere (the CUDA front end) go straight
+ * to the reference family's entropy coder with jpeg_write_coefficients (jctrans.c:43) -- colour conversion,
+ * downsampling, DCT and quantisation are skipped, Huffman optimisation and (optionally) the progressive scan
+ * script run as usual.  Planes are laid out as ljt_frontend returns them.  With progressive == 0 the byte stream
+ * must equal ljt_encode's for the same image and tables. */
+int ljt_write_coefficients(const int16_t *y, const int16_t *cb, const int16_t *cr, uint32_t w, uint32_t h,
+                           const uint16_t qt_luma[64], const uint16_t qt_chroma[64], int progressive,
+                           unsigned char **out, unsigned long *out_size)
+{
+    struct jpeg_compress_struct cinfo;
+    struct jpeg_error_mgr jerr;
+    cinfo.err = jpeg_std_error(&jerr);
+    jpeg_create_compress(&cinfo);
+    *out = NULL; *out_size = 0;
+    jpeg_mem_dest(&cinfo, out, out_size);
+    cinfo.image_width = w;
+    cinfo.image_height = h;
+    cinfo.input_components = 3;
+    cinfo.in_color_space = JCS_RGB;
+    jpeg_set_defaults(&cinfo);               /* YCbCr, 2x2 / 1x1 / 1x1 (jcparam.c:365-373) */
+    put_table(&cinfo, 0, qt_luma);
+    put_table(&cinfo, 1, qt_chroma);
+    cinfo.optimize_coding = TRUE;
+    if (progressive) jpeg_simple_progression(&cinfo);
+
+    /* MCU-padded block counts, as jcmaster.c:137-171 / jccoefct.c size the full-image buffers */
+    const unsigned cw = (w + 15) / 16, chh = (h + 15) / 16;
+    const unsigned WB[3] = { cw * 2, cw, cw }, HB[3] = { chh * 2, chh, chh };
+    const int vs[3] = { 2, 1, 1 };
+    jvirt_barray_ptr arrays[3];
+    for (int ci = 0; ci < 3; ci++)
+        arrays[ci] = (*cinfo.mem->request_virt_barray)((j_common_ptr)&cinfo, JPOOL_IMAGE, FALSE, WB[ci], HB[ci], vs[ci]);
+    jpeg_write_coefficients(&cinfo, arrays);  /* realises the arrays; they are read at jpeg_finish_compress */
+    const int16_t *src[3] = { y, cb, cr };
+    for (int ci = 0; ci < 3; ci++)
+        for (unsigned by = 0; by < HB[ci]; by++) {
+            JBLOCKARRAY rows = (*cinfo.mem->access_virt_barray)((j_common_ptr)&cinfo, arrays[ci], by, 1, TRUE);
+            for (unsigned bx = 0; bx < WB[ci]; bx++)
+                for (int k = 0; k < 64; k++)
+                    rows[0][bx][k] = src[ci][((size_t)by * WB[ci] + bx) * 64 + k];
+        }
+    jpeg_finish_compress(&cinfo);
+    jpeg_destroy_compress(&cinfo);
+    return 0;
+}
+
+/* Decodes a JPEG byte stream to RGBA (alpha 255) with the same library: used to check that a stream written
+ * from hand-off coefficients is a valid image of the right size.  out must hold w*h*4 bytes. */
+int ljt_decode_rgba(const unsigned char *jpg, unsigned long size, uint32_t *w, uint32_t *h, uint8_t *out, size_t out_cap)
+{
+    struct jpeg_decompress_struct d;
+    struct jpeg_error_mgr jerr;
+    d.err = jpeg_std_error(&jerr);
+    jpeg_create_decompress(&d);
+    jpeg_mem_src(&d, jpg, size);
+    jpeg_read_header(&d, TRUE);
+    d.out_color_space = JCS_EXT_RGBA;
+    jpeg_start_decompress(&d);
+    *w = d.output_width; *h = d.output_height;
+    if ((size_t)d.output_width * d.output_height * 4 > out_cap) { jpeg_destroy_decompress(&d); return 1; }
+    while (d.output_scanline < d.output_height) {
+        JSAMPROW row = (JSAMPROW)(out + (size_t)d.output_scanline * d.output_width * 4);
+        jpeg_read_scanlines(&d, &row, 1);
+    }
+    jpeg_finish_decompress(&d);
+    jpeg_destroy_decompress(&d);
+    return 0;
+}

@@ -9,8 +9,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libslimg_b200.so")
-SOURCES = ["geometry.cpp", "taps.cpp", "fastplan.cpp", "vplan.cpp", "tcplan.cpp", "k1_remap.cu", "k2_resize.cu", "k2_fast.cu", "k2_vfirst.cu", "k2_tc.cu", "k3_jpeg.cu", "api.cu"]
-HEADERS = ["host.h", "kernels.cuh", os.path.join("..", "..", "include", "slimg_b200.h")]
+SOURCES = ["geometry.cpp", "taps.cpp", "fastplan.cpp", "vplan.cpp", "tcplan.cpp", "k1_remap.cu", "k2_resize.cu", "k2_fast.cu", "k2_vfirst.cu", "k2_tc.cu", "k3_jpeg.cu", "api.cu", "uniffi_abi.cpp"]
+HEADERS = ["host.h", "kernels.cuh", os.path.join("..", "..", "include", "slimg_b200.h"),
+           os.path.join("..", "..", "include", "slimg_uniffi.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -242,6 +242,20 @@ def test_jpeg_frontend_bit_exact(w, h, q, base):
         assert np.array_equal(g, wv), f"{name}: {np.count_nonzero(g != wv)} coefficients differ"
 
 
+@pytest.mark.skipif(oracle.ref_lib() is None, reason="oracle/_ref not built")
+@pytest.mark.parametrize("w,h", [(53, 37), (640, 481), (1920, 1080)])
+def test_jpeg_coefficients_feed_the_reference_entropy_coder(w, h):
+    """the GPU front end's coefficients go to libjpeg-turbo's entropy coder through
+    jpeg_write_coefficients (jctrans.c:43); the JPEG file is byte-identical to the one the full CPU encoder writes."""
+    img = noise_image(w, h, 17)
+    ql, qc = oracle.ref_jpeg_quant_table(70, 0), oracle.ref_jpeg_quant_table(70, 1)
+    y, cb, cr = _planes(*ll.jpeg_frontend(_ll_img(img), list(ql), list(qc)))
+    got = oracle.ref_jpeg_write_coefficients(y, cb, cr, w, h, ql, qc)
+    assert got == oracle.ref_jpeg_encode(img, ql, qc)
+    prog = oracle.ref_jpeg_write_coefficients(y, cb, cr, w, h, ql, qc, progressive=True)       # codec/jpeg.rs:61
+    assert oracle.ref_jpeg_decode(prog, w, h).shape == (h, w, 4)
+
+
 # ---- batched device-resident entry points (what bench.py times) ---------------------------------------
 
 def test_batch_device_matches_single_image_calls():

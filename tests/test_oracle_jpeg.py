@@ -53,3 +53,17 @@ def test_frontend_matches_real_libjpeg_turbo(w, h):
         assert np.array_equal(ql, oracle.ref_jpeg_quant_table(q, 0))
         for a, b in zip(oracle.jpeg_frontend(img, ql, qc), oracle.ref_jpeg_frontend(img, ql, qc)):
             assert np.array_equal(a, b)
+
+
+@pytest.mark.skipif(oracle.ref_lib() is None, reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("w,h", [(16, 16), (53, 37), (129, 65)])
+def test_coefficient_handoff_writes_the_same_jpeg(w, h):
+    """coefficients handed to the entropy coder with jpeg_write_coefficients (jctrans.c:43) give
+    the byte stream the full encoder writes -- the front end can be replaced without the file changing."""
+    img = noise_image(w, h, 5)
+    ql, qc = oracle.ref_jpeg_quant_table(70, 0), oracle.ref_jpeg_quant_table(70, 1)
+    y, cb, cr = oracle.jpeg_frontend(img, ql, qc)
+    assert oracle.ref_jpeg_write_coefficients(y, cb, cr, w, h, ql, qc) == oracle.ref_jpeg_encode(img, ql, qc)
+    prog = oracle.ref_jpeg_write_coefficients(y, cb, cr, w, h, ql, qc, progressive=True)     # codec/jpeg.rs:61
+    assert prog[:3] == b"\xff\xd8\xff"
+    assert np.array_equal(oracle.ref_jpeg_decode(prog, w, h), oracle.ref_jpeg_decode(oracle.ref_jpeg_encode(img, ql, qc), w, h))
