@@ -498,7 +498,7 @@ static void build_quant(const uint16_t ql[64], const uint16_t qc[64], QuantDev &
             if (fr == 0) { fq >>= 1; r--; }
             else if (fr <= divisor / 2u) c++;
             else fq++;
-            q.recip[k][i] = uint32_t(fq); q.corr[k][i] = c; q.shift[k][i] = uint8_t(r);
+            q.recip[k][i] = uint32_t(fq); q.corr[k][i] = c; q.shift32[k][i] = uint32_t(r - 32);
         }
 }
 

@@ -11,24 +11,32 @@
 //   convsamp / islow FDCT / quantize   jcdctmgr.c:373-438, jfdctint.c:143-286
 //   dummy blocks         jccoefct.c:286-319
 //
-// One CTA = kMcus consecutive MCUs (16x16 pixels each) of one MCU row: 4 Y blocks + Cb + Cr per
-// MCU.  Stage 1 converts the 16 x (16*kMcus) pixel strip into Y / Cb / Cr sample tiles in shared
-// memory; stage 2 runs the row DCTs, stage 3 the column DCTs + quantisation, stage 4 patches the
-// dummy blocks and streams the coefficients out 16 bytes per thread.
+// One CTA = up to kMcus consecutive MCUs (16x16 pixels each) of one MCU row: 4 Y blocks + Cb + Cr per MCU.
+//   stage 1  every thread converts patches of 4 x 2 pixels (two 16-byte loads): 8 Y samples go to the Y tile as two
+//            packed words, the 2 x 2 chroma averages (bias 1,2) straight to the half-resolution Cb / Cr tiles --
+//            the full-resolution chroma planes of the reference never exist
+//   stage 2  ONE THREAD PER 8x8 BLOCK, the whole block in registers: 8 row DCTs, 8 column DCTs, reciprocal
+//            quantisation with the tables as constant-bank immediates (warps are homogeneous: 4 warps of Y blocks,
+//            one of Cb, one of Cr), dummy-block patch through a 192-entry DC table, 8 x 16-byte stores
+// No DCT workspace in shared memory, two CTA barriers in all.
 //
-// Roofline: HBM.  Algorithmic bytes per image = w*h*4 read + (Y_HB*Y_WB + 2*C_HB*C_WB)*128 written.
+// Roofline: nominally HBM (w*h*4 read + (Y_HB*Y_WB + 2*C_HB*C_WB)*128 written = 7 B/px), but at ~45 integer
+// operations per pixel the kernel sits just above the INT32 ridge of the B200 (37 Tops / 6.55 TB/s = 5.7 op/B
+// against 6.4 op/B): the ALU pipe bounds it.
+#include <algorithm>
+#include <cstdlib>
+
 #include "kernels.cuh"
 
 namespace slimg {
 
 namespace {
 
-constexpr int kMcus = 8;                        // MCUs per CTA
-constexpr int kStripW = 16 * kMcus;             // 128 pixels
+constexpr int kMcus = 32;                       // MCUs per CTA
+constexpr int kStripW = 16 * kMcus;             // 512 pixels
 constexpr int kThreads = 256;
 constexpr int kBlocksY = 4 * kMcus, kBlocksC = kMcus;
-constexpr int kBlocks = kBlocksY + 2 * kBlocksC;  // 48 blocks per CTA
-constexpr int kWsStride = 72;                   // 64 + 8 ints: column pass is bank-conflict free
+constexpr int kBlocks = kBlocksY + 2 * kBlocksC;  // 192 blocks per CTA, one thread each
 
 #define SLIMG_FIX(x) int((x) * 65536.0 + 0.5)
 
@@ -70,138 +78,367 @@ __device__ __forceinline__ void fdct8(const int in[8], int out[8]) {
 }
 
 struct Smem {
-    uint8_t ys[16][kStripW];          // Y samples
-    uint8_t cbf[16][kStripW];         // full-resolution Cb / Cr (chroma row mapping)
-    uint8_t crf[16][kStripW];
-    int ws[kBlocks * kWsStride];      // DCT workspace
-    int16_t coef[kBlocks][64];        // quantised coefficients
-    uint32_t recip[2][64], corr[2][64];
-    uint8_t shift[2][64];
+    uint32_t ys[16][kStripW / 4];     // Y samples, 4 per word
+    uint16_t cb[8][kStripW / 4];      // downsampled Cb / Cr, 2 per halfword (one halfword per stage-1 patch)
+    uint16_t cr[8][kStripW / 4];
+    int16_t dc[kBlocksY];             // quantised DC of every Y block (dummy-block patch)
 };
 
-__global__ void __launch_bounds__(kThreads) jpeg_frontend_kernel(const JpegParams p) {
+__device__ __forceinline__ void ycc3(uint32_t px, int &y, int &cb, int &cr) {
+    uint8_t a, b, c;
+    rgb_to_ycc(px, a, b, c);
+    y = a; cb = b; cr = c;
+}
+
+// reciprocal quantisation of one coefficient (jcdctmgr.c:408-438); shift >= 34 always (divisor = q << 3 >= 8), so
+// the 64-bit product >> shift is the high word >> (shift - 32)
+template <int TBL, int IDX>
+__device__ __forceinline__ int quant1(const JpegParams &p, int t) {
+    const uint32_t a = uint32_t(t < 0 ? -t : t) + p.q.corr[TBL][IDX];
+    const uint32_t q = __umulhi(a, p.q.recip[TBL][IDX]) >> p.q.shift32[TBL][IDX];
+    return t < 0 ? -int(q) : int(q);
+}
+
+template <int TBL, int K>
+__device__ __forceinline__ void quant_row(const JpegParams &p, int (&b)[8][8]) {
+    b[K][0] = quant1<TBL, K * 8 + 0>(p, b[K][0]); b[K][1] = quant1<TBL, K * 8 + 1>(p, b[K][1]);
+    b[K][2] = quant1<TBL, K * 8 + 2>(p, b[K][2]); b[K][3] = quant1<TBL, K * 8 + 3>(p, b[K][3]);
+    b[K][4] = quant1<TBL, K * 8 + 4>(p, b[K][4]); b[K][5] = quant1<TBL, K * 8 + 5>(p, b[K][5]);
+    b[K][6] = quant1<TBL, K * 8 + 6>(p, b[K][6]); b[K][7] = quant1<TBL, K * 8 + 7>(p, b[K][7]);
+}
+
+// forward DCT (jpeg_fdct_islow: rows, then columns) and quantisation of the block held in b[row][col]
+template <int TBL>
+__device__ __forceinline__ void fdct_quant(const JpegParams &p, int (&b)[8][8]) {
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        int out[8];
+        fdct8<1>(b[r], out);
+#pragma unroll
+        for (int k = 0; k < 8; k++) b[r][k] = out[k];
+    }
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        int in[8], out[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) in[k] = b[k][c];
+        fdct8<2>(in, out);
+#pragma unroll
+        for (int k = 0; k < 8; k++) b[k][c] = out[k];
+    }
+    quant_row<TBL, 0>(p, b); quant_row<TBL, 1>(p, b); quant_row<TBL, 2>(p, b); quant_row<TBL, 3>(p, b);
+    quant_row<TBL, 4>(p, b); quant_row<TBL, 5>(p, b); quant_row<TBL, 6>(p, b); quant_row<TBL, 7>(p, b);
+}
+
+__device__ __forceinline__ void unpack8(uint32_t lo, uint32_t hi, int (&row)[8]) {
+    row[0] = int(lo & 0xff) - 128; row[1] = int((lo >> 8) & 0xff) - 128; row[2] = int((lo >> 16) & 0xff) - 128; row[3] = int(lo >> 24) - 128;
+    row[4] = int(hi & 0xff) - 128; row[5] = int((hi >> 8) & 0xff) - 128; row[6] = int((hi >> 16) & 0xff) - 128; row[7] = int(hi >> 24) - 128;
+}
+
+__device__ __forceinline__ void store_block(int16_t *d, const int (&b)[8][8]) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        uint4 v;
+        v.x = (uint32_t(b[k][0]) & 0xffffu) | (uint32_t(b[k][1]) << 16);
+        v.y = (uint32_t(b[k][2]) & 0xffffu) | (uint32_t(b[k][3]) << 16);
+        v.z = (uint32_t(b[k][4]) & 0xffffu) | (uint32_t(b[k][5]) << 16);
+        v.w = (uint32_t(b[k][6]) & 0xffffu) | (uint32_t(b[k][7]) << 16);
+        *reinterpret_cast<uint4 *>(d + k * 8) = v;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 2) jpeg_frontend_kernel(const __grid_constant__ JpegParams p) {
     __shared__ Smem sm;
     const int tid = threadIdx.x;
     const uint32_t *src = reinterpret_cast<const uint32_t *>(p.src + size_t(blockIdx.z) * p.src_img_bytes);
     const int mx0 = blockIdx.x * kMcus, my = blockIdx.y;
+    const int nm = min(kMcus, int(p.c_wb) - mx0);          // MCUs of this CTA
     const int x0 = mx0 * 16, y0 = my * 16;
     const int w = int(p.w), h = int(p.h);
     const int creal = (h + 1) / 2;   // chroma rows that come from real downsampling
+    const bool vec_ok = (w & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0;
 
-    for (int i = tid; i < 128; i += kThreads) {
-        sm.recip[0][i] = p.q.recip[0][i]; sm.corr[0][i] = p.q.corr[0][i]; sm.shift[0][i] = p.q.shift[0][i];
-    }
-
-    // stage 1: colour conversion with edge replication.  Y uses row min(y, h-1).  Chroma row cy
-    // past creal-1 repeats the last DOWNSAMPLED row (jcprepct.c:174-183), so its two source
-    // rows are those of row creal-1, which differ from the Y mapping when h is even.
-    for (int i = tid; i < 16 * kStripW; i += kThreads) {
-        const int r = i / kStripW, c = i - r * kStripW;
-        const int sx = min(x0 + c, w - 1);
-        const int yy = y0 + r;
-        const int sy = min(yy, h - 1);
-        const int cyy = min(yy >> 1, creal - 1);
-        const int scy = min(2 * cyy + (yy & 1), h - 1);
-        uint8_t yv, cb, cr;
-        rgb_to_ycc(__ldg(src + size_t(sy) * w + sx), yv, cb, cr);
-        sm.ys[r][c] = yv;
-        if (scy != sy) {
-            uint8_t y2;
-            rgb_to_ycc(__ldg(src + size_t(scy) * w + sx), y2, cb, cr);
-        }
-        sm.cbf[r][c] = cb; sm.crf[r][c] = cr;
-    }
-    __syncthreads();
-
-    // stage 2: row DCTs.  Block order in the CTA: Y blocks [by2][bx] (by2 = 0,1; bx = 0..2*kMcus-1),
-    // then Cb blocks, then Cr blocks.  Chroma rows are downsampled on the fly (h2v2, bias 1,2,..).
-    for (int i = tid; i < kBlocks * 8; i += kThreads) {
-        const int b = i >> 3, r = i & 7;
-        int in[8], out[8];
-        if (b < kBlocksY) {
-            const int by2 = b / (2 * kMcus), bx = b - by2 * (2 * kMcus);
-            const uint8_t *s = &sm.ys[by2 * 8 + r][bx * 8];
+    // stage 1: colour conversion with edge replication.  Y uses row min(y, h-1).  Chroma row cy past creal-1 repeats
+    // the last DOWNSAMPLED row (jcprepct.c:174-183), so its two source rows are those of row creal-1, which differ
+    // from the Y mapping only below the image.
+    for (int i = tid; i < 8 * (kStripW / 4); i += kThreads) {
+        const int pr = i / (kStripW / 4), pc = i - pr * (kStripW / 4);
+        if (pc * 4 >= nm * 16) continue;
+        const int x = x0 + 4 * pc;
+        const int yy0 = y0 + 2 * pr;
+        const int sy[2] = {min(yy0, h - 1), min(yy0 + 1, h - 1)};
+        const int cyy = min(yy0 >> 1, creal - 1);
+        const int sc[2] = {min(2 * cyy, h - 1), min(2 * cyy + 1, h - 1)};
+        uint32_t px[2][4];
 #pragma unroll
-            for (int k = 0; k < 8; k++) in[k] = int(s[k]) - 128;
-        } else {
-            const bool is_cr = b >= kBlocksY + kBlocksC;
-            const int bx = b - kBlocksY - (is_cr ? kBlocksC : 0);
-            const uint8_t(*f)[kStripW] = is_cr ? sm.crf : sm.cbf;
-            const uint8_t *s0 = &f[2 * r][bx * 16], *s1 = &f[2 * r + 1][bx * 16];
+        for (int r = 0; r < 2; r++) {
+            const uint32_t *row = src + size_t(sy[r]) * w;
+            if (vec_ok && x + 3 < w) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4 *>(row + x));
+                px[r][0] = v.x; px[r][1] = v.y; px[r][2] = v.z; px[r][3] = v.w;
+            } else {
 #pragma unroll
-            for (int k = 0; k < 8; k++) {
-                const int bias = 1 + (k & 1);
-                in[k] = ((int(s0[2 * k]) + int(s0[2 * k + 1]) + int(s1[2 * k]) + int(s1[2 * k + 1]) + bias) >> 2) - 128;
+                for (int k = 0; k < 4; k++) px[r][k] = __ldg(row + min(x + k, w - 1));
             }
         }
-        fdct8<1>(in, out);
-        int *d = &sm.ws[b * kWsStride + r * 8];
+        int yv[2][4], cbv[2][4], crv[2][4];
 #pragma unroll
-        for (int k = 0; k < 8; k++) d[k] = out[k];
-    }
-    __syncthreads();
-
-    // stage 3: column DCTs + quantisation (jcdctmgr.c:408-438, reciprocal form)
-    for (int i = tid; i < kBlocks * 8; i += kThreads) {
-        const int b = i >> 3, c = i & 7;
-        const int tbl = b < kBlocksY ? 0 : 1;
-        int in[8], out[8];
-        const int *s = &sm.ws[b * kWsStride + c];
+        for (int r = 0; r < 2; r++)
 #pragma unroll
-        for (int k = 0; k < 8; k++) in[k] = s[k * 8];
-        fdct8<2>(in, out);
+            for (int k = 0; k < 4; k++) ycc3(px[r][k], yv[r][k], cbv[r][k], crv[r][k]);
+        if (sc[0] != sy[0] || sc[1] != sy[1]) {            // below the image: chroma comes from other rows than Y
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
-            const int idx = k * 8 + c;
-            const int t = out[k];
-            const uint32_t a = uint32_t(t < 0 ? -t : t) + sm.corr[tbl][idx];
-            const uint32_t q = uint32_t((uint64_t(a) * sm.recip[tbl][idx]) >> sm.shift[tbl][idx]);
-            sm.coef[b][idx] = int16_t(t < 0 ? -int(q) : int(q));
+            for (int r = 0; r < 2; r++)
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    int unused;
+                    ycc3(__ldg(src + size_t(sc[r]) * w + min(x + k, w - 1)), unused, cbv[r][k], crv[r][k]);
+                }
         }
+#pragma unroll
+        for (int r = 0; r < 2; r++)
+            sm.ys[2 * pr + r][pc] = uint32_t(yv[r][0]) | (uint32_t(yv[r][1]) << 8) | (uint32_t(yv[r][2]) << 16) | (uint32_t(yv[r][3]) << 24);
+        // h2v2_downsample (jcsample.c:272-284): bias 1 for even output columns, 2 for odd ones
+        const int cb0 = (cbv[0][0] + cbv[0][1] + cbv[1][0] + cbv[1][1] + 1) >> 2, cb1 = (cbv[0][2] + cbv[0][3] + cbv[1][2] + cbv[1][3] + 2) >> 2;
+        const int cr0 = (crv[0][0] + crv[0][1] + crv[1][0] + crv[1][1] + 1) >> 2, cr1 = (crv[0][2] + crv[0][3] + crv[1][2] + crv[1][3] + 2) >> 2;
+        sm.cb[pr][pc] = uint16_t(cb0 | (cb1 << 8));
+        sm.cr[pr][pc] = uint16_t(cr0 | (cr1 << 8));
     }
     __syncthreads();
 
-    // stage 4a: dummy Y blocks (jccoefct.c:286-294 right edge, :301-319 bottom rows): AC = 0,
-    // DC = the DC of the last real block to the left / of the MCU's last block in the row above.
-    const int ybx0 = mx0 * 2, yby0 = my * 2;
-    for (int i = tid; i < kBlocksY * 64; i += kThreads) {
-        const int b = i >> 6, k = i & 63;
-        const int by2 = b / (2 * kMcus), bx = b - by2 * (2 * kMcus);
-        const int gbx = ybx0 + bx, gby = yby0 + by2;
-        if (gbx >= int(p.y_WB)) continue;
-        const bool dummy_right = gbx >= int(p.y_wb), dummy_bottom = gby >= int(p.y_hb);
-        if (!dummy_right && !dummy_bottom) continue;
-        int16_t v = 0;
-        if (k == 0) {
-            int sb_x = bx, sb_y = by2;
-            if (dummy_bottom) { sb_y = by2 - 1; sb_x = bx | 1; }               // last block of this MCU, row above
-            if (ybx0 + sb_x >= int(p.y_wb)) sb_x = int(p.y_wb) - 1 - ybx0;      // which may itself be a right-edge dummy
-            v = sm.coef[sb_y * (2 * kMcus) + sb_x][0];
-        }
-        sm.coef[b][k] = v;   // sources are real blocks, never rewritten here: no hazard
-    }
-    __syncthreads();
-
-    // stage 4b: stream out, 16 bytes per thread; a Y block row of the CTA is one contiguous run
+    // stage 2: one thread per block.  Threads [0, 4*kMcus): Y block (by2, bx); then kMcus Cb blocks, kMcus Cr blocks.
     int16_t *yout = p.y + size_t(blockIdx.z) * p.y_img_elems;
     int16_t *cbout = p.cb + size_t(blockIdx.z) * p.c_img_elems;
     int16_t *crout = p.cr + size_t(blockIdx.z) * p.c_img_elems;
-    for (int i = tid; i < kBlocks * 8; i += kThreads) {
-        const int b = i >> 3, part = i & 7;
-        int16_t *d;
-        if (b < kBlocksY) {
-            const int by2 = b / (2 * kMcus), bx = b - by2 * (2 * kMcus);
-            const int gbx = ybx0 + bx, gby = yby0 + by2;
-            if (gbx >= int(p.y_WB) || gby >= int(p.y_HB)) continue;
-            d = yout + (size_t(gby) * p.y_WB + gbx) * 64;
+    const int ybx0 = mx0 * 2, yby0 = my * 2;
+    int b[8][8];
+    const bool is_y = tid < kBlocksY;
+    const int by2 = tid / (2 * kMcus), bx = is_y ? tid - by2 * (2 * kMcus) : (tid - kBlocksY) % kBlocksC;
+    const bool is_cr = tid >= kBlocksY + kBlocksC;
+    const bool active = tid < kBlocks && (is_y ? bx < 2 * nm : bx < nm);
+    if (active) {
+        if (is_y) {
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                const uint2 v = *reinterpret_cast<const uint2 *>(&sm.ys[by2 * 8 + r][bx * 2]);
+                unpack8(v.x, v.y, b[r]);
+            }
+            fdct_quant<0>(p, b);
+            sm.dc[tid] = int16_t(b[0][0]);
         } else {
-            const bool is_cr = b >= kBlocksY + kBlocksC;
-            const int bx = b - kBlocksY - (is_cr ? kBlocksC : 0);
-            const int gbx = mx0 + bx;
-            if (gbx >= int(p.c_wb)) continue;
-            d = (is_cr ? crout : cbout) + (size_t(my) * p.c_wb + gbx) * 64;
+            const uint16_t(*f)[kStripW / 4] = is_cr ? sm.cr : sm.cb;
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                const uint2 v = *reinterpret_cast<const uint2 *>(&f[r][bx * 4]);
+                unpack8(v.x, v.y, b[r]);
+            }
+            fdct_quant<1>(p, b);
         }
-        *reinterpret_cast<uint4 *>(d + part * 8) = *reinterpret_cast<const uint4 *>(&sm.coef[b][part * 8]);
+    }
+    __syncthreads();
+    if (!active) return;
+    if (is_y) {
+        // dummy Y blocks (jccoefct.c:286-294 right edge, :301-319 bottom rows): AC = 0, DC = the DC of the last real
+        // block to the left / of the MCU's last block in the row above
+        const int gbx = ybx0 + bx, gby = yby0 + by2;
+        if (gbx >= int(p.y_WB) || gby >= int(p.y_HB)) return;
+        const bool dummy_right = gbx >= int(p.y_wb), dummy_bottom = gby >= int(p.y_hb);
+        if (dummy_right || dummy_bottom) {
+            int sb_x = bx, sb_y = by2;
+            if (dummy_bottom) { sb_y = by2 - 1; sb_x = bx | 1; }               // last block of this MCU, row above
+            if (ybx0 + sb_x >= int(p.y_wb)) sb_x = int(p.y_wb) - 1 - ybx0;      // which may itself be a right-edge dummy
+            const int dc = sm.dc[sb_y * (2 * kMcus) + sb_x];
+#pragma unroll
+            for (int r = 0; r < 8; r++)
+#pragma unroll
+                for (int k = 0; k < 8; k++) b[r][k] = 0;
+            b[0][0] = dc;
+        }
+        store_block(yout + (size_t(gby) * p.y_WB + gbx) * 64, b);
+    } else {
+        const int gbx = mx0 + bx;
+        store_block((is_cr ? crout : cbout) + (size_t(my) * p.c_wb + gbx) * 64, b);
+    }
+}
+
+// ---- warp-autonomous variant: the production kernel ----------------------------------------------------------------
+// The CTA-wide version above keeps a whole 8x8 block per thread: ~5000 instructions of straight-line code that every
+// warp runs through once per block, so the SM stalls on instruction fetch (ncu: stall_no_instruction ~1 per issue) and
+// on its two CTA barriers (stall_barrier 2.3), and issues at 46 % whatever the memory side does.  Here:
+//   * every WARP owns a tile of kWMcus MCUs (256 x 16 pixels) and runs both stages on it by itself (__syncwarp only);
+//   * stage 2 gives a block to 8 LANES: lane r runs the row DCT of row r, the 8x8 intermediate is transposed through
+//     a padded per-warp scratch (conflict-free 16-byte stores, conflict-free column reads), lane c runs the column DCT
+//     of column c and quantises its 8 coefficients with table entries it keeps in registers.  The loop body is ~250
+//     instructions, shared by all blocks.
+constexpr int kWMcus = 16;
+constexpr int kWW = 16 * kWMcus;                // 256 pixels
+constexpr int kWarpsPerCta = 4;
+constexpr int kRowStride = 12;                  // words between scratch rows: 16-byte chunks of 8 lanes hit distinct banks
+constexpr int kBlkStride = 8 * kRowStride + 8;  // words between the scratch blocks of a warp: column reads of 4 blocks disjoint
+
+struct WarpSmem {
+    // row pitches == 4 words mod 32: the 8 rows a group of lanes reads for one block land in distinct banks
+    uint32_t ys[16][kWW / 4 + 4];     // Y samples, 4 per word
+    uint16_t cb[8][kWW / 4 + 8];      // downsampled Cb / Cr, one halfword (2 samples) per stage-1 patch
+    uint16_t cr[8][kWW / 4 + 8];
+    int scratch[4 * kBlkStride];      // row-pass output of the 4 blocks in flight
+    int16_t dc[2][2 * kWMcus];        // quantised DC of the Y blocks (dummy-block patch)
+};
+
+// row DCT by lane r of the group, transpose through scratch, column DCT + quantisation by lane c; returns the 8
+// coefficients (k, c), k = 0..7, of the block
+__device__ __forceinline__ void block_dct(int *scr, int l8, uint32_t lo, uint32_t hi, const uint32_t (*qt)[64], int (&out)[8]) {
+    int in[8], mid[8];
+    unpack8(lo, hi, in);
+    fdct8<1>(in, mid);
+    *reinterpret_cast<int4 *>(scr + l8 * kRowStride) = make_int4(mid[0], mid[1], mid[2], mid[3]);
+    *reinterpret_cast<int4 *>(scr + l8 * kRowStride + 4) = make_int4(mid[4], mid[5], mid[6], mid[7]);
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 8; k++) in[k] = scr[k * kRowStride + l8];
+    __syncwarp();
+    fdct8<2>(in, mid);
+#pragma unroll
+    for (int k = 0; k < 8; k++) {          // jcdctmgr.c:408-438, reciprocal form; shift >= 34, see build_quant
+        const int t = mid[k];
+        const uint32_t a = uint32_t(t < 0 ? -t : t) + qt[1][k * 8 + l8];
+        const uint32_t q = __umulhi(a, qt[0][k * 8 + l8]) >> qt[2][k * 8 + l8];
+        out[k] = t < 0 ? -int(q) : int(q);
+    }
+}
+
+template <int UNROLL, int MINB>
+__global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_kernel(const __grid_constant__ JpegParams p, const uint32_t n_images) {
+    __shared__ __align__(16) WarpSmem wsm[kWarpsPerCta];
+    const int lane = threadIdx.x & 31, l8 = lane & 7, q4 = lane >> 3;
+    WarpSmem &sm = wsm[threadIdx.x >> 5];
+    int *scr = sm.scratch + q4 * kBlkStride;
+    const int w = int(p.w), h = int(p.h);
+    const int creal = (h + 1) / 2;   // chroma rows that come from real downsampling
+    const bool vec_ok = (w & 3) == 0 && (reinterpret_cast<uintptr_t>(p.src) & 15) == 0 && (p.src_img_bytes & 15) == 0;
+    const uint32_t tiles_x = (p.c_wb + kWMcus - 1) / kWMcus, tiles_img = tiles_x * p.c_hb;
+    const uint64_t n_tiles = uint64_t(tiles_img) * n_images;
+    const uint64_t gw = uint64_t(blockIdx.x) * kWarpsPerCta + (threadIdx.x >> 5), nw = uint64_t(gridDim.x) * kWarpsPerCta;
+
+    // both quantisation tables in shared memory: a lane reads its own column of them (a per-lane index into the
+    // constant bank would serialise, and 48 table registers per lane cost a third of the occupancy)
+    __shared__ uint32_t qt[2][3][64];
+    for (int i = threadIdx.x; i < 128; i += 32 * kWarpsPerCta) {
+        qt[i >> 6][0][i & 63] = p.q.recip[i >> 6][i & 63]; qt[i >> 6][1][i & 63] = p.q.corr[i >> 6][i & 63]; qt[i >> 6][2][i & 63] = p.q.shift32[i >> 6][i & 63];
+    }
+    __syncthreads();
+
+#pragma unroll 1
+    for (uint64_t t = gw; t < n_tiles; t += nw) {
+        const uint32_t z = uint32_t(t / tiles_img), rem = uint32_t(t - uint64_t(z) * tiles_img);
+        const int my = int(rem / tiles_x), mx0 = int(rem - uint32_t(my) * tiles_x) * kWMcus;
+        const int nm = min(kWMcus, int(p.c_wb) - mx0);
+        const int x0 = mx0 * 16, y0 = my * 16;
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(p.src + size_t(z) * p.src_img_bytes);
+
+        // stage 1: colour conversion with edge replication.  Y uses row min(y, h-1).  Chroma row cy past creal-1
+        // repeats the last DOWNSAMPLED row (jcprepct.c:174-183): other source rows than Y, below the image only.
+#pragma unroll(UNROLL)
+        for (int i = lane; i < ((p.debug & 1u) ? 0 : 8 * (kWW / 4)); i += 32) {
+            const int pr = i / (kWW / 4), pc = i - pr * (kWW / 4);
+            if (pc * 4 >= nm * 16) continue;
+            const int x = x0 + 4 * pc;
+            const int yy0 = y0 + 2 * pr;
+            const int sy[2] = {min(yy0, h - 1), min(yy0 + 1, h - 1)};
+            const int cyy = min(yy0 >> 1, creal - 1);
+            const int sc[2] = {min(2 * cyy, h - 1), min(2 * cyy + 1, h - 1)};
+            uint32_t px[2][4];
+#pragma unroll
+            for (int r = 0; r < 2; r++) {
+                const uint32_t *row = src + size_t(sy[r]) * w;
+                if (vec_ok && x + 3 < w) {
+                    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(row + x));
+                    px[r][0] = v.x; px[r][1] = v.y; px[r][2] = v.z; px[r][3] = v.w;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) px[r][k] = __ldg(row + min(x + k, w - 1));
+                }
+            }
+            int yv[2][4], cbv[2][4], crv[2][4];
+#pragma unroll
+            for (int r = 0; r < 2; r++)
+#pragma unroll
+                for (int k = 0; k < 4; k++) ycc3(px[r][k], yv[r][k], cbv[r][k], crv[r][k]);
+            if (sc[0] != sy[0] || sc[1] != sy[1]) {
+#pragma unroll
+                for (int r = 0; r < 2; r++)
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        int unused;
+                        ycc3(__ldg(src + size_t(sc[r]) * w + min(x + k, w - 1)), unused, cbv[r][k], crv[r][k]);
+                    }
+            }
+#pragma unroll
+            for (int r = 0; r < 2; r++)
+                sm.ys[2 * pr + r][pc] = uint32_t(yv[r][0]) | (uint32_t(yv[r][1]) << 8) | (uint32_t(yv[r][2]) << 16) | (uint32_t(yv[r][3]) << 24);
+            // h2v2_downsample (jcsample.c:272-284): bias 1 for even output columns, 2 for odd ones
+            const int cb0 = (cbv[0][0] + cbv[0][1] + cbv[1][0] + cbv[1][1] + 1) >> 2, cb1 = (cbv[0][2] + cbv[0][3] + cbv[1][2] + cbv[1][3] + 2) >> 2;
+            const int cr0 = (crv[0][0] + crv[0][1] + crv[1][0] + crv[1][1] + 1) >> 2, cr1 = (crv[0][2] + crv[0][3] + crv[1][2] + crv[1][3] + 2) >> 2;
+            sm.cb[pr][pc] = uint16_t(cb0 | (cb1 << 8));
+            sm.cr[pr][pc] = uint16_t(cr0 | (cr1 << 8));
+        }
+        __syncwarp();
+
+        // stage 2, Y: 4 blocks per step (one per group of 8 lanes), block rows one after the other
+        int16_t *yout = p.y + size_t(z) * p.y_img_elems;
+        const int ybx0 = mx0 * 2, yby0 = my * 2;
+        const int nby = min(2 * nm, int(p.y_wb) - ybx0);          // real Y block columns of the tile
+        const int nrow = min(2, int(p.y_hb) - yby0);              // real Y block rows
+#pragma unroll 1
+        for (int s = 0; s < ((p.debug & 2u) ? 0 : nrow * (kWMcus / 2)); s++) {
+            const int by2 = s / (kWMcus / 2), bx = (s - by2 * (kWMcus / 2)) * 4 + q4;
+            if ((s - by2 * (kWMcus / 2)) * 4 >= nby) continue;     // warp-uniform: the whole step lies right of the image
+            const uint2 v = *reinterpret_cast<const uint2 *>(&sm.ys[by2 * 8 + l8][min(bx, 2 * kWMcus - 1) * 2]);
+            int out[8];
+            block_dct(scr, l8, v.x, v.y, qt[0], out);
+            if (bx < nby) {
+                if (l8 == 0) sm.dc[by2][bx] = int16_t(out[0]);
+                int16_t *d = yout + (size_t(yby0 + by2) * p.y_WB + ybx0 + bx) * 64 + l8;
+#pragma unroll
+                for (int k = 0; k < 8; k++) d[k * 8] = int16_t(out[k]);
+            }
+        }
+        // chroma: steps of 4 blocks, Cb then Cr (both quantise with table 1)
+#pragma unroll 1
+        for (int s = 0; s < ((p.debug & 2u) ? 0 : 2 * (kWMcus / 4)); s++) {
+            const int pl = s / (kWMcus / 4), bx0 = (s - pl * (kWMcus / 4)) * 4, bx = bx0 + q4;
+            if (bx0 >= nm) continue;
+            const uint16_t(*f)[kWW / 4 + 8] = pl ? sm.cr : sm.cb;
+            const uint2 v = *reinterpret_cast<const uint2 *>(&f[l8][bx * 4]);
+            int out[8];
+            block_dct(scr, l8, v.x, v.y, qt[1], out);
+            if (bx < nm) {
+                int16_t *d = (pl ? p.cr : p.cb) + size_t(z) * p.c_img_elems + (size_t(my) * p.c_wb + mx0 + bx) * 64 + l8;
+#pragma unroll
+                for (int k = 0; k < 8; k++) d[k * 8] = int16_t(out[k]);
+            }
+        }
+        __syncwarp();
+        // dummy Y blocks (jccoefct.c:286-294 right edge, :301-319 bottom rows; edge tiles only): AC = 0, DC = the DC of
+        // the last real block to the left / of the MCU's last block in the row above
+        if (nby < 2 * nm || nrow < 2) {
+            for (int i = lane; i < 2 * 2 * nm; i += 32) {
+                const int by2 = i / (2 * nm), bx = i - by2 * (2 * nm);
+                const int gbx = ybx0 + bx, gby = yby0 + by2;
+                if (gbx >= int(p.y_WB) || gby >= int(p.y_HB)) continue;
+                const bool dummy_right = gbx >= int(p.y_wb), dummy_bottom = gby >= int(p.y_hb);
+                if (!dummy_right && !dummy_bottom) continue;
+                int sb_x = bx, sb_y = by2;
+                if (dummy_bottom) { sb_y = by2 - 1; sb_x = bx | 1; }               // last block of this MCU, row above
+                if (ybx0 + sb_x >= int(p.y_wb)) sb_x = int(p.y_wb) - 1 - ybx0;      // which may itself be a right-edge dummy
+                const uint32_t dc = uint32_t(uint16_t(sm.dc[sb_y][sb_x]));
+                uint4 *d = reinterpret_cast<uint4 *>(yout + (size_t(gby) * p.y_WB + gbx) * 64);
+                d[0] = make_uint4(dc, 0u, 0u, 0u);
+#pragma unroll
+                for (int k = 1; k < 8; k++) d[k] = make_uint4(0u, 0u, 0u, 0u);
+            }
+        }
+        __syncwarp();                    // the sample tiles and dc[] are rewritten by the next tile
     }
 }
 
@@ -211,6 +448,24 @@ cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStr
     if (n_images == 0 || p.w == 0 || p.h == 0) return cudaSuccess;
     const unsigned mcus_x = p.c_wb, mcus_y = p.c_hb;
     if (mcus_y > 65535) return cudaErrorInvalidValue;
+    if (!std::getenv("SLIMG_B200_JPEG_CTA")) {          // the CTA-wide kernel is kept for A/B comparison only
+        const char *var_env = std::getenv("SLIMG_B200_JPEG_VAR");
+        const int var = var_env ? std::atoi(var_env) : 2;      // measured best on B200: 24 warps/SM, 76 registers
+        auto kern = var == 1 ? jpeg_frontend_warp_kernel<2, 5> : var == 2 ? jpeg_frontend_warp_kernel<1, 6> : var == 3 ? jpeg_frontend_warp_kernel<4, 5> :
+                    var == 4 ? jpeg_frontend_warp_kernel<4, 6> : var == 5 ? jpeg_frontend_warp_kernel<8, 4> : var == 6 ? jpeg_frontend_warp_kernel<8, 5> : var == 7 ? jpeg_frontend_warp_kernel<1, 8> : var == 8 ? jpeg_frontend_warp_kernel<2, 7> : jpeg_frontend_warp_kernel<4, 4>;
+        int dev = 0, sms = 148, per_sm = 4;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * kWarpsPerCta, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+        const uint64_t tiles = uint64_t((mcus_x + kWMcus - 1) / kWMcus) * mcus_y * n_images;
+        const unsigned grid = unsigned(std::min<uint64_t>((tiles + kWarpsPerCta - 1) / kWarpsPerCta, uint64_t(sms) * per_sm));
+        JpegParams q = p;
+        const char *dbg = std::getenv("SLIMG_B200_JPEG_DEBUG");
+        q.debug = dbg ? uint32_t(std::atoi(dbg)) : 0u;
+        kern<<<grid, 32 * kWarpsPerCta, 0, stream>>>(q, n_images);
+        count_launch();
+        return cudaGetLastError();
+    }
     for (uint32_t first = 0; first < n_images; first += 65535) {
         JpegParams q = p;
         q.src += size_t(first) * p.src_img_bytes;

@@ -172,7 +172,7 @@ cudaError_t launch_resize_tc(const TcParams &p, uint32_t n_images, cudaStream_t 
 struct QuantDev {                      // jcdctmgr.c:173-221 compute_reciprocal, per table entry
     uint32_t recip[2][64];
     uint32_t corr[2][64];
-    uint8_t shift[2][64];              // total right shift (r in compute_reciprocal)
+    uint32_t shift32[2][64];           // total right shift (r in compute_reciprocal) minus 32: always >= 2
 };
 struct JpegParams {
     const uint8_t *src;
@@ -182,6 +182,7 @@ struct JpegParams {
     uint32_t w, h;
     uint32_t y_wb, y_hb, y_WB, y_HB, c_wb, c_hb;
     QuantDev q;
+    uint32_t debug;                    // experiment switches (SLIMG_B200_JPEG_DEBUG), 0 in production
 };
 cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStream_t stream);
 
