@@ -270,7 +270,7 @@ __global__ void __launch_bounds__(kThreads, 2) jpeg_frontend_kernel(const __grid
 //     a padded per-warp scratch (conflict-free 16-byte stores, conflict-free column reads), lane c runs the column DCT
 //     of column c and quantises its 8 coefficients with table entries it keeps in registers.  The loop body is ~250
 //     instructions, shared by all blocks.
-constexpr int kWMcus = 16;
+constexpr int kWMcus = 8;
 constexpr int kWW = 16 * kWMcus;                // 256 pixels
 constexpr int kWarpsPerCta = 4;
 constexpr int kRowStride = 12;                  // words between scratch rows: 16-byte chunks of 8 lanes hit distinct banks
@@ -450,7 +450,7 @@ cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStr
     if (mcus_y > 65535) return cudaErrorInvalidValue;
     if (!std::getenv("SLIMG_B200_JPEG_CTA")) {          // the CTA-wide kernel is kept for A/B comparison only
         const char *var_env = std::getenv("SLIMG_B200_JPEG_VAR");
-        const int var = var_env ? std::atoi(var_env) : 2;      // measured best on B200: 24 warps/SM, 76 registers
+        const int var = var_env ? std::atoi(var_env) : 7;      // measured best on B200: 32 warps/SM, 64 registers
         auto kern = var == 1 ? jpeg_frontend_warp_kernel<2, 5> : var == 2 ? jpeg_frontend_warp_kernel<1, 6> : var == 3 ? jpeg_frontend_warp_kernel<4, 5> :
                     var == 4 ? jpeg_frontend_warp_kernel<4, 6> : var == 5 ? jpeg_frontend_warp_kernel<8, 4> : var == 6 ? jpeg_frontend_warp_kernel<8, 5> : var == 7 ? jpeg_frontend_warp_kernel<1, 8> : var == 8 ? jpeg_frontend_warp_kernel<2, 7> : jpeg_frontend_warp_kernel<4, 4>;
         int dev = 0, sms = 148, per_sm = 4;
