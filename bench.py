@@ -193,7 +193,7 @@ def run_reference(args, rank: int):
             break
     value = total_n * MPX_PER_IMAGE / total_t
     sample = f"{per_step} synthetic 24 MP RGBA8 images per step, {threads} threads, one image per thread"
-    print(json.dumps({
+    _emit(json.dumps({
         "impl": "reference", "metric": "Mpx/s resize->crop->extend", "value": value, "unit": "Mpx/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * total_t / max(1, total_n // per_step), "higher_is_better": True, "scaling": "weak",
@@ -214,8 +214,27 @@ def workload_config(args, batch):
 
 # ---- B200 arm ------------------------------------------------------------------------------------------
 
+_REAL_STDOUT = None
+
+
+def _claim_stdout():
+    """stdout carries exactly ONE JSON line: everything else a library prints there (NCCL's version banner, torchrun
+    notices) is sent to stderr for the length of the run."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def _emit(line: str):
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (line + "\n").encode())
+
+
 def main():
     args = parse_args()
+    _claim_stdout()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -343,7 +362,7 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps({
+        _emit(json.dumps({
             "metric": "Mpx/s resize->crop->extend", "value": value, "unit": "Mpx/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",

@@ -16,6 +16,9 @@
 // This file holds the GENERIC kernel: any ratio on either axis (up, down, mixed).  One CTA =
 // one tile of the final canvas.  Stage 1 (vertical taps) gathers u8 source pixels into an f32
 // tile in shared memory, stage 2 (horizontal taps) reads that tile.
+#include <climits>
+#include <cstdlib>
+
 #include "kernels.cuh"
 
 namespace slimg {
@@ -105,6 +108,139 @@ __global__ void __launch_bounds__(kThreads) resize_generic_kernel(const ResizePa
     }
 }
 
+// ---- few-tap variant: both axes have at most kNT taps (upscales, ratios up to ~1.1) ------------------------------------
+// Same taps, same f32 accumulation order as the kernel above (bit-identical results), organised for the case where the
+// OUTPUT dominates (config C4b, 1024^2 x 4: 4 MB in, 67 MB out, 7 taps per axis):
+//   stage 0  the source pixels the tile needs are converted to f32 ONCE (byte -> float through the mantissa, no I2F)
+//   stage 1  vertical taps out of that tile, weights of the tile's rows staged in shared memory
+//   stage 2  a thread owns one output column and walks down the tile's rows with its horizontal weights in registers;
+//            clamp + round half away without F2I (add 0.5, then a round-toward-zero add of 2^23 leaves the integer in
+//            the mantissa)
+constexpr int kNT = 8;
+
+__device__ __forceinline__ float4 unpack_rgba_fast(uint32_t v) {
+    // 0x4B000000 | byte is the float 2^23 + byte, exactly
+    return make_float4(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7440)) - 8388608.0f,
+                       __uint_as_float(__byte_perm(v, 0x4B000000u, 0x7441)) - 8388608.0f,
+                       __uint_as_float(__byte_perm(v, 0x4B000000u, 0x7442)) - 8388608.0f,
+                       __uint_as_float(__byte_perm(v, 0x4B000000u, 0x7443)) - 8388608.0f);
+}
+// clamp(t, 0, 255), then floor(t + 0.5): the byte ends up in the low mantissa bits
+__device__ __forceinline__ uint32_t quantize_bits(float t) {
+    t = fminf(fmaxf(t, 0.0f), 255.0f) + 0.5f;
+    return __float_as_uint(__fadd_rz(t, 8388608.0f));
+}
+__device__ __forceinline__ uint32_t pack_rgba_fast(const float4 &t) {
+    const uint32_t xy = __byte_perm(quantize_bits(t.x), quantize_bits(t.y), 0x0040);
+    const uint32_t zw = __byte_perm(quantize_bits(t.z), quantize_bits(t.w), 0x0040);
+    return __byte_perm(xy, zw, 0x5410);
+}
+
+__global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizeParams p, const int src_rows_max) {
+    extern __shared__ float4 smem_f4[];
+    float4 *S = smem_f4;                                   // [src_rows_max][span_max] source pixels as f32
+    float4 *V = S + size_t(src_rows_max) * p.span_max;     // [tile_h][span_max] vertical-pass result
+    float *wy = reinterpret_cast<float *>(V + size_t(p.tile_h) * p.span_max);   // [tile_h][kNT]
+
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(p.src + size_t(blockIdx.z) * p.src_img_bytes);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(p.dst + size_t(blockIdx.z) * p.dst_img_bytes);
+    const int fx0 = blockIdx.x * p.tile_w, fy0 = blockIdx.y * p.tile_h;
+    const int fx1 = min(fx0 + p.tile_w, int(p.fw)), fy1 = min(fy0 + p.tile_h, int(p.fh));
+    const int ix0 = max(fx0, int(p.fox)), ix1 = min(fx1, int(p.fox + p.pw));
+    const int iy0 = max(fy0, int(p.foy)), iy1 = min(fy1, int(p.foy + p.ph));
+    const bool has_pixels = ix0 < ix1 && iy0 < iy1;
+    const int nrows = has_pixels ? iy1 - iy0 : 0;
+    const int ox0 = ix0 - int(p.fox) + int(p.px), oy0 = iy0 - int(p.foy) + int(p.py);
+    const int xs0 = has_pixels ? p.tile_x0[blockIdx.x] : 0;
+    const int span = has_pixels ? p.tile_span[blockIdx.x] : 0;
+    const int nt_y = p.ay.max_taps, nt_x = p.ax.max_taps;
+
+    // source rows of the tile (one thread per output row, reduced through shared memory)
+    __shared__ int s_ylo, s_yhi;
+    if (threadIdx.x == 0) { s_ylo = INT_MAX; s_yhi = 0; }
+    __syncthreads();
+    if (int(threadIdx.x) < nrows) {
+        const int n = p.ay.count[oy0 + threadIdx.x], l = p.ay.left[oy0 + threadIdx.x];
+        if (n > 0) { atomicMin(&s_ylo, l); atomicMax(&s_yhi, l + n); }
+    }
+    __syncthreads();
+    const int ylo = s_ylo == INT_MAX ? 0 : s_ylo, yhi = s_ylo == INT_MAX ? 0 : s_yhi;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int kW = kThreads / 32;
+    // stage 0: source tile as f32 (a warp per source row) + the vertical weights of the tile's rows
+    for (int r = warp; r < yhi - ylo; r += kW) {
+        const uint32_t *row = src + size_t(p.ry + ylo + r) * p.sw + (p.rx + xs0);
+        for (int c = lane; c < span; c += 32) S[r * p.span_max + c] = unpack_rgba_fast(__ldg(row + c));
+    }
+    for (int item = threadIdx.x; item < nrows * kNT; item += kThreads) {
+        const int r = item / kNT, i = item - r * kNT;
+        wy[item] = i < nt_y ? p.ay.w[size_t(oy0 + r) * nt_y + i] : 0.0f;
+    }
+    __syncthreads();
+
+    // stage 1: vertical taps, a warp per output row (row constants are warp-uniform)
+    for (int r = warp; r < nrows; r += kW) {
+        const int oy = oy0 + r;
+        const int n = p.ay.count[oy];
+        const float4 *s0 = S + (p.ay.left[oy] - ylo) * p.span_max;
+        float w[kNT];
+#pragma unroll
+        for (int i = 0; i < kNT; i++) w[i] = wy[r * kNT + i];
+        const float fwgt = p.ay.fillw[oy];
+        const float4 acc0 = make_float4(p.fill_pre[0] * fwgt, p.fill_pre[1] * fwgt, p.fill_pre[2] * fwgt, p.fill_pre[3] * fwgt);
+        for (int c = lane; c < span; c += 32) {
+            float4 acc = acc0;
+#pragma unroll
+            for (int i = 0; i < kNT; i++) {
+                if (i < n) {
+                    const float4 v = s0[i * p.span_max + c];
+                    acc.x = fmaf(v.x, w[i], acc.x); acc.y = fmaf(v.y, w[i], acc.y);
+                    acc.z = fmaf(v.z, w[i], acc.z); acc.w = fmaf(v.w, w[i], acc.w);
+                }
+            }
+            V[r * p.span_max + c] = acc;
+        }
+    }
+    __syncthreads();
+
+    // stage 2: a thread owns canvas column fx0 + tx and every (256 / tile_w)-th row of the tile
+    const int tw = fx1 - fx0, th = fy1 - fy0;
+    const int tx = threadIdx.x % p.tile_w, ty0 = threadIdx.x / p.tile_w, tys = kThreads / p.tile_w;
+    if (tx < tw) {
+        const int fx = fx0 + tx;
+        const bool in_cols = has_pixels && fx >= ix0 && fx < ix1;
+        float wx[kNT];
+        int n = 0, toff = 0;
+        float fwgt = 0.0f;
+        if (in_cols) {
+            const int ox = ox0 + (fx - ix0);
+            n = p.ax.count[ox];
+            toff = p.ax.left[ox] - xs0;
+            fwgt = p.ax.fillw[ox];
+#pragma unroll
+            for (int i = 0; i < kNT; i++) wx[i] = i < nt_x ? p.ax.w[size_t(ox) * nt_x + i] : 0.0f;
+        }
+        for (int ty = ty0; ty < th; ty += tys) {
+            const int fy = fy0 + ty;
+            uint32_t out = p.fill_post;
+            if (in_cols && fy >= iy0 && fy < iy1) {
+                const float4 *t = V + (fy - iy0) * p.span_max + toff;
+                float4 acc = make_float4(p.fill_pre[0] * fwgt, p.fill_pre[1] * fwgt, p.fill_pre[2] * fwgt, p.fill_pre[3] * fwgt);
+#pragma unroll
+                for (int i = 0; i < kNT; i++) {
+                    if (i < n) {
+                        const float4 v = t[i];
+                        acc.x = fmaf(v.x, wx[i], acc.x); acc.y = fmaf(v.y, wx[i], acc.y);
+                        acc.z = fmaf(v.z, wx[i], acc.z); acc.w = fmaf(v.w, wx[i], acc.w);
+                    }
+                }
+                out = pack_rgba_fast(acc);
+            }
+            dst[size_t(fy) * p.fw + fx] = out;
+        }
+    }
+}
+
 }  // namespace
 
 cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cudaStream_t stream) {
@@ -121,6 +257,30 @@ cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cuda
         configured_dev = dev;
     }
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
+    // few taps on both axes (upscales): the register-weight kernel; its source tile holds at most tile_h + kNT rows
+    const bool few = p.ax.max_taps <= kNT && p.ay.max_taps <= kNT && kThreads % p.tile_w == 0 && !std::getenv("SLIMG_B200_NO_FEWTAPS");
+    const int src_rows_max = 2 * p.tile_h + kNT;      // ratio < 2 on an axis with at most kNT taps
+    const size_t smem_few = (size_t(src_rows_max) + size_t(p.tile_h)) * size_t(p.span_max > 0 ? p.span_max : 1) * sizeof(float4) +
+                            size_t(p.tile_h) * kNT * sizeof(float);
+    if (few && smem_few <= 200 * 1024) {
+        static thread_local int few_dev = -1;
+        if (few_dev != dev) {
+            cudaError_t e = cudaFuncSetAttribute(resize_fewtaps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e != cudaSuccess) return e;
+            few_dev = dev;
+        }
+        for (uint32_t first = 0; first < n_images; first += 65535) {
+            ResizeParams q = p;
+            q.src += size_t(first) * p.src_img_bytes;
+            q.dst += size_t(first) * p.dst_img_bytes;
+            const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
+            resize_fewtaps_kernel<<<dim3(tiles_x, tiles_y, nz), kThreads, smem_few, stream>>>(q, src_rows_max);
+            count_launch();
+            cudaError_t e = cudaGetLastError();
+            if (e != cudaSuccess) return e;
+        }
+        return cudaSuccess;
+    }
     for (uint32_t first = 0; first < n_images; first += 65535) {
         ResizeParams q = p;
         q.src += size_t(first) * p.src_img_bytes;
