@@ -125,6 +125,10 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
     // tiling of the final canvas for the generic kernel
     int tile_w = g.vw >= g.Rw ? 32 : 64;
     int tile_h = g.vh >= g.Rh ? 8 : 16;
+    // upscales with few taps run the register-weight kernel (k2_resize.cu): its per-thread set-up is amortised over a
+    // taller tile
+    const bool few_taps = tx.max_taps <= 8 && ty.max_taps <= 8;
+    if (few_taps && g.Rh > g.vh && g.Rw > g.vw) tile_h = 64;
     std::vector<int32_t> tile_x0, tile_span;
     int span_max = 0;
     for (;;) {
@@ -170,6 +174,21 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
     p.fw = g.fw; p.fh = g.fh; p.fox = g.fox; p.foy = g.foy;
     p.fill_post = pack_fill(g.fill_post);
     p.tile_w = tile_w; p.tile_h = tile_h; p.span_max = span_max;
+    p.few_rows_max = 0;
+    if (few_taps) {       // most source rows any tile row-block needs (the few-tap kernel stages them as f32)
+        for (int64_t fy0 = 0; fy0 < int64_t(g.fh); fy0 += tile_h) {
+            const int64_t iy0 = std::max<int64_t>(fy0, g.foy), iy1 = std::min<int64_t>(std::min<int64_t>(fy0 + tile_h, g.fh), int64_t(g.foy) + g.ph);
+            int lo = INT32_MAX, hi = 0;
+            for (int64_t fy = iy0; fy < iy1; fy++) {
+                const int64_t oy = fy - g.foy + g.py;
+                if (ty.count[oy] == 0) continue;
+                lo = std::min(lo, ty.left[oy]);
+                hi = std::max(hi, ty.left[oy] + ty.count[oy]);
+            }
+            if (lo < hi) p.few_rows_max = std::max(p.few_rows_max, hi - lo);
+        }
+        p.few_rows_max = std::max(p.few_rows_max, 1);
+    }
     p.tile_x0 = (const int32_t *)plan->tx0.p;
     p.tile_span = (const int32_t *)plan->tspan.p;
     // which resize kernel: SLIMG_B200_RESIZE_PATH = vfirst (default) | hfirst | generic

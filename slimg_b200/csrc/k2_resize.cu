@@ -16,6 +16,7 @@
 // This file holds the GENERIC kernel: any ratio on either axis (up, down, mixed).  One CTA =
 // one tile of the final canvas.  Stage 1 (vertical taps) gathers u8 source pixels into an f32
 // tile in shared memory, stage 2 (horizontal taps) reads that tile.
+#include <algorithm>
 #include <climits>
 #include <cstdlib>
 
@@ -116,7 +117,7 @@ __global__ void __launch_bounds__(kThreads) resize_generic_kernel(const ResizePa
 //   stage 2  a thread owns one output column and walks down the tile's rows with its horizontal weights in registers;
 //            clamp + round half away without F2I (add 0.5, then a round-toward-zero add of 2^23 leaves the integer in
 //            the mantissa)
-constexpr int kNT = 8;
+constexpr int kNT = 8;                 // most taps per axis the few-tap kernel takes (template NT = the plan's max)
 
 __device__ __forceinline__ float4 unpack_rgba_fast(uint32_t v) {
     // 0x4B000000 | byte is the float 2^23 + byte, exactly
@@ -136,11 +137,15 @@ __device__ __forceinline__ uint32_t pack_rgba_fast(const float4 &t) {
     return __byte_perm(xy, zw, 0x5410);
 }
 
+// Taps beyond a row's / column's count carry zero weights (taps.cpp pads them) and read zero-filled padding of the
+// tiles, so the tap loops run NT unconditional iterations: no predicates, no branches.
+template <int NT>
 __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizeParams p, const int src_rows_max) {
     extern __shared__ float4 smem_f4[];
-    float4 *S = smem_f4;                                   // [src_rows_max][span_max] source pixels as f32
-    float4 *V = S + size_t(src_rows_max) * p.span_max;     // [tile_h][span_max] vertical-pass result
-    float *wy = reinterpret_cast<float *>(V + size_t(p.tile_h) * p.span_max);   // [tile_h][kNT]
+    const int vpitch = p.span_max + NT;
+    float4 *S = smem_f4;                                   // [src_rows_max + NT][span_max] source pixels as f32
+    float4 *V = S + size_t(src_rows_max + NT) * p.span_max;     // [tile_h][span_max + NT] vertical-pass result
+    float *wy = reinterpret_cast<float *>(V + size_t(p.tile_h) * vpitch);   // [tile_h][NT]
 
     const uint32_t *src = reinterpret_cast<const uint32_t *>(p.src + size_t(blockIdx.z) * p.src_img_bytes);
     uint32_t *dst = reinterpret_cast<uint32_t *>(p.dst + size_t(blockIdx.z) * p.dst_img_bytes);
@@ -168,12 +173,14 @@ __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizePa
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int kW = kThreads / 32;
     // stage 0: source tile as f32 (a warp per source row) + the vertical weights of the tile's rows
-    for (int r = warp; r < yhi - ylo; r += kW) {
+    for (int r = warp; r < yhi - ylo + NT; r += kW) {
         const uint32_t *row = src + size_t(p.ry + ylo + r) * p.sw + (p.rx + xs0);
-        for (int c = lane; c < span; c += 32) S[r * p.span_max + c] = unpack_rgba_fast(__ldg(row + c));
+        const bool real = r < yhi - ylo;
+        for (int c = lane; c < span; c += 32)
+            S[r * p.span_max + c] = real ? unpack_rgba_fast(__ldg(row + c)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
-    for (int item = threadIdx.x; item < nrows * kNT; item += kThreads) {
-        const int r = item / kNT, i = item - r * kNT;
+    for (int item = threadIdx.x; item < nrows * NT; item += kThreads) {
+        const int r = item / NT, i = item - r * NT;
         wy[item] = i < nt_y ? p.ay.w[size_t(oy0 + r) * nt_y + i] : 0.0f;
     }
     __syncthreads();
@@ -181,24 +188,23 @@ __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizePa
     // stage 1: vertical taps, a warp per output row (row constants are warp-uniform)
     for (int r = warp; r < nrows; r += kW) {
         const int oy = oy0 + r;
-        const int n = p.ay.count[oy];
-        const float4 *s0 = S + (p.ay.left[oy] - ylo) * p.span_max;
-        float w[kNT];
+        const float4 *s0 = S + (p.ay.count[oy] > 0 ? p.ay.left[oy] - ylo : 0) * p.span_max;
+        float w[NT];
 #pragma unroll
-        for (int i = 0; i < kNT; i++) w[i] = wy[r * kNT + i];
+        for (int i = 0; i < NT; i++) w[i] = wy[r * NT + i];
         const float fwgt = p.ay.fillw[oy];
         const float4 acc0 = make_float4(p.fill_pre[0] * fwgt, p.fill_pre[1] * fwgt, p.fill_pre[2] * fwgt, p.fill_pre[3] * fwgt);
-        for (int c = lane; c < span; c += 32) {
+        for (int c = lane; c < span + NT; c += 32) {
             float4 acc = acc0;
+            if (c < span) {
 #pragma unroll
-            for (int i = 0; i < kNT; i++) {
-                if (i < n) {
+                for (int i = 0; i < NT; i++) {
                     const float4 v = s0[i * p.span_max + c];
                     acc.x = fmaf(v.x, w[i], acc.x); acc.y = fmaf(v.y, w[i], acc.y);
                     acc.z = fmaf(v.z, w[i], acc.z); acc.w = fmaf(v.w, w[i], acc.w);
                 }
-            }
-            V[r * p.span_max + c] = acc;
+            } else acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);     // padding read by zero-weight taps
+            V[r * vpitch + c] = acc;
         }
     }
     __syncthreads();
@@ -209,30 +215,27 @@ __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizePa
     if (tx < tw) {
         const int fx = fx0 + tx;
         const bool in_cols = has_pixels && fx >= ix0 && fx < ix1;
-        float wx[kNT];
-        int n = 0, toff = 0;
+        float wx[NT];
+        int toff = 0;
         float fwgt = 0.0f;
         if (in_cols) {
             const int ox = ox0 + (fx - ix0);
-            n = p.ax.count[ox];
-            toff = p.ax.left[ox] - xs0;
+            toff = p.ax.count[ox] > 0 ? p.ax.left[ox] - xs0 : 0;
             fwgt = p.ax.fillw[ox];
 #pragma unroll
-            for (int i = 0; i < kNT; i++) wx[i] = i < nt_x ? p.ax.w[size_t(ox) * nt_x + i] : 0.0f;
+            for (int i = 0; i < NT; i++) wx[i] = i < nt_x ? p.ax.w[size_t(ox) * nt_x + i] : 0.0f;
         }
         for (int ty = ty0; ty < th; ty += tys) {
             const int fy = fy0 + ty;
             uint32_t out = p.fill_post;
             if (in_cols && fy >= iy0 && fy < iy1) {
-                const float4 *t = V + (fy - iy0) * p.span_max + toff;
+                const float4 *t = V + (fy - iy0) * vpitch + toff;
                 float4 acc = make_float4(p.fill_pre[0] * fwgt, p.fill_pre[1] * fwgt, p.fill_pre[2] * fwgt, p.fill_pre[3] * fwgt);
 #pragma unroll
-                for (int i = 0; i < kNT; i++) {
-                    if (i < n) {
-                        const float4 v = t[i];
-                        acc.x = fmaf(v.x, wx[i], acc.x); acc.y = fmaf(v.y, wx[i], acc.y);
-                        acc.z = fmaf(v.z, wx[i], acc.z); acc.w = fmaf(v.w, wx[i], acc.w);
-                    }
+                for (int i = 0; i < NT; i++) {
+                    const float4 v = t[i];
+                    acc.x = fmaf(v.x, wx[i], acc.x); acc.y = fmaf(v.y, wx[i], acc.y);
+                    acc.z = fmaf(v.z, wx[i], acc.z); acc.w = fmaf(v.w, wx[i], acc.w);
                 }
                 out = pack_rgba_fast(acc);
             }
@@ -258,14 +261,18 @@ cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cuda
     }
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     // few taps on both axes (upscales): the register-weight kernel; its source tile holds at most tile_h + kNT rows
-    const bool few = p.ax.max_taps <= kNT && p.ay.max_taps <= kNT && kThreads % p.tile_w == 0 && !std::getenv("SLIMG_B200_NO_FEWTAPS");
-    const int src_rows_max = 2 * p.tile_h + kNT;      // ratio < 2 on an axis with at most kNT taps
-    const size_t smem_few = (size_t(src_rows_max) + size_t(p.tile_h)) * size_t(p.span_max > 0 ? p.span_max : 1) * sizeof(float4) +
-                            size_t(p.tile_h) * kNT * sizeof(float);
+    const bool few = p.few_rows_max > 0 && p.ax.max_taps <= kNT && p.ay.max_taps <= kNT && kThreads % p.tile_w == 0 && !std::getenv("SLIMG_B200_NO_FEWTAPS");
+    const int src_rows_max = p.few_rows_max;
+    const int nt = std::max(p.ax.max_taps, p.ay.max_taps) <= 7 ? 7 : 8;
+    const size_t span_alloc = size_t(p.span_max > 0 ? p.span_max : 1);
+    const size_t smem_few = (size_t(src_rows_max + nt) * span_alloc + size_t(p.tile_h) * (span_alloc + nt)) * sizeof(float4) +
+                            size_t(p.tile_h) * nt * sizeof(float);
     if (few && smem_few <= 200 * 1024) {
+        auto kern = nt == 7 ? resize_fewtaps_kernel<7> : resize_fewtaps_kernel<8>;
         static thread_local int few_dev = -1;
         if (few_dev != dev) {
-            cudaError_t e = cudaFuncSetAttribute(resize_fewtaps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            cudaError_t e = cudaFuncSetAttribute(resize_fewtaps_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(resize_fewtaps_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             if (e != cudaSuccess) return e;
             few_dev = dev;
         }
@@ -274,7 +281,7 @@ cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cuda
             q.src += size_t(first) * p.src_img_bytes;
             q.dst += size_t(first) * p.dst_img_bytes;
             const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
-            resize_fewtaps_kernel<<<dim3(tiles_x, tiles_y, nz), kThreads, smem_few, stream>>>(q, src_rows_max);
+            kern<<<dim3(tiles_x, tiles_y, nz), kThreads, smem_few, stream>>>(q, src_rows_max);
             count_launch();
             cudaError_t e = cudaGetLastError();
             if (e != cudaSuccess) return e;
