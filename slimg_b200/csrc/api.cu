@@ -174,7 +174,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
     p.fw = g.fw; p.fh = g.fh; p.fox = g.fox; p.foy = g.foy;
     p.fill_post = pack_fill(g.fill_post);
     p.tile_w = tile_w; p.tile_h = tile_h; p.span_max = span_max;
-    p.few_rows_max = 0;
+    p.few_rows_max = 0; p.few_k = 1;
     if (few_taps) {       // most source rows any tile row-block needs (the few-tap kernel stages them as f32)
         for (int64_t fy0 = 0; fy0 < int64_t(g.fh); fy0 += tile_h) {
             const int64_t iy0 = std::max<int64_t>(fy0, g.foy), iy1 = std::min<int64_t>(std::min<int64_t>(fy0 + tile_h, g.fh), int64_t(g.foy) + g.ph);
@@ -188,6 +188,20 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
             if (lo < hi) p.few_rows_max = std::max(p.few_rows_max, hi - lo);
         }
         p.few_rows_max = std::max(p.few_rows_max, 1);
+        // four adjacent canvas columns (aligned to 4) may share one window of max_taps + 2 intermediate values?
+        // (measured on B200, C4b: the 4-column variant needs 103 registers, halves the occupancy and runs at 171 us against
+        // 94 us for one column per thread -- kept behind SLIMG_B200_FEW_K4 for the next round)
+        p.few_k = (tile_w % 4 == 0 && g.Rw > g.vw && std::getenv("SLIMG_B200_FEW_K4") != nullptr) ? 4 : 1;
+        for (int64_t fxg = 0; fxg < int64_t(g.fw) && p.few_k == 4; fxg += 4) {
+            int lo = INT32_MAX, hi = INT32_MIN;
+            for (int64_t fx = std::max<int64_t>(fxg, g.fox); fx < std::min<int64_t>(std::min<int64_t>(fxg + 4, g.fw), int64_t(g.fox) + g.pw); fx++) {
+                const int64_t ox = fx - g.fox + g.px;
+                if (tx.count[ox] == 0) continue;
+                lo = std::min(lo, tx.left[ox]);
+                hi = std::max(hi, tx.left[ox]);
+            }
+            if (lo <= hi && hi - lo > 2) p.few_k = 1;
+        }
     }
     p.tile_x0 = (const int32_t *)plan->tx0.p;
     p.tile_span = (const int32_t *)plan->tspan.p;

@@ -139,10 +139,10 @@ __device__ __forceinline__ uint32_t pack_rgba_fast(const float4 &t) {
 
 // Taps beyond a row's / column's count carry zero weights (taps.cpp pads them) and read zero-filled padding of the
 // tiles, so the tap loops run NT unconditional iterations: no predicates, no branches.
-template <int NT>
+template <int NT, int K>
 __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizeParams p, const int src_rows_max) {
     extern __shared__ float4 smem_f4[];
-    const int vpitch = p.span_max + NT;
+    const int vpitch = p.span_max + NT + 2;
     float4 *S = smem_f4;                                   // [src_rows_max + NT][span_max] source pixels as f32
     float4 *V = S + size_t(src_rows_max + NT) * p.span_max;     // [tile_h][span_max + NT] vertical-pass result
     float *wy = reinterpret_cast<float *>(V + size_t(p.tile_h) * vpitch);   // [tile_h][NT]
@@ -194,7 +194,7 @@ __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizePa
         for (int i = 0; i < NT; i++) w[i] = wy[r * NT + i];
         const float fwgt = p.ay.fillw[oy];
         const float4 acc0 = make_float4(p.fill_pre[0] * fwgt, p.fill_pre[1] * fwgt, p.fill_pre[2] * fwgt, p.fill_pre[3] * fwgt);
-        for (int c = lane; c < span + NT; c += 32) {
+        for (int c = lane; c < span + NT + 2; c += 32) {
             float4 acc = acc0;
             if (c < span) {
 #pragma unroll
@@ -209,37 +209,79 @@ __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizePa
     }
     __syncthreads();
 
-    // stage 2: a thread owns canvas column fx0 + tx and every (256 / tile_w)-th row of the tile
+    // stage 2: a thread owns K adjacent canvas columns and every (256 * K / tile_w)-th row of the tile.  With K = 4
+    // (upscales: neighbouring output columns read almost the same taps) the U = NT + 2 intermediate values of the
+    // columns' common window are loaded once per row and reused by all four columns -- the kernel is bound by shared-
+    // memory bandwidth otherwise (one 16-byte load per 4 FMAs).  Weights are re-based to the common window, zero outside
+    // a column's own taps: extra zero-weight FMAs do not change the f32 sums.
+    constexpr int U = K == 1 ? NT : NT + 2;
     const int tw = fx1 - fx0, th = fy1 - fy0;
-    const int tx = threadIdx.x % p.tile_w, ty0 = threadIdx.x / p.tile_w, tys = kThreads / p.tile_w;
+    const int ngx = p.tile_w / K;
+    const int gx = threadIdx.x % ngx, ty0 = threadIdx.x / ngx, tys = kThreads / ngx;
+    const int tx = gx * K;
     if (tx < tw) {
-        const int fx = fx0 + tx;
-        const bool in_cols = has_pixels && fx >= ix0 && fx < ix1;
-        float wx[NT];
-        int toff = 0;
-        float fwgt = 0.0f;
-        if (in_cols) {
-            const int ox = ox0 + (fx - ix0);
-            toff = p.ax.count[ox] > 0 ? p.ax.left[ox] - xs0 : 0;
-            fwgt = p.ax.fillw[ox];
+        float wx[K][U];
+        float fwgt[K];
+        bool valid[K];
+        int toff = INT_MAX;
 #pragma unroll
-            for (int i = 0; i < NT; i++) wx[i] = i < nt_x ? p.ax.w[size_t(ox) * nt_x + i] : 0.0f;
+        for (int k = 0; k < K; k++) {
+            const int fx = fx0 + tx + k;
+            valid[k] = has_pixels && fx >= ix0 && fx < ix1;
+            fwgt[k] = 0.0f;
+            if (valid[k]) {
+                const int ox = ox0 + (fx - ix0);
+                fwgt[k] = p.ax.fillw[ox];
+                if (p.ax.count[ox] > 0) toff = min(toff, p.ax.left[ox] - xs0);
+            }
+        }
+        if (toff == INT_MAX) toff = 0;
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+#pragma unroll
+            for (int j = 0; j < U; j++) wx[k][j] = 0.0f;
+            if (valid[k]) {
+                const int ox = ox0 + (fx0 + tx + k - ix0);
+                const int d = p.ax.count[ox] > 0 ? p.ax.left[ox] - xs0 - toff : 0;      // 0..U-NT by the plan's check
+#pragma unroll
+                for (int j = 0; j < U; j++) {
+                    const int i = j - d;
+                    if (i >= 0 && i < nt_x) wx[k][j] = p.ax.w[size_t(ox) * nt_x + i];
+                }
+            }
         }
         for (int ty = ty0; ty < th; ty += tys) {
             const int fy = fy0 + ty;
-            uint32_t out = p.fill_post;
-            if (in_cols && fy >= iy0 && fy < iy1) {
-                const float4 *t = V + (fy - iy0) * vpitch + toff;
-                float4 acc = make_float4(p.fill_pre[0] * fwgt, p.fill_pre[1] * fwgt, p.fill_pre[2] * fwgt, p.fill_pre[3] * fwgt);
+            uint32_t out[K];
 #pragma unroll
-                for (int i = 0; i < NT; i++) {
-                    const float4 v = t[i];
-                    acc.x = fmaf(v.x, wx[i], acc.x); acc.y = fmaf(v.y, wx[i], acc.y);
-                    acc.z = fmaf(v.z, wx[i], acc.z); acc.w = fmaf(v.w, wx[i], acc.w);
+            for (int k = 0; k < K; k++) out[k] = p.fill_post;
+            if (fy >= iy0 && fy < iy1) {
+                const float4 *t = V + (fy - iy0) * vpitch + toff;
+                float4 acc[K];
+#pragma unroll
+                for (int k = 0; k < K; k++)
+                    acc[k] = make_float4(p.fill_pre[0] * fwgt[k], p.fill_pre[1] * fwgt[k], p.fill_pre[2] * fwgt[k], p.fill_pre[3] * fwgt[k]);
+#pragma unroll
+                for (int j = 0; j < U; j++) {
+                    const float4 v = t[j];
+#pragma unroll
+                    for (int k = 0; k < K; k++) {
+                        acc[k].x = fmaf(v.x, wx[k][j], acc[k].x); acc[k].y = fmaf(v.y, wx[k][j], acc[k].y);
+                        acc[k].z = fmaf(v.z, wx[k][j], acc[k].z); acc[k].w = fmaf(v.w, wx[k][j], acc[k].w);
+                    }
                 }
-                out = pack_rgba_fast(acc);
+#pragma unroll
+                for (int k = 0; k < K; k++)
+                    if (valid[k]) out[k] = pack_rgba_fast(acc[k]);
             }
-            dst[size_t(fy) * p.fw + fx] = out;
+            uint32_t *o = dst + size_t(fy) * p.fw + fx0 + tx;
+            if (K == 4 && tx + 3 < tw && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+                *reinterpret_cast<uint4 *>(o) = make_uint4(out[0], out[K > 1 ? 1 : 0], out[K > 2 ? 2 : 0], out[K > 3 ? 3 : 0]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < K; k++)
+                    if (tx + k < tw) o[k] = out[k];
+            }
         }
     }
 }
@@ -265,14 +307,17 @@ cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cuda
     const int src_rows_max = p.few_rows_max;
     const int nt = std::max(p.ax.max_taps, p.ay.max_taps) <= 7 ? 7 : 8;
     const size_t span_alloc = size_t(p.span_max > 0 ? p.span_max : 1);
-    const size_t smem_few = (size_t(src_rows_max + nt) * span_alloc + size_t(p.tile_h) * (span_alloc + nt)) * sizeof(float4) +
+    const size_t smem_few = (size_t(src_rows_max + nt) * span_alloc + size_t(p.tile_h) * (span_alloc + nt + 2)) * sizeof(float4) +
                             size_t(p.tile_h) * nt * sizeof(float);
     if (few && smem_few <= 200 * 1024) {
-        auto kern = nt == 7 ? resize_fewtaps_kernel<7> : resize_fewtaps_kernel<8>;
+        const bool k4 = p.few_k == 4 && p.tile_w % 4 == 0 && kThreads % (p.tile_w / 4) == 0;
+        auto kern = nt == 7 ? (k4 ? resize_fewtaps_kernel<7, 4> : resize_fewtaps_kernel<7, 1>) : (k4 ? resize_fewtaps_kernel<8, 4> : resize_fewtaps_kernel<8, 1>);
         static thread_local int few_dev = -1;
         if (few_dev != dev) {
-            cudaError_t e = cudaFuncSetAttribute(resize_fewtaps_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-            if (e == cudaSuccess) e = cudaFuncSetAttribute(resize_fewtaps_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            cudaError_t e = cudaFuncSetAttribute(resize_fewtaps_kernel<7, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(resize_fewtaps_kernel<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(resize_fewtaps_kernel<7, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(resize_fewtaps_kernel<8, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             if (e != cudaSuccess) return e;
             few_dev = dev;
         }
