@@ -334,8 +334,9 @@ def main():
             if failed:
                 raise SystemExit("e2e batch failed: " + lib.slimg_b200_last_error().decode())
 
-        e2e_steps = max(2, min(args.steps, 5))
-        e2e_step()
+        e2e_steps = max(3, min(args.steps, 8))
+        for _ in range(2):                    # warm-up: stream-ordered pool growth, plan upload, page pinning
+            e2e_step()
         barrier()
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
