@@ -470,8 +470,10 @@ static slimg_status validate_image(const slimg_image *in, const slimg_pipeline_o
 }
 
 // one image, host in / host out, on the current device
+// `done` (optional): a cudaEventBlockingSync event the wait goes through, so a scheduler worker SLEEPS while its image
+// is in flight instead of spinning on the stream (8 ranks x 4 workers would otherwise fight over the host cores)
 static slimg_status pipeline_one(const slimg_image *in, const slimg_pipeline_options &o, int order, slimg_image *out,
-                                 cudaStream_t stream, bool caller_buffer) {
+                                 cudaStream_t stream, bool caller_buffer, cudaEvent_t done = nullptr) {
     slimg_status st = validate_image(in, o, order);
     if (st != SLIMG_OK) return st;
     PipeGeom g;
@@ -512,7 +514,10 @@ static slimg_status pipeline_one(const slimg_image *in, const slimg_pipeline_opt
     }
     if ((st = run_pipeline_device(g, d_src, 1, d_dst, stream)) != SLIMG_OK) return cleanup(st);
     if ((e = cudaMemcpyAsync(host_out, d_dst, dst_bytes, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "D2H"));
-    if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return cleanup(cuda_fail(e, "pipeline kernels"));
+    if (done) {
+        if ((e = cudaEventRecord(done, stream)) != cudaSuccess || (e = cudaEventSynchronize(done)) != cudaSuccess)
+            return cleanup(cuda_fail(e, "pipeline kernels"));
+    } else if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return cleanup(cuda_fail(e, "pipeline kernels"));
     cleanup(SLIMG_OK);
     out->width = g.fw; out->height = g.fh; out->data = host_out; out->len = dst_bytes;
     return SLIMG_OK;
@@ -756,10 +761,15 @@ int32_t slimg_b200_pipeline_batch_host(const slimg_image *in, uint32_t n, const 
         if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return; }
         cudaStream_t s = nullptr;
         if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return; }
+        cudaEvent_t done = nullptr;
+        if (std::getenv("SLIMG_B200_SPIN_SYNC") || cudaEventCreateWithFlags(&done, cudaEventBlockingSync | cudaEventDisableTiming) != cudaSuccess) {
+            cudaGetLastError();
+            done = nullptr;
+        }
         for (;;) {
             const uint32_t i = next.fetch_add(1);
             if (i >= n) break;
-            slimg_status st = pipeline_one(&in[i], *opts, order, &out[i], s, true);
+            slimg_status st = pipeline_one(&in[i], *opts, order, &out[i], s, true, done);
             statuses[i] = st;
             if (st != SLIMG_OK) {
                 std::lock_guard<std::mutex> lk(err_mu);
@@ -767,6 +777,7 @@ int32_t slimg_b200_pipeline_batch_host(const slimg_image *in, uint32_t n, const 
             }
         }
         cudaStreamSynchronize(s);
+        if (done) cudaEventDestroy(done);
         cudaStreamDestroy(s);
     };
     std::vector<std::thread> threads;
