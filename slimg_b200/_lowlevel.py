@@ -87,7 +87,10 @@ def library() -> C.CDLL:
     if _lib is not None:
         return _lib
     path = _build.LIB_PATH
-    if _build.needs_build():
+    override = os.environ.get("SLIMG_B200_LIB")         # A/B of two builds of the same sources
+    if override:
+        path = override
+    elif _build.needs_build():
         path = _build.build()
     if not os.path.exists(path):
         raise ImportError(f"libslimg_b200.so not found at {path}; run `python -m slimg_b200._build`")

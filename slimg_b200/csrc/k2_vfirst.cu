@@ -39,7 +39,7 @@ namespace slimg {
 
 namespace {
 
-constexpr int kWarps = 16;
+constexpr int kWarps = kVfWarps;
 constexpr int kThreads = kWarps * 32;
 constexpr int kStepRows = 16;                // source rows per ring step (one mbarrier each) == kWarps
 constexpr int kMaxSteps = 32;                // ring of at most 512 rows (one step per producer lane)
@@ -194,10 +194,10 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
 
     // ---- roles ---------------------------------------------------------------------------------------
     //   warps [0, ntile)        pass 2: one tile of 8 output columns each, all four channels
-    //   warps [ntile, 14)       pass 1: each warp owns `upw` units of UNIT 16-byte blocks of the strip, for every group
-    //   warp 14                 signaller: waits for a group's record, source rows and free V buffer, then hands
+    //   warps [ntile, kWarps-2) pass 1: each warp owns `upw` units of UNIT 16-byte blocks of the strip, for every group
+    //   warp kWarps-2           signaller: waits for a group's record, source rows and free V buffer, then hands
     //                           pass 1 ONE barrier per group
-    //   warp 15                 producer: ring refills and group records through the TMA engine
+    //   warp kWarps-1           producer: ring refills and group records through the TMA engine
     // They meet only on mbarriers: no CTA-wide barrier inside the band loop.
     const int ntile = (col1 - col0 + 7) >> 3;
     const int n_p1 = kWarps - 2 - ntile;

@@ -135,6 +135,10 @@ struct VfParams {
     uint32_t debug;                  // experiment switches (SLIMG_B200_VF_DEBUG), 0 in production
     uint32_t pf_steps;               // ring steps prefetched into L2 ahead of the ring (0 = off)
 };
+#ifndef SLIMG_VF_WARPS
+#define SLIMG_VF_WARPS 16     /* measured on B200, C3: 16 warps x 4-block units 1300 Gpx/s; 20 x 3-block 1113; 24 x 3-block 1062 */
+#endif
+constexpr int kVfWarps = SLIMG_VF_WARPS;   // warps of a strip CTA: pass-2 tiles + pass-1 warps + signaller + producer
 constexpr int kVfMaxVBufs = 4;      // most V buffers the kernel supports (VfParams::vbufs)
 cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStream_t stream);
 size_t vfirst_smem_tail_bytes();

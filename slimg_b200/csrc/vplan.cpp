@@ -208,9 +208,9 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         }
     };
     // pass 1 splits a strip's 16-byte blocks statically: units of `unit` blocks, upw consecutive units per warp
-    // over the (14 - tiles) pass-1 warps (the last warps may own fewer, or none)
+    // over the (kVfWarps - 2 - tiles) pass-1 warps (the last warps may own fewer, or none)
     auto pad_blocks = [&](int64_t raw, uint32_t ncols, int unit, int &upw) {
-        const int64_t n_p1 = 14 - int64_t((ncols + 7) / 8);   // k2_vfirst.cu: 16 warps - producer - signaller - tiles
+        const int64_t n_p1 = kVfWarps - 2 - int64_t((ncols + 7) / 8);   // k2_vfirst.cu: all warps - producer - signaller - tiles
         const int64_t nunits = (raw + unit - 1) / unit;
         upw = int((nunits + n_p1 - 1) / n_p1);
         return nunits * unit;
