@@ -338,9 +338,12 @@ def main():
         for _ in range(2):                    # warm-up: stream-ordered pool growth, plan upload, page pinning
             e2e_step()
         barrier()
+        step_ms = []
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
+            t1 = time.perf_counter()
             e2e_step()
+            step_ms.append(round(1e3 * (time.perf_counter() - t1), 2))
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         e2e_value = _shard.whole_job_throughput(nb * e2e_steps * MPX_PER_IMAGE, world, _shard.max_over_ranks(dt, device="cuda"))
@@ -348,7 +351,7 @@ def main():
         e2e = {"value": e2e_value, "unit": "Mpx/s", "h2d_bytes_per_step": nb * h2d_bytes, "d2h_bytes_per_step": nb * out_bytes,
                "host_image_bytes_per_step": nb * in_bytes,
                "images_per_gpu_per_step": nb, "steps": e2e_steps, "timer": "host wall clock around the C-ABI calls, max over ranks",
-               "result_checksum": checksum}
+               "result_checksum": checksum, "step_ms": step_ms}
         lib.slimg_b200_host_free(pin_in); lib.slimg_b200_host_free(pin_out)
 
     cpu = None
