@@ -451,8 +451,9 @@ cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStr
     if (!std::getenv("SLIMG_B200_JPEG_CTA")) {          // the CTA-wide kernel is kept for A/B comparison only
         const char *var_env = std::getenv("SLIMG_B200_JPEG_VAR");
         const int var = var_env ? std::atoi(var_env) : 7;      // measured best on B200: 32 warps/SM, 64 registers
-        auto kern = var == 1 ? jpeg_frontend_warp_kernel<2, 5> : var == 2 ? jpeg_frontend_warp_kernel<1, 6> : var == 3 ? jpeg_frontend_warp_kernel<4, 5> :
-                    var == 4 ? jpeg_frontend_warp_kernel<4, 6> : var == 5 ? jpeg_frontend_warp_kernel<8, 4> : var == 6 ? jpeg_frontend_warp_kernel<8, 5> : var == 7 ? jpeg_frontend_warp_kernel<1, 8> : var == 8 ? jpeg_frontend_warp_kernel<2, 7> : jpeg_frontend_warp_kernel<4, 4>;
+        // <stage-1 unroll, CTAs per SM>: measured on B200 (24 MP, q=70): <1,8> 67.9 us, <1,6> 69.2 us, <4,4> 79.7 us -- occupancy
+        // beats loads in flight per warp
+        auto kern = var == 0 ? jpeg_frontend_warp_kernel<4, 4> : var == 2 ? jpeg_frontend_warp_kernel<1, 6> : jpeg_frontend_warp_kernel<1, 8>;
         int dev = 0, sms = 148, per_sm = 4;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
