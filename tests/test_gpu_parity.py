@@ -319,3 +319,65 @@ def test_batch_host_scheduler_isolates_failures():
         want = oracle.pipeline(imgs[i], crop_mode=oracle.CropMode.region(0, 0, 10, 10), resize_mode=oracle.ResizeMode.scale(0.5))
         _close(got, want)
         lib.slimg_b200_image_free(C.byref(cout[i]))
+
+
+# ---- no kernel writes outside its output (the box has no compute-sanitizer: guard bands instead) -----------------
+
+GUARD_CASES = [
+    # (w, h, resize, crop, extend, fill, order)
+    (1200, 800, ("width", 160), ("aspect", 16, 9), ("aspect", 1, 1), WHITE, "chain"),       # V-first + fill CTAs
+    (1200, 800, ("width", 160), ("aspect", 16, 9), ("aspect", 1, 1), WHITE, "convert"),
+    (150, 90, ("scale", 3.0), None, None, None, "convert"),                                   # few-tap kernel
+    (333, 222, ("exact", 500, 100), None, None, None, "convert"),                             # generic kernel (up x, down y)
+    (401, 299, None, ("region", 7, 9, 300, 200), ("size", 333, 257), (10, 200, 30, 128), "convert"),   # K1 remap
+    (1001, 667, ("width", 125), None, ("aspect", 3, 2), CLEAR, "chain"),                      # odd pitch, unaligned rows
+]
+
+
+@pytest.mark.parametrize("w,h,resize,crop,extend,fill,order", GUARD_CASES)
+def test_batch_device_writes_only_its_output(w, h, resize, crop, extend, fill, order):
+    import torch
+    n = 3
+    imgs = np.stack([noise_image(w, h, 40 + i) for i in range(n)])
+    src = torch.from_numpy(imgs).cuda()
+    o, l = _modes(resize, crop, extend, fill)
+    od = ll.ORDER_CHAIN if order == "chain" else ll.ORDER_CONVERT
+    ow, oh = ll.pipeline_output_dims(w, h, l, od)
+    nbytes, guard = n * oh * ow * 4, 1 << 16
+    buf = torch.full((nbytes + 2 * guard,), 0xA5, dtype=torch.uint8, device="cuda")
+    ll.pipeline_batch_device(src.data_ptr(), n, w, h, l, od, buf.data_ptr() + guard, nbytes,
+                             torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    host = buf.cpu().numpy()
+    assert (host[:guard] == 0xA5).all() and (host[guard + nbytes:] == 0xA5).all(), "kernel wrote outside its output"
+    got = host[guard:guard + nbytes].reshape(n, oh, ow, 4)
+    for i in range(n):
+        if order == "convert":
+            want = oracle.pipeline(imgs[i], **o)
+        else:
+            want = imgs[i]
+            if o["resize_mode"] is not None: want = oracle.resize(want, o["resize_mode"])
+            if o["crop_mode"] is not None: want = oracle.crop(want, o["crop_mode"])
+            if o["extend_mode"] is not None: want = oracle.extend(want, o["extend_mode"], fill if fill is not None else WHITE)
+        _close(got[i], want, mean_tol=0.05)
+
+
+def test_jpeg_batch_device_writes_only_its_planes():
+    import torch
+    n, w, h = 2, 250, 131
+    imgs = np.stack([noise_image(w, h, 50 + i) for i in range(n)])
+    src = torch.from_numpy(imgs).cuda()
+    g = ll.jpeg_geometry(w, h)
+    ql, qc = ll.jpeg_quant_table(70, 0), ll.jpeg_quant_table(70, 1)
+    ny, nc, guard = n * g.y_HB * g.y_WB * 64, n * g.c_HB * g.c_WB * 64, 4096
+    bufs = [torch.full((k + 2 * guard,), 0x5A5A, dtype=torch.int16, device="cuda") for k in (ny, nc, nc)]
+    ll.jpeg_frontend_batch_device(src.data_ptr(), n, w, h, ql, qc, *[b.data_ptr() + 2 * guard for b in bufs],
+                                  torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    for b, k in zip(bufs, (ny, nc, nc)):
+        hb = b.cpu().numpy()
+        assert (hb[:guard] == 0x5A5A).all() and (hb[guard + k:] == 0x5A5A).all(), "kernel wrote outside its plane"
+    for i in range(n):
+        want = oracle.jpeg_frontend(imgs[i], np.array(ql, np.uint16), np.array(qc, np.uint16))
+        got_y = bufs[0].cpu().numpy()[guard:guard + ny].reshape(n, g.y_HB, g.y_WB, 64)[i]
+        assert np.array_equal(got_y, want[0])
