@@ -253,8 +253,8 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         // band start of the group after next, fetched a group early: ring steps entirely above a group's successor's
         // band start are free once the group is done
         int a_next = n_iter > 1 ? int(__ldg(p.recs + size_t(rec0 + 1) * p.rec_words + 1)) : ye;
-#pragma unroll 1
         uint32_t buf = 0, par = 0;
+#pragma unroll 1
         for (int it = 0; it < n_iter; it++) {
             const int a_cur = a_next;
             a_next = it + 2 < n_iter ? int(__ldg(p.recs + size_t(rec0 + it + 2) * p.rec_words + 1)) : ye;
@@ -271,8 +271,8 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         const int ring_rows = int(p.ring_rows);
         int a0 = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words + 1)) : 0;
         int need = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words + 2)) : 0;
-#pragma unroll 1
         uint32_t buf = 0, par = 0;
+#pragma unroll 1
         for (int it = 0; it < n_iter; it++) {
             const int a0_cur = a0, need_cur = need;
             if (it + 1 < n_iter) {                           // next group's header, in flight while this one is waited for
@@ -314,8 +314,8 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             for (int d = 0; d < NDIG; d++) s2[l][d] = p.s2[l][d];
         int j_next = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words)) : 0;
 
-#pragma unroll 1
         uint32_t buf = 0, par = 0;
+#pragma unroll 1
         for (int it = 0; it < n_iter; it++, buf = buf + 1 == p.vbufs ? 0 : buf + 1, par ^= buf == 0 ? 1u : 0u) {
             const int j = j_next;
             if (it + 1 < n_iter) j_next = int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words));
@@ -378,8 +378,8 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         const int ring_rows = int(p.ring_rows);
         const uint32_t boff0 = uint32_t(w1 * upw_all) * (UNIT * 16u);
 
-#pragma unroll 1
         uint32_t buf = 0, par = 0;
+#pragma unroll 1
         for (int it = 0; it < n_iter; it++, buf = buf + 1 == p.vbufs ? 0 : buf + 1, par ^= buf == 0 ? 1u : 0u) {
             const uint32_t *rec = recbuf + uint32_t(it & (kRecBufs - 1)) * p.rec_words;
             mbar_wait(&tail.go[buf], par);
