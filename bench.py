@@ -335,7 +335,7 @@ def main():
                 raise SystemExit("e2e batch failed: " + lib.slimg_b200_last_error().decode())
 
         e2e_steps = max(3, min(args.steps, 8))
-        for _ in range(2):                    # warm-up: stream-ordered pool growth, plan upload, page pinning
+        for _ in range(3):                    # warm-up: stream-ordered pool growth, plan upload, page pinning
             e2e_step()
         barrier()
         step_ms = []
