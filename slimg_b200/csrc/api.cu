@@ -191,16 +191,19 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
         // four adjacent canvas columns (aligned to 4) may share one window of max_taps + 2 intermediate values?
         // (measured on B200, C4b: the 4-column variant needs 103 registers, halves the occupancy and runs at 171 us against
         // 94 us for one column per thread -- kept behind SLIMG_B200_FEW_K4 for the next round)
-        p.few_k = (tile_w % 4 == 0 && g.Rw > g.vw && std::getenv("SLIMG_B200_FEW_K4") != nullptr) ? 4 : 1;
-        for (int64_t fxg = 0; fxg < int64_t(g.fw) && p.few_k == 4; fxg += 4) {
+        const char *fk_env = std::getenv("SLIMG_B200_FEW_K");
+        const int fk = fk_env ? std::atoi(fk_env) : (std::getenv("SLIMG_B200_FEW_K4") ? 4 : 1);
+        p.few_k = ((fk == 2 || fk == 4) && tile_w % fk == 0 && g.Rw > g.vw) ? fk : 1;
+        // an aligned group of few_k columns must fit one window of max_taps + few_k / 2 intermediate values
+        for (int64_t fxg = 0; fxg < int64_t(g.fw) && p.few_k > 1; fxg += p.few_k) {
             int lo = INT32_MAX, hi = INT32_MIN;
-            for (int64_t fx = std::max<int64_t>(fxg, g.fox); fx < std::min<int64_t>(std::min<int64_t>(fxg + 4, g.fw), int64_t(g.fox) + g.pw); fx++) {
+            for (int64_t fx = std::max<int64_t>(fxg, g.fox); fx < std::min<int64_t>(std::min<int64_t>(fxg + p.few_k, g.fw), int64_t(g.fox) + g.pw); fx++) {
                 const int64_t ox = fx - g.fox + g.px;
                 if (tx.count[ox] == 0) continue;
                 lo = std::min(lo, tx.left[ox]);
                 hi = std::max(hi, tx.left[ox]);
             }
-            if (lo <= hi && hi - lo > 2) p.few_k = 1;
+            if (lo <= hi && hi - lo > p.few_k / 2) p.few_k = 1;
         }
     }
     p.tile_x0 = (const int32_t *)plan->tx0.p;

@@ -160,39 +160,57 @@ __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizePa
     const int span = has_pixels ? p.tile_span[blockIdx.x] : 0;
     const int nt_y = p.ay.max_taps, nt_x = p.ax.max_taps;
 
-    // source rows of the tile (one thread per output row, reduced through shared memory)
+    // source rows of the tile (one thread per output row, reduced through shared memory); the row's band start and
+    // fill weight are kept in shared memory so that stage 1 starts a row without waiting for global loads
     __shared__ int s_ylo, s_yhi;
+    __shared__ int s_left[64];
+    __shared__ float s_fillw[64];
     if (threadIdx.x == 0) { s_ylo = INT_MAX; s_yhi = 0; }
     __syncthreads();
     if (int(threadIdx.x) < nrows) {
         const int n = p.ay.count[oy0 + threadIdx.x], l = p.ay.left[oy0 + threadIdx.x];
+        s_left[threadIdx.x] = n > 0 ? l : -1;
+        s_fillw[threadIdx.x] = p.ay.fillw[oy0 + threadIdx.x];
         if (n > 0) { atomicMin(&s_ylo, l); atomicMax(&s_yhi, l + n); }
     }
-    __syncthreads();
-    const int ylo = s_ylo == INT_MAX ? 0 : s_ylo, yhi = s_ylo == INT_MAX ? 0 : s_yhi;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    constexpr int kW = kThreads / 32;
-    // stage 0: source tile as f32 (a warp per source row) + the vertical weights of the tile's rows
-    for (int r = warp; r < yhi - ylo + NT; r += kW) {
-        const uint32_t *row = src + size_t(p.ry + ylo + r) * p.sw + (p.rx + xs0);
-        const bool real = r < yhi - ylo;
-        for (int c = lane; c < span; c += 32)
-            S[r * p.span_max + c] = real ? unpack_rgba_fast(__ldg(row + c)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    }
+    // the vertical weights of the tile's rows (independent of the reduction: in flight across the barrier)
     for (int item = threadIdx.x; item < nrows * NT; item += kThreads) {
         const int r = item / NT, i = item - r * NT;
         wy[item] = i < nt_y ? p.ay.w[size_t(oy0 + r) * nt_y + i] : 0.0f;
     }
     __syncthreads();
+    const int ylo = s_ylo == INT_MAX ? 0 : s_ylo, yhi = s_ylo == INT_MAX ? 0 : s_yhi;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int kW = kThreads / 32;
+    // stage 0: source tile as f32, a warp per source row, four rows' loads in flight per lane
+    {
+        const int nreal = yhi - ylo, nall = nreal + NT;
+        const uint32_t *base = src + size_t(p.ry + ylo) * p.sw + (p.rx + xs0);
+        for (int c = lane; c < span; c += 32)
+            for (int r0 = warp; r0 < nall; r0 += 4 * kW) {
+                uint32_t v[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int r = r0 + u * kW;
+                    v[u] = r < nreal ? __ldg(base + size_t(r) * p.sw + c) : 0u;
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int r = r0 + u * kW;
+                    if (r < nall) S[r * p.span_max + c] = r < nreal ? unpack_rgba_fast(v[u]) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                }
+            }
+    }
+    __syncthreads();
 
     // stage 1: vertical taps, a warp per output row (row constants are warp-uniform)
     for (int r = warp; r < nrows; r += kW) {
-        const int oy = oy0 + r;
-        const float4 *s0 = S + (p.ay.count[oy] > 0 ? p.ay.left[oy] - ylo : 0) * p.span_max;
+        const int l = s_left[r];
+        const float4 *s0 = S + (l >= 0 ? l - ylo : 0) * p.span_max;
         float w[NT];
 #pragma unroll
         for (int i = 0; i < NT; i++) w[i] = wy[r * NT + i];
-        const float fwgt = p.ay.fillw[oy];
+        const float fwgt = s_fillw[r];
         const float4 acc0 = make_float4(p.fill_pre[0] * fwgt, p.fill_pre[1] * fwgt, p.fill_pre[2] * fwgt, p.fill_pre[3] * fwgt);
         for (int c = lane; c < span + NT + 2; c += 32) {
             float4 acc = acc0;
@@ -214,26 +232,27 @@ __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizePa
     // columns' common window are loaded once per row and reused by all four columns -- the kernel is bound by shared-
     // memory bandwidth otherwise (one 16-byte load per 4 FMAs).  Weights are re-based to the common window, zero outside
     // a column's own taps: extra zero-weight FMAs do not change the f32 sums.
-    constexpr int U = K == 1 ? NT : NT + 2;
+    constexpr int U = K == 1 ? NT : K == 2 ? NT + 1 : NT + 2;
     const int tw = fx1 - fx0, th = fy1 - fy0;
     const int ngx = p.tile_w / K;
     const int gx = threadIdx.x % ngx, ty0 = threadIdx.x / ngx, tys = kThreads / ngx;
     const int tx = gx * K;
     if (tx < tw) {
         float wx[K][U];
-        float fwgt[K];
+        float4 acc0[K];                 // the fill's share of the column's weights: the sum starts there
         bool valid[K];
         int toff = INT_MAX;
 #pragma unroll
         for (int k = 0; k < K; k++) {
             const int fx = fx0 + tx + k;
             valid[k] = has_pixels && fx >= ix0 && fx < ix1;
-            fwgt[k] = 0.0f;
+            float fwgt = 0.0f;
             if (valid[k]) {
                 const int ox = ox0 + (fx - ix0);
-                fwgt[k] = p.ax.fillw[ox];
+                fwgt = p.ax.fillw[ox];
                 if (p.ax.count[ox] > 0) toff = min(toff, p.ax.left[ox] - xs0);
             }
+            acc0[k] = make_float4(p.fill_pre[0] * fwgt, p.fill_pre[1] * fwgt, p.fill_pre[2] * fwgt, p.fill_pre[3] * fwgt);
         }
         if (toff == INT_MAX) toff = 0;
 #pragma unroll
@@ -250,17 +269,22 @@ __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizePa
                 }
             }
         }
-        for (int ty = ty0; ty < th; ty += tys) {
-            const int fy = fy0 + ty;
+        // rows [vy0, vy1) of the tile carry pixels, the others are fill; addresses advance by constants
+        const int vy0 = has_pixels ? iy0 - fy0 : th, vy1 = has_pixels ? iy1 - fy0 : th;
+        int vi = (ty0 - vy0) * vpitch + toff;
+        const int vstep = tys * vpitch;
+        uint32_t *o = dst + size_t(fy0 + ty0) * p.fw + fx0 + tx;
+        const size_t ostep = size_t(tys) * p.fw;
+        const bool vec_ok = K > 1 && tx + K - 1 < tw && ((reinterpret_cast<uintptr_t>(o) | (ostep * 4)) & (4 * K - 1)) == 0;
+        for (int ty = ty0; ty < th; ty += tys, vi += vstep, o += ostep) {
             uint32_t out[K];
 #pragma unroll
             for (int k = 0; k < K; k++) out[k] = p.fill_post;
-            if (fy >= iy0 && fy < iy1) {
-                const float4 *t = V + (fy - iy0) * vpitch + toff;
+            if (ty >= vy0 && ty < vy1) {
+                const float4 *t = V + vi;
                 float4 acc[K];
 #pragma unroll
-                for (int k = 0; k < K; k++)
-                    acc[k] = make_float4(p.fill_pre[0] * fwgt[k], p.fill_pre[1] * fwgt[k], p.fill_pre[2] * fwgt[k], p.fill_pre[3] * fwgt[k]);
+                for (int k = 0; k < K; k++) acc[k] = acc0[k];
 #pragma unroll
                 for (int j = 0; j < U; j++) {
                     const float4 v = t[j];
@@ -274,9 +298,10 @@ __global__ void __launch_bounds__(kThreads) resize_fewtaps_kernel(const ResizePa
                 for (int k = 0; k < K; k++)
                     if (valid[k]) out[k] = pack_rgba_fast(acc[k]);
             }
-            uint32_t *o = dst + size_t(fy) * p.fw + fx0 + tx;
-            if (K == 4 && tx + 3 < tw && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+            if (K == 4 && vec_ok) {
                 *reinterpret_cast<uint4 *>(o) = make_uint4(out[0], out[K > 1 ? 1 : 0], out[K > 2 ? 2 : 0], out[K > 3 ? 3 : 0]);
+            } else if (K == 2 && vec_ok) {
+                *reinterpret_cast<uint2 *>(o) = make_uint2(out[0], out[K > 1 ? 1 : 0]);
             } else {
 #pragma unroll
                 for (int k = 0; k < K; k++)
@@ -303,19 +328,22 @@ cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cuda
     }
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     // few taps on both axes (upscales): the register-weight kernel; its source tile holds at most tile_h + kNT rows
-    const bool few = p.few_rows_max > 0 && p.ax.max_taps <= kNT && p.ay.max_taps <= kNT && kThreads % p.tile_w == 0 && !std::getenv("SLIMG_B200_NO_FEWTAPS");
+    const bool few = p.few_rows_max > 0 && p.tile_h <= 64 && p.ax.max_taps <= kNT && p.ay.max_taps <= kNT && kThreads % p.tile_w == 0 && !std::getenv("SLIMG_B200_NO_FEWTAPS");
     const int src_rows_max = p.few_rows_max;
     const int nt = std::max(p.ax.max_taps, p.ay.max_taps) <= 7 ? 7 : 8;
     const size_t span_alloc = size_t(p.span_max > 0 ? p.span_max : 1);
     const size_t smem_few = (size_t(src_rows_max + nt) * span_alloc + size_t(p.tile_h) * (span_alloc + nt + 2)) * sizeof(float4) +
                             size_t(p.tile_h) * nt * sizeof(float);
     if (few && smem_few <= 200 * 1024) {
-        const bool k4 = p.few_k == 4 && p.tile_w % 4 == 0 && kThreads % (p.tile_w / 4) == 0;
-        auto kern = nt == 7 ? (k4 ? resize_fewtaps_kernel<7, 4> : resize_fewtaps_kernel<7, 1>) : (k4 ? resize_fewtaps_kernel<8, 4> : resize_fewtaps_kernel<8, 1>);
+        const int k = (p.few_k == 4 || p.few_k == 2) && p.tile_w % p.few_k == 0 && kThreads % (p.tile_w / p.few_k) == 0 ? p.few_k : 1;
+        auto kern = nt == 7 ? (k == 4 ? resize_fewtaps_kernel<7, 4> : k == 2 ? resize_fewtaps_kernel<7, 2> : resize_fewtaps_kernel<7, 1>)
+                            : (k == 4 ? resize_fewtaps_kernel<8, 4> : k == 2 ? resize_fewtaps_kernel<8, 2> : resize_fewtaps_kernel<8, 1>);
         static thread_local int few_dev = -1;
         if (few_dev != dev) {
             cudaError_t e = cudaFuncSetAttribute(resize_fewtaps_kernel<7, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             if (e == cudaSuccess) e = cudaFuncSetAttribute(resize_fewtaps_kernel<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(resize_fewtaps_kernel<7, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(resize_fewtaps_kernel<8, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             if (e == cudaSuccess) e = cudaFuncSetAttribute(resize_fewtaps_kernel<7, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             if (e == cudaSuccess) e = cudaFuncSetAttribute(resize_fewtaps_kernel<8, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             if (e != cudaSuccess) return e;

@@ -47,7 +47,7 @@ struct ResizeParams {
     uint32_t fill_post;                // packed RGBA of the rest of the canvas
     // tiling (generic kernel)
     int32_t tile_w, tile_h, span_max;
-    int32_t few_k;                     // 4: aligned groups of 4 canvas columns share a tap window of max_taps + 2 (upscales); else 1
+    int32_t few_k;                     // 2 / 4: aligned groups of that many canvas columns share a tap window of max_taps + few_k / 2 (upscales); else 1
     int32_t few_rows_max;              // > 0: both axes have <= 8 taps; most source rows a tile row-block reads
     const int32_t *tile_x0;            // [tiles_x] first source-rect column a tile column needs
     const int32_t *tile_span;          // [tiles_x] number of source-rect columns it needs
