@@ -229,7 +229,14 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     const char *early_env = std::getenv("SLIMG_B200_EARLY_GO");
     const char *unit_env = std::getenv("SLIMG_B200_UNIT");
     const char *vbufs_env = std::getenv("SLIMG_B200_VBUFS");
-    out.vbufs = vbufs_env ? uint32_t(std::min(kVfMaxVBufs, std::max(2, std::atoi(vbufs_env)))) : 4u;
+    // Bands of at most 3 chunks (ratios up to ~5.5x): a group's pass 1 is short, three V buffers keep it fed and the
+    // shared memory of the fourth buys a wider strip (measured on B200: 4000x3000 -> 800, 40-column strips with 3 V
+    // buffers 11.9 us per image against 13.7 us for 32 columns with 4; 7680x4320 -> 1920 unchanged).  Longer bands
+    // (the 7.5x of the headline config) keep 4 V buffers and two groups of ring look-ahead.
+    const bool short_bands = out.nch1 <= 3 && !std::getenv("SLIMG_B200_NO_SHORT_BAND_POLICY");
+    out.vbufs = vbufs_env ? uint32_t(std::min(kVfMaxVBufs, std::max(2, std::atoi(vbufs_env)))) : (short_bands ? 3u : 4u);
+    const double look_min = short_bands ? 1.5 : kLookGroups;
+    const int min_p1 = short_bands ? 7 : 1;              // pass-1 warps a strip must leave (tiles take one warp each)
     uint32_t cols = 0;
     int unit = 0;
     bool early = false;
@@ -280,7 +287,8 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         while (rr + 16 <= ring_cap && smem_for(best_blk, rr + 16, pch, pv) <= kSmemBudget) rr += 16;
         if (!fb_cols) { fb_cols = even; fb_ring = rr; fb_unit = best_u; fb_early = e; }
         const double look = (double(rr) - 32.0 * out.nch1) / rows_per_group;
-        if (look >= kLookGroups || cols_env) { cols = even; unit = best_u; early = e; ring_rows = rr; }
+        const int n_p1 = kVfWarps - 2 - int((even + 7) / 8);
+        if ((look >= look_min && n_p1 >= min_p1) || cols_env) { cols = even; unit = best_u; early = e; ring_rows = rr; }
     }
     if (cols == 0) { cols = fb_cols; unit = fb_unit; early = fb_early; ring_rows = fb_ring; }
     if (cols == 0) return;
