@@ -1,5 +1,5 @@
 """Device-resident timing of one pipeline geometry (CUDA events, L2 flushed by batch size).
-usage: time_config.py NAME   with NAME in c1 | c3 | c3conv | c4a | c4b | c2"""
+usage: time_config.py NAME   with NAME in c1 | c3 | c3conv | c4a | c4b | c2 | r6 | r55 | r3 | r2 | r15 (other ratios of a 24 MP source)"""
 import json, sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -11,6 +11,11 @@ CFG = {
     "c3": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(800), crop=ll.CropMode.ASPECT_RATIO(16, 9), extend=ll.ExtendMode.ASPECT_RATIO(1, 1), fill_color=ll.FillColor.SOLID(255, 255, 255, 255)), ll.ORDER_CHAIN, 64),
     "c3conv": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(800), crop=ll.CropMode.ASPECT_RATIO(16, 9), extend=ll.ExtendMode.ASPECT_RATIO(1, 1), fill_color=ll.FillColor.SOLID(255, 255, 255, 255)), ll.ORDER_CONVERT, 64),
     "c4a": (7680, 4320, dict(resize=ll.ResizeMode.WIDTH(1920)), ll.ORDER_CONVERT, 32),
+    "r6": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(1000)), ll.ORDER_CONVERT, 64),
+    "r55": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(1090)), ll.ORDER_CONVERT, 64),
+    "r3": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(2000)), ll.ORDER_CONVERT, 32),
+    "r2": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(3000)), ll.ORDER_CONVERT, 32),
+    "r15": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(4000)), ll.ORDER_CONVERT, 32),
     "c4b": (1024, 1024, dict(resize=ll.ResizeMode.SCALE(4.0)), ll.ORDER_CONVERT, 64),
 }
 name = sys.argv[1]
