@@ -229,11 +229,12 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     const char *early_env = std::getenv("SLIMG_B200_EARLY_GO");
     const char *unit_env = std::getenv("SLIMG_B200_UNIT");
     const char *vbufs_env = std::getenv("SLIMG_B200_VBUFS");
-    // Bands of at most 3 chunks (ratios up to ~5.5x): a group's pass 1 is short, three V buffers keep it fed and the
-    // shared memory of the fourth buys a wider strip (measured on B200: 4000x3000 -> 800, 40-column strips with 3 V
-    // buffers 11.9 us per image against 13.7 us for 32 columns with 4; 7680x4320 -> 1920 unchanged).  Longer bands
-    // (the 7.5x of the headline config) keep 4 V buffers and two groups of ring look-ahead.
-    const bool short_bands = out.nch1 <= 3 && !std::getenv("SLIMG_B200_NO_SHORT_BAND_POLICY");
+    // Bands of exactly 3 chunks (ratios of about 4.5x to 6.5x): three V buffers keep pass 1 fed and the shared memory
+    // of the fourth buys a wider strip or a deeper ring (measured on B200: 4000x3000 -> 800, 40-column strips with 3 V
+    // buffers 11.9 us per image against 13.7 us for 32 columns with 4; 6000 -> 1000 20.9 against 24.9 us; 6000 -> 1090
+    // 24.5 against 28.9).  Longer bands (the 7.5x of the headline config) and shorter ones (4x and below, where the
+    // same rule measured 4-11 % slower) keep 4 V buffers and two groups of ring look-ahead.
+    const bool short_bands = out.nch1 == 3 && !std::getenv("SLIMG_B200_NO_SHORT_BAND_POLICY");
     out.vbufs = vbufs_env ? uint32_t(std::min(kVfMaxVBufs, std::max(2, std::atoi(vbufs_env)))) : (short_bands ? 3u : 4u);
     const double look_min = short_bands ? 1.5 : kLookGroups;
     const int min_p1 = short_bands ? 7 : 1;              // pass-1 warps a strip must leave (tiles take one warp each)
