@@ -117,8 +117,8 @@ __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
 __device__ __forceinline__ float int_to_float(int x) { return __int_as_float(x + 0x4B400000) - 12582912.0f; }
 
 __device__ __forceinline__ uint32_t quantize_channel(float t) {
-    t = fminf(fmaxf(t, 0.0f), 255.0f);      // clamp, then f32::round (half away; value is >= 0)
-    return uint32_t(floorf(t + 0.5f));
+    t = fminf(fmaxf(t, 0.0f), 255.0f) + 0.5f;      // clamp, then f32::round (half away; value is >= 0) = floor(t + 0.5):
+    return __float_as_uint(__fadd_rz(t, 8388608.0f)) & 0xffu;      // 2^23 + floor(t) by truncation, no FRND / F2I
 }
 
 struct SmemTail {                             // after the ring, the V planes and the two group records
