@@ -80,6 +80,27 @@ __global__ void k_prmt(uint32_t *out, int n, uint32_t sel) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// integer-pipe rates that decide K3's instruction choices: 16 independent chains per thread, one op per chain per step
+#define INT_KERNEL(NAME, EXPR)                                                                  \
+    __global__ void NAME(uint32_t *out, int n, uint32_t m) {                                    \
+        uint32_t acc[16];                                                                       \
+        for (int j = 0; j < 16; j++) acc[j] = threadIdx.x * 2654435761u + j;                    \
+        for (int i = 0; i < n; i++) {                                                           \
+            _Pragma("unroll") for (int j = 0; j < 16; j++) { const uint32_t x = acc[j], y = acc[(j + 1) & 15]; acc[j] = (EXPR); } \
+        }                                                                                       \
+        uint32_t s = 0;                                                                         \
+        for (int j = 0; j < 16; j++) s ^= acc[j];                                               \
+        out[blockIdx.x * blockDim.x + threadIdx.x] = s;                                         \
+    }
+INT_KERNEL(k_imad, x * m + y)
+INT_KERNEL(k_imadhi, __umulhi(x, m) + y)
+INT_KERNEL(k_shf, __funnelshift_r(x, y, m))
+INT_KERNEL(k_shr, (uint32_t(int(x) >> (m & 31)) ^ y))
+INT_KERNEL(k_lop3, (x & m) ^ y)
+INT_KERNEL(k_iadd3, x + y + m)
+INT_KERNEL(k_dp4a, __dp4a(x, m, y))
+INT_KERNEL(k_f2isat, ([&] { uint32_t r; asm("cvt.rzi.sat.u8.f32 %0, %1;" : "=r"(r) : "f"(__uint_as_float((x & 0x007fffffu) | 0x42000000u))); return r + y; }()))
+
 __global__ void k_i2f(float *out, int n) {
     uint32_t v[16];
     float acc[16];
@@ -141,6 +162,17 @@ int main() {
     printf("prmt                : %8.3f ms  %8.2f Tops/s  (%.1f op/clk/SM @1.9GHz)\n", ms, warps * 32 * ITERS * 16 / ms / 1e9, warps * 32 * ITERS * 16 / (ms * 1e-3) / sms / 1.9e9);
     ms = time_ms([&] { k_i2f<<<blocks, threads>>>((float *)buf, ITERS); });
     printf("and+i2f+shr chain   : %8.3f ms  %8.2f Tcvt/s  (%.1f cvt/clk/SM @1.9GHz)\n", ms, warps * 32 * ITERS * 16 / ms / 1e9, warps * 32 * ITERS * 16 / (ms * 1e-3) / sms / 1.9e9);
+#define RUN_INT(NAME, LABEL, ARG)                                                                                \
+    ms = time_ms([&] { NAME<<<blocks, threads>>>((uint32_t *)buf, ITERS, ARG); });                               \
+    printf("%-20s: %8.3f ms  %8.2f Tops/s  (%.1f op/clk/SM @1.9GHz)\n", LABEL, ms, warps * 32 * ITERS * 16 / ms / 1e9, warps * 32 * ITERS * 16 / (ms * 1e-3) / sms / 1.9e9);
+    RUN_INT(k_imad, "imad (lo)", 2654435761u)
+    RUN_INT(k_imadhi, "imad.hi + add", 1u << 21)
+    RUN_INT(k_shf, "shf (funnel)", 11u)
+    RUN_INT(k_shr, "shr.s32 + xor", 11u)
+    RUN_INT(k_lop3, "lop3 (and-xor)", 0x00ff00ffu)
+    RUN_INT(k_iadd3, "iadd3", 12345u)
+    RUN_INT(k_dp4a, "dp4a u8*s8", 0x4c8b1d00u)
+    RUN_INT(k_f2isat, "lop+f2i.sat.u8+add", 0u)
     k_denorm<<<1, 32>>>((float *)buf);
     float h[2];
     CK(cudaMemcpy(h, buf, 8, cudaMemcpyDeviceToHost));
