@@ -40,12 +40,32 @@ constexpr int kBlocks = kBlocksY + 2 * kBlocksC;  // 192 blocks per CTA, one thr
 
 #define SLIMG_FIX(x) int((x) * 65536.0 + 0.5)
 
+// The three dot products of rgb_ycc_convert as IDP.4A on the packed pixel: every 16-bit coefficient is split into a
+// signed high digit and an unsigned low digit (c = 256 hi + lo), the 0.5 coefficient (32768 = 2 * 64 * 256) is spread
+// over two byte slots of a permuted pixel.  6 IDP.4A + 2 PRMT + 3 IMAD instead of unpacking three bytes and 9 IMAD; the
+// integer sums are identical (no intermediate exceeds 2^25).
+__host__ __device__ constexpr uint32_t pack4(int a, int b, int c, int d) {
+    return uint32_t(a & 0xff) | (uint32_t(b & 0xff) << 8) | (uint32_t(c & 0xff) << 16) | (uint32_t(d & 0xff) << 24);
+}
+static_assert(SLIMG_FIX(0.29900) == 76 * 256 + 139 && SLIMG_FIX(0.58700) == 150 * 256 + 70 && SLIMG_FIX(0.11400) == 29 * 256 + 47, "Y digits");
+static_assert(-SLIMG_FIX(0.16874) == -44 * 256 + 205 && -SLIMG_FIX(0.33126) == -85 * 256 + 51 && SLIMG_FIX(0.50000) == 128 * 256, "Cb digits");
+static_assert(-SLIMG_FIX(0.41869) == -108 * 256 + 209 && -SLIMG_FIX(0.08131) == -21 * 256 + 47, "Cr digits");
+__device__ __forceinline__ int dp4a_uu(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {       // unsigned bytes of a, signed bytes of b
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 __device__ __forceinline__ void rgb_to_ycc(uint32_t px, uint8_t &y, uint8_t &cb, uint8_t &cr) {
-    const int r = px & 0xff, g = (px >> 8) & 0xff, b = (px >> 16) & 0xff;
     constexpr int half = 1 << 15, cboff = 128 << 16;
-    y  = uint8_t((SLIMG_FIX(0.29900) * r + SLIMG_FIX(0.58700) * g + SLIMG_FIX(0.11400) * b + half) >> 16);
-    cb = uint8_t((-SLIMG_FIX(0.16874) * r - SLIMG_FIX(0.33126) * g + SLIMG_FIX(0.50000) * b + cboff + half - 1) >> 16);
-    cr = uint8_t((SLIMG_FIX(0.50000) * r - SLIMG_FIX(0.41869) * g - SLIMG_FIX(0.08131) * b + cboff + half - 1) >> 16);
+    const uint32_t rgbb = __byte_perm(px, 0u, 0x2210), rgbr = __byte_perm(px, 0u, 0x0210);
+    y  = uint8_t((dp4a_uu(px, pack4(76, 150, 29, 0), 0) * 256 + dp4a_uu(px, pack4(139, 70, 47, 0), half)) >> 16);
+    cb = uint8_t((dp4a_us(rgbb, pack4(-44, -85, 64, 64), 0) * 256 + dp4a_uu(px, pack4(205, 51, 0, 0), cboff + half - 1)) >> 16);
+    cr = uint8_t((dp4a_us(rgbr, pack4(64, -108, -21, 64), 0) * 256 + dp4a_uu(px, pack4(0, 209, 47, 0), cboff + half - 1)) >> 16);
 }
 
 __device__ __forceinline__ int descale(int x, int n) { return (x + (1 << (n - 1))) >> n; }
