@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SLIMG_B200_ABI_VERSION 1
+#define SLIMG_B200_ABI_VERSION 2
 
 /* ---- status = SlimgError tag (crates/slimg-ffi/src/lib.rs:195-227) ---- */
 typedef enum {
@@ -152,17 +152,34 @@ typedef struct {
     slimg_jpeg_geometry geom;
     uint16_t qt_luma[64], qt_chroma[64];
     int16_t *y, *cb, *cr;              /* host; released by slimg_b200_jpeg_coefs_free */
+    /* the same planes BEFORE quantisation (the DCT output, scaled by 8 as jfdctint.c leaves it): what MozJPEG keeps
+     * per block for its trellis pass.  NULL unless SLIMG_JPEG_UNQUANTISED was asked for. */
+    int16_t *y_uq, *cb_uq, *cr_uq;
 } slimg_jpeg_coefs;
 
 enum { SLIMG_QT_ANNEX_K = 0,            /* libjpeg-turbo jcparam.c:73-92 */
        SLIMG_QT_MOZJPEG = 1 };          /* MozJPEG default table set 3, luma == chroma */
+
+/* flags of the JPEG entry points */
+enum { SLIMG_JPEG_UNQUANTISED = 1 };    /* also return the un-quantised coefficient planes */
 
 void slimg_b200_jpeg_geometry(uint32_t w, uint32_t h, slimg_jpeg_geometry *g);
 /* jpeg_set_quality(q, force_baseline = FALSE): jcparam.c:28-65,130-168 */
 void slimg_b200_jpeg_quant_table(int quality, int which /*0 luma,1 chroma*/, int base, uint16_t out[64]);
 slimg_status slimg_b200_jpeg_frontend(const slimg_image *in, const uint16_t qt_luma[64],
                                       const uint16_t qt_chroma[64], slimg_jpeg_coefs *out);
+slimg_status slimg_b200_jpeg_frontend_ex(const slimg_image *in, const uint16_t qt_luma[64],
+                                         const uint16_t qt_chroma[64], uint32_t flags, slimg_jpeg_coefs *out);
 void slimg_b200_jpeg_coefs_free(slimg_jpeg_coefs *c);
+
+/* convert(image, {format: Jpeg, ...}) up to the entropy coder (pipeline.rs:66-95 -> codec/jpeg.rs:51-72): the pixel
+ * stages and the JPEG front end run back to back on the device -- the resized image never leaves HBM, only the
+ * coefficient planes come back.  out->geom.width / height are the dimensions PipelineResult reports
+ * (pipeline.rs:97-102).  Feed the planes to the reference encoder with jpeg_write_coefficients (jctrans.c:43), see
+ * INTEGRATION.md. */
+slimg_status slimg_b200_pipeline_jpeg(const slimg_image *in, const slimg_pipeline_options *opts, int order,
+                                      const uint16_t qt_luma[64], const uint16_t qt_chroma[64], uint32_t flags,
+                                      slimg_jpeg_coefs *out);
 
 /* ---- batched, device-resident variants (what bench.py's `value` times) ----
  * `src` / `dst` are DEVICE pointers on the current CUDA device; images are packed back to back
@@ -175,12 +192,31 @@ slimg_status slimg_b200_pipeline_batch_device(const uint8_t *src, uint32_t n, ui
 slimg_status slimg_b200_jpeg_frontend_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
                                                    const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
                                                    int16_t *y, int16_t *cb, int16_t *cr, void *stream);
+/* same, with the un-quantised planes as well (all three or none) */
+slimg_status slimg_b200_jpeg_frontend_batch_device_ex(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
+                                                      const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                                                      int16_t *y, int16_t *cb, int16_t *cr,
+                                                      int16_t *y_uq, int16_t *cb_uq, int16_t *cr_uq, void *stream);
+/* pixel pipeline + JPEG front end on device-resident batches; `pixels` is device scratch for the n final images
+ * (n * out_w*out_h*4 bytes, the pipeline's output, which the front end reads back from HBM / L2) */
+slimg_status slimg_b200_pipeline_jpeg_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
+                                                   const slimg_pipeline_options *opts, int order,
+                                                   const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                                                   uint8_t *pixels, size_t pixels_capacity,
+                                                   int16_t *y, int16_t *cb, int16_t *cr,
+                                                   int16_t *y_uq, int16_t *cb_uq, int16_t *cr_uq, void *stream);
 
 /* ---- batched, host buffers: the `--jobs` scheduler (cli/src/commands/mod.rs:64-72 and the
- * par_iter sites crop.rs:112, extend.rs:114, convert.rs:60).  Images are independent; they are
- * dealt to `n_devices` GPUs x `streams_per_device` in-flight slots through pinned staging
- * buffers.  Per-image failures are isolated like ErrorCollector (mod.rs:113-145):
- * statuses[i] carries image i's status and the call returns the number of failed images. ---- */
+ * par_iter sites crop.rs:112, extend.rs:114, convert.rs:60).  Images are independent (and may differ in size: a
+ * directory of photos); they are dealt to `n_devices` GPUs x `streams_per_device` in-flight slots by a pull-based
+ * queue.  Host buffers may be pinned (slimg_b200_host_alloc: copied straight over PCIe) or ordinary pageable memory
+ * (a Rust Vec, Python bytes, a RustBuffer: staged through the library's pinned ring in chunks, the staging memcpy
+ * overlapping the DMA of the previous chunk).  Per-image failures are isolated like ErrorCollector
+ * (mod.rs:113-145): statuses[i] carries image i's status and the call returns the number of failed images.
+ *
+ * out[] is IN/OUT: an entry whose `data` is non-NULL with `len` >= the image's output size is a caller-owned
+ * destination and is written in place; otherwise (data == NULL, or too small) the library allocates the buffer
+ * (release with slimg_b200_image_free).  Zero-initialise entries you do not own. ---- */
 typedef struct {
     int32_t n_devices;           /* 0 = all visible devices */
     int32_t streams_per_device;  /* 0 = default (3) */
@@ -191,12 +227,28 @@ int32_t slimg_b200_pipeline_batch_host(const slimg_image *in, uint32_t n,
                                        const slimg_pipeline_options *opts, int order,
                                        const slimg_batch_config *cfg,
                                        slimg_image *out, slimg_status *statuses);
+/* the same scheduler for convert-to-JPEG: out[i] receives library-allocated coefficient planes
+ * (slimg_b200_jpeg_coefs_free each) */
+int32_t slimg_b200_pipeline_jpeg_batch_host(const slimg_image *in, uint32_t n,
+                                            const slimg_pipeline_options *opts, int order,
+                                            const uint16_t qt_luma[64], const uint16_t qt_chroma[64], uint32_t flags,
+                                            const slimg_batch_config *cfg,
+                                            slimg_jpeg_coefs *out, slimg_status *statuses);
 
 /* ---- misc ---- */
 const char *slimg_b200_last_error(void);          /* thread-local, never NULL */
 int32_t     slimg_b200_abi_version(void);
 int32_t     slimg_b200_device_count(void);        /* 0 when no usable CUDA device */
 uint64_t    slimg_b200_kernel_launches(void);     /* kernels this library has launched, process-wide */
+/* which kernel served the calling thread's last pixel-pipeline launch (tests and benches assert on it) */
+enum { SLIMG_PATH_NONE = 0, SLIMG_PATH_REMAP = 1,     /* K1: crop / extend only */
+       SLIMG_PATH_GENERIC = 2, SLIMG_PATH_FEWTAPS = 3, /* K2 f32 kernels (k2_resize.cu) */
+       SLIMG_PATH_HFIRST = 4,                          /* K2 H-first (k2_fast.cu): downscales beyond 9x */
+       SLIMG_PATH_VFIRST = 5,                          /* K2 integer tensor pipeline, mma.sync (k2_vfirst.cu) */
+       SLIMG_PATH_TC = 6,                              /* K2 integer tensor pipeline, tcgen05 (k2_tc.cu) */
+       SLIMG_PATH_TILE = 7 };                          /* K2 integer tile kernel: ratios below 3x and upscales (k2_tile.cu) */
+int32_t     slimg_b200_last_resize_path(void);
+uint64_t    slimg_b200_path_launches(int32_t path);  /* launches per path, process-wide */
 /* pinned host allocations for callers that want zero-copy staging (e2e bench) */
 void       *slimg_b200_host_alloc(size_t bytes);
 void        slimg_b200_host_free(void *p);

@@ -87,6 +87,18 @@ typedef int32_t (*slimg_decode_hook)(void *user, const uint8_t *data, size_t len
                                      int32_t *format, const char **message);
 void slimg_b200_set_codec_hooks(slimg_encode_hook enc, slimg_decode_hook dec, void *user);
 
+/* Format::Jpeg with the front end on the GPU: when this hook is installed, convert(.., Jpeg) runs
+ * crop -> extend -> resize -> RGB->YCbCr 4:2:0 -> FDCT -> quantisation on the device (slimg_b200_pipeline_jpeg), no
+ * pixel ever returns to the host, and the hook -- the reference library's ENTROPY coder -- receives the coefficient
+ * planes: with libjpeg-turbo / MozJPEG that is jpeg_write_coefficients (jctrans.c:43) in place of
+ * write_scanlines (crates/slimg-core/src/codec/jpeg.rs:66-76).  libslimg_jpeg_handoff.so
+ * (slimg_b200/jpeg_handoff/) provides slimg_jpeg_handoff_hook with this signature.
+ * table_base: SLIMG_QT_MOZJPEG (the reference encoder's tables) or SLIMG_QT_ANNEX_K; flags: SLIMG_JPEG_UNQUANTISED
+ * to also hand over the un-quantised planes (MozJPEG's trellis input).  Output buffer: malloc'ed by the hook. */
+typedef int32_t (*slimg_jpeg_coef_hook)(void *user, const slimg_jpeg_coefs *coefs, uint8_t quality,
+                                        uint8_t **out, size_t *out_len, const char **message);
+void slimg_b200_set_jpeg_coefficient_hook(slimg_jpeg_coef_hook hook, void *user, int32_t table_base, uint32_t flags);
+
 #ifdef __cplusplus
 }
 #endif

@@ -70,6 +70,9 @@ def build(force: bool = False) -> None:
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     if os.path.isdir("/root/reference") and (force or not os.path.exists(_REF_PATH)):
         subprocess.check_call(["make", "-C", os.path.join(_HERE, "ref_ljt"), "-s", "-j8"])
+    if os.path.isdir("/root/reference"):
+        from . import stage_ref_binding
+        stage_ref_binding.stage()      # the reference's own binding tests, unmodified, for tests/test_reference_binding.py
 
 
 _lib: Optional[C.CDLL] = None
@@ -235,6 +238,16 @@ def jpeg_frontend(img: np.ndarray, qt_luma: np.ndarray, qt_chroma: np.ndarray):
     ql = np.ascontiguousarray(qt_luma, np.uint16); qc = np.ascontiguousarray(qt_chroma, np.uint16)
     lib().so_jpeg_frontend(_ptr(img, _u8p), C.c_uint32(w), C.c_uint32(h), _ptr(ql, _u16p), _ptr(qc, _u16p),
                            _ptr(y, _i16p), _ptr(cb, _i16p), _ptr(cr, _i16p))
+    return y, cb, cr
+
+
+def jpeg_frontend_unquantised(img: np.ndarray):
+    """The DCT output before quantisation (jfdctint.c:143-286, scaled by 8), same plane layout."""
+    img = _as_rgba(img)
+    h, w = img.shape[:2]
+    y, cb, cr = _coef_planes(jpeg_geometry(w, h))
+    lib().so_jpeg_frontend_unquantised(_ptr(img, _u8p), C.c_uint32(w), C.c_uint32(h), _ptr(y, _i16p), _ptr(cb, _i16p),
+                                       _ptr(cr, _i16p))
     return y, cb, cr
 
 

@@ -474,6 +474,9 @@ void so_quantize(const int32_t ws[64], const uint16_t qt[64], int16_t out[64])
     }
 }
 
+/* qt == NULL: keep the DCT output un-quantised (what MozJPEG copies aside for its trellis pass, SURVEY.md App. B --
+ * mozjpeg-sys is not in the reference tree, so only the value, jfdctint.c's output, is pinned; that MozJPEG stores it
+ * per block is restated from memory) */
 static void so_do_block(const uint8_t *plane, size_t stride, uint32_t bx, uint32_t by,
                         const uint16_t qt[64], int16_t *out)
 {
@@ -482,7 +485,8 @@ static void so_do_block(const uint8_t *plane, size_t stride, uint32_t bx, uint32
         for (int c = 0; c < 8; c++)
             ws[r * 8 + c] = (int32_t)plane[((size_t)by * 8 + r) * stride + (size_t)bx * 8 + c] - 128; /* convsamp :373-400 */
     so_fdct_islow(ws);
-    so_quantize(ws, qt, out);
+    if (qt) so_quantize(ws, qt, out);
+    else for (int i = 0; i < 64; i++) out[i] = (int16_t)ws[i];
 }
 
 /* one component: real blocks from the padded sample plane, then the dummy blocks of
@@ -555,4 +559,10 @@ void so_jpeg_frontend(const uint8_t *rgba, uint32_t w, uint32_t h,
     so_component(Cb, cw, g.c_wb, g.c_hb, g.c_WB, g.c_HB, 1, qt_chroma, cbc);
     so_component(Cr, cw, g.c_wb, g.c_hb, g.c_WB, g.c_HB, 1, qt_chroma, crc);
     free(Y); free(B); free(R); free(Cb); free(Cr);
+}
+
+/* The un-quantised coefficient planes (same layout, dummy blocks made the same way from the un-quantised DCs). */
+void so_jpeg_frontend_unquantised(const uint8_t *rgba, uint32_t w, uint32_t h, int16_t *yc, int16_t *cbc, int16_t *crc)
+{
+    so_jpeg_frontend(rgba, w, h, NULL, NULL, yc, cbc, crc);
 }

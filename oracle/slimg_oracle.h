@@ -79,6 +79,8 @@ void so_jpeg_frontend(const uint8_t *rgba, uint32_t w, uint32_t h,
                       const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
                       int16_t *y, int16_t *cb, int16_t *cr);
 /* pieces, exported for unit tests */
+/* qt_luma == qt_chroma == NULL: un-quantised planes (jfdctint.c:143-286 output) */
+void so_jpeg_frontend_unquantised(const uint8_t *rgba, uint32_t w, uint32_t h, int16_t *y, int16_t *cb, int16_t *cr);
 void so_rgb_ycc(uint8_t r, uint8_t g, uint8_t b, uint8_t out[3]);          /* jccolor.c:209-237, jccolext.c:61-68 */
 void so_fdct_islow(int32_t blk[64]);                                        /* jfdctint.c:143-286 */
 void so_quantize(const int32_t ws[64], const uint16_t qt[64], int16_t out[64]); /* jcdctmgr.c:173-221,408-438 */

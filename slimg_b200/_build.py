@@ -47,7 +47,20 @@ def build(force: bool = False, verbose: bool = False) -> str:
         sys.stderr.write(res.stdout + res.stderr)
     if res.returncode:
         raise RuntimeError("nvcc failed building libslimg_b200.so")
+    build_jpeg_handoff()
     return LIB_PATH
+
+
+def build_jpeg_handoff() -> None:
+    """libslimg_jpeg_handoff.so (slimg_b200/jpeg_handoff/): the hand-off of the GPU's coefficient planes to a libjpeg
+    entropy coder.  Needs a libjpeg: JPEG_INC / JPEG_LIB in the environment, or the libjpeg-turbo sources the
+    reference vendors (present in the build container; the built .so travels to the GPU box)."""
+    mk = os.path.join(HERE, "jpeg_handoff")
+    ref = os.environ.get("SLIMG_REFERENCE", "/root/reference")
+    if os.environ.get("JPEG_INC"):
+        subprocess.run(["make", "-C", mk, "-s"], check=False)
+    elif os.path.isdir(os.path.join(ref, "crates", "libjxl-sys", "libjxl", "third_party", "libjpeg-turbo")):
+        subprocess.run(["make", "-C", mk, "-s", "-j8", f"REF={ref}"], check=False)
 
 
 if __name__ == "__main__":

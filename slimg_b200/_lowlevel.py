@@ -56,7 +56,8 @@ class CJpegGeometry(C.Structure):
 
 class CJpegCoefs(C.Structure):
     _fields_ = [("geom", CJpegGeometry), ("qt_luma", C.c_uint16 * 64), ("qt_chroma", C.c_uint16 * 64),
-                ("y", C.POINTER(C.c_int16)), ("cb", C.POINTER(C.c_int16)), ("cr", C.POINTER(C.c_int16))]
+                ("y", C.POINTER(C.c_int16)), ("cb", C.POINTER(C.c_int16)), ("cr", C.POINTER(C.c_int16)),
+                ("y_uq", C.POINTER(C.c_int16)), ("cb_uq", C.POINTER(C.c_int16)), ("cr_uq", C.POINTER(C.c_int16))]
 
 
 class CBatchConfig(C.Structure):
@@ -65,6 +66,9 @@ class CBatchConfig(C.Structure):
 
 ORDER_CONVERT, ORDER_CHAIN = 0, 1
 QT_ANNEX_K, QT_MOZJPEG = 0, 1
+JPEG_UNQUANTISED = 1
+PATH_NONE, PATH_REMAP, PATH_GENERIC, PATH_FEWTAPS, PATH_HFIRST, PATH_VFIRST, PATH_TC, PATH_TILE = range(8)
+PATH_NAMES = ("none", "remap", "generic", "fewtaps", "hfirst", "vfirst", "tc", "tile")
 
 # every symbol include/slimg_b200.h declares (tests/test_abi.py checks the .so exports them all)
 ABI_SYMBOLS = (
@@ -75,7 +79,9 @@ ABI_SYMBOLS = (
     "slimg_b200_jpeg_coefs_free", "slimg_b200_pipeline_batch_device", "slimg_b200_jpeg_frontend_batch_device",
     "slimg_b200_pipeline_batch_host", "slimg_b200_last_error", "slimg_b200_abi_version",
     "slimg_b200_device_count", "slimg_b200_kernel_launches", "slimg_b200_host_alloc", "slimg_b200_host_free",
-    "slimg_b200_pipeline_source_window",
+    "slimg_b200_pipeline_source_window", "slimg_b200_jpeg_frontend_ex", "slimg_b200_pipeline_jpeg",
+    "slimg_b200_jpeg_frontend_batch_device_ex", "slimg_b200_pipeline_jpeg_batch_device",
+    "slimg_b200_pipeline_jpeg_batch_host", "slimg_b200_last_resize_path", "slimg_b200_path_launches",
 )
 
 _lib: Optional[C.CDLL] = None
@@ -121,6 +127,13 @@ def library() -> C.CDLL:
         "slimg_b200_kernel_launches": (C.c_uint64, []),
         "slimg_b200_host_alloc": (vp, [C.c_size_t]),
         "slimg_b200_host_free": (None, [vp]),
+        "slimg_b200_jpeg_frontend_ex": (C.c_int, [C.POINTER(CImage), C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.c_uint32, C.POINTER(CJpegCoefs)]),
+        "slimg_b200_pipeline_jpeg": (C.c_int, [C.POINTER(CImage), C.POINTER(CPipelineOptions), C.c_int, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.c_uint32, C.POINTER(CJpegCoefs)]),
+        "slimg_b200_jpeg_frontend_batch_device_ex": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), vp, vp, vp, vp, vp, vp, vp]),
+        "slimg_b200_pipeline_jpeg_batch_device": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(CPipelineOptions), C.c_int, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), vp, C.c_size_t, vp, vp, vp, vp, vp, vp, vp]),
+        "slimg_b200_pipeline_jpeg_batch_host": (C.c_int32, [C.POINTER(CImage), C.c_uint32, C.POINTER(CPipelineOptions), C.c_int, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.c_uint32, C.POINTER(CBatchConfig), C.POINTER(CJpegCoefs), C.POINTER(C.c_int)]),
+        "slimg_b200_last_resize_path": (C.c_int32, []),
+        "slimg_b200_path_launches": (C.c_uint64, [C.c_int32]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)
@@ -383,24 +396,69 @@ def jpeg_quant_table(quality: int, which: int, base: int = QT_ANNEX_K):
     return list(out)
 
 
-def jpeg_frontend(image: ImageData, qt_luma, qt_chroma):
-    """-> (geometry, y, cb, cr) with the planes as bytes of int16 [HB][WB][64]."""
+class JpegCoefficients:
+    """Coefficient planes of one image: int16 ``[HB][WB][64]`` (natural order) for Y, Cb, Cr as bytes, the
+    quantisation tables they were computed with, and -- when asked for -- the un-quantised planes."""
+
+    def __init__(self, geom, y, cb, cr, qt_luma, qt_chroma, y_uq=None, cb_uq=None, cr_uq=None):
+        self.geometry, self.y, self.cb, self.cr = geom, y, cb, cr
+        self.qt_luma, self.qt_chroma = list(qt_luma), list(qt_chroma)
+        self.y_uq, self.cb_uq, self.cr_uq = y_uq, cb_uq, cr_uq
+
+    @property
+    def width(self): return self.geometry.width
+
+    @property
+    def height(self): return self.geometry.height
+
+
+def _take_coefs(out: CJpegCoefs) -> JpegCoefficients:
+    try:
+        g = out.geom
+        ye, ce = g.y_HB * g.y_WB * 64, g.c_HB * g.c_WB * 64
+        planes = [C.string_at(out.y, ye * 2), C.string_at(out.cb, ce * 2), C.string_at(out.cr, ce * 2)]
+        uq = [None, None, None]
+        if out.y_uq:
+            uq = [C.string_at(out.y_uq, ye * 2), C.string_at(out.cb_uq, ce * 2), C.string_at(out.cr_uq, ce * 2)]
+        return JpegCoefficients(CJpegGeometry.from_buffer_copy(bytes(g)), *planes, list(out.qt_luma), list(out.qt_chroma), *uq)
+    finally:
+        library().slimg_b200_jpeg_coefs_free(C.byref(out))
+
+
+def jpeg_frontend_ex(image: ImageData, qt_luma, qt_chroma, flags: int = 0) -> JpegCoefficients:
     cin, keep = _in_image(image)
     ql = (C.c_uint16 * 64)(*qt_luma)
     qc = (C.c_uint16 * 64)(*qt_chroma)
     out = CJpegCoefs()
-    _check(library().slimg_b200_jpeg_frontend(C.byref(cin), ql, qc, C.byref(out)))
+    _check(library().slimg_b200_jpeg_frontend_ex(C.byref(cin), ql, qc, flags, C.byref(out)))
     del keep
-    try:
-        g = out.geom
-        ye, ce = g.y_HB * g.y_WB * 64, g.c_HB * g.c_WB * 64
-        y = C.string_at(out.y, ye * 2)
-        cb = C.string_at(out.cb, ce * 2)
-        cr = C.string_at(out.cr, ce * 2)
-        geom = CJpegGeometry.from_buffer_copy(bytes(g))
-        return geom, y, cb, cr
-    finally:
-        library().slimg_b200_jpeg_coefs_free(C.byref(out))
+    return _take_coefs(out)
+
+
+def jpeg_frontend(image: ImageData, qt_luma, qt_chroma):
+    """-> (geometry, y, cb, cr) with the planes as bytes of int16 [HB][WB][64]."""
+    c = jpeg_frontend_ex(image, qt_luma, qt_chroma, 0)
+    return c.geometry, c.y, c.cb, c.cr
+
+
+def pipeline_jpeg(image: ImageData, options: CPipelineOptions, qt_luma, qt_chroma, order: int = ORDER_CONVERT,
+                  flags: int = 0) -> JpegCoefficients:
+    """convert(.., Jpeg) up to the entropy coder: pixel stages + JPEG front end on the device, coefficients back."""
+    cin, keep = _in_image(image)
+    ql = (C.c_uint16 * 64)(*qt_luma)
+    qc = (C.c_uint16 * 64)(*qt_chroma)
+    out = CJpegCoefs()
+    _check(library().slimg_b200_pipeline_jpeg(C.byref(cin), C.byref(options), order, ql, qc, flags, C.byref(out)))
+    del keep
+    return _take_coefs(out)
+
+
+def last_resize_path() -> int:
+    return library().slimg_b200_last_resize_path()
+
+
+def path_launches(path: int) -> int:
+    return library().slimg_b200_path_launches(path)
 
 
 def pipeline_batch_device(src_ptr: int, n: int, w: int, h: int, options: CPipelineOptions, order: int,
@@ -415,6 +473,24 @@ def jpeg_frontend_batch_device(src_ptr: int, n: int, w: int, h: int, qt_luma, qt
     ql = (C.c_uint16 * 64)(*qt_luma)
     qc = (C.c_uint16 * 64)(*qt_chroma)
     _check(library().slimg_b200_jpeg_frontend_batch_device(src_ptr, n, w, h, ql, qc, y_ptr, cb_ptr, cr_ptr, stream))
+
+
+def jpeg_frontend_batch_device_ex(src_ptr, n, w, h, qt_luma, qt_chroma, y_ptr, cb_ptr, cr_ptr, yu_ptr, cbu_ptr, cru_ptr,
+                                  stream: int = 0) -> None:
+    ql = (C.c_uint16 * 64)(*qt_luma)
+    qc = (C.c_uint16 * 64)(*qt_chroma)
+    _check(library().slimg_b200_jpeg_frontend_batch_device_ex(src_ptr, n, w, h, ql, qc, y_ptr, cb_ptr, cr_ptr,
+                                                              yu_ptr, cbu_ptr, cru_ptr, stream))
+
+
+def pipeline_jpeg_batch_device(src_ptr, n, w, h, options: CPipelineOptions, order, qt_luma, qt_chroma, pixels_ptr,
+                               pixels_capacity, y_ptr, cb_ptr, cr_ptr, yu_ptr=None, cbu_ptr=None, cru_ptr=None,
+                               stream: int = 0) -> None:
+    ql = (C.c_uint16 * 64)(*qt_luma)
+    qc = (C.c_uint16 * 64)(*qt_chroma)
+    _check(library().slimg_b200_pipeline_jpeg_batch_device(src_ptr, n, w, h, C.byref(options), order, ql, qc, pixels_ptr,
+                                                           pixels_capacity, y_ptr, cb_ptr, cr_ptr, yu_ptr, cbu_ptr, cru_ptr,
+                                                           stream))
 
 
 def device_count() -> int:
@@ -455,3 +531,87 @@ def format_from_magic_bytes(data: bytes) -> Optional[Format]:
     if d[:2] == b"\xff\x0a" or d[:12] == b"\x00\x00\x00\x0cJXL \r\n\x87\n": return Format.JXL
     if d[:4] == b"qoif": return Format.QOI
     return None
+
+
+# -- convert / decode / optimize: the UniFFI-generated module exports them (crates/slimg-ffi/src/lib.rs:277-318,
+#    342-351).  The pixel stages and the JPEG front end run on the GPU; entropy coding and decoding are host codecs
+#    that plug in here (slimg_b200/_host_codecs.py installs what this machine has). ----------------------------------
+
+
+@dataclass
+class DecodeResult:
+    image: ImageData
+    format: Format
+
+
+_ENCODERS = {}       # Format -> callable(ImageData, quality) -> bytes          (pixels in)
+_JPEG_ENTROPY = []   # [callable(JpegCoefficients, quality) -> bytes]            (coefficients in: no pixel download)
+_DECODERS = []       # [callable(bytes) -> Optional[DecodeResult]]
+JPEG_TABLES = QT_MOZJPEG   # which base tables convert(.., JPEG) quantises with (the reference encoder is MozJPEG)
+
+
+def register_encoder(fmt: Format, fn) -> None:
+    _ENCODERS[fmt] = fn
+
+
+def register_jpeg_entropy_coder(fn) -> None:
+    _JPEG_ENTROPY[:] = [fn]
+
+
+def register_decoder(fn) -> None:
+    _DECODERS.append(fn)
+
+
+def _load_host_codecs() -> None:
+    from . import _host_codecs
+    _host_codecs.install()
+
+
+def convert(image: ImageData, options: PipelineOptions) -> PipelineResult:
+    """slimg_core::convert (pipeline.rs:66-103): crop -> extend -> resize (one fused launch), then encode."""
+    _load_host_codecs()
+    fmt = options.format
+    q = int(options.quality)
+    copts = options._to_c()
+    if fmt == Format.JPEG and _JPEG_ENTROPY:
+        ql, qc = jpeg_quant_table(q, 0, JPEG_TABLES), jpeg_quant_table(q, 1, JPEG_TABLES)
+        coefs = pipeline_jpeg(image, copts, ql, qc, ORDER_CONVERT)
+        return PipelineResult(_JPEG_ENTROPY[0](coefs, q), fmt, coefs.width, coefs.height)
+    enc = _ENCODERS.get(fmt)
+    if enc is None:     # the reference reports this before touching pixels (pipeline.rs:67-69)
+        raise SlimgError.Encode(f"no host encoder for {fmt.name}: entropy coding stays on the reference libraries "
+                                "(slimg_b200._lowlevel.register_encoder)")
+    px = pipeline(image, copts, ORDER_CONVERT)
+    return PipelineResult(enc(px, q), fmt, px.width, px.height)
+
+
+def decode(data: bytes) -> DecodeResult:
+    _load_host_codecs()
+    if format_from_magic_bytes(data) is None:
+        raise SlimgError.UnknownFormat("unrecognised magic bytes")
+    for dec in _DECODERS:
+        res = dec(bytes(data))
+        if res is not None:
+            return res
+    raise SlimgError.Decode("no host decoder for this format: decoding stays on the reference codecs")
+
+
+def decode_file(path: str) -> DecodeResult:
+    try:
+        with open(path, "rb") as fh:
+            data = fh.read()
+    except OSError as exc:
+        raise SlimgError.Io(str(exc)) from exc
+    return decode(data)
+
+
+def optimize(data: bytes, quality: int) -> PipelineResult:
+    res = decode(data)
+    return convert(res.image, PipelineOptions(format=res.format, quality=quality))
+
+
+def install_as_slimg_lowlevel() -> None:
+    """Make ``import slimg`` (the reference's UNMODIFIED Python package, bindings/python/slimg) run on this library:
+    registers this module as ``slimg._lowlevel``, the name the wrapper imports (_types.py:13)."""
+    import sys
+    sys.modules["slimg._lowlevel"] = sys.modules[__name__]

@@ -20,6 +20,12 @@ namespace slimg {
 
 static std::atomic<uint64_t> g_launches{0};
 void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+static std::atomic<uint64_t> g_path_launches[8];
+static thread_local int t_last_path = SLIMG_PATH_NONE;
+void note_path(int path) {
+    t_last_path = path;
+    if (path >= 0 && path < 8) g_path_launches[path].fetch_add(1, std::memory_order_relaxed);
+}
 
 static slimg_status cuda_fail(cudaError_t e, const char *what) {
     return fail(SLIMG_ERR_IMAGE, std::string("CUDA: ") + what + ": " + cudaGetErrorString(e));
@@ -36,19 +42,41 @@ static uint32_t pack_fill(const uint8_t f[4]) {
 
 // ---- resize plans: device-resident tap tables + tiling, cached per (device, geometry) -------
 
+// All tables of a plan live in one or two device slabs: a plan costs one cudaMalloc instead of ~30, and dropping it is
+// one cudaFree (mixed-size corpora build a plan per geometry).
+struct PlanArena {
+    std::vector<void *> slabs;
+    size_t used = 0, cap = 0;
+    ~PlanArena() { for (void *s : slabs) cudaFree(s); }
+    cudaError_t alloc(size_t bytes, void **p) {
+        const size_t need = (bytes + 255) & ~size_t(255);
+        if (slabs.empty() || used + need > cap) {
+            const size_t slab = std::max<size_t>(need, size_t(4) << 20);
+            void *s = nullptr;
+            cudaError_t e = cudaMalloc(&s, slab);
+            if (e != cudaSuccess) return e;
+            slabs.push_back(s); used = 0; cap = slab;
+        }
+        *p = static_cast<uint8_t *>(slabs.back()) + used;
+        used += need;
+        return cudaSuccess;
+    }
+};
+static thread_local PlanArena *t_arena = nullptr;      // the arena of the plan being built on this thread
+
 struct DevArray {
     void *p = nullptr;
-    ~DevArray() { if (p) cudaFree(p); }
     template <class T> cudaError_t upload(const std::vector<T> &v) {
         size_t bytes = (v.empty() ? 1 : v.size()) * sizeof(T);
-        cudaError_t e = cudaMalloc(&p, bytes);
+        cudaError_t e = t_arena->alloc(bytes, &p);
         if (e != cudaSuccess) return e;
-        if (!v.empty()) e = cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+        if (!v.empty()) e = cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, cudaStreamPerThread);
         return e;
     }
 };
 
 struct ResizePlan {
+    PlanArena arena;
     DevArray xl, xc, xw, xf, yl, yc, yw, yf, tx0, tspan;
     ResizeParams params{};   // src/dst/strides filled per launch
     // rows / columns of the source any kernel of this plan reads with a non-zero weight (what a host-fed call uploads)
@@ -81,9 +109,12 @@ static GeomKey make_key(const PipeGeom &g) {
     return k;
 }
 
+constexpr size_t kPlanCacheEntries = 64;     // per device; least recently used geometry goes first
 struct DeviceCtx {
     std::mutex mu;
-    std::map<GeomKey, std::shared_ptr<ResizePlan>> plans;
+    struct Entry { std::shared_ptr<ResizePlan> plan; uint64_t stamp; };
+    std::map<GeomKey, Entry> plans;
+    uint64_t clock = 0;
 };
 
 static DeviceCtx &device_ctx(int dev) {
@@ -116,8 +147,20 @@ static void window_from_taps(const PipeGeom &g, const AxisTaps &tx, const AxisTa
     }
 }
 
-static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizePlan> &out) {
+// SLIMG_B200_RESIZE_PATH: which K2 kernel a downscale should prefer.  Unset = the production order (V-first integer
+// pipeline, then H-first for bands the V-first ring cannot hold, then the f32 kernels); "tc" / "hfirst" / "generic"
+// force one of the others where the geometry qualifies (tests run every path; benches A/B them).  Part of the plan key.
+static std::string requested_path() {
+    const char *path_env = std::getenv("SLIMG_B200_RESIZE_PATH");
+    return path_env && *path_env ? path_env : "vfirst";
+}
+static uint32_t path_code(const std::string &p) {
+    return p == "tc" ? 1u : p == "hfirst" ? 2u : p == "generic" ? 3u : 0u;
+}
+
+static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path, std::shared_ptr<ResizePlan> &out) {
     auto plan = std::make_shared<ResizePlan>();
+    struct ArenaScope { ArenaScope(PlanArena *a) { t_arena = a; } ~ArenaScope() { t_arena = nullptr; } } scope(&plan->arena);
     AxisTaps tx, ty;
     build_axis_taps(g.vw, g.Rw, g.vox, g.rw, tx);
     build_axis_taps(g.vh, g.Rh, g.voy, g.rh, ty);
@@ -208,9 +251,6 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
     }
     p.tile_x0 = (const int32_t *)plan->tx0.p;
     p.tile_span = (const int32_t *)plan->tspan.p;
-    // which resize kernel: SLIMG_B200_RESIZE_PATH = vfirst (default) | hfirst | generic
-    const char *path_env = std::getenv("SLIMG_B200_RESIZE_PATH");
-    const std::string path = path_env ? path_env : "vfirst";
     if (path == "tc") {
         TcPlanHost tp;
         build_tcplan(g, tx, ty, tp);
@@ -326,6 +366,8 @@ static slimg_status build_resize_plan(const PipeGeom &g, std::shared_ptr<ResizeP
         f.n_bands = 1; f.n_fill_blocks = fp.need_fill ? 1 : 0;
         plan->fast = true;
     }
+    // the tables were copied on this thread's stream from vectors that die here
+    if ((e = cudaStreamSynchronize(cudaStreamPerThread)) != cudaSuccess) return cuda_fail(e, "uploading resize plan");
     out = plan;
     return SLIMG_OK;
 }
@@ -334,14 +376,35 @@ static slimg_status get_resize_plan(const PipeGeom &g, std::shared_ptr<ResizePla
     int dev = 0;
     CU(cudaGetDevice(&dev));
     DeviceCtx &ctx = device_ctx(dev);
-    const GeomKey key = make_key(g);
-    std::lock_guard<std::mutex> lk(ctx.mu);
-    auto it = ctx.plans.find(key);
-    if (it != ctx.plans.end()) { out = it->second; return SLIMG_OK; }
-    if (ctx.plans.size() > 256) ctx.plans.clear();   // bounded; in-flight launches hold shared_ptrs... see below
-    slimg_status st = build_resize_plan(g, out);
-    if (st == SLIMG_OK) ctx.plans[key] = out;
-    return st;
+    const std::string path = requested_path();
+    GeomKey key = make_key(g);
+    key.v[23] = path_code(path);
+    {
+        std::lock_guard<std::mutex> lk(ctx.mu);
+        auto it = ctx.plans.find(key);
+        if (it != ctx.plans.end()) { it->second.stamp = ++ctx.clock; out = it->second.plan; return SLIMG_OK; }
+    }
+    // built outside the lock: other workers of this device keep launching cached geometries meanwhile (two workers that
+    // miss on the same geometry both build it; the second insert is dropped)
+    slimg_status st = build_resize_plan(g, path, out);
+    if (st != SLIMG_OK) return st;
+    std::shared_ptr<ResizePlan> victim;                 // freed after the lock is released (cudaFree synchronises)
+    {
+        std::lock_guard<std::mutex> lk(ctx.mu);
+        auto it = ctx.plans.find(key);
+        if (it != ctx.plans.end()) { victim = out; it->second.stamp = ++ctx.clock; out = it->second.plan; }
+        else {
+            if (ctx.plans.size() >= kPlanCacheEntries) {
+                auto lru = ctx.plans.begin();
+                for (auto j = ctx.plans.begin(); j != ctx.plans.end(); ++j)
+                    if (j->second.stamp < lru->second.stamp) lru = j;
+                victim = lru->second.plan;              // in-flight launches that still use it hold their own reference
+                ctx.plans.erase(lru);
+            }
+            ctx.plans[key] = DeviceCtx::Entry{out, ++ctx.clock};
+        }
+    }
+    return SLIMG_OK;
 }
 
 // Rows [r0,r1) x columns [c0,c1) of the source that the pipeline reads for this geometry.
@@ -386,12 +449,16 @@ static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, u
         p.dy = int32_t(shift_y - int64_t(g.voy) + g.ry);
         p.fill_in = pack_fill(g.fill_pre); p.fill_out = pack_fill(g.fill_post);
         CU(launch_remap(p, n, stream));
+        note_path(SLIMG_PATH_REMAP);
         return SLIMG_OK;
     }
     std::shared_ptr<ResizePlan> plan;
     slimg_status st = get_resize_plan(g, plan);
     if (st != SLIMG_OK) return st;
-    if (plan->tc && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    // A fast path whose launch is refused (no tensor-map entry point in the driver, an uninstantiated template case)
+    // falls through to the next one; the generic kernel takes everything.
+    const bool aligned = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+    if (plan->tc && aligned) {
         TcParams t = plan->tparams;
         t.src = src; t.dst = dst; t.src_img_bytes = src_bytes; t.dst_img_bytes = dst_bytes;
         // bands of 16-row blocks: enough CTAs to fill the GPU when the batch is small
@@ -399,10 +466,10 @@ static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, u
         uint32_t bands = uint32_t((2 * 148 + ctas_per_band - 1) / ctas_per_band);
         bands = std::max<uint32_t>(1, std::min<uint32_t>(bands, std::max<uint32_t>(1, t.n_blocks / 2)));
         t.n_bands = bands;
-        CU(launch_resize_tc(t, n, stream));
-        return SLIMG_OK;
+        if (launch_resize_tc(t, n, stream) == cudaSuccess) { note_path(SLIMG_PATH_TC); return SLIMG_OK; }
+        cudaGetLastError();
     }
-    if (plan->vfirst && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    if (plan->vfirst && aligned) {
         VfParams v = plan->vparams;
         v.src = src; v.dst = dst; v.src_img_bytes = src_bytes; v.dst_img_bytes = dst_bytes;
         // bands of output-row groups: enough CTAs to fill the GPU when the batch is small, no halo
@@ -411,10 +478,10 @@ static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, u
         uint32_t bands = uint32_t((2 * 148 + ctas_per_band - 1) / ctas_per_band);
         bands = std::max<uint32_t>(1, std::min<uint32_t>(bands, std::max<uint32_t>(1, v.n_recs / 4)));
         v.n_bands = bands;
-        CU(launch_resize_vfirst(v, n, stream));
-        return SLIMG_OK;
+        if (launch_resize_vfirst(v, n, stream) == cudaSuccess) { note_path(SLIMG_PATH_VFIRST); return SLIMG_OK; }
+        cudaGetLastError();
     }
-    if (plan->fast && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    if (plan->fast && aligned) {
         FastResizeParams f = plan->fparams;
         f.src = src; f.dst = dst; f.src_img_bytes = src_bytes; f.dst_img_bytes = dst_bytes;
         // bands of output rows: enough CTAs to fill the GPU when the batch is small, none of the
@@ -423,8 +490,8 @@ static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, u
         uint32_t bands = uint32_t((2 * 148 * 2 + ctas_per_band - 1) / ctas_per_band);
         bands = std::max<uint32_t>(1, std::min<uint32_t>(bands, std::max<uint32_t>(1, f.ph / 8)));
         f.n_bands = bands;
-        CU(launch_resize_fast(f, n, stream));
-        return SLIMG_OK;
+        if (launch_resize_fast(f, n, stream) == cudaSuccess) { note_path(SLIMG_PATH_HFIRST); return SLIMG_OK; }
+        cudaGetLastError();
     }
     ResizeParams p = plan->params;
     p.src = src; p.dst = dst; p.src_img_bytes = src_bytes; p.dst_img_bytes = dst_bytes;
@@ -489,62 +556,106 @@ static void keep_pool_memory(int device) {
         cudaGetLastError();
 }
 
-// one image, host in / host out, on the current device
-// `done` (optional): a cudaEventBlockingSync event the wait goes through, so a scheduler worker SLEEPS while its image
-// is in flight instead of spinning on the stream (8 ranks x 4 workers would otherwise fight over the host cores)
-static slimg_status pipeline_one(const slimg_image *in, const slimg_pipeline_options &o, int order, slimg_image *out,
-                                 cudaStream_t stream, bool caller_buffer, cudaEvent_t done = nullptr) {
-    slimg_status st = validate_image(in, o, order);
-    if (st != SLIMG_OK) return st;
-    PipeGeom g;
-    if ((st = build_geometry(in->width, in->height, o, order, g)) != SLIMG_OK) return st;
-    const size_t src_bytes = size_t(g.sw) * g.sh * 4, dst_bytes = size_t(g.fw) * g.fh * 4;
+// ---- pinned staging for pageable host buffers -------------------------------------------------------------------
+// Callers behind this boundary hand over ordinary heap memory (a Rust Vec, Python bytes, a UniFFI RustBuffer).  A
+// cudaMemcpyAsync from such memory is staged by the driver synchronously, one bounce buffer at a time; here the copy
+// goes through two pinned slots instead, the memcpy into one slot overlapping the DMA out of the other.  Rings are
+// pooled per device (their events belong to a device) and handed to one worker at a time.
+constexpr size_t kStageChunk = size_t(8) << 20;
+struct StagingRing {
+    int device = -1;
+    uint8_t *slot[2] = {nullptr, nullptr};
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    bool pending[2] = {false, false};
+};
+static std::mutex g_ring_mu;
+static std::vector<StagingRing *> g_ring_pool;
 
+static StagingRing *acquire_ring(int device) {
     {
-        int dev = 0;
-        if (cudaGetDevice(&dev) == cudaSuccess) keep_pool_memory(dev);
+        std::lock_guard<std::mutex> lk(g_ring_mu);
+        for (size_t i = 0; i < g_ring_pool.size(); i++)
+            if (g_ring_pool[i]->device == device) {
+                StagingRing *r = g_ring_pool[i];
+                g_ring_pool.erase(g_ring_pool.begin() + long(i));
+                return r;
+            }
     }
-    uint8_t *host_out = nullptr;
-    if (caller_buffer && out->data && out->len >= dst_bytes) host_out = out->data;
-    else {
-        host_out = static_cast<uint8_t *>(std::malloc(dst_bytes ? dst_bytes : 1));
-        if (!host_out) return fail(SLIMG_ERR_IMAGE, "out of host memory");
-    }
-    uint8_t *d_src = nullptr, *d_dst = nullptr;
-    auto cleanup = [&](slimg_status s) {
-        if (d_src) cudaFreeAsync(d_src, stream);
-        if (d_dst) cudaFreeAsync(d_dst, stream);
-        if (s != SLIMG_OK && host_out != out->data) std::free(host_out);
-        return s;
-    };
-    cudaError_t e;
-    if ((e = cudaMallocAsync((void **)&d_src, src_bytes, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
-    if ((e = cudaMallocAsync((void **)&d_dst, dst_bytes ? dst_bytes : 1, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
-    // upload only what the kernels read: the rows (and, when the window is much narrower than the image, the columns)
-    // of the source behind the kept output rectangle; the rest of d_src stays unwritten and unread (staging that
-    // over-reads a ring step meets zero weights: integer 0 x anything = 0)
-    uint32_t r0 = 0, r1 = g.sh, c0 = 0, c1 = g.sw;
-    if ((st = source_window(g, r0, r1, c0, c1)) != SLIMG_OK) return cleanup(st);
-    if (r1 > r0 && c1 > c0) {
-        if (uint64_t(c1 - c0) * 10 < uint64_t(g.sw) * 9) {
-            const size_t off = (size_t(r0) * g.sw + c0) * 4;
-            e = cudaMemcpy2DAsync(d_src + off, size_t(g.sw) * 4, in->data + off, size_t(g.sw) * 4, size_t(c1 - c0) * 4, r1 - r0,
-                                  cudaMemcpyHostToDevice, stream);
-        } else {
-            const size_t off = size_t(r0) * g.sw * 4;
-            e = cudaMemcpyAsync(d_src + off, in->data + off, size_t(r1 - r0) * g.sw * 4, cudaMemcpyHostToDevice, stream);
+    auto *r = new StagingRing();
+    r->device = device;
+    for (int k = 0; k < 2; k++)
+        if (cudaMallocHost((void **)&r->slot[k], kStageChunk) != cudaSuccess ||
+            cudaEventCreateWithFlags(&r->ev[k], cudaEventBlockingSync | cudaEventDisableTiming) != cudaSuccess) {
+            cudaGetLastError();
+            for (int j = 0; j < 2; j++) { if (r->slot[j]) cudaFreeHost(r->slot[j]); if (r->ev[j]) cudaEventDestroy(r->ev[j]); }
+            delete r;
+            return nullptr;
         }
-        if (e != cudaSuccess) return cleanup(cuda_fail(e, "H2D"));
+    return r;
+}
+static void release_ring(StagingRing *r) {
+    if (!r) return;
+    std::lock_guard<std::mutex> lk(g_ring_mu);
+    g_ring_pool.push_back(r);
+}
+struct RingLease {                       // a worker's ring, acquired on first use
+    StagingRing *ring = nullptr;
+    ~RingLease() { release_ring(ring); }
+    StagingRing *get() {
+        if (!ring) { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) ring = acquire_ring(dev); }
+        return ring;
     }
-    if ((st = run_pipeline_device(g, d_src, 1, d_dst, stream)) != SLIMG_OK) return cleanup(st);
-    if ((e = cudaMemcpyAsync(host_out, d_dst, dst_bytes, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "D2H"));
-    if (done) {
-        if ((e = cudaEventRecord(done, stream)) != cudaSuccess || (e = cudaEventSynchronize(done)) != cudaSuccess)
-            return cleanup(cuda_fail(e, "pipeline kernels"));
-    } else if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return cleanup(cuda_fail(e, "pipeline kernels"));
-    cleanup(SLIMG_OK);
-    out->width = g.fw; out->height = g.fh; out->data = host_out; out->len = dst_bytes;
-    return SLIMG_OK;
+};
+
+static bool is_pinned(const void *p) {
+    if (std::getenv("SLIMG_B200_NO_STAGING")) return true;          // A/B: let the driver stage pageable copies
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+
+// host -> device; `src` may be pageable.  Enqueues on `stream`; when it returns, `src` has been read.
+static cudaError_t copy_h2d(uint8_t *dst, const uint8_t *src, size_t bytes, cudaStream_t stream, RingLease &lease) {
+    if (bytes == 0) return cudaSuccess;
+    StagingRing *r = nullptr;
+    if (is_pinned(src) || !(r = lease.get())) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream);
+    cudaError_t e = cudaSuccess;
+    int k = 0;
+    for (size_t off = 0; off < bytes; off += kStageChunk, k ^= 1) {
+        const size_t n = std::min(kStageChunk, bytes - off);
+        if (r->pending[k]) { if ((e = cudaEventSynchronize(r->ev[k])) != cudaSuccess) return e; r->pending[k] = false; }
+        std::memcpy(r->slot[k], src + off, n);
+        if ((e = cudaMemcpyAsync(dst + off, r->slot[k], n, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return e;
+        if ((e = cudaEventRecord(r->ev[k], stream)) != cudaSuccess) return e;
+        r->pending[k] = true;
+    }
+    return cudaSuccess;
+}
+
+// device -> host; `dst` may be pageable.  With a pinned `dst` the copy is only enqueued; with a pageable one the call
+// returns when the bytes are in place.
+static cudaError_t copy_d2h(uint8_t *dst, const uint8_t *src, size_t bytes, cudaStream_t stream, RingLease &lease) {
+    if (bytes == 0) return cudaSuccess;
+    StagingRing *r = nullptr;
+    if (is_pinned(dst) || !(r = lease.get())) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream);
+    cudaError_t e = cudaSuccess;
+    for (int k = 0; k < 2; k++)          // slots still draining an upload of this worker
+        if (r->pending[k]) { if ((e = cudaEventSynchronize(r->ev[k])) != cudaSuccess) return e; r->pending[k] = false; }
+    size_t prev_off = 0, prev_n = 0;
+    int k = 0;
+    for (size_t off = 0; off < bytes; off += kStageChunk, k ^= 1) {
+        const size_t n = std::min(kStageChunk, bytes - off);
+        if ((e = cudaMemcpyAsync(r->slot[k], src + off, n, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return e;
+        if ((e = cudaEventRecord(r->ev[k], stream)) != cudaSuccess) return e;
+        if (prev_n) {                    // the previous chunk, while this one is on the link
+            if ((e = cudaEventSynchronize(r->ev[k ^ 1])) != cudaSuccess) return e;
+            std::memcpy(dst + prev_off, r->slot[k ^ 1], prev_n);
+        }
+        prev_off = off; prev_n = n;
+    }
+    if ((e = cudaEventSynchronize(r->ev[k ^ 1])) != cudaSuccess) return e;
+    std::memcpy(dst + prev_off, r->slot[k ^ 1], prev_n);
+    return cudaSuccess;
 }
 
 // compute_reciprocal (jcdctmgr.c:173-221), DCTELEM = int, divisor = quantval << 3 (:245-251)
@@ -574,11 +685,13 @@ static void jpeg_geometry(uint32_t w, uint32_t h, slimg_jpeg_geometry &g) {
 }
 
 static slimg_status run_jpeg_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h, const uint16_t ql[64],
-                                    const uint16_t qc[64], int16_t *y, int16_t *cb, int16_t *cr, cudaStream_t stream) {
+                                    const uint16_t qc[64], int16_t *y, int16_t *cb, int16_t *cr, int16_t *yu, int16_t *cbu,
+                                    int16_t *cru, cudaStream_t stream) {
     slimg_jpeg_geometry g;
     jpeg_geometry(w, h, g);
     JpegParams p{};
     p.src = src; p.y = y; p.cb = cb; p.cr = cr;
+    p.yu = yu; p.cbu = cbu; p.cru = cru;
     p.src_img_bytes = size_t(w) * h * 4;
     p.y_img_elems = size_t(g.y_HB) * g.y_WB * 64;
     p.c_img_elems = size_t(g.c_HB) * g.c_WB * 64;
@@ -586,6 +699,108 @@ static slimg_status run_jpeg_device(const uint8_t *src, uint32_t n, uint32_t w, 
     p.y_wb = g.y_wb; p.y_hb = g.y_hb; p.y_WB = g.y_WB; p.y_HB = g.y_HB; p.c_wb = g.c_wb; p.c_hb = g.c_hb;
     build_quant(ql, qc, p.q);
     CU(launch_jpeg_frontend(p, n, stream));
+    return SLIMG_OK;
+}
+
+
+// what a convert-to-JPEG call wants after the pixel stages
+struct JpegRequest {
+    const uint16_t *ql, *qc;
+    uint32_t flags;
+    slimg_jpeg_coefs *out;
+};
+
+// one image, host in / host out, on the current device: the pixel stages, then (jpeg != nullptr) the JPEG front end on
+// the image that is still in HBM -- only coefficients come back
+// `done` (optional): a cudaEventBlockingSync event the wait goes through, so a scheduler worker SLEEPS while its image
+// is in flight instead of spinning on the stream (8 ranks x 4 workers would otherwise fight over the host cores)
+static slimg_status pipeline_one(const slimg_image *in, const slimg_pipeline_options &o, int order, slimg_image *out,
+                                 const JpegRequest *jpeg, cudaStream_t stream, bool caller_buffer, RingLease &lease,
+                                 cudaEvent_t done = nullptr) {
+    slimg_status st = validate_image(in, o, order);
+    if (st != SLIMG_OK) return st;
+    PipeGeom g;
+    if ((st = build_geometry(in->width, in->height, o, order, g)) != SLIMG_OK) return st;
+    const size_t src_bytes = size_t(g.sw) * g.sh * 4, dst_bytes = size_t(g.fw) * g.fh * 4;
+    const bool identity = !o.has_resize && !o.has_crop && !o.has_extend;
+
+    {
+        int dev = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess) keep_pool_memory(dev);
+    }
+    uint8_t *host_out = nullptr;           // pixels (no jpeg) or the coefficient planes (jpeg)
+    size_t ye = 0, ce = 0, coef_elems = 0;
+    slimg_jpeg_geometry jg{};
+    const bool uq = jpeg && (jpeg->flags & SLIMG_JPEG_UNQUANTISED);
+    if (jpeg) {
+        jpeg_geometry(g.fw, g.fh, jg);
+        ye = size_t(jg.y_HB) * jg.y_WB * 64; ce = size_t(jg.c_HB) * jg.c_WB * 64;
+        coef_elems = (ye + 2 * ce) * (uq ? 2 : 1);
+        host_out = static_cast<uint8_t *>(std::malloc(coef_elems * 2));
+    } else if (caller_buffer && out->data && out->len >= dst_bytes) host_out = out->data;
+    else host_out = static_cast<uint8_t *>(std::malloc(dst_bytes ? dst_bytes : 1));
+    if (!host_out) return fail(SLIMG_ERR_IMAGE, "out of host memory");
+    const bool own_out = jpeg || host_out != out->data;
+    uint8_t *d_src = nullptr, *d_dst = nullptr;
+    int16_t *d_coef = nullptr;
+    auto cleanup = [&](slimg_status s) {
+        if (d_src) cudaFreeAsync(d_src, stream);
+        if (d_dst) cudaFreeAsync(d_dst, stream);
+        if (d_coef) cudaFreeAsync(d_coef, stream);
+        if (s != SLIMG_OK && own_out) std::free(host_out);
+        return s;
+    };
+    cudaError_t e;
+    if ((e = cudaMallocAsync((void **)&d_src, src_bytes, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    if (!(jpeg && identity) &&
+        (e = cudaMallocAsync((void **)&d_dst, dst_bytes ? dst_bytes : 1, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    if (jpeg && (e = cudaMallocAsync((void **)&d_coef, coef_elems * 2, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    // upload only what the kernels read: the rows (and, when the window is much narrower than the image, the columns)
+    // of the source behind the kept output rectangle; the rest of d_src stays unwritten and unread (staging that
+    // over-reads a ring step meets zero weights: integer 0 x anything = 0)
+    uint32_t r0 = 0, r1 = g.sh, c0 = 0, c1 = g.sw;
+    if (!(jpeg && identity) && (st = source_window(g, r0, r1, c0, c1)) != SLIMG_OK) return cleanup(st);
+    if (r1 > r0 && c1 > c0) {
+        if (uint64_t(c1 - c0) * 10 < uint64_t(g.sw) * 9 && is_pinned(in->data)) {
+            const size_t off = (size_t(r0) * g.sw + c0) * 4;
+            e = cudaMemcpy2DAsync(d_src + off, size_t(g.sw) * 4, in->data + off, size_t(g.sw) * 4, size_t(c1 - c0) * 4, r1 - r0,
+                                  cudaMemcpyHostToDevice, stream);
+        } else {
+            const size_t off = size_t(r0) * g.sw * 4;
+            e = copy_h2d(d_src + off, in->data + off, size_t(r1 - r0) * g.sw * 4, stream, lease);
+        }
+        if (e != cudaSuccess) return cleanup(cuda_fail(e, "H2D"));
+    }
+    const uint8_t *d_pixels = d_src;
+    if (!(jpeg && identity)) {
+        if ((st = run_pipeline_device(g, d_src, 1, d_dst, stream)) != SLIMG_OK) return cleanup(st);
+        d_pixels = d_dst;
+    }
+    if (jpeg) {
+        int16_t *dy = d_coef, *dcb = dy + ye, *dcr = dcb + ce;
+        int16_t *dyu = uq ? dcr + ce : nullptr, *dcbu = uq ? dyu + ye : nullptr, *dcru = uq ? dcbu + ce : nullptr;
+        if ((st = run_jpeg_device(d_pixels, 1, g.fw, g.fh, jpeg->ql, jpeg->qc, dy, dcb, dcr, dyu, dcbu, dcru, stream)) != SLIMG_OK)
+            return cleanup(st);
+        if ((e = copy_d2h(host_out, reinterpret_cast<const uint8_t *>(d_coef), coef_elems * 2, stream, lease)) != cudaSuccess)
+            return cleanup(cuda_fail(e, "D2H"));
+    } else if ((e = copy_d2h(host_out, d_dst, dst_bytes, stream, lease)) != cudaSuccess) return cleanup(cuda_fail(e, "D2H"));
+    if (done) {
+        if ((e = cudaEventRecord(done, stream)) != cudaSuccess || (e = cudaEventSynchronize(done)) != cudaSuccess)
+            return cleanup(cuda_fail(e, "pipeline kernels"));
+    } else if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return cleanup(cuda_fail(e, "pipeline kernels"));
+    cleanup(SLIMG_OK);
+    if (jpeg) {
+        slimg_jpeg_coefs &c = *jpeg->out;
+        std::memset(&c, 0, sizeof c);
+        c.geom = jg;
+        std::memcpy(c.qt_luma, jpeg->ql, 128);
+        std::memcpy(c.qt_chroma, jpeg->qc, 128);
+        int16_t *h = reinterpret_cast<int16_t *>(host_out);
+        c.y = h; c.cb = h + ye; c.cr = h + ye + ce;
+        if (uq) { c.y_uq = h + ye + 2 * ce; c.cb_uq = c.y_uq + ye; c.cr_uq = c.cb_uq + ce; }
+    } else {
+        out->width = g.fw; out->height = g.fh; out->data = host_out; out->len = dst_bytes;
+    }
     return SLIMG_OK;
 }
 
@@ -626,7 +841,8 @@ slimg_status slimg_b200_pipeline(const slimg_image *in, const slimg_pipeline_opt
     if ((st = build_geometry(in->width, in->height, *opts, order, g)) != SLIMG_OK) return st;
     if ((st = check_device()) != SLIMG_OK) return st;
     out->data = nullptr; out->len = 0;
-    return pipeline_one(in, *opts, order, out, cudaStreamPerThread, false);
+    RingLease lease;
+    return pipeline_one(in, *opts, order, out, nullptr, cudaStreamPerThread, false, lease);
 }
 
 slimg_status slimg_b200_crop(const slimg_image *in, const slimg_crop_mode *mode, slimg_image *out) {
@@ -694,55 +910,77 @@ void slimg_b200_jpeg_quant_table(int quality, int which, int base, uint16_t out[
     }
 }
 
-slimg_status slimg_b200_jpeg_frontend_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
-                                                   const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
-                                                   int16_t *y, int16_t *cb, int16_t *cr, void *stream) {
+slimg_status slimg_b200_jpeg_frontend_batch_device_ex(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
+                                                      const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                                                      int16_t *y, int16_t *cb, int16_t *cr, int16_t *y_uq, int16_t *cb_uq,
+                                                      int16_t *cr_uq, void *stream) {
     if (!qt_luma || !qt_chroma || (n && (!src || !y || !cb || !cr))) return fail(SLIMG_ERR_IMAGE, "null argument");
+    if ((y_uq || cb_uq || cr_uq) && !(y_uq && cb_uq && cr_uq)) return fail(SLIMG_ERR_IMAGE, "un-quantised planes: all three or none");
     if (w == 0 || h == 0) return fail(SLIMG_ERR_ENCODE, "image has a zero dimension");
     slimg_status st = check_device();
     if (st != SLIMG_OK) return st;
-    return run_jpeg_device(src, n, w, h, qt_luma, qt_chroma, y, cb, cr, static_cast<cudaStream_t>(stream));
+    return run_jpeg_device(src, n, w, h, qt_luma, qt_chroma, y, cb, cr, y_uq, cb_uq, cr_uq, static_cast<cudaStream_t>(stream));
 }
 
-slimg_status slimg_b200_jpeg_frontend(const slimg_image *in, const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
-                                      slimg_jpeg_coefs *out) {
+slimg_status slimg_b200_jpeg_frontend_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
+                                                   const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                                                   int16_t *y, int16_t *cb, int16_t *cr, void *stream) {
+    return slimg_b200_jpeg_frontend_batch_device_ex(src, n, w, h, qt_luma, qt_chroma, y, cb, cr, nullptr, nullptr, nullptr, stream);
+}
+
+slimg_status slimg_b200_pipeline_jpeg_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
+                                                   const slimg_pipeline_options *opts, int order,
+                                                   const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                                                   uint8_t *pixels, size_t pixels_capacity, int16_t *y, int16_t *cb,
+                                                   int16_t *cr, int16_t *y_uq, int16_t *cb_uq, int16_t *cr_uq, void *stream) {
+    if (!opts || !qt_luma || !qt_chroma || (n && (!src || !pixels || !y || !cb || !cr))) return fail(SLIMG_ERR_IMAGE, "null argument");
+    if ((y_uq || cb_uq || cr_uq) && !(y_uq && cb_uq && cr_uq)) return fail(SLIMG_ERR_IMAGE, "un-quantised planes: all three or none");
+    if (w == 0 || h == 0) return fail(bad_buffer_status(*opts, order), "image has a zero dimension");
+    PipeGeom g;
+    slimg_status st = build_geometry(w, h, *opts, order, g);
+    if (st != SLIMG_OK) return st;
+    if (size_t(g.fw) * g.fh * 4 * n > pixels_capacity) return fail(SLIMG_ERR_IMAGE, "pixel scratch buffer too small");
+    if ((st = check_device()) != SLIMG_OK) return st;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if ((st = run_pipeline_device(g, src, n, pixels, s)) != SLIMG_OK) return st;
+    return run_jpeg_device(pixels, n, g.fw, g.fh, qt_luma, qt_chroma, y, cb, cr, y_uq, cb_uq, cr_uq, s);
+}
+
+slimg_status slimg_b200_jpeg_frontend_ex(const slimg_image *in, const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                                         uint32_t flags, slimg_jpeg_coefs *out) {
     if (!in || !qt_luma || !qt_chroma || !out) return fail(SLIMG_ERR_IMAGE, "null argument");
     const size_t expected = size_t(in->width) * in->height * 4;
     if (in->width == 0 || in->height == 0 || in->len < expected || !in->data)
         return fail(SLIMG_ERR_ENCODE, "invalid image data for the JPEG front end");
     slimg_status st = check_device();
     if (st != SLIMG_OK) return st;
-    std::memset(out, 0, sizeof *out);
-    jpeg_geometry(in->width, in->height, out->geom);
-    std::memcpy(out->qt_luma, qt_luma, 128);
-    std::memcpy(out->qt_chroma, qt_chroma, 128);
-    const size_t ye = size_t(out->geom.y_HB) * out->geom.y_WB * 64, ce = size_t(out->geom.c_HB) * out->geom.c_WB * 64;
-    cudaStream_t stream = cudaStreamPerThread;
-    uint8_t *d_src = nullptr;
-    int16_t *d_coef = nullptr;
-    int16_t *h_coef = static_cast<int16_t *>(std::malloc((ye + 2 * ce) * 2));
-    if (!h_coef) return fail(SLIMG_ERR_IMAGE, "out of host memory");
-    auto cleanup = [&](slimg_status s) {
-        if (d_src) cudaFreeAsync(d_src, stream);
-        if (d_coef) cudaFreeAsync(d_coef, stream);
-        if (s != SLIMG_OK) std::free(h_coef);
-        return s;
-    };
-    cudaError_t e;
-    if ((e = cudaMallocAsync((void **)&d_src, expected, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
-    if ((e = cudaMallocAsync((void **)&d_coef, (ye + 2 * ce) * 2, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
-    if ((e = cudaMemcpyAsync(d_src, in->data, expected, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "H2D"));
-    if ((st = run_jpeg_device(d_src, 1, in->width, in->height, qt_luma, qt_chroma, d_coef, d_coef + ye, d_coef + ye + ce, stream)) != SLIMG_OK)
-        return cleanup(st);
-    if ((e = cudaMemcpyAsync(h_coef, d_coef, (ye + 2 * ce) * 2, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "D2H"));
-    if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return cleanup(cuda_fail(e, "jpeg front end kernel"));
-    cleanup(SLIMG_OK);
-    out->y = h_coef; out->cb = h_coef + ye; out->cr = h_coef + ye + ce;
-    return SLIMG_OK;
+    const slimg_pipeline_options none{};
+    const JpegRequest req{qt_luma, qt_chroma, flags, out};
+    RingLease lease;
+    return pipeline_one(in, none, SLIMG_ORDER_CONVERT, nullptr, &req, cudaStreamPerThread, false, lease);
+}
+
+slimg_status slimg_b200_jpeg_frontend(const slimg_image *in, const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                                      slimg_jpeg_coefs *out) {
+    return slimg_b200_jpeg_frontend_ex(in, qt_luma, qt_chroma, 0, out);
+}
+
+slimg_status slimg_b200_pipeline_jpeg(const slimg_image *in, const slimg_pipeline_options *opts, int order,
+                                      const uint16_t qt_luma[64], const uint16_t qt_chroma[64], uint32_t flags,
+                                      slimg_jpeg_coefs *out) {
+    if (!opts || !qt_luma || !qt_chroma || !out) return fail(SLIMG_ERR_IMAGE, "null argument");
+    slimg_status st = validate_image(in, *opts, order);
+    if (st != SLIMG_OK) return st;
+    PipeGeom g;
+    if ((st = build_geometry(in->width, in->height, *opts, order, g)) != SLIMG_OK) return st;
+    if ((st = check_device()) != SLIMG_OK) return st;
+    const JpegRequest req{qt_luma, qt_chroma, flags, out};
+    RingLease lease;
+    return pipeline_one(in, *opts, order, nullptr, &req, cudaStreamPerThread, false, lease);
 }
 
 void slimg_b200_jpeg_coefs_free(slimg_jpeg_coefs *c) {
-    if (c && c->y) { std::free(c->y); c->y = c->cb = c->cr = nullptr; }
+    if (c && c->y) { std::free(c->y); c->y = c->cb = c->cr = c->y_uq = c->cb_uq = c->cr_uq = nullptr; }
 }
 
 slimg_status slimg_b200_pipeline_source_window(uint32_t w, uint32_t h, const slimg_pipeline_options *opts, int order,
@@ -762,9 +1000,11 @@ slimg_status slimg_b200_pipeline_source_window(uint32_t w, uint32_t h, const sli
     return SLIMG_OK;
 }
 
-int32_t slimg_b200_pipeline_batch_host(const slimg_image *in, uint32_t n, const slimg_pipeline_options *opts, int order,
-                                       const slimg_batch_config *cfg, slimg_image *out, slimg_status *statuses) {
-    if (!opts || (n && (!in || !out))) { fail(SLIMG_ERR_IMAGE, "null argument"); return -1; }
+// the scheduler behind both batch entry points: jq == nullptr -> pixels into out[], else coefficients into jout[]
+static int32_t batch_host(const slimg_image *in, uint32_t n, const slimg_pipeline_options *opts, int order,
+                          const slimg_batch_config *cfg, slimg_image *out, const JpegRequest *jq, slimg_jpeg_coefs *jout,
+                          slimg_status *statuses) {
+    if (!opts || (n && (!in || (!out && !jout)))) { fail(SLIMG_ERR_IMAGE, "null argument"); return -1; }
     if (check_device() != SLIMG_OK) {
         for (uint32_t i = 0; statuses && i < n; i++) statuses[i] = SLIMG_ERR_IMAGE;
         return int32_t(n);
@@ -791,17 +1031,24 @@ int32_t slimg_b200_pipeline_batch_host(const slimg_image *in, uint32_t n, const 
             cudaGetLastError();
             done = nullptr;
         }
-        for (;;) {
-            const uint32_t i = next.fetch_add(1);
-            if (i >= n) break;
-            slimg_status st = pipeline_one(&in[i], *opts, order, &out[i], s, true, done);
-            statuses[i] = st;
-            if (st != SLIMG_OK) {
-                std::lock_guard<std::mutex> lk(err_mu);
-                if (first_error.empty()) first_error = "image " + std::to_string(i) + ": " + last_error_string();
+        {
+            RingLease lease;                                  // pinned staging, only touched for pageable buffers
+            for (;;) {
+                const uint32_t i = next.fetch_add(1);
+                if (i >= n) break;
+                slimg_status st;
+                if (jq) {
+                    const JpegRequest req{jq->ql, jq->qc, jq->flags, &jout[i]};
+                    st = pipeline_one(&in[i], *opts, order, nullptr, &req, s, false, lease, done);
+                } else st = pipeline_one(&in[i], *opts, order, &out[i], nullptr, s, true, lease, done);
+                statuses[i] = st;
+                if (st != SLIMG_OK) {
+                    std::lock_guard<std::mutex> lk(err_mu);
+                    if (first_error.empty()) first_error = "image " + std::to_string(i) + ": " + last_error_string();
+                }
             }
+            cudaStreamSynchronize(s);
         }
-        cudaStreamSynchronize(s);
         if (done) cudaEventDestroy(done);
         cudaStreamDestroy(s);
     };
@@ -816,5 +1063,22 @@ int32_t slimg_b200_pipeline_batch_host(const slimg_image *in, uint32_t n, const 
     if (!first_error.empty()) set_error(first_error);
     return failed;
 }
+
+int32_t slimg_b200_pipeline_batch_host(const slimg_image *in, uint32_t n, const slimg_pipeline_options *opts, int order,
+                                       const slimg_batch_config *cfg, slimg_image *out, slimg_status *statuses) {
+    return batch_host(in, n, opts, order, cfg, out, nullptr, nullptr, statuses);
+}
+
+int32_t slimg_b200_pipeline_jpeg_batch_host(const slimg_image *in, uint32_t n, const slimg_pipeline_options *opts, int order,
+                                            const uint16_t qt_luma[64], const uint16_t qt_chroma[64], uint32_t flags,
+                                            const slimg_batch_config *cfg, slimg_jpeg_coefs *out, slimg_status *statuses) {
+    if (!qt_luma || !qt_chroma) { fail(SLIMG_ERR_IMAGE, "null argument"); return -1; }
+    for (uint32_t i = 0; out && i < n; i++) std::memset(&out[i], 0, sizeof out[i]);
+    const JpegRequest jq{qt_luma, qt_chroma, flags, nullptr};
+    return batch_host(in, n, opts, order, cfg, nullptr, &jq, out, statuses);
+}
+
+int32_t slimg_b200_last_resize_path(void) { return t_last_path; }
+uint64_t slimg_b200_path_launches(int32_t path) { return path >= 0 && path < 8 ? g_path_launches[path].load() : 0; }
 
 }  // extern "C"

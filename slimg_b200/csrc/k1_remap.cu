@@ -96,25 +96,34 @@ __global__ void __launch_bounds__(kThreads) remap_pixels_kernel(const RemapParam
 
 cudaError_t launch_remap(const RemapParams &p, uint32_t n_images, cudaStream_t stream) {
     if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
-    const unsigned rows = (p.fh + kRowsPerThread - 1) / kRowsPerThread;
     const bool quads = (p.fw % 4 == 0) && (p.dst_img_bytes % 16 == 0) &&
                        ((reinterpret_cast<uintptr_t>(p.dst) & 15) == 0);
-    // gridDim.y/z are limited to 65535: fh <= 262140 rows and n <= 65535 images per launch
-    for (uint32_t first = 0; first < n_images; first += 65535) {
-        RemapParams q = p;
-        q.src += size_t(first) * p.src_img_bytes;
-        q.dst += size_t(first) * p.dst_img_bytes;
-        const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
-        if (quads) {
-            dim3 grid((p.fw / 4 + kThreads - 1) / kThreads, rows, nz);
-            remap_quads_kernel<<<grid, kThreads, 0, stream>>>(q);
-        } else {
-            dim3 grid((p.fw + kThreads - 1) / kThreads, rows, nz);
-            remap_pixels_kernel<<<grid, kThreads, 0, stream>>>(q);
+    // gridDim.y/z are limited to 65535: taller canvases go in slices of 65535 * kRowsPerThread rows (the slice is a
+    // canvas of its own whose rectangles are shifted up by its first row), batches in slices of 65535 images
+    constexpr uint32_t kSliceRows = 65535u * kRowsPerThread;
+    for (uint32_t y0 = 0; y0 < p.fh; y0 += kSliceRows) {
+        const uint32_t slice_h = p.fh - y0 < kSliceRows ? p.fh - y0 : kSliceRows;
+        const unsigned rows = (slice_h + kRowsPerThread - 1) / kRowsPerThread;
+        for (uint32_t first = 0; first < n_images; first += 65535) {
+            RemapParams q = p;
+            q.src += size_t(first) * p.src_img_bytes;
+            q.dst += size_t(first) * p.dst_img_bytes + size_t(y0) * p.fw * 4;
+            q.fh = slice_h;
+            q.ay0 = p.ay0 - int32_t(y0); q.ay1 = p.ay1 - int32_t(y0);
+            q.by0 = p.by0 - int32_t(y0); q.by1 = p.by1 - int32_t(y0);
+            q.dy = p.dy + int32_t(y0);
+            const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
+            if (quads) {
+                dim3 grid((p.fw / 4 + kThreads - 1) / kThreads, rows, nz);
+                remap_quads_kernel<<<grid, kThreads, 0, stream>>>(q);
+            } else {
+                dim3 grid((p.fw + kThreads - 1) / kThreads, rows, nz);
+                remap_pixels_kernel<<<grid, kThreads, 0, stream>>>(q);
+            }
+            count_launch();
+            cudaError_t e = cudaGetLastError();
+            if (e != cudaSuccess) return e;
         }
-        count_launch();
-        cudaError_t e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
     }
     return cudaSuccess;
 }

@@ -356,6 +356,7 @@ cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cuda
             const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
             kern<<<dim3(tiles_x, tiles_y, nz), kThreads, smem_few, stream>>>(q, src_rows_max);
             count_launch();
+            note_path(SLIMG_PATH_FEWTAPS);
             cudaError_t e = cudaGetLastError();
             if (e != cudaSuccess) return e;
         }
@@ -368,6 +369,7 @@ cudaError_t launch_resize_generic(const ResizeParams &p, uint32_t n_images, cuda
         const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
         resize_generic_kernel<<<dim3(tiles_x, tiles_y, nz), kThreads, smem, stream>>>(q);
         count_launch();
+        note_path(SLIMG_PATH_GENERIC);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }

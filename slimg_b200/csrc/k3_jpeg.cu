@@ -11,18 +11,20 @@
 //   convsamp / islow FDCT / quantize   jcdctmgr.c:373-438, jfdctint.c:143-286
 //   dummy blocks         jccoefct.c:286-319
 //
-// One CTA = up to kMcus consecutive MCUs (16x16 pixels each) of one MCU row: 4 Y blocks + Cb + Cr per MCU.
-//   stage 1  every thread converts patches of 4 x 2 pixels (two 16-byte loads): 8 Y samples go to the Y tile as two
-//            packed words, the 2 x 2 chroma averages (bias 1,2) straight to the half-resolution Cb / Cr tiles --
-//            the full-resolution chroma planes of the reference never exist
-//   stage 2  ONE THREAD PER 8x8 BLOCK, the whole block in registers: 8 row DCTs, 8 column DCTs, reciprocal
-//            quantisation with the tables as constant-bank immediates (warps are homogeneous: 4 warps of Y blocks,
-//            one of Cb, one of Cr), dummy-block patch through a 192-entry DC table, 8 x 16-byte stores
-// No DCT workspace in shared memory, two CTA barriers in all.
+// One WARP = a tile of kWMcus consecutive MCUs (16x16 pixels each) of one MCU row; a persistent grid of warps walks the
+// tiles of the whole batch (no CTA-wide barrier after the table load):
+//   stage 1  every lane converts patches of 4 x 2 pixels (two 16-byte loads, the next patch's loads issued before the
+//            current one is converted): 8 Y samples go to the warp's Y tile as two packed words, the 2 x 2 chroma
+//            averages (bias 1,2) straight to the half-resolution Cb / Cr tiles -- the full-resolution chroma planes of
+//            the reference never exist
+//   stage 2  a block belongs to 8 LANES: lane r runs the row DCT of row r, the 8x8 intermediate is transposed through a
+//            padded per-warp scratch, lane c runs the column DCT of column c and quantises its 8 coefficients with
+//            table entries read from shared memory; optionally the un-quantised coefficients are stored as well (the
+//            block MozJPEG keeps for its trellis pass)
 //
-// Roofline: nominally HBM (w*h*4 read + (Y_HB*Y_WB + 2*C_HB*C_WB)*128 written = 7 B/px), but at ~45 integer
-// operations per pixel the kernel sits just above the INT32 ridge of the B200 (37 Tops / 6.55 TB/s = 5.7 op/B
-// against 6.4 op/B): the ALU pipe bounds it.
+// Roofline: nominally HBM (w*h*4 read + (Y_HB*Y_WB + 2*C_HB*C_WB)*128 written = 7 B/px), but at ~65 integer
+// instructions per pixel the kernel is bound by instruction issue (every integer instruction of this part issues at
+// ~65 lanes/clk/SM, profiles/r01f_microbench_b200.txt).
 #include <algorithm>
 #include <cstdlib>
 
@@ -31,12 +33,6 @@
 namespace slimg {
 
 namespace {
-
-constexpr int kMcus = 32;                       // MCUs per CTA
-constexpr int kStripW = 16 * kMcus;             // 512 pixels
-constexpr int kThreads = 256;
-constexpr int kBlocksY = 4 * kMcus, kBlocksC = kMcus;
-constexpr int kBlocks = kBlocksY + 2 * kBlocksC;  // 192 blocks per CTA, one thread each
 
 #define SLIMG_FIX(x) int((x) * 65536.0 + 0.5)
 
@@ -97,57 +93,10 @@ __device__ __forceinline__ void fdct8(const int in[8], int out[8]) {
     out[1] = descale(t7 + z1 + z4, sh);
 }
 
-struct Smem {
-    uint32_t ys[16][kStripW / 4];     // Y samples, 4 per word
-    uint16_t cb[8][kStripW / 4];      // downsampled Cb / Cr, 2 per halfword (one halfword per stage-1 patch)
-    uint16_t cr[8][kStripW / 4];
-    int16_t dc[kBlocksY];             // quantised DC of every Y block (dummy-block patch)
-};
-
 __device__ __forceinline__ void ycc3(uint32_t px, int &y, int &cb, int &cr) {
     uint8_t a, b, c;
     rgb_to_ycc(px, a, b, c);
     y = a; cb = b; cr = c;
-}
-
-// reciprocal quantisation of one coefficient (jcdctmgr.c:408-438); shift >= 34 always (divisor = q << 3 >= 8), so
-// the 64-bit product >> shift is the high word >> (shift - 32)
-template <int TBL, int IDX>
-__device__ __forceinline__ int quant1(const JpegParams &p, int t) {
-    const uint32_t a = uint32_t(t < 0 ? -t : t) + p.q.corr[TBL][IDX];
-    const uint32_t q = __umulhi(a, p.q.recip[TBL][IDX]) >> p.q.shift32[TBL][IDX];
-    return t < 0 ? -int(q) : int(q);
-}
-
-template <int TBL, int K>
-__device__ __forceinline__ void quant_row(const JpegParams &p, int (&b)[8][8]) {
-    b[K][0] = quant1<TBL, K * 8 + 0>(p, b[K][0]); b[K][1] = quant1<TBL, K * 8 + 1>(p, b[K][1]);
-    b[K][2] = quant1<TBL, K * 8 + 2>(p, b[K][2]); b[K][3] = quant1<TBL, K * 8 + 3>(p, b[K][3]);
-    b[K][4] = quant1<TBL, K * 8 + 4>(p, b[K][4]); b[K][5] = quant1<TBL, K * 8 + 5>(p, b[K][5]);
-    b[K][6] = quant1<TBL, K * 8 + 6>(p, b[K][6]); b[K][7] = quant1<TBL, K * 8 + 7>(p, b[K][7]);
-}
-
-// forward DCT (jpeg_fdct_islow: rows, then columns) and quantisation of the block held in b[row][col]
-template <int TBL>
-__device__ __forceinline__ void fdct_quant(const JpegParams &p, int (&b)[8][8]) {
-#pragma unroll
-    for (int r = 0; r < 8; r++) {
-        int out[8];
-        fdct8<1>(b[r], out);
-#pragma unroll
-        for (int k = 0; k < 8; k++) b[r][k] = out[k];
-    }
-#pragma unroll
-    for (int c = 0; c < 8; c++) {
-        int in[8], out[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) in[k] = b[k][c];
-        fdct8<2>(in, out);
-#pragma unroll
-        for (int k = 0; k < 8; k++) b[k][c] = out[k];
-    }
-    quant_row<TBL, 0>(p, b); quant_row<TBL, 1>(p, b); quant_row<TBL, 2>(p, b); quant_row<TBL, 3>(p, b);
-    quant_row<TBL, 4>(p, b); quant_row<TBL, 5>(p, b); quant_row<TBL, 6>(p, b); quant_row<TBL, 7>(p, b);
 }
 
 __device__ __forceinline__ void unpack8(uint32_t lo, uint32_t hi, int (&row)[8]) {
@@ -155,143 +104,9 @@ __device__ __forceinline__ void unpack8(uint32_t lo, uint32_t hi, int (&row)[8])
     row[4] = int(hi & 0xff) - 128; row[5] = int((hi >> 8) & 0xff) - 128; row[6] = int((hi >> 16) & 0xff) - 128; row[7] = int(hi >> 24) - 128;
 }
 
-__device__ __forceinline__ void store_block(int16_t *d, const int (&b)[8][8]) {
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-        uint4 v;
-        v.x = (uint32_t(b[k][0]) & 0xffffu) | (uint32_t(b[k][1]) << 16);
-        v.y = (uint32_t(b[k][2]) & 0xffffu) | (uint32_t(b[k][3]) << 16);
-        v.z = (uint32_t(b[k][4]) & 0xffffu) | (uint32_t(b[k][5]) << 16);
-        v.w = (uint32_t(b[k][6]) & 0xffffu) | (uint32_t(b[k][7]) << 16);
-        *reinterpret_cast<uint4 *>(d + k * 8) = v;
-    }
-}
-
-__global__ void __launch_bounds__(kThreads, 2) jpeg_frontend_kernel(const __grid_constant__ JpegParams p) {
-    __shared__ Smem sm;
-    const int tid = threadIdx.x;
-    const uint32_t *src = reinterpret_cast<const uint32_t *>(p.src + size_t(blockIdx.z) * p.src_img_bytes);
-    const int mx0 = blockIdx.x * kMcus, my = blockIdx.y;
-    const int nm = min(kMcus, int(p.c_wb) - mx0);          // MCUs of this CTA
-    const int x0 = mx0 * 16, y0 = my * 16;
-    const int w = int(p.w), h = int(p.h);
-    const int creal = (h + 1) / 2;   // chroma rows that come from real downsampling
-    const bool vec_ok = (w & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0;
-
-    // stage 1: colour conversion with edge replication.  Y uses row min(y, h-1).  Chroma row cy past creal-1 repeats
-    // the last DOWNSAMPLED row (jcprepct.c:174-183), so its two source rows are those of row creal-1, which differ
-    // from the Y mapping only below the image.
-    for (int i = tid; i < 8 * (kStripW / 4); i += kThreads) {
-        const int pr = i / (kStripW / 4), pc = i - pr * (kStripW / 4);
-        if (pc * 4 >= nm * 16) continue;
-        const int x = x0 + 4 * pc;
-        const int yy0 = y0 + 2 * pr;
-        const int sy[2] = {min(yy0, h - 1), min(yy0 + 1, h - 1)};
-        const int cyy = min(yy0 >> 1, creal - 1);
-        const int sc[2] = {min(2 * cyy, h - 1), min(2 * cyy + 1, h - 1)};
-        uint32_t px[2][4];
-#pragma unroll
-        for (int r = 0; r < 2; r++) {
-            const uint32_t *row = src + size_t(sy[r]) * w;
-            if (vec_ok && x + 3 < w) {
-                const uint4 v = __ldg(reinterpret_cast<const uint4 *>(row + x));
-                px[r][0] = v.x; px[r][1] = v.y; px[r][2] = v.z; px[r][3] = v.w;
-            } else {
-#pragma unroll
-                for (int k = 0; k < 4; k++) px[r][k] = __ldg(row + min(x + k, w - 1));
-            }
-        }
-        int yv[2][4], cbv[2][4], crv[2][4];
-#pragma unroll
-        for (int r = 0; r < 2; r++)
-#pragma unroll
-            for (int k = 0; k < 4; k++) ycc3(px[r][k], yv[r][k], cbv[r][k], crv[r][k]);
-        if (sc[0] != sy[0] || sc[1] != sy[1]) {            // below the image: chroma comes from other rows than Y
-#pragma unroll
-            for (int r = 0; r < 2; r++)
-#pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    int unused;
-                    ycc3(__ldg(src + size_t(sc[r]) * w + min(x + k, w - 1)), unused, cbv[r][k], crv[r][k]);
-                }
-        }
-#pragma unroll
-        for (int r = 0; r < 2; r++)
-            sm.ys[2 * pr + r][pc] = uint32_t(yv[r][0]) | (uint32_t(yv[r][1]) << 8) | (uint32_t(yv[r][2]) << 16) | (uint32_t(yv[r][3]) << 24);
-        // h2v2_downsample (jcsample.c:272-284): bias 1 for even output columns, 2 for odd ones
-        const int cb0 = (cbv[0][0] + cbv[0][1] + cbv[1][0] + cbv[1][1] + 1) >> 2, cb1 = (cbv[0][2] + cbv[0][3] + cbv[1][2] + cbv[1][3] + 2) >> 2;
-        const int cr0 = (crv[0][0] + crv[0][1] + crv[1][0] + crv[1][1] + 1) >> 2, cr1 = (crv[0][2] + crv[0][3] + crv[1][2] + crv[1][3] + 2) >> 2;
-        sm.cb[pr][pc] = uint16_t(cb0 | (cb1 << 8));
-        sm.cr[pr][pc] = uint16_t(cr0 | (cr1 << 8));
-    }
-    __syncthreads();
-
-    // stage 2: one thread per block.  Threads [0, 4*kMcus): Y block (by2, bx); then kMcus Cb blocks, kMcus Cr blocks.
-    int16_t *yout = p.y + size_t(blockIdx.z) * p.y_img_elems;
-    int16_t *cbout = p.cb + size_t(blockIdx.z) * p.c_img_elems;
-    int16_t *crout = p.cr + size_t(blockIdx.z) * p.c_img_elems;
-    const int ybx0 = mx0 * 2, yby0 = my * 2;
-    int b[8][8];
-    const bool is_y = tid < kBlocksY;
-    const int by2 = tid / (2 * kMcus), bx = is_y ? tid - by2 * (2 * kMcus) : (tid - kBlocksY) % kBlocksC;
-    const bool is_cr = tid >= kBlocksY + kBlocksC;
-    const bool active = tid < kBlocks && (is_y ? bx < 2 * nm : bx < nm);
-    if (active) {
-        if (is_y) {
-#pragma unroll
-            for (int r = 0; r < 8; r++) {
-                const uint2 v = *reinterpret_cast<const uint2 *>(&sm.ys[by2 * 8 + r][bx * 2]);
-                unpack8(v.x, v.y, b[r]);
-            }
-            fdct_quant<0>(p, b);
-            sm.dc[tid] = int16_t(b[0][0]);
-        } else {
-            const uint16_t(*f)[kStripW / 4] = is_cr ? sm.cr : sm.cb;
-#pragma unroll
-            for (int r = 0; r < 8; r++) {
-                const uint2 v = *reinterpret_cast<const uint2 *>(&f[r][bx * 4]);
-                unpack8(v.x, v.y, b[r]);
-            }
-            fdct_quant<1>(p, b);
-        }
-    }
-    __syncthreads();
-    if (!active) return;
-    if (is_y) {
-        // dummy Y blocks (jccoefct.c:286-294 right edge, :301-319 bottom rows): AC = 0, DC = the DC of the last real
-        // block to the left / of the MCU's last block in the row above
-        const int gbx = ybx0 + bx, gby = yby0 + by2;
-        if (gbx >= int(p.y_WB) || gby >= int(p.y_HB)) return;
-        const bool dummy_right = gbx >= int(p.y_wb), dummy_bottom = gby >= int(p.y_hb);
-        if (dummy_right || dummy_bottom) {
-            int sb_x = bx, sb_y = by2;
-            if (dummy_bottom) { sb_y = by2 - 1; sb_x = bx | 1; }               // last block of this MCU, row above
-            if (ybx0 + sb_x >= int(p.y_wb)) sb_x = int(p.y_wb) - 1 - ybx0;      // which may itself be a right-edge dummy
-            const int dc = sm.dc[sb_y * (2 * kMcus) + sb_x];
-#pragma unroll
-            for (int r = 0; r < 8; r++)
-#pragma unroll
-                for (int k = 0; k < 8; k++) b[r][k] = 0;
-            b[0][0] = dc;
-        }
-        store_block(yout + (size_t(gby) * p.y_WB + gbx) * 64, b);
-    } else {
-        const int gbx = mx0 + bx;
-        store_block((is_cr ? crout : cbout) + (size_t(my) * p.c_wb + gbx) * 64, b);
-    }
-}
-
-// ---- warp-autonomous variant: the production kernel ----------------------------------------------------------------
-// The CTA-wide version above keeps a whole 8x8 block per thread: ~5000 instructions of straight-line code that every
-// warp runs through once per block, so the SM stalls on instruction fetch (ncu: stall_no_instruction ~1 per issue) and
-// on its two CTA barriers (stall_barrier 2.3), and issues at 46 % whatever the memory side does.  Here:
-//   * every WARP owns a tile of kWMcus MCUs (256 x 16 pixels) and runs both stages on it by itself (__syncwarp only);
-//   * stage 2 gives a block to 8 LANES: lane r runs the row DCT of row r, the 8x8 intermediate is transposed through
-//     a padded per-warp scratch (conflict-free 16-byte stores, conflict-free column reads), lane c runs the column DCT
-//     of column c and quantises its 8 coefficients with table entries it keeps in registers.  The loop body is ~250
-//     instructions, shared by all blocks.
+// ---- the kernel: warp-autonomous tiles -------------------------------------------------------------------------
 constexpr int kWMcus = 8;
-constexpr int kWW = 16 * kWMcus;                // 256 pixels
+constexpr int kWW = 16 * kWMcus;                // 128 pixels
 constexpr int kWarpsPerCta = 4;
 constexpr int kRowStride = 12;                  // words between scratch rows: 16-byte chunks of 8 lanes hit distinct banks
 constexpr int kBlkStride = 8 * kRowStride + 8;  // words between the scratch blocks of a warp: column reads of 4 blocks disjoint
@@ -302,12 +117,13 @@ struct WarpSmem {
     uint16_t cb[8][kWW / 4 + 8];      // downsampled Cb / Cr, one halfword (2 samples) per stage-1 patch
     uint16_t cr[8][kWW / 4 + 8];
     int scratch[4 * kBlkStride];      // row-pass output of the 4 blocks in flight
-    int16_t dc[2][2 * kWMcus];        // quantised DC of the Y blocks (dummy-block patch)
+    int16_t dc[2][2][2 * kWMcus];     // [quantised, un-quantised] DC of the Y blocks (dummy-block patch)
 };
 
 // row DCT by lane r of the group, transpose through scratch, column DCT + quantisation by lane c; returns the 8
-// coefficients (k, c), k = 0..7, of the block
-__device__ __forceinline__ void block_dct(int *scr, int l8, uint32_t lo, uint32_t hi, const uint32_t (*qt)[64], int (&out)[8]) {
+// coefficients (k, c), k = 0..7, of the block in out[] and, with UQ, the un-quantised ones in uq[]
+template <bool UQ>
+__device__ __forceinline__ void block_dct(int *scr, int l8, uint32_t lo, uint32_t hi, const uint32_t (*qt)[64], int (&out)[8], int (&uq)[8]) {
     int in[8], mid[8];
     unpack8(lo, hi, in);
     fdct8<1>(in, mid);
@@ -321,13 +137,16 @@ __device__ __forceinline__ void block_dct(int *scr, int l8, uint32_t lo, uint32_
 #pragma unroll
     for (int k = 0; k < 8; k++) {          // jcdctmgr.c:408-438, reciprocal form; shift >= 34, see build_quant
         const int t = mid[k];
+        if (UQ) uq[k] = t;
         const uint32_t a = uint32_t(t < 0 ? -t : t) + qt[1][k * 8 + l8];
         const uint32_t q = __umulhi(a, qt[0][k * 8 + l8]) >> qt[2][k * 8 + l8];
         out[k] = t < 0 ? -int(q) : int(q);
     }
 }
 
-template <int UNROLL, int MINB>
+// PIPE: 1 = the loads of stage-1 patch j+1 are issued before patch j is converted; 2 = additionally, the first patch of
+// the warp's NEXT tile is loaded before stage 2 of the current one (8 more live registers across the DCT)
+template <int PIPE, int MINB, bool UQ>
 __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_kernel(const __grid_constant__ JpegParams p, const uint32_t n_images) {
     __shared__ __align__(16) WarpSmem wsm[kWarpsPerCta];
     const int lane = threadIdx.x & 31, l8 = lane & 7, q4 = lane >> 3;
@@ -348,64 +167,99 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
     }
     __syncthreads();
 
+    // the two 16-byte loads of stage-1 patch (pr, lane) of the tile at (x0, y0) of image `src`
+    auto load_patch = [&](const uint32_t *src, int x0, int y0, int pr, uint32_t (&px)[2][4]) {
+        const int x = x0 + 4 * lane, yy0 = y0 + 2 * pr;
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+            const uint32_t *row = src + size_t(min(yy0 + r, h - 1)) * w;
+            if (vec_ok && x + 3 < w) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4 *>(row + x));
+                px[r][0] = v.x; px[r][1] = v.y; px[r][2] = v.z; px[r][3] = v.w;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; k++) px[r][k] = __ldg(row + min(x + k, w - 1));
+            }
+        }
+    };
+    // colour conversion of one patch with edge replication.  Y uses row min(y, h-1).  Chroma row cy past creal-1 repeats
+    // the last DOWNSAMPLED row (jcprepct.c:174-183): other source rows than Y, below the image only.
+    auto convert_patch = [&](const uint32_t *src, int x0, int y0, int pr, const uint32_t (&px)[2][4]) {
+        const int x = x0 + 4 * lane, yy0 = y0 + 2 * pr;
+        const int sy[2] = {min(yy0, h - 1), min(yy0 + 1, h - 1)};
+        const int cyy = min(yy0 >> 1, creal - 1);
+        const int sc[2] = {min(2 * cyy, h - 1), min(2 * cyy + 1, h - 1)};
+        int yv[2][4], cbv[2][4], crv[2][4];
+#pragma unroll
+        for (int r = 0; r < 2; r++)
+#pragma unroll
+            for (int k = 0; k < 4; k++) ycc3(px[r][k], yv[r][k], cbv[r][k], crv[r][k]);
+        if (sc[0] != sy[0] || sc[1] != sy[1]) {
+#pragma unroll
+            for (int r = 0; r < 2; r++)
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    int unused;
+                    ycc3(__ldg(src + size_t(sc[r]) * w + min(x + k, w - 1)), unused, cbv[r][k], crv[r][k]);
+                }
+        }
+#pragma unroll
+        for (int r = 0; r < 2; r++)
+            sm.ys[2 * pr + r][lane] = uint32_t(yv[r][0]) | (uint32_t(yv[r][1]) << 8) | (uint32_t(yv[r][2]) << 16) | (uint32_t(yv[r][3]) << 24);
+        // h2v2_downsample (jcsample.c:272-284): bias 1 for even output columns, 2 for odd ones
+        const int cb0 = (cbv[0][0] + cbv[0][1] + cbv[1][0] + cbv[1][1] + 1) >> 2, cb1 = (cbv[0][2] + cbv[0][3] + cbv[1][2] + cbv[1][3] + 2) >> 2;
+        const int cr0 = (crv[0][0] + crv[0][1] + crv[1][0] + crv[1][1] + 1) >> 2, cr1 = (crv[0][2] + crv[0][3] + crv[1][2] + crv[1][3] + 2) >> 2;
+        sm.cb[pr][lane] = uint16_t(cb0 | (cb1 << 8));
+        sm.cr[pr][lane] = uint16_t(cr0 | (cr1 << 8));
+    };
+    auto tile_at = [&](uint64_t t, uint32_t &z, int &my, int &mx0) {
+        z = uint32_t(t / tiles_img);
+        const uint32_t rem = uint32_t(t - uint64_t(z) * tiles_img);
+        my = int(rem / tiles_x); mx0 = int(rem - uint32_t(my) * tiles_x) * kWMcus;
+    };
+
+    uint32_t pa[2][4], pb[2][4];           // patch registers: even / odd patch rows
+    if (PIPE == 2 && gw < n_tiles) {
+        uint32_t z; int my, mx0;
+        tile_at(gw, z, my, mx0);
+        if (lane * 4 < min(kWMcus, int(p.c_wb) - mx0) * 16)
+            load_patch(reinterpret_cast<const uint32_t *>(p.src + size_t(z) * p.src_img_bytes), mx0 * 16, my * 16, 0, pa);
+    }
 #pragma unroll 1
     for (uint64_t t = gw; t < n_tiles; t += nw) {
-        const uint32_t z = uint32_t(t / tiles_img), rem = uint32_t(t - uint64_t(z) * tiles_img);
-        const int my = int(rem / tiles_x), mx0 = int(rem - uint32_t(my) * tiles_x) * kWMcus;
+        uint32_t z; int my, mx0;
+        tile_at(t, z, my, mx0);
         const int nm = min(kWMcus, int(p.c_wb) - mx0);
         const int x0 = mx0 * 16, y0 = my * 16;
         const uint32_t *src = reinterpret_cast<const uint32_t *>(p.src + size_t(z) * p.src_img_bytes);
 
-        // stage 1: colour conversion with edge replication.  Y uses row min(y, h-1).  Chroma row cy past creal-1
-        // repeats the last DOWNSAMPLED row (jcprepct.c:174-183): other source rows than Y, below the image only.
-#pragma unroll(UNROLL)
-        for (int i = lane; i < ((p.debug & 1u) ? 0 : 8 * (kWW / 4)); i += 32) {
-            const int pr = i / (kWW / 4), pc = i - pr * (kWW / 4);
-            if (pc * 4 >= nm * 16) continue;
-            const int x = x0 + 4 * pc;
-            const int yy0 = y0 + 2 * pr;
-            const int sy[2] = {min(yy0, h - 1), min(yy0 + 1, h - 1)};
-            const int cyy = min(yy0 >> 1, creal - 1);
-            const int sc[2] = {min(2 * cyy, h - 1), min(2 * cyy + 1, h - 1)};
-            uint32_t px[2][4];
-#pragma unroll
-            for (int r = 0; r < 2; r++) {
-                const uint32_t *row = src + size_t(sy[r]) * w;
-                if (vec_ok && x + 3 < w) {
-                    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(row + x));
-                    px[r][0] = v.x; px[r][1] = v.y; px[r][2] = v.z; px[r][3] = v.w;
-                } else {
-#pragma unroll
-                    for (int k = 0; k < 4; k++) px[r][k] = __ldg(row + min(x + k, w - 1));
+        // stage 1: patch rows 0..7 of column `lane` (lanes right of a partial tile idle)
+        if (!(p.debug & 1u) && lane * 4 < nm * 16) {
+            if (PIPE == 0) {
+#pragma unroll 1
+                for (int pr = 0; pr < 8; pr++) { load_patch(src, x0, y0, pr, pa); convert_patch(src, x0, y0, pr, pa); }
+            } else {
+                if (PIPE == 1) load_patch(src, x0, y0, 0, pa);
+#pragma unroll 1
+                for (int pr = 0; pr < 8; pr += 2) {
+                    load_patch(src, x0, y0, pr + 1, pb);
+                    convert_patch(src, x0, y0, pr, pa);
+                    if (pr + 2 < 8) load_patch(src, x0, y0, pr + 2, pa);
+                    convert_patch(src, x0, y0, pr + 1, pb);
                 }
             }
-            int yv[2][4], cbv[2][4], crv[2][4];
-#pragma unroll
-            for (int r = 0; r < 2; r++)
-#pragma unroll
-                for (int k = 0; k < 4; k++) ycc3(px[r][k], yv[r][k], cbv[r][k], crv[r][k]);
-            if (sc[0] != sy[0] || sc[1] != sy[1]) {
-#pragma unroll
-                for (int r = 0; r < 2; r++)
-#pragma unroll
-                    for (int k = 0; k < 4; k++) {
-                        int unused;
-                        ycc3(__ldg(src + size_t(sc[r]) * w + min(x + k, w - 1)), unused, cbv[r][k], crv[r][k]);
-                    }
-            }
-#pragma unroll
-            for (int r = 0; r < 2; r++)
-                sm.ys[2 * pr + r][pc] = uint32_t(yv[r][0]) | (uint32_t(yv[r][1]) << 8) | (uint32_t(yv[r][2]) << 16) | (uint32_t(yv[r][3]) << 24);
-            // h2v2_downsample (jcsample.c:272-284): bias 1 for even output columns, 2 for odd ones
-            const int cb0 = (cbv[0][0] + cbv[0][1] + cbv[1][0] + cbv[1][1] + 1) >> 2, cb1 = (cbv[0][2] + cbv[0][3] + cbv[1][2] + cbv[1][3] + 2) >> 2;
-            const int cr0 = (crv[0][0] + crv[0][1] + crv[1][0] + crv[1][1] + 1) >> 2, cr1 = (crv[0][2] + crv[0][3] + crv[1][2] + crv[1][3] + 2) >> 2;
-            sm.cb[pr][pc] = uint16_t(cb0 | (cb1 << 8));
-            sm.cr[pr][pc] = uint16_t(cr0 | (cr1 << 8));
+        }
+        if (PIPE == 2 && t + nw < n_tiles) {           // first patch of the next tile: in flight during stage 2
+            uint32_t zn; int myn, mxn;
+            tile_at(t + nw, zn, myn, mxn);
+            if (lane * 4 < min(kWMcus, int(p.c_wb) - mxn) * 16)
+                load_patch(reinterpret_cast<const uint32_t *>(p.src + size_t(zn) * p.src_img_bytes), mxn * 16, myn * 16, 0, pa);
         }
         __syncwarp();
 
         // stage 2, Y: 4 blocks per step (one per group of 8 lanes), block rows one after the other
         int16_t *yout = p.y + size_t(z) * p.y_img_elems;
+        int16_t *yuq = UQ ? p.yu + size_t(z) * p.y_img_elems : nullptr;
         const int ybx0 = mx0 * 2, yby0 = my * 2;
         const int nby = min(2 * nm, int(p.y_wb) - ybx0);          // real Y block columns of the tile
         const int nrow = min(2, int(p.y_hb) - yby0);              // real Y block rows
@@ -414,13 +268,17 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
             const int by2 = s / (kWMcus / 2), bx = (s - by2 * (kWMcus / 2)) * 4 + q4;
             if ((s - by2 * (kWMcus / 2)) * 4 >= nby) continue;     // warp-uniform: the whole step lies right of the image
             const uint2 v = *reinterpret_cast<const uint2 *>(&sm.ys[by2 * 8 + l8][min(bx, 2 * kWMcus - 1) * 2]);
-            int out[8];
-            block_dct(scr, l8, v.x, v.y, qt[0], out);
+            int out[8], uq[8];
+            block_dct<UQ>(scr, l8, v.x, v.y, qt[0], out, uq);
             if (bx < nby) {
-                if (l8 == 0) sm.dc[by2][bx] = int16_t(out[0]);
-                int16_t *d = yout + (size_t(yby0 + by2) * p.y_WB + ybx0 + bx) * 64 + l8;
+                if (l8 == 0) { sm.dc[0][by2][bx] = int16_t(out[0]); if (UQ) sm.dc[1][by2][bx] = int16_t(uq[0]); }
+                const size_t off = (size_t(yby0 + by2) * p.y_WB + ybx0 + bx) * 64 + l8;
 #pragma unroll
-                for (int k = 0; k < 8; k++) d[k * 8] = int16_t(out[k]);
+                for (int k = 0; k < 8; k++) yout[off + k * 8] = int16_t(out[k]);
+                if (UQ) {
+#pragma unroll
+                    for (int k = 0; k < 8; k++) yuq[off + k * 8] = int16_t(uq[k]);
+                }
             }
         }
         // chroma: steps of 4 blocks, Cb then Cr (both quantise with table 1)
@@ -430,12 +288,18 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
             if (bx0 >= nm) continue;
             const uint16_t(*f)[kWW / 4 + 8] = pl ? sm.cr : sm.cb;
             const uint2 v = *reinterpret_cast<const uint2 *>(&f[l8][bx * 4]);
-            int out[8];
-            block_dct(scr, l8, v.x, v.y, qt[1], out);
+            int out[8], uq[8];
+            block_dct<UQ>(scr, l8, v.x, v.y, qt[1], out, uq);
             if (bx < nm) {
-                int16_t *d = (pl ? p.cr : p.cb) + size_t(z) * p.c_img_elems + (size_t(my) * p.c_wb + mx0 + bx) * 64 + l8;
+                const size_t off = size_t(z) * p.c_img_elems + (size_t(my) * p.c_wb + mx0 + bx) * 64 + l8;
+                int16_t *d = (pl ? p.cr : p.cb) + off;
 #pragma unroll
                 for (int k = 0; k < 8; k++) d[k * 8] = int16_t(out[k]);
+                if (UQ) {
+                    int16_t *du = (pl ? p.cru : p.cbu) + off;
+#pragma unroll
+                    for (int k = 0; k < 8; k++) du[k * 8] = int16_t(uq[k]);
+                }
             }
         }
         __syncwarp();
@@ -451,11 +315,14 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
                 int sb_x = bx, sb_y = by2;
                 if (dummy_bottom) { sb_y = by2 - 1; sb_x = bx | 1; }               // last block of this MCU, row above
                 if (ybx0 + sb_x >= int(p.y_wb)) sb_x = int(p.y_wb) - 1 - ybx0;      // which may itself be a right-edge dummy
-                const uint32_t dc = uint32_t(uint16_t(sm.dc[sb_y][sb_x]));
-                uint4 *d = reinterpret_cast<uint4 *>(yout + (size_t(gby) * p.y_WB + gbx) * 64);
-                d[0] = make_uint4(dc, 0u, 0u, 0u);
 #pragma unroll
-                for (int k = 1; k < 8; k++) d[k] = make_uint4(0u, 0u, 0u, 0u);
+                for (int u = 0; u < (UQ ? 2 : 1); u++) {
+                    const uint32_t dc = uint32_t(uint16_t(sm.dc[u][sb_y][sb_x]));
+                    uint4 *d = reinterpret_cast<uint4 *>((u ? yuq : yout) + (size_t(gby) * p.y_WB + gbx) * 64);
+                    d[0] = make_uint4(dc, 0u, 0u, 0u);
+#pragma unroll
+                    for (int k = 1; k < 8; k++) d[k] = make_uint4(0u, 0u, 0u, 0u);
+                }
             }
         }
         __syncwarp();                    // the sample tiles and dc[] are rewritten by the next tile
@@ -467,39 +334,33 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
 cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStream_t stream) {
     if (n_images == 0 || p.w == 0 || p.h == 0) return cudaSuccess;
     const unsigned mcus_x = p.c_wb, mcus_y = p.c_hb;
-    if (mcus_y > 65535) return cudaErrorInvalidValue;
-    if (!std::getenv("SLIMG_B200_JPEG_CTA")) {          // the CTA-wide kernel is kept for A/B comparison only
-        const char *var_env = std::getenv("SLIMG_B200_JPEG_VAR");
-        const int var = var_env ? std::atoi(var_env) : 7;      // measured best on B200: 32 warps/SM, 64 registers
-        // <stage-1 unroll, CTAs per SM>: measured on B200 (24 MP, q=70): <1,8> 67.9 us, <1,6> 69.2 us, <4,4> 79.7 us -- occupancy
-        // beats loads in flight per warp
-        auto kern = var == 0 ? jpeg_frontend_warp_kernel<4, 4> : var == 2 ? jpeg_frontend_warp_kernel<1, 6> : jpeg_frontend_warp_kernel<1, 8>;
-        int dev = 0, sms = 148, per_sm = 4;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * kWarpsPerCta, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
-        const uint64_t tiles = uint64_t((mcus_x + kWMcus - 1) / kWMcus) * mcus_y * n_images;
-        const unsigned grid = unsigned(std::min<uint64_t>((tiles + kWarpsPerCta - 1) / kWarpsPerCta, uint64_t(sms) * per_sm));
-        JpegParams q = p;
-        const char *dbg = std::getenv("SLIMG_B200_JPEG_DEBUG");
-        q.debug = dbg ? uint32_t(std::atoi(dbg)) : 0u;
-        kern<<<grid, 32 * kWarpsPerCta, 0, stream>>>(q, n_images);
-        count_launch();
-        return cudaGetLastError();
-    }
-    for (uint32_t first = 0; first < n_images; first += 65535) {
-        JpegParams q = p;
-        q.src += size_t(first) * p.src_img_bytes;
-        q.y += size_t(first) * p.y_img_elems;
-        q.cb += size_t(first) * p.c_img_elems;
-        q.cr += size_t(first) * p.c_img_elems;
-        const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
-        jpeg_frontend_kernel<<<dim3((mcus_x + kMcus - 1) / kMcus, mcus_y, nz), kThreads, 0, stream>>>(q);
-        count_launch();
-        cudaError_t e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
-    }
-    return cudaSuccess;
+    const bool uq = p.yu != nullptr;
+    if (uq && (!p.cbu || !p.cru)) return cudaErrorInvalidValue;
+    // SLIMG_B200_JPEG_VAR (A/B): 0 = no stage-1 prefetch, 1 = patch j+1 in flight while patch j is converted (default),
+    // 2 = also the next tile's first patch across stage 2 (80 registers, 6 CTAs/SM), 3 / 4 = as 1 with 7 / 6 CTAs/SM.  Round 1 measured occupancy (32 warps/SM at <= 64 registers)
+    // above everything else: <unroll 1, 8 CTAs/SM> 67.9 us, <1, 6> 69.2 us, <unroll 4, 4> 79.7 us per 24 MP image.
+    const char *var_env = std::getenv("SLIMG_B200_JPEG_VAR");
+    const int var = var_env ? std::atoi(var_env) : 1;
+    using Kern = void (*)(const JpegParams, const uint32_t);
+    Kern kern;
+#define SLIMG_K3_PICK(U)                                                                                         \
+    (var == 0 ? jpeg_frontend_warp_kernel<0, 8, U> : var == 2 ? jpeg_frontend_warp_kernel<2, 6, U>                \
+     : var == 3 ? jpeg_frontend_warp_kernel<1, 7, U> : var == 4 ? jpeg_frontend_warp_kernel<1, 6, U>              \
+                                                                : jpeg_frontend_warp_kernel<1, 8, U>)
+    kern = uq ? SLIMG_K3_PICK(true) : SLIMG_K3_PICK(false);
+#undef SLIMG_K3_PICK
+    int dev = 0, sms = 148, per_sm = 4;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 32 * kWarpsPerCta, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+    const uint64_t tiles = uint64_t((mcus_x + kWMcus - 1) / kWMcus) * mcus_y * n_images;
+    const unsigned grid = unsigned(std::min<uint64_t>((tiles + kWarpsPerCta - 1) / kWarpsPerCta, uint64_t(sms) * per_sm));
+    JpegParams q = p;
+    const char *dbg = std::getenv("SLIMG_B200_JPEG_DEBUG");
+    q.debug = dbg ? uint32_t(std::atoi(dbg)) : 0u;
+    kern<<<grid, 32 * kWarpsPerCta, 0, stream>>>(q, n_images);
+    count_launch();
+    return cudaGetLastError();
 }
 
 }  // namespace slimg

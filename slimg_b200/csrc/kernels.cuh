@@ -5,6 +5,8 @@
 #include <cstddef>
 #include <cstdint>
 
+#include "../../include/slimg_b200.h"
+
 namespace slimg {
 
 // ---- K1: crop / extend as one remapped copy (k1_remap.cu) -----------------------------------
@@ -183,6 +185,7 @@ struct QuantDev {                      // jcdctmgr.c:173-221 compute_reciprocal,
 struct JpegParams {
     const uint8_t *src;
     int16_t *y, *cb, *cr;
+    int16_t *yu, *cbu, *cru;           // optional: the un-quantised coefficients (MozJPEG's trellis input), same layout; all NULL = off
     size_t src_img_bytes;
     size_t y_img_elems, c_img_elems;   // int16 elements per image in each plane
     uint32_t w, h;
@@ -194,5 +197,7 @@ cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStr
 
 // process-wide count of kernels launched by this library (slimg_b200_kernel_launches)
 void count_launch(uint64_t n = 1);
+// which kernel served a launch (SLIMG_PATH_* of include/slimg_b200.h): thread-local last value + process-wide counters
+void note_path(int path);
 
 }  // namespace slimg

@@ -211,6 +211,11 @@ struct Hooks {
     slimg_encode_hook enc = nullptr;
     slimg_decode_hook dec = nullptr;
     void *user = nullptr;
+    // Format::Jpeg when a coefficient-taking entropy coder is installed: convert never downloads pixels
+    slimg_jpeg_coef_hook jpeg = nullptr;
+    void *jpeg_user = nullptr;
+    int32_t jpeg_tables = SLIMG_QT_MOZJPEG;
+    uint32_t jpeg_flags = 0;
 };
 Hooks g_hooks;
 
@@ -286,6 +291,9 @@ uint16_t uniffi_slimg_ffi_checksum_func_resize(void) { return 48866; }
 void slimg_b200_set_codec_hooks(slimg_encode_hook enc, slimg_decode_hook dec, void *user) {
     g_hooks.enc = enc; g_hooks.dec = dec; g_hooks.user = user;
 }
+void slimg_b200_set_jpeg_coefficient_hook(slimg_jpeg_coef_hook hook, void *user, int32_t table_base, uint32_t flags) {
+    g_hooks.jpeg = hook; g_hooks.jpeg_user = user; g_hooks.jpeg_tables = table_base; g_hooks.jpeg_flags = flags;
+}
 
 // ---- pixel functions -----------------------------------------------------------------------------------------
 RustBuffer uniffi_slimg_ffi_fn_func_resize(RustBuffer image, RustBuffer mode, RustCallStatus *status) {   // lib.rs:334-339
@@ -353,10 +361,31 @@ RustBuffer uniffi_slimg_ffi_fn_func_convert(RustBuffer image, RustBuffer options
     RustBuffer ret = kEmpty;
     if (!ok || !ro.done()) ret = panic(status, "convert: malformed argument buffer");
     else {
-        slimg_image px{0, 0, nullptr, 0};
-        const slimg_status s = slimg_b200_pipeline(&in, &o, SLIMG_ORDER_CONVERT, &px);      // pipeline.rs:71-89
-        if (s != SLIMG_OK) ret = raise_last(status, s);
-        else { ret = encode_with_hook(status, px, format, quality); slimg_b200_image_free(&px); }
+        if (format == 1 && g_hooks.jpeg) {
+            // pipeline.rs:71-95 with codec/jpeg.rs:51-72 folded in: pixel stages and the JPEG front end run back to
+            // back on the device, only coefficients come back, the installed entropy coder writes the file
+            uint16_t ql[64], qc[64];
+            slimg_b200_jpeg_quant_table(quality, 0, g_hooks.jpeg_tables, ql);       // codec/jpeg.rs:60 set_quality
+            slimg_b200_jpeg_quant_table(quality, 1, g_hooks.jpeg_tables, qc);
+            slimg_jpeg_coefs coefs;
+            const slimg_status s = slimg_b200_pipeline_jpeg(&in, &o, SLIMG_ORDER_CONVERT, ql, qc, g_hooks.jpeg_flags, &coefs);
+            if (s != SLIMG_OK) ret = raise_last(status, s);
+            else {
+                uint8_t *out = nullptr;
+                size_t out_len = 0;
+                const char *msg = nullptr;
+                const int32_t rc = g_hooks.jpeg(g_hooks.jpeg_user, &coefs, quality, &out, &out_len, &msg);
+                if (rc != SLIMG_OK) ret = raise(status, rc, msg ? msg : "JPEG entropy coder hook failed");
+                else { ret = lower_pipeline_result(out, out_len, format, coefs.geom.width, coefs.geom.height); set_ok(status); }
+                std::free(out);
+                slimg_b200_jpeg_coefs_free(&coefs);
+            }
+        } else {
+            slimg_image px{0, 0, nullptr, 0};
+            const slimg_status s = slimg_b200_pipeline(&in, &o, SLIMG_ORDER_CONVERT, &px);      // pipeline.rs:71-89
+            if (s != SLIMG_OK) ret = raise_last(status, s);
+            else { ret = encode_with_hook(status, px, format, quality); slimg_b200_image_free(&px); }
+        }
     }
     release(image); release(options);
     return ret;

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     lib = ctypes.CDLL(_build.build())
     for name in _declared_symbols():
         assert hasattr(lib, name), name
-    assert ll.library().slimg_b200_abi_version() == 1
+    assert ll.library().slimg_b200_abi_version() == 2
 
 
 def test_error_categories_before_device_work():

@@ -28,20 +28,36 @@ def _fill_ll(f):
     return ll.FillColor.TRANSPARENT() if f == CLEAR else ll.FillColor.SOLID(*f)
 
 
-def _close(got, want, mean_tol=0.02):
-    """+-1 LSB is the bar (BASELINE.json).  The mean bound catches systematic error: on noise a
-    correct f32 kernel flips well under 1% of the roundings.  Structured inputs at exact ratios
-    (a gradient halved) put many samples EXACTLY on .5, where the reference's own f32 rounding
-    noise picks the side, so any other summation order disagrees on about half of them: those
-    cases pass mean_tol explicitly."""
+# Per-kind bounds on the MEAN abs error (the max is always <= 1 LSB, BASELINE.json).  noise / alpha_ramp: a correct
+# kernel flips well under 1 % of the roundings.  constant: the fixed-point weights sum exactly (vplan.cpp: quantise), so
+# a constant image must come back exactly.  gradient / checker at exact ratios put many samples EXACTLY on .5, where the
+# reference's own f32 rounding noise picks the side and any other summation order disagrees on part of them: bounds
+# are twice the largest value measured over all cases of that kind (profiles/r02_parity.txt).
+MEAN_BOUND = {"noise": 0.02, "alpha_ramp": 0.02, "constant": 0.0, "gradient": 0.25, "checker": 0.25, "guard": 0.05}
+_REPORT = []
+
+
+def _close(got, want, kind="noise", label=""):
     assert got.shape == want.shape, (got.shape, want.shape)
     d = np.abs(got.astype(np.int16) - want.astype(np.int16))
-    assert d.max() <= 1, f"max abs err {d.max()}"
-    assert d.mean() <= mean_tol, f"mean abs err {d.mean()}"
-    return d.max(), d.mean()
+    mx, mean = int(d.max()) if d.size else 0, float(d.mean()) if d.size else 0.0
+    _REPORT.append((label or kind, kind, got.shape[1], got.shape[0], mx, mean, ll.PATH_NAMES[ll.last_resize_path()]))
+    assert mx <= 1, f"max abs err {mx}"
+    assert mean <= MEAN_BOUND[kind], f"mean abs err {mean} (bound {MEAN_BOUND[kind]} for {kind})"
+    return mx, mean
 
 
-TIE_HEAVY = {"gradient", "checker", "constant"}
+@pytest.fixture(scope="module", autouse=True)
+def _parity_report():
+    """Every resize comparison of this module: max / mean abs error and the kernel that served it."""
+    yield
+    import os
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    with open(os.path.join(out, "parity_report.txt"), "w") as fh:
+        fh.write("# case | input kind | out WxH | max abs err | mean abs err | kernel path\n")
+        for label, kind, w, h, mx, mean, path in _REPORT:
+            fh.write(f"{label} | {kind} | {w}x{h} | {mx} | {mean:.6f} | {path}\n")
 
 
 # ---- K1: crop / extend, bit-exact ---------------------------------------------------------------
@@ -109,13 +125,13 @@ def test_resize_within_one_lsb(kind, w, h, mode):
     img = IMAGE_KINDS[kind](w, h)
     want = oracle.resize(img, getattr(oracle.ResizeMode, mode[0])(*mode[1:]))
     got = _np(ll.resize(_ll_img(img), getattr(ll.ResizeMode, mode[0].upper())(*mode[1:])))
-    _close(got, want, 0.25 if kind in TIE_HEAVY else 0.02)
+    _close(got, want, kind, f"resize {kind} {w}x{h} {mode}")
 
 
 @pytest.mark.parametrize("case", list(resize_cases()), ids=lambda c: c["id"])
 def test_resize_golden_vectors(case):
     got = _np(ll.resize(_ll_img(case["img"]), ll.ResizeMode.EXACT(case["nw"], case["nh"])))
-    _close(got, case["out"], 0.25 if case["id"].split("-")[0] in TIE_HEAVY else 0.02)
+    _close(got, case["out"], case["id"].split("-")[0] if case["id"].split("-")[0] in MEAN_BOUND else "noise", "golden " + case["id"])
 
 
 def test_resize_same_size_is_a_copy():
@@ -152,7 +168,7 @@ def test_convert_order_fill_takes_part_in_the_taps(w, h, resize, crop, extend, f
     img = noise_image(w, h, 5)
     o, l = _modes(resize, crop, extend, fill)
     want = oracle.pipeline(img, **o)                                  # crop -> extend -> resize
-    _close(_np(ll.pipeline(_ll_img(img), l, ll.ORDER_CONVERT)), want)
+    _close(_np(ll.pipeline(_ll_img(img), l, ll.ORDER_CONVERT)), want, "noise", f"convert-order {w}x{h} {resize}")
 
 
 CHAIN_CASES = [
@@ -176,7 +192,7 @@ def test_chain_order_resize_crop_extend(w, h, resize, crop, extend, fill):
     if o["extend_mode"] is not None:
         want = oracle.extend(want, o["extend_mode"], WHITE if fill is None else fill)
     got = _np(ll.pipeline(_ll_img(img), l, ll.ORDER_CHAIN))
-    _close(got, want)
+    _close(got, want, "noise", f"chain-order {w}x{h} {resize}")
     # the padding itself must be bit-exact
     if o["extend_mode"] is not None:
         pad = np.ones(want.shape[:2], bool)
@@ -194,7 +210,7 @@ def test_baseline_resize_configs_full_size(name, w, h, mode):
     img = noise_image(w, h, 8)
     want = oracle.resize(img, getattr(oracle.ResizeMode, mode[0])(*mode[1:]))
     got = _np(ll.resize(_ll_img(img), getattr(ll.ResizeMode, mode[0].upper())(*mode[1:])))
-    mx, mean = _close(got, want)
+    mx, mean = _close(got, want, "noise", f"{name} full size")
     print(f"{name}: max abs err {mx}, mean abs err {mean:.6f}")
 
 
@@ -210,7 +226,7 @@ def test_config3_24mp_full_size(order):
         want = oracle.extend(oracle.crop(oracle.resize(img, o["resize_mode"]), o["crop_mode"]), o["extend_mode"], WHITE)
         got = _np(ll.pipeline(_ll_img(img), l, ll.ORDER_CHAIN))
     assert got.shape == (800, 800, 4)
-    mx, mean = _close(got, want)
+    mx, mean = _close(got, want, "noise", f"C3 {order} full size")
     print(f"C3 {order}: max abs err {mx}, mean abs err {mean:.6f}")
 
 
@@ -317,7 +333,7 @@ def test_batch_host_scheduler_isolates_failures():
     for i in (0, 1, 3, 4):
         got = np.frombuffer(C.string_at(cout[i].data, cout[i].len), np.uint8).reshape(cout[i].height, cout[i].width, 4)
         want = oracle.pipeline(imgs[i], crop_mode=oracle.CropMode.region(0, 0, 10, 10), resize_mode=oracle.ResizeMode.scale(0.5))
-        _close(got, want)
+        _close(got, want, "noise", "batch_host mixed sizes")
         lib.slimg_b200_image_free(C.byref(cout[i]))
 
 
@@ -359,7 +375,7 @@ def test_batch_device_writes_only_its_output(w, h, resize, crop, extend, fill, o
             if o["resize_mode"] is not None: want = oracle.resize(want, o["resize_mode"])
             if o["crop_mode"] is not None: want = oracle.crop(want, o["crop_mode"])
             if o["extend_mode"] is not None: want = oracle.extend(want, o["extend_mode"], fill if fill is not None else WHITE)
-        _close(got[i], want, mean_tol=0.05)
+        _close(got[i], want, "guard", f"guard band {w}x{h} {order}")
 
 
 def test_jpeg_batch_device_writes_only_its_planes():
