@@ -10,7 +10,11 @@ shard them with no data-path collective ("scaling": "weak").
   e2e       same metric through the host-buffer C ABI (slimg_b200_pipeline_batch_host): pinned
             host inputs, H2D + kernel + D2H inside the timed region
   roofline  algorithmic HBM bytes per launch / measured launch time, against MEASURED_PEAKS.json
-  cpu_baseline  the CPU oracle (restated reference path) on this box's host cores, bounded sample
+  cpu_baseline  the CPU oracle (restated reference path) on this box's host cores, bounded sample, at
+                --jobs = all cores and --jobs = 1 (cli/src/commands/mod.rs:64-72)
+  configs   (N = 1 only) every other BASELINE config -- C1, C2, C3 in the reference's convert order, C4a, C4b, C5 and
+            the fused C3 -> JPEG front end -- timed device-resident the same way, each with its algorithmic bytes,
+            roofline fraction and a parity check of one image against the oracle outside the timed region
 
 `--impl reference` times the reference's CPU path (the oracle port: the reference is Rust and
 cannot be built on this image) on the same config, rank 0 only.
@@ -50,6 +54,10 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-images", type=int, default=0, help="images in the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the per-config table (C1, C2, C4a, C4b, C5 ...)")
+    ap.add_argument("--no-pageable", action="store_true", help="skip the pageable-host-buffer e2e leg")
+    ap.add_argument("--probe-h2d", action="store_true",
+                    help="only run the pinned H2D copy probe (same bytes and stream count as the e2e leg, no kernels)")
     return ap.parse_args()
 
 
@@ -83,12 +91,26 @@ def measured_peak_gbs():
     return 6650.0, "fallback"
 
 
+def build_id() -> str:
+    """Hash of everything libslimg_b200.so is built from: an ncu capture belongs to one build."""
+    import hashlib
+    h = hashlib.sha256()
+    csrc = os.path.join(ROOT, "slimg_b200", "csrc")
+    for name in sorted(os.listdir(csrc)) + [os.path.join("..", "_build.py"), os.path.join("..", "..", "include", "slimg_b200.h")]:
+        with open(os.path.join(csrc, name), "rb") as fh:
+            h.update(name.encode()); h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
 def measured_traffic(order: str, batch: int):
     """dram__bytes_read.sum + dram__bytes_write.sum of the K2 launch from the committed ncu --set full capture
-    (profiles/traffic.json: bytes per image of that capture), scaled to this launch's batch; None if absent."""
+    (profiles/traffic.json: bytes per image), scaled to this launch's batch.  None unless the capture was taken with
+    THIS build of the library (traffic.json records the build id next to the capture)."""
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[order]
-        return float(t["dram_bytes_per_image"]) * batch
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if t.get("build_id") != build_id():
+            return None
+        return float(t[order]["dram_bytes_per_image"]) * batch
     except Exception:
         return None
 
@@ -212,6 +234,137 @@ def workload_config(args, batch):
             "l2_policy": "inputs larger than L2 (batch >> 126 MB), no flush needed", "parallelism": f"dp{args.gpus}"}
 
 
+
+# ---- the other BASELINE configs (N = 1): device-resident, CUDA events, one oracle check each ---------------------------
+
+def config_table(ll, torch, peak, main_src):
+    """C1, C2, C3 in convert order, C4a, C4b, C5 (+ un-quantised output) and C3 fused with the JPEG front end: time per
+    image over 10 back-to-back launches after 3 warm-ups (inputs are far larger than L2), algorithmic bytes as
+    SURVEY.md 8(d) defines them, and parity of the batch's first image against the oracle (outside the timed region)."""
+    import oracle
+    R, Cm, E = oracle.ResizeMode, oracle.CropMode, oracle.ExtendMode
+    WHITE = (255, 255, 255, 255)
+    stream = torch.cuda.current_stream().cuda_stream
+    out = {}
+
+    def timed(fn, n=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    def err(got, want):
+        d = np.abs(got.astype(np.int16) - want.astype(np.int16))
+        return {"max_abs_err": int(d.max()), "mean_abs_err": float(d.mean())}
+
+    def pixel_config(name, w, h, kw, order, batch, alg_bytes, oracle_fn, src=None):
+        opts = ll.make_options(**kw)
+        ow, oh = ll.pipeline_output_dims(w, h, opts, order)
+        if src is None:
+            gen = torch.Generator(device="cuda").manual_seed(0x51136 + len(out))
+            src = torch.randint(0, 256, (batch, h, w, 4), dtype=torch.uint8, device="cuda", generator=gen)
+        dst = torch.empty((batch, oh, ow, 4), dtype=torch.uint8, device="cuda")
+        ms = timed(lambda: ll.pipeline_batch_device(src.data_ptr(), batch, w, h, opts, order, dst.data_ptr(), dst.numel(), stream))
+        path = ll.PATH_NAMES[ll.last_resize_path()]
+        us = ms / batch * 1e3
+        rec = {"us_per_image": us, "mpx_per_s": w * h / us, "algorithmic_bytes": alg_bytes,
+               "frac": alg_bytes / (us * 1e-6) / 1e9 / peak, "batch": batch, "kernel": path}
+        rec.update(err(dst[0].cpu().numpy(), oracle_fn(src[0].cpu().numpy())))
+        out[name] = rec
+        del dst
+        return src
+
+    pixel_config("C1 4000x3000 -> Width(800)", 4000, 3000, dict(resize=ll.ResizeMode.WIDTH(800)), ll.ORDER_CONVERT, 64,
+                 48_000_000 + 1_920_000, lambda a: oracle.resize(a, R.width(800)))
+    pixel_config("C2 4000x3000 crop 16:9 + extend 1:1 transparent", 4000, 3000,
+                 dict(crop=ll.CropMode.ASPECT_RATIO(16, 9), extend=ll.ExtendMode.ASPECT_RATIO(1, 1), fill_color=ll.FillColor.TRANSPARENT()),
+                 ll.ORDER_CONVERT, 32, 36_000_000 + 64_000_000,
+                 lambda a: oracle.pipeline(a, crop_mode=Cm.aspect_ratio(16, 9), extend_mode=E.aspect_ratio(1, 1), fill=(0, 0, 0, 0)))
+    c3 = dict(resize=ll.ResizeMode.WIDTH(800), crop=ll.CropMode.ASPECT_RATIO(16, 9), extend=ll.ExtendMode.ASPECT_RATIO(1, 1),
+              fill_color=ll.FillColor.SOLID(*WHITE))
+    pixel_config("C3 convert order (crop 16:9 -> extend 1:1 -> Width(800))", SRC_W, SRC_H, c3, ll.ORDER_CONVERT, 64,
+                 algorithmic_bytes_per_image("convert"),
+                 lambda a: oracle.pipeline(a, crop_mode=Cm.aspect_ratio(16, 9), extend_mode=E.aspect_ratio(1, 1), fill=WHITE, resize_mode=R.width(800)),
+                 src=main_src[:64])
+    pixel_config("C4a 7680x4320 -> Width(1920)", 7680, 4320, dict(resize=ll.ResizeMode.WIDTH(1920)), ll.ORDER_CONVERT, 32,
+                 132_710_400 + 8_294_400, lambda a: oracle.resize(a, R.width(1920)))
+    pixel_config("C4b 1024x1024 -> Scale(4.0)", 1024, 1024, dict(resize=ll.ResizeMode.SCALE(4.0)), ll.ORDER_CONVERT, 64,
+                 4_194_304 + 67_108_864, lambda a: oracle.resize(a, R.scale(4.0)))
+
+    # C5: JPEG front end, q = 70, 24 MP batch; MozJPEG's table set (the reference encoder) -- coefficients vs the oracle
+    nb = 32
+    g = ll.jpeg_geometry(SRC_W, SRC_H)
+    ql, qc = ll.jpeg_quant_table(70, 0, ll.QT_MOZJPEG), ll.jpeg_quant_table(70, 1, ll.QT_MOZJPEG)
+    mk = lambda hb, wb: torch.empty((nb, hb, wb, 64), dtype=torch.int16, device="cuda")
+    y, cb, cr = mk(g.y_HB, g.y_WB), mk(g.c_HB, g.c_WB), mk(g.c_HB, g.c_WB)
+    src5 = main_src[:nb]
+    ms = timed(lambda: ll.jpeg_frontend_batch_device(src5.data_ptr(), nb, SRC_W, SRC_H, ql, qc, y.data_ptr(), cb.data_ptr(), cr.data_ptr(), stream))
+    want = oracle.jpeg_frontend(src5[0].cpu().numpy(), np.array(ql, np.uint16), np.array(qc, np.uint16))
+    diff = sum(int(np.count_nonzero(t[0].cpu().numpy() != wv)) for t, wv in zip((y, cb, cr), want))
+    us = ms / nb * 1e3
+    out["C5 JPEG front end q=70 (RGB->YCbCr 4:2:0, FDCT, quantise), 6000x4000"] = {
+        "us_per_image": us, "mpx_per_s": SRC_W * SRC_H / us, "algorithmic_bytes": 96_000_000 + 72_000_000,
+        "frac": 168e6 / (us * 1e-6) / 1e9 / peak, "batch": nb, "kernel": "jpeg_frontend_warp_kernel", "differing_coefficients": diff}
+    yu, cbu, cru = mk(g.y_HB, g.y_WB), mk(g.c_HB, g.c_WB), mk(g.c_HB, g.c_WB)
+    ms = timed(lambda: ll.jpeg_frontend_batch_device_ex(src5.data_ptr(), nb, SRC_W, SRC_H, ql, qc, y.data_ptr(), cb.data_ptr(), cr.data_ptr(),
+                                                        yu.data_ptr(), cbu.data_ptr(), cru.data_ptr(), stream))
+    wantu = oracle.jpeg_frontend_unquantised(src5[0].cpu().numpy())
+    diff = sum(int(np.count_nonzero(t[0].cpu().numpy() != wv)) for t, wv in zip((y, cb, cr, yu, cbu, cru), want + wantu))
+    us = ms / nb * 1e3
+    out["C5 + un-quantised side output (MozJPEG trellis input)"] = {
+        "us_per_image": us, "mpx_per_s": SRC_W * SRC_H / us, "algorithmic_bytes": 96_000_000 + 144_000_000,
+        "frac": 240e6 / (us * 1e-6) / 1e9 / peak, "batch": nb, "kernel": "jpeg_frontend_warp_kernel", "differing_coefficients": diff}
+    del y, cb, cr, yu, cbu, cru
+
+    # convert(.., Jpeg) on the device: C3 (chain order) and the front end of its 800x800 result, pixels never leave HBM
+    nb = 64
+    opts = ll.make_options(**c3)
+    g8 = ll.jpeg_geometry(800, 800)
+    px = torch.empty((nb, 800, 800, 4), dtype=torch.uint8, device="cuda")
+    mk = lambda hb, wb: torch.empty((nb, hb, wb, 64), dtype=torch.int16, device="cuda")
+    y, cb, cr = mk(g8.y_HB, g8.y_WB), mk(g8.c_HB, g8.c_WB), mk(g8.c_HB, g8.c_WB)
+    srcj = main_src[:nb]
+    ms = timed(lambda: ll.pipeline_jpeg_batch_device(srcj.data_ptr(), nb, SRC_W, SRC_H, opts, ll.ORDER_CHAIN, ql, qc, px.data_ptr(), px.numel(),
+                                                     y.data_ptr(), cb.data_ptr(), cr.data_ptr(), stream=stream))
+    want = oracle.jpeg_frontend(px[0].cpu().numpy(), np.array(ql, np.uint16), np.array(qc, np.uint16))
+    diff = sum(int(np.count_nonzero(t[0].cpu().numpy() != wv)) for t, wv in zip((y, cb, cr), want))
+    us = ms / nb * 1e3
+    alg = algorithmic_bytes_per_image("chain") - 800 * 800 * 4 + (g8.y_HB * g8.y_WB + 2 * g8.c_HB * g8.c_WB) * 128
+    out["C3 chain -> JPEG front end (convert to JPEG up to the entropy coder, 2 launches)"] = {
+        "us_per_image": us, "mpx_per_s": SRC_W * SRC_H / us, "algorithmic_bytes": alg, "frac": alg / (us * 1e-6) / 1e9 / peak,
+        "batch": nb, "kernel": "K2 + K3", "differing_coefficients": diff}
+    return out
+
+
+def h2d_ceiling(torch, pin_ptr, image_stride, window_bytes, nb, n_streams, reps, sync_all):
+    """The e2e leg's copy pattern with no kernels: nb pinned source windows per step over n_streams streams.
+    Returns seconds for `reps` steps (after one warm-up step)."""
+    import ctypes as C
+    host = np.ctypeslib.as_array(C.cast(pin_ptr, C.POINTER(C.c_uint8)), shape=(nb, image_stride))
+    th = torch.from_numpy(host)
+    streams = [torch.cuda.Stream() for _ in range(n_streams)]
+    dev = [torch.empty(window_bytes, dtype=torch.uint8, device="cuda") for _ in range(n_streams)]
+
+    def one_step():
+        for i in range(nb):
+            with torch.cuda.stream(streams[i % n_streams]):
+                dev[i % n_streams].copy_(th[i, :window_bytes], non_blocking=True)
+        torch.cuda.synchronize()
+
+    one_step()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        one_step()
+    return time.perf_counter() - t0
+
+
 # ---- B200 arm ------------------------------------------------------------------------------------------
 
 _REAL_STDOUT = None
@@ -293,13 +446,16 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
     value = _shard.whole_job_throughput(B * args.steps * MPX_PER_IMAGE, world, ms_max * 1e-3)
 
+    if args.probe_h2d:
+        args.no_cpu = True
+        args.no_configs = True
     # roofline of the (single) kernel of the step, from this rank's own launches
     peak, peak_kind = measured_peak_gbs()
     alg_bytes = algorithmic_bytes_per_image(args.order) * B
     launch_ms = ms / max(1, launches)
     achieved = alg_bytes / (launch_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": measured_traffic(args.order, B), "peak_kind": peak_kind, "kernel": "resize pipeline (K2)",
+                "traffic": measured_traffic(args.order, B), "peak_kind": peak_kind, "kernel": "resize pipeline (K2), path " + ll.PATH_NAMES[ll.last_resize_path()],
                 "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": launch_ms}
 
     # end to end through the host-buffer C ABI
@@ -335,32 +491,107 @@ def main():
                 raise SystemExit("e2e batch failed: " + lib.slimg_b200_last_error().decode())
 
         e2e_steps = max(3, min(args.steps, 8))
-        for _ in range(3):                    # warm-up: stream-ordered pool growth, plan upload, page pinning
-            e2e_step()
-        barrier()
-        step_ms = []
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            t1 = time.perf_counter()
-            e2e_step()
-            step_ms.append(round(1e3 * (time.perf_counter() - t1), 2))
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        e2e_value = _shard.whole_job_throughput(nb * e2e_steps * MPX_PER_IMAGE, world, _shard.max_over_ranks(dt, device="cuda"))
+
+        def timed_e2e(step_fn, steps):
+            for _ in range(3):                # warm-up: stream-ordered pool growth, plan upload, page pinning
+                step_fn()
+            barrier()
+            step_ms = []
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                t1 = time.perf_counter()
+                step_fn()
+                step_ms.append(round(1e3 * (time.perf_counter() - t1), 2))
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            return _shard.max_over_ranks(dt, device="cuda"), step_ms
+
+        dt_max, step_ms = timed_e2e(e2e_step, e2e_steps)
+        e2e_value = _shard.whole_job_throughput(nb * e2e_steps * MPX_PER_IMAGE, world, dt_max)
         checksum = int(np.ctypeslib.as_array(C.cast(pin_out, C.POINTER(C.c_uint8)), shape=(nb * out_bytes,))[::4097].sum())
         e2e = {"value": e2e_value, "unit": "Mpx/s", "h2d_bytes_per_step": nb * h2d_bytes, "d2h_bytes_per_step": nb * out_bytes,
                "host_image_bytes_per_step": nb * in_bytes,
                "images_per_gpu_per_step": nb, "steps": e2e_steps, "timer": "host wall clock around the C-ABI calls, max over ranks",
-               "result_checksum": checksum, "step_ms": step_ms}
+               "result_checksum": checksum, "step_ms": step_ms, "host_buffers": "pinned (slimg_b200_host_alloc)"}
+
+        # the ceiling of that leg: the same pinned H2D pattern (bytes, 4 streams, all ranks at once) with no kernels
+        barrier()
+        t_copy = h2d_ceiling(torch, pin_in, in_bytes, h2d_bytes, nb, 4, 3, barrier)
+        t_copy = _shard.max_over_ranks(t_copy, device="cuda")
+        ceiling = _shard.whole_job_throughput(nb * 3 * MPX_PER_IMAGE, world, t_copy)
+        e2e["h2d_copy_ceiling"] = {"value": ceiling, "unit": "Mpx/s", "aggregate_h2d_gbs": world * nb * 3 * h2d_bytes / t_copy / 1e9,
+                                   "what": "same pinned source windows over 4 streams per GPU, no kernels, all ranks at once"}
+        e2e["frac_of_copy_ceiling"] = e2e_value / ceiling
+
+        # the drop-in case: the caller's buffers are ordinary heap memory (a Rust Vec, Python bytes, a RustBuffer);
+        # the library stages them through its pinned ring
+        if not args.no_pageable:
+            page_in = np.empty((nb, in_bytes), np.uint8)
+            page_in[:] = host
+            page_out = np.empty((nb, out_bytes), np.uint8)
+
+            def pageable_step():
+                for i in range(nb):
+                    cin[i] = ll.CImage(SRC_W, SRC_H, page_in[i].ctypes.data, in_bytes)
+                    cout[i] = ll.CImage(0, 0, page_out[i].ctypes.data, out_bytes)
+                failed = lib.slimg_b200_pipeline_batch_host(cin, nb, C.byref(opts), order, C.byref(cfg), cout, st)
+                if failed:
+                    raise SystemExit("pageable e2e batch failed: " + lib.slimg_b200_last_error().decode())
+
+            p_steps = max(3, min(args.steps, 4))
+            dt_p, step_ms_p = timed_e2e(pageable_step, p_steps)
+            same = bool((page_out == np.ctypeslib.as_array(C.cast(pin_out, C.POINTER(C.c_uint8)), shape=(nb, out_bytes))).all())
+            e2e["pageable"] = {"value": _shard.whole_job_throughput(nb * p_steps * MPX_PER_IMAGE, world, dt_p), "unit": "Mpx/s",
+                               "steps": p_steps, "step_ms": step_ms_p, "host_buffers": "pageable (numpy heap arrays), staged through the library's pinned ring",
+                               "equals_pinned_result": same}
+            e2e["pageable"]["frac_of_pinned"] = e2e["pageable"]["value"] / e2e_value
+            del page_in, page_out
+
+        # the library's own multi-device scheduler: ONE process (rank 0) feeding every GPU of the box (n_devices = world),
+        # no Python per rank -- the `--jobs` analogue proper; the other ranks wait
+        if world > 1:
+            barrier()
+            if rank == 0:
+                n_all = nb * world
+                cin_all = (ll.CImage * n_all)()
+                cout_all = (ll.CImage * n_all)()
+                st_all = (C.c_int * n_all)()
+                outs_all = lib.slimg_b200_host_alloc(n_all * out_bytes)
+                cfg_all = ll.CBatchConfig(world, 4, None)
+
+                def all_step():
+                    for i in range(n_all):
+                        cin_all[i] = ll.CImage(SRC_W, SRC_H, pin_in + (i % nb) * in_bytes, in_bytes)
+                        cout_all[i] = ll.CImage(0, 0, outs_all + i * out_bytes, out_bytes)
+                    if lib.slimg_b200_pipeline_batch_host(cin_all, n_all, C.byref(opts), order, C.byref(cfg_all), cout_all, st_all):
+                        raise SystemExit("one-process e2e batch failed: " + lib.slimg_b200_last_error().decode())
+
+                for _ in range(2):
+                    all_step()
+                t0 = time.perf_counter()
+                for _ in range(3):
+                    all_step()
+                dt_all = time.perf_counter() - t0
+                e2e["one_process_all_devices"] = {"value": n_all * 3 * MPX_PER_IMAGE / dt_all, "unit": "Mpx/s", "n_devices": world,
+                                                  "streams_per_device": 4, "images_per_step": n_all}
+                lib.slimg_b200_host_free(outs_all)
+            barrier()
         lib.slimg_b200_host_free(pin_in); lib.slimg_b200_host_free(pin_out)
+
+    configs = None
+    if world == 1 and not args.no_configs:
+        configs = config_table(ll, torch, peak, src)
 
     cpu = None
     if rank == 0 and not args.no_cpu:
         threads = host_threads()
         n_img = args.cpu_images or max(32, min(256, threads * 8))
         dt, mpx = cpu_run(args.order, n_img, threads)
-        cpu = {"value": mpx, "unit": "Mpx/s", "cores": threads, "kind": "port",
-               "sample": f"{n_img} synthetic 24 MP images of the same workload, one image per thread, {dt:.1f} s wall"}
+        dt1, mpx1 = cpu_run(args.order, 3, 1)          # --jobs 1: one image at a time
+        cpu = {"value": mpx, "unit": "Mpx/s", "cores": threads, "kind": "port", "jobs": threads,
+               "sample": f"{n_img} synthetic 24 MP images of the same workload, one image per thread, {dt:.1f} s wall",
+               "jobs_1": {"value": mpx1, "unit": "Mpx/s", "cores": 1, "jobs": 1,
+                          "sample": f"3 images of the same workload on one thread, {dt1:.1f} s wall"}}
 
     if world > 1:
         dist.barrier()
@@ -371,7 +602,7 @@ def main():
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
             "config": workload_config(args, B), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-            "gpu_launches": int(launches), "clocks": clocks,
+            "gpu_launches": int(launches), "clocks": clocks, "configs": configs, "build_id": build_id(),
         }))
 
 
