@@ -89,6 +89,10 @@ struct ResizePlan {
     bool vfirst = false;
     DevArray v_recs, v_rowc, v_col0, v_src0, v_nblk, v_bytes, v_upw, v_nunits, v_kb0, v_tnch, v_b2, v_cx;
     VfParams vparams{};
+    // integer tile kernel (k2_tile.cu): ratios below ~3.5x and upscales
+    bool tile = false;
+    DevArray l_recs, l_rowc, l_y0, l_rows, l_src0, l_nblk, l_kb0, l_b2, l_cx;
+    TileParams lparams{};
     // tcgen05 pipeline (k2_tc.cu), preferred over the mma.sync pipeline when the geometry qualifies
     bool tc = false;
     DevArray t_crecs, t_c0, t_c1, t_bias, t_col0, t_src0, t_kb0, t_b2, t_cx;
@@ -155,7 +159,7 @@ static std::string requested_path() {
     return path_env && *path_env ? path_env : "vfirst";
 }
 static uint32_t path_code(const std::string &p) {
-    return p == "tc" ? 1u : p == "hfirst" ? 2u : p == "generic" ? 3u : 0u;
+    return p == "tc" ? 1u : p == "hfirst" ? 2u : p == "generic" ? 3u : p == "tile" ? 4u : p == "notile" ? 5u : 0u;
 }
 
 static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path, std::shared_ptr<ResizePlan> &out) {
@@ -251,6 +255,34 @@ static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path
     }
     p.tile_x0 = (const int32_t *)plan->tx0.p;
     p.tile_span = (const int32_t *)plan->tspan.p;
+    if (path == "vfirst" || path == "tile") {        // "notile": the banded pipelines at small ratios too (A/B)
+        TilePlanHost lp;
+        build_tileplan(g, tx, ty, path == "tile", lp);
+        if (std::getenv("SLIMG_B200_DEBUG"))
+            std::fprintf(stderr, "[slimg_b200] tileplan ok=%d tile=%ux%u blocks=%ux%u rows_max=%u nch1=%d nch2=%d pitch=%u pitch_v=%u smem=%u\n",
+                         int(lp.ok), lp.tw, lp.th, lp.n_colblk, lp.n_rowblk, lp.rows_max, lp.nch1, lp.nch2, lp.pitch, lp.pitch_v, lp.smem_bytes);
+        if (lp.ok) {
+            if ((e = plan->l_recs.upload(lp.recs)) || (e = plan->l_rowc.upload(lp.row_computed)) || (e = plan->l_y0.upload(lp.rb_y0)) ||
+                (e = plan->l_rows.upload(lp.rb_rows)) || (e = plan->l_src0.upload(lp.cb_src0)) || (e = plan->l_nblk.upload(lp.cb_nblk)) ||
+                (e = plan->l_kb0.upload(lp.tile_kb0)) || (e = plan->l_b2.upload(lp.b2)) || (e = plan->l_cx.upload(lp.cx)))
+                return cuda_fail(e, "uploading tile resize plan");
+            TileParams &l = plan->lparams;
+            l.sw = g.sw; l.sh = g.sh; l.ry = g.ry; l.rh = g.rh; l.pw = g.pw; l.ph = g.ph;
+            l.tw = lp.tw; l.th = lp.th; l.nch1 = lp.nch1; l.nch2 = lp.nch2; l.sh1 = lp.sh1; l.rec_words = lp.rec_words;
+            l.recs = (const uint32_t *)plan->l_recs.p; l.row_computed = (const uint8_t *)plan->l_rowc.p;
+            l.n_rowblk = lp.n_rowblk; l.n_colblk = lp.n_colblk;
+            l.rb_y0 = (const int32_t *)plan->l_y0.p; l.rb_rows = (const int32_t *)plan->l_rows.p;
+            l.cb_src0 = (const int32_t *)plan->l_src0.p; l.cb_nblk = (const int32_t *)plan->l_nblk.p;
+            l.tile_kb0 = (const int32_t *)plan->l_kb0.p; l.b2 = (const uint32_t *)plan->l_b2.p; l.cx = (const float *)plan->l_cx.p;
+            for (int a = 0; a < 2; a++)
+                for (int d = 0; d < 2; d++) l.s2[a][d] = lp.s2[a][d];
+            l.pitch = lp.pitch; l.pitch_v = lp.pitch_v; l.rows_max = lp.rows_max; l.smem_bytes = lp.smem_bytes;
+            l.fw = g.fw; l.fh = g.fh; l.fox = g.fox; l.foy = g.foy;
+            l.fill_post = pack_fill(g.fill_post); l.fill_pre_packed = pack_fill(g.fill_pre);
+            l.need_fill = (lp.need_fill ? 1u : 0u) | (lp.rows_pure_fill ? 2u : 0u);
+            plan->tile = true;
+        }
+    }
     if (path == "tc") {
         TcPlanHost tp;
         build_tcplan(g, tx, ty, tp);
@@ -283,7 +315,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path
             plan->tc = true;
         }
     }
-    if (path == "vfirst" || (path == "tc" && !plan->tc)) {
+    if (((path == "vfirst" || path == "tile") && !plan->tile) || path == "notile" || (path == "tc" && !plan->tc)) {
         const char *dig_env = std::getenv("SLIMG_B200_DIGITS");
         const int ndig = dig_env && dig_env[0] == '3' ? 3 : 2;
         VPlanHost vp;
@@ -458,6 +490,12 @@ static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, u
     // A fast path whose launch is refused (no tensor-map entry point in the driver, an uninstantiated template case)
     // falls through to the next one; the generic kernel takes everything.
     const bool aligned = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+    if (plan->tile && aligned) {
+        TileParams l = plan->lparams;
+        l.src = src; l.dst = dst; l.src_img_bytes = src_bytes; l.dst_img_bytes = dst_bytes;
+        if (launch_resize_tile(l, n, stream) == cudaSuccess) { note_path(SLIMG_PATH_TILE); return SLIMG_OK; }
+        cudaGetLastError();
+    }
     if (plan->tc && aligned) {
         TcParams t = plan->tparams;
         t.src = src; t.dst = dst; t.src_img_bytes = src_bytes; t.dst_img_bytes = dst_bytes;

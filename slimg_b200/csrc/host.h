@@ -119,6 +119,26 @@ bool split_digits(int64_t x, int ndig, int8_t d[3]);                         // 
 int pick_scale(float maxw, int ndig);
 void put_b(uint32_t *frag, int k, int n, int8_t v);                          // mma.m16n8k32 B fragment slot
 
+// ---- integer tile kernel plan (tileplan.cpp, k2_tile.cu): ratios below ~3.5x and upscales ------------------------
+struct TilePlanHost {
+    bool ok = false;
+    uint32_t tw = 32, th = 32;             // kept output columns / rows per CTA (multiples of 8)
+    int nch1 = 0, nch2 = 0, sh1 = 0;
+    uint32_t rec_words = 0;
+    std::vector<uint32_t> recs;            // [groups of 8 kept rows][rec_words]: {a0, need, chunks, .., bias[8][4]} + weight fragments
+    std::vector<uint8_t> row_computed;     // [ph]
+    uint32_t n_rowblk = 0, n_colblk = 0, rows_max = 0;
+    std::vector<int32_t> rb_y0, rb_rows;   // [n_rowblk] first source-rectangle row / rows a row block stages
+    std::vector<int32_t> cb_src0, cb_nblk; // [n_colblk] first staged source pixel (multiple of 4) / 16-byte blocks per row (even)
+    std::vector<int32_t> tile_kb0;         // [n_colblk][tw / 8] first block of the tile's k range
+    std::vector<uint32_t> b2;              // [n_colblk][tw / 8][nch2][2 digits][32 lanes][2]
+    std::vector<float> cx;                 // [pw][4]
+    float s2[2][2] = {{0, 0}, {0, 0}};
+    uint32_t v_words = 0, pitch = 0, pitch_v = 0, smem_bytes = 0;
+    bool need_fill = false, rows_pure_fill = false;
+};
+void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, bool forced, TilePlanHost &out);
+
 // ---- tcgen05 pipeline plan (tcplan.cpp, k2_tc.cu) -------------------------------------------------------
 // Vertical pass on the 5th-generation tensor cores: source rows stream through a shared-memory ring in chunks of
 // 32 rows (the K of one tcgen05.mma.kind::i8), accumulators for blocks of 16 kept output rows live in TMEM.

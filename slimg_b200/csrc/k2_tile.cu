@@ -1,0 +1,291 @@
+// k2_tile.cu -- Lanczos3 at ratios below ~3.5x and for upscales: both passes as integer tensor-core GEMMs out of one
+// shared-memory tile (BASELINE config C4b, the 2x "retina" downscale, thumbnails of small images).
+//
+// Replaces image 0.25.9's vertical_sample / horizontal_sample pair behind slimg_core::resize::resize
+// (crates/slimg-core/src/resize.rs:64-90), crop / extend fused in as address arithmetic (pipeline.rs:71-89).  Same
+// taps, weights and pass order as the reference (taps.cpp), in the fixed point of vplan.cpp / tileplan.cpp.
+//
+// One CTA = a tile of tw x th kept output pixels of one image:
+//   stage   cp.async (16 bytes, L1 bypass) of the tile's source footprint into shared memory: rows_max x pitch bytes
+//   pass 1  per group of 8 output rows:  D1[16 bytes of the row][8 rows] += A[16][32 source rows] * B[32][8]
+//           A straight from the staged rows with ldmatrix.m16n16.x2.trans.b8, B = weight digits from the plan (L2);
+//           digit recombination, >> to the 16-bit intermediate, two u8 limb planes per group in shared memory
+//   pass 2  per group and tile of 8 output columns:  D2[(channel,row) 16][8 columns] += A[16][32 px] * B[32][8] for
+//           both limbs; f32 recombination, clamp, round half away, packed RGBA stores to the final canvas position
+// Two __syncthreads in all; several CTAs per SM overlap each other's staging and arithmetic.  Everything the tile does
+// not compute (canvas outside the kept rectangle, kept rows whose taps are all fill) is written by fill CTAs
+// (blockIdx.x == n_colblk), one canvas row per warp, 16-byte stores.
+#include <algorithm>
+
+#include "kernels.cuh"
+
+namespace slimg {
+
+namespace {
+
+constexpr int kWarps = 8, kThreads = kWarps * 32;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void ldsm_t(uint32_t (&a)[4], uint32_t addr) {      // see k2_vfirst.cu
+    asm volatile("ldmatrix.sync.aligned.m16n16.x2.trans.shared.b8 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]) : "r"(addr));
+}
+__device__ __forceinline__ void imma(int (&d)[4], const uint32_t (&a)[4], const uint2 &b) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
+}
+__device__ __forceinline__ void imma_z(int (&d)[4], const uint32_t (&a)[4], const uint2 &b) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "r"(0));
+}
+__device__ __forceinline__ void imma_c(int (&d)[4], const uint32_t (&a)[4], const uint2 &b, int c0, int c1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%10,%11};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "r"(c0), "r"(c1));
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
+    asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+// exact s32 -> f32 for |x| < 2^22 without the quarter-rate I2F
+__device__ __forceinline__ float int_to_float(int x) { return __int_as_float(x + 0x4B400000) - 12582912.0f; }
+__device__ __forceinline__ uint32_t quantize_channel(float t) {
+    t = fminf(fmaxf(t, 0.0f), 255.0f) + 0.5f;      // clamp, then f32::round (half away; value is >= 0) = floor(t + 0.5):
+    return __float_as_uint(__fadd_rz(t, 8388608.0f)) & 0xffu;      // 2^23 + floor(t) by truncation, no FRND / F2I
+}
+
+__device__ __forceinline__ void fill_span(uint32_t *row, int x0, int x1, uint32_t v, int lane) {
+    if (x1 <= x0) return;
+    const int head = min(x1 - x0, int(((16u - (uint32_t(reinterpret_cast<uintptr_t>(row + x0)) & 15u)) & 15u) >> 2));
+    if (lane < head) row[x0 + lane] = v;
+    const int xb = x0 + head, nvec = (x1 - xb) >> 2;
+    const uint4 vv = make_uint4(v, v, v, v);
+    for (int i = lane; i < nvec; i += 32) reinterpret_cast<uint4 *>(row + xb)[i] = vv;
+    const int xt = xb + nvec * 4;
+    if (xt + lane < x1) row[xt + lane] = v;
+}
+
+template <int NCH1, int NCH2>
+__global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TileParams p) {
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    uint32_t *dst = reinterpret_cast<uint32_t *>(p.dst + size_t(blockIdx.z) * p.dst_img_bytes);
+
+    if (blockIdx.x >= p.n_colblk) {              // fill CTA: canvas rows part, part + nparts, ... ; one row per warp
+        const int fw = int(p.fw), kx0 = int(p.fox), kx1 = int(p.fox + p.pw);
+        const bool all_computed = (p.need_fill & 2u) == 0;
+#pragma unroll 1
+        for (int fr = int(blockIdx.y) * kWarps + warp; fr < int(p.fh); fr += int(gridDim.y) * kWarps) {
+            const int i = fr - int(p.foy);
+            const bool kept = i >= 0 && i < int(p.ph);
+            uint32_t *row = dst + size_t(fr) * fw;
+            if (!kept) { fill_span(row, 0, fw, p.fill_post, lane); continue; }
+            fill_span(row, 0, kx0, p.fill_post, lane);
+            if (!(all_computed || p.row_computed[i])) fill_span(row, kx0, kx1, p.fill_pre_packed, lane);
+            fill_span(row, kx1, fw, p.fill_post, lane);
+        }
+        return;
+    }
+
+    const int cb = blockIdx.x, rb = blockIdx.y;
+    const int col0 = cb * int(p.tw), col1 = min(int(p.pw), col0 + int(p.tw));
+    const int n_groups = (int(p.ph) + 7) >> 3;
+    const int g0 = rb * int(p.th >> 3), ng = min(n_groups - g0, int(p.th >> 3));
+    const int y0 = p.rb_y0[rb], nrows = p.rb_rows[rb];
+    const int s0 = p.cb_src0[cb], nblk = p.cb_nblk[cb];
+    if (nrows <= 0) return;                      // every row of the block is pure fill: the fill CTAs write it
+
+    const uint32_t sbase = smem_u32(smem_raw);
+    const uint32_t vbase = sbase + p.rows_max * p.pitch;
+    const uint32_t vplane = 32u * p.pitch_v;     // one limb of one group
+
+    // ---- stage the source footprint: rows [y0, y0 + nrows) of the rectangle, pixels [s0, s0 + 4 nblk) ----------
+    {
+        const uint8_t *src = p.src + size_t(blockIdx.z) * p.src_img_bytes;
+        const int total = nrows * nblk;
+        for (int i = tid; i < total; i += kThreads) {
+            const int r = i / nblk, b = i - r * nblk;
+            const int px = s0 + 4 * b;
+            const uint32_t d = sbase + uint32_t(r) * p.pitch + uint32_t(b) * 16u;
+            if (px + 4 <= int(p.sw)) cp_async16(d, src + (size_t(p.ry + y0 + r) * p.sw + px) * 4);
+            else *reinterpret_cast<uint4 *>(smem_raw + size_t(r) * p.pitch + size_t(b) * 16) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+
+    // ---- pass 1: vertical taps, 8 output rows x pairs of 16-byte blocks ------------------------------------------
+    {
+        const int wpg = max(1, kWarps / ng);             // warps that share a group
+        const int gstep = kWarps / wpg;
+        const int ch = g & 3, hh = g >> 2;
+        const int sh1 = p.sh1;
+        const int npair = nblk >> 1;
+#pragma unroll 1
+        for (int gi = warp / wpg; gi < ng; gi += gstep) {
+            const uint32_t *rec = p.recs + size_t(g0 + gi) * p.rec_words;
+            const int a0 = int(__ldg(rec)), nch = int(__ldg(rec + 2));
+            if (nch == 0) continue;                      // pure-fill rows
+            uint2 bw1[NCH1][2];
+#pragma unroll
+            for (int c = 0; c < NCH1; c++)
+#pragma unroll
+                for (int d = 0; d < 2; d++) bw1[c][d] = __ldg(reinterpret_cast<const uint2 *>(rec + 64) + (c * 2 + d) * 32 + lane);
+            const int bias0 = int(__ldg(rec + 8 + (2 * t) * 4 + ch)), bias1 = int(__ldg(rec + 8 + (2 * t + 1) * 4 + ch));
+            uint32_t rowoff[NCH1];
+#pragma unroll
+            for (int c = 0; c < NCH1; c++) rowoff[c] = sbase + uint32_t(min(a0 - y0 + 32 * c + lane, nrows - 1)) * p.pitch;
+            const uint32_t vrow = vbase + uint32_t(gi) * 2u * vplane + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u;
+#pragma unroll 1
+            for (int q = warp % wpg; q < npair; q += wpg) {
+                const uint32_t boff = uint32_t(q) * 32u;
+                int acc[2][2][4];
+#pragma unroll
+                for (int c = 0; c < NCH1; c++) {         // groups with shorter bands carry zero weights in the rest
+                    uint32_t a[2][4];
+#pragma unroll
+                    for (int u = 0; u < 2; u++) ldsm_t(a[u], rowoff[c] + boff + uint32_t(u) * 16u);
+#pragma unroll
+                    for (int d = 0; d < 2; d++)
+#pragma unroll
+                        for (int u = 0; u < 2; u++) {
+                            if (c == 0 && d == 0) imma_c(acc[u][d], a[u], bw1[c][d], bias0, bias1);   // the sum starts at the bias
+                            else if (c == 0) imma_z(acc[u][d], a[u], bw1[c][d]);
+                            else imma(acc[u][d], a[u], bw1[c][d]);
+                        }
+                }
+#pragma unroll
+                for (int u = 0; u < 2; u++) {            // recombine the digit planes (exact), re-quantise to u16, split into limbs
+                    int v[4];
+#pragma unroll
+                    for (int i = 0; i < 4; i++) v[i] = (acc[u][0][i] + (acc[u][1][i] << 8)) >> sh1;
+                    // v[0],v[2]: pixel hh / hh+2 of output row 2t; v[1],v[3]: same pixels of row 2t+1
+                    const uint32_t w0 = __byte_perm(uint32_t(v[0]), uint32_t(v[2]), 0x5140);
+                    const uint32_t w1r = __byte_perm(uint32_t(v[1]), uint32_t(v[3]), 0x5140);
+                    const uint32_t send = hh ? w0 : w1r, mine = hh ? w1r : w0;
+                    const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 16);
+                    const uint32_t pa = hh ? recv : mine, pb = hh ? mine : recv;              // pixels (0,2) and (1,3)
+                    const uint32_t word = (uint32_t(q) * 2u + uint32_t(u)) * 4u;
+                    sts32(vrow + word, __byte_perm(pa, pb, 0x5410));                 // low limbs
+                    sts32(vrow + vplane + word, __byte_perm(pa, pb, 0x7632));        // high limbs
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- pass 2: horizontal taps, 4 channels x 8 rows x 8 output columns per step ---------------------------------
+    {
+        const int T = int(p.tw >> 3);
+        const int ntile = (col1 - col0 + 7) >> 3;
+        const int wpt = max(1, kWarps / T);              // warps that share a column tile
+        const int tstep = kWarps / wpt;
+#pragma unroll 1
+        for (int tile = warp / wpt; tile < ntile; tile += tstep) {
+            const int kb0 = p.tile_kb0[cb * T + tile];
+            uint2 bw2[NCH2][2];
+#pragma unroll
+            for (int c = 0; c < NCH2; c++)
+#pragma unroll
+                for (int d = 0; d < 2; d++)
+                    bw2[c][d] = __ldg(reinterpret_cast<const uint2 *>(p.b2) + ((size_t(cb * T + tile) * NCH2 + c) * 2 + d) * 32 + lane);
+            const int ocol = col0 + tile * 8 + 2 * t;          // this lane's two kept output columns
+            float cxr[2][4];
+#pragma unroll
+            for (int e = 0; e < 2; e++)
+#pragma unroll
+                for (int c = 0; c < 4; c++) cxr[e][c] = ocol + e < col1 ? p.cx[size_t(ocol + e) * 4 + c] : 0.0f;
+#pragma unroll 1
+            for (int gi = warp % wpt; gi < ng; gi += wpt) {
+                if (__ldg(p.recs + size_t(g0 + gi) * p.rec_words + 2) == 0u) continue;
+                const uint32_t vbuf = vbase + uint32_t(gi) * 2u * vplane;
+                int acc[2][2][2][4];               // [channel pair][limb][digit]
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++) {
+                    const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
+                    const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
+#pragma unroll
+                    for (int c = 0; c < NCH2; c++)
+#pragma unroll
+                        for (int l = 0; l < 2; l++) {
+                            uint32_t a[4];
+                            const uint32_t o = uint32_t(l) * vplane + uint32_t(c) * 32u;
+                            a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
+#pragma unroll
+                            for (int d = 0; d < 2; d++) {
+                                if (c == 0) imma_z(acc[mt][l][d], a, bw2[c][d]);
+                                else imma(acc[mt][l][d], a, bw2[c][d]);
+                            }
+                        }
+                }
+                uint32_t px[2] = {0u, 0u};         // packed RGBA of columns ocol, ocol+1 of output row g
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {  // i = 0,1: channel 2mt, columns +0, +1; i = 2,3: channel 2mt+1
+                        float f = cxr[i & 1][2 * mt + (i >> 1)];
+#pragma unroll
+                        for (int l = 0; l < 2; l++)
+#pragma unroll
+                            for (int d = 0; d < 2; d++) f = fmaf(int_to_float(acc[mt][l][d][i]), p.s2[l][d], f);
+                        px[i & 1] |= quantize_channel(f) << (8 * (2 * mt + (i >> 1)));
+                    }
+                const int i_row = (g0 + gi) * 8 + g;
+                if (i_row < int(p.ph) && p.row_computed[i_row]) {
+                    uint32_t *o = dst + size_t(p.foy + i_row) * p.fw + p.fox + ocol;
+                    if (ocol + 1 < col1 && (reinterpret_cast<uintptr_t>(o) & 7) == 0) *reinterpret_cast<uint2 *>(o) = make_uint2(px[0], px[1]);
+                    else {
+                        if (ocol < col1) o[0] = px[0];
+                        if (ocol + 1 < col1) o[1] = px[1];
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <int NCH1, int NCH2>
+cudaError_t launch_tile_t(const TileParams &p, uint32_t n_images, cudaStream_t stream) {
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (configured_dev != dev) {
+        cudaError_t e = cudaFuncSetAttribute(resize_tile_kernel<NCH1, NCH2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (e != cudaSuccess) return e;
+        configured_dev = dev;
+    }
+    TileParams q = p;
+    for (uint32_t first = 0; first < n_images; first += 65535) {
+        q.src = p.src + size_t(first) * p.src_img_bytes;
+        q.dst = p.dst + size_t(first) * p.dst_img_bytes;
+        const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
+        resize_tile_kernel<NCH1, NCH2><<<dim3(p.n_colblk + (p.need_fill ? 1u : 0u), p.n_rowblk, nz), kThreads, p.smem_bytes, stream>>>(q);
+        count_launch();
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+}  // namespace
+
+cudaError_t launch_resize_tile(const TileParams &p, uint32_t n_images, cudaStream_t stream) {
+    if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
+    if (p.n_rowblk == 0 || p.n_rowblk > 65535 || p.n_colblk == 0 || p.smem_bytes > 100 * 1024) return cudaErrorInvalidValue;
+#define SLIMG_TILE_CASE(A, B) if (p.nch1 == A && p.nch2 == B) return launch_tile_t<A, B>(p, n_images, stream);
+#define SLIMG_TILE_ROW(A) SLIMG_TILE_CASE(A, 1) SLIMG_TILE_CASE(A, 2) SLIMG_TILE_CASE(A, 3) SLIMG_TILE_CASE(A, 4)
+    SLIMG_TILE_ROW(1) SLIMG_TILE_ROW(2) SLIMG_TILE_ROW(3) SLIMG_TILE_ROW(4)
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace slimg

@@ -145,6 +145,33 @@ constexpr int kVfMaxVBufs = 4;      // most V buffers the kernel supports (VfPar
 cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStream_t stream);
 size_t vfirst_smem_tail_bytes();
 
+// ---- K2 integer tile kernel (k2_tile.cu, plan in tileplan.cpp): ratios below ~3.5x and upscales ---------------------
+struct TileParams {
+    const uint8_t *src;
+    uint8_t *dst;
+    size_t src_img_bytes, dst_img_bytes;
+    uint32_t sw, sh;                 // source pitch (pixels) and height
+    uint32_t ry, rh;                 // first row / rows of the source rectangle
+    uint32_t pw, ph;                 // columns / rows of the resize output that are kept
+    uint32_t tw, th;                 // kept columns / rows per CTA
+    int32_t nch1, nch2, sh1;
+    uint32_t rec_words;
+    const uint32_t *recs;            // [groups][rec_words]
+    const uint8_t *row_computed;     // [ph]
+    uint32_t n_rowblk, n_colblk;
+    const int32_t *rb_y0, *rb_rows;  // [n_rowblk]
+    const int32_t *cb_src0, *cb_nblk;   // [n_colblk]
+    const int32_t *tile_kb0;         // [n_colblk][tw / 8]
+    const uint32_t *b2;              // [n_colblk][tw / 8][nch2][2][32 lanes][2]
+    const float *cx;                 // [pw][4]
+    float s2[2][2];
+    uint32_t pitch, pitch_v, rows_max, smem_bytes;
+    uint32_t fw, fh, fox, foy;
+    uint32_t fill_post, fill_pre_packed;
+    uint32_t need_fill;              // bit 0: some canvas pixels are not computed; bit 1: some kept rows are pure fill
+};
+cudaError_t launch_resize_tile(const TileParams &p, uint32_t n_images, cudaStream_t stream);
+
 // ---- K2 tcgen05 pipeline (k2_tc.cu, plan in tcplan.cpp) ---------------------------------------------------
 struct TcParams {
     const uint8_t *src;

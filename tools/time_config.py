@@ -17,6 +17,10 @@ CFG = {
     "r2": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(3000)), ll.ORDER_CONVERT, 32),
     "r15": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(4000)), ll.ORDER_CONVERT, 32),
     "c4b": (1024, 1024, dict(resize=ll.ResizeMode.SCALE(4.0)), ll.ORDER_CONVERT, 64),
+    "up2": (2048, 2048, dict(resize=ll.ResizeMode.SCALE(2.0)), ll.ORDER_CONVERT, 32),
+    "thumb": (4000, 3000, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 64),          # gui/src-tauri/src/commands.rs:129-133
+    "thumb24": (6000, 4000, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 64),
+    "thumbs": (1024, 768, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 256),
 }
 name = sys.argv[1]
 w, h, kw, order, B = CFG[name]
@@ -35,4 +39,4 @@ for _ in range(n): step()
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / n
 inb, outb = w * h * 4, ow * oh * 4
-print(f"{name:7s} {os.environ.get('AB', ''):40s} {ms / B * 1e3:8.2f} us/image  {B * w * h / ms / 1e6:8.1f} Gpx/s  full-in+out {(inb + outb) * B / ms / 1e6:7.0f} GB/s")
+print(f"{name:7s} {os.environ.get('AB', ''):28s} path={ll.PATH_NAMES[ll.last_resize_path()]:8s} {ms / B * 1e3:8.2f} us/image  {B * w * h / ms / 1e6:8.1f} Gpx/s  full-in+out {(inb + outb) * B / ms / 1e6:7.0f} GB/s")
