@@ -118,7 +118,7 @@ def measured_traffic(order: str, batch: int):
 # ---- clocks ------------------------------------------------------------------------------------------
 
 class ClockSampler:
-    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+    FIELDS = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
               "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -135,7 +135,21 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
-    def stop(self):
+    def wait_first_sample(self, timeout=3.0):
+        """nvidia-smi needs a moment to start: do not open the timed region before it samples."""
+        t0 = time.time()
+        while self.proc is not None and time.time() - t0 < timeout:
+            try:
+                if os.path.getsize(self.path) > 0:
+                    return
+            except OSError:
+                return
+            time.sleep(0.01)
+
+    def stop(self, t_begin=None, t_end=None):
+        """Median SM clock and the throttle reasons seen between wall-clock times t_begin and t_end (the timed region,
+        widened to the sampling period when it is shorter than that)."""
+        import datetime
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if self.proc is None:
             return out
@@ -144,25 +158,30 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm, reasons = [], set()
+        rows = []
         try:
             for line in open(self.path):
                 f = [x.strip() for x in line.split(",")]
                 if len(f) < 9:
                     continue
                 try:
-                    sm.append(float(f[1])); out["sm_max_mhz"] = float(f[2])
+                    ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                    rows.append((ts, float(f[1]), float(f[2]), [v.lower().startswith("active") for v in f[5:9]]))
                 except ValueError:
                     continue
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
             os.unlink(self.path)
         except Exception:
             pass
-        if sm:
-            out["sm_mhz"] = float(np.median(sm)); out["samples"] = len(sm)
-        out["reasons"] = sorted(reasons)
+        if t_begin is not None and rows:
+            inside = [r for r in rows if t_begin - 0.03 <= r[0] <= t_end + 0.03]
+            if not inside:      # nearest sample to the middle of the region
+                mid = 0.5 * (t_begin + t_end)
+                inside = [min(rows, key=lambda r: abs(r[0] - mid))]
+            rows = inside
+        if rows:
+            out["sm_mhz"] = float(np.median([r[1] for r in rows])); out["sm_max_mhz"] = rows[-1][2]; out["samples"] = len(rows)
+            names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+            out["reasons"] = sorted({n for r in rows for n, on in zip(names, r[3]) if on})
         return out
 
 
@@ -426,24 +445,28 @@ def main():
     def step():
         ll.pipeline_batch_device(src.data_ptr(), B, SRC_W, SRC_H, opts, order, dst.data_ptr(), dst.numel(), stream)
 
-    for _ in range(max(args.warmup, 3)):
-        step()
-    barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    if rank == 0:
+        sampler.wait_first_sample()
     launches0 = ll.kernel_launches()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    t_begin = time.time()
     ev0.record()
     for _ in range(args.steps):
         step()
     ev1.record()
     barrier()
+    t_end = time.time()
     ms = ev0.elapsed_time(ev1)
     launches = ll.kernel_launches() - launches0
     ms_max = _shard.max_over_ranks(ms, device="cuda")
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(t_begin, t_end) if rank == 0 else None
     value = _shard.whole_job_throughput(B * args.steps * MPX_PER_IMAGE, world, ms_max * 1e-3)
 
     if args.probe_h2d:
@@ -530,11 +553,14 @@ def main():
             page_in[:] = host
             page_out = np.empty((nb, out_bytes), np.uint8)
 
+            # the staging memcpy is the bound here (one host thread moves ~9 GB/s): eight workers per GPU instead of four
+            cfg_p = ll.CBatchConfig(1, 8, dev)
+
             def pageable_step():
                 for i in range(nb):
                     cin[i] = ll.CImage(SRC_W, SRC_H, page_in[i].ctypes.data, in_bytes)
                     cout[i] = ll.CImage(0, 0, page_out[i].ctypes.data, out_bytes)
-                failed = lib.slimg_b200_pipeline_batch_host(cin, nb, C.byref(opts), order, C.byref(cfg), cout, st)
+                failed = lib.slimg_b200_pipeline_batch_host(cin, nb, C.byref(opts), order, C.byref(cfg_p), cout, st)
                 if failed:
                     raise SystemExit("pageable e2e batch failed: " + lib.slimg_b200_last_error().decode())
 
@@ -542,7 +568,7 @@ def main():
             dt_p, step_ms_p = timed_e2e(pageable_step, p_steps)
             same = bool((page_out == np.ctypeslib.as_array(C.cast(pin_out, C.POINTER(C.c_uint8)), shape=(nb, out_bytes))).all())
             e2e["pageable"] = {"value": _shard.whole_job_throughput(nb * p_steps * MPX_PER_IMAGE, world, dt_p), "unit": "Mpx/s",
-                               "steps": p_steps, "step_ms": step_ms_p, "host_buffers": "pageable (numpy heap arrays), staged through the library's pinned ring",
+                               "steps": p_steps, "step_ms": step_ms_p, "host_buffers": "pageable (numpy heap arrays), staged through the library's pinned ring", "streams_per_device": 8,
                                "equals_pinned_result": same}
             e2e["pageable"]["frac_of_pinned"] = e2e["pageable"]["value"] / e2e_value
             del page_in, page_out

@@ -264,7 +264,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path
         if (lp.ok) {
             if ((e = plan->l_recs.upload(lp.recs)) || (e = plan->l_rowc.upload(lp.row_computed)) || (e = plan->l_y0.upload(lp.rb_y0)) ||
                 (e = plan->l_rows.upload(lp.rb_rows)) || (e = plan->l_src0.upload(lp.cb_src0)) || (e = plan->l_nblk.upload(lp.cb_nblk)) ||
-                (e = plan->l_kb0.upload(lp.tile_kb0)) || (e = plan->l_b2.upload(lp.b2)) || (e = plan->l_cx.upload(lp.cx)))
+                (e = plan->l_kb0.upload(lp.tile_kb0)) || (e = plan->l_b2.upload(lp.b2)) || (e = plan->l_cx.upload(lp.cxi)))
                 return cuda_fail(e, "uploading tile resize plan");
             TileParams &l = plan->lparams;
             l.sw = g.sw; l.sh = g.sh; l.ry = g.ry; l.rh = g.rh; l.pw = g.pw; l.ph = g.ph;
@@ -273,9 +273,8 @@ static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path
             l.n_rowblk = lp.n_rowblk; l.n_colblk = lp.n_colblk;
             l.rb_y0 = (const int32_t *)plan->l_y0.p; l.rb_rows = (const int32_t *)plan->l_rows.p;
             l.cb_src0 = (const int32_t *)plan->l_src0.p; l.cb_nblk = (const int32_t *)plan->l_nblk.p;
-            l.tile_kb0 = (const int32_t *)plan->l_kb0.p; l.b2 = (const uint32_t *)plan->l_b2.p; l.cx = (const float *)plan->l_cx.p;
-            for (int a = 0; a < 2; a++)
-                for (int d = 0; d < 2; d++) l.s2[a][d] = lp.s2[a][d];
+            l.tile_kb0 = (const int32_t *)plan->l_kb0.p; l.b2 = (const uint32_t *)plan->l_b2.p; l.cxi = (const int32_t *)plan->l_cx.p;
+            l.sh2 = lp.sh2; l.packed = lp.packed ? 1u : 0u;
             l.pitch = lp.pitch; l.pitch_v = lp.pitch_v; l.rows_max = lp.rows_max; l.smem_bytes = lp.smem_bytes;
             l.fw = g.fw; l.fh = g.fh; l.fox = g.fox; l.foy = g.foy;
             l.fill_post = pack_fill(g.fill_post); l.fill_pre_packed = pack_fill(g.fill_pre);
@@ -306,7 +305,8 @@ static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path
             t.tile_kb0 = (const int32_t *)plan->t_kb0.p; t.b2 = (const uint32_t *)plan->t_b2.p; t.cx = (const float *)plan->t_cx.p;
             for (int l = 0; l < 2; l++)
                 for (int d = 0; d < 3; d++) t.s2[l][d] = tp.s2[l][d];
-            t.slots = tp.slots; t.slot_bytes = tp.slot_bytes; t.pitch_v = tp.pitch_v; t.smem_bytes = tp.smem_bytes; t.nbuf = tp.nbuf;
+            t.slots = tp.slots; t.slot_bytes = tp.slot_bytes; t.pitch_v = tp.pitch_v; t.smem_bytes = tp.smem_bytes; t.nbuf = tp.nbuf; t.vbufs = tp.vbufs;
+            { const char *pf = std::getenv("SLIMG_B200_TC_PREFETCH"); t.pf_chunks = pf ? uint32_t(std::atoi(pf)) : 6u; }
             t.fw = g.fw; t.fh = g.fh; t.fox = g.fox; t.foy = g.foy;
             t.fill_post = pack_fill(g.fill_post); t.fill_pre_packed = pack_fill(g.fill_pre);
             t.n_bands = 1; t.need_fill = tp.need_fill ? 1u : 0u;
@@ -502,7 +502,7 @@ static slimg_status run_pipeline_device(const PipeGeom &g, const uint8_t *src, u
         // bands of 16-row blocks: enough CTAs to fill the GPU when the batch is small
         const uint64_t ctas_per_band = uint64_t(t.n_strips) * n;
         uint32_t bands = uint32_t((2 * 148 + ctas_per_band - 1) / ctas_per_band);
-        bands = std::max<uint32_t>(1, std::min<uint32_t>(bands, std::max<uint32_t>(1, t.n_blocks / 2)));
+        bands = std::max<uint32_t>(1, std::min<uint32_t>(bands, std::max<uint32_t>(1, t.n_blocks / 4)));
         t.n_bands = bands;
         if (launch_resize_tc(t, n, stream) == cudaSuccess) { note_path(SLIMG_PATH_TC); return SLIMG_OK; }
         cudaGetLastError();

@@ -131,9 +131,10 @@ struct TilePlanHost {
     std::vector<int32_t> rb_y0, rb_rows;   // [n_rowblk] first source-rectangle row / rows a row block stages
     std::vector<int32_t> cb_src0, cb_nblk; // [n_colblk] first staged source pixel (multiple of 4) / 16-byte blocks per row (even)
     std::vector<int32_t> tile_kb0;         // [n_colblk][tw / 8] first block of the tile's k range
-    std::vector<uint32_t> b2;              // [n_colblk][tw / 8][nch2][2 digits][32 lanes][2]
-    std::vector<float> cx;                 // [pw][4]
-    float s2[2][2] = {{0, 0}, {0, 0}};
+    std::vector<uint32_t> b2;              // [n_colblk][tw / 8][nch2][2 digits][32 lanes][2]; packed: [n_colblk][tw / 8][3][32][2]
+    std::vector<int32_t> cxi;              // [pw][4] constant term + rounding half, units of 2^-sh2
+    int sh2 = 0;                           // final right shift of the pass-2 integer sum
+    bool packed = false;                   // both limbs in one K = 32 (every tile's taps span <= 16 staged pixels: upscales)
     uint32_t v_words = 0, pitch = 0, pitch_v = 0, smem_bytes = 0;
     bool need_fill = false, rows_pure_fill = false;
 };
@@ -145,12 +146,12 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
 struct TcPlanHost {
     bool ok = false;
     int ndig = 2, sh1 = 0;
-    // vertical: blocks of 16 kept output rows, chunks of 32 source-rectangle rows
+    // vertical: blocks of 8 kept output rows, chunks of 32 source-rectangle rows
     uint32_t n_blocks = 0, n_chunks = 0, nb_max = 0;
-    uint32_t crec_words = 0;               // words per chunk record: 16 header + nb_max * ndig * 128 (weight tiles)
+    uint32_t crec_words = 0;               // words per chunk record: 16 header + nb_max * 128 (one N = 16 weight tile per block)
     std::vector<uint32_t> crecs;           // [n_chunks][crec_words]
     std::vector<int32_t> blk_c0, blk_c1;   // [n_blocks] first / last chunk of each block
-    std::vector<int32_t> bias;             // [n_blocks*16][4]
+    std::vector<int32_t> bias;             // [n_blocks*8][4]
     // horizontal: strips of kept output columns, tiles of 8; staged span starts on a 128-byte boundary
     uint32_t n_strips = 0, n_panels = 0;   // panels of 128 bytes (32 pixels) staged per strip (max over strips)
     int nch2 = 0;
@@ -160,7 +161,7 @@ struct TcPlanHost {
     std::vector<uint32_t> b2;              // [n_strips][8][nch2][ndig][32][2]
     std::vector<float> cx;                 // [pw][4]
     float s2[2][3] = {{0, 0, 0}, {0, 0, 0}};
-    uint32_t slots = 0, slot_bytes = 0, pitch_v = 0, smem_bytes = 0, nbuf = 0;
+    uint32_t slots = 0, slot_bytes = 0, pitch_v = 0, smem_bytes = 0, nbuf = 0, vbufs = 3;
     bool need_fill = false;
 };
 void build_tcplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, TcPlanHost &out);

@@ -10,10 +10,10 @@
 // Here the vertical pass is INPUT-stationary: source rows stream through a ring in chunks of 32 rows, each chunk is
 // multiplied into the accumulators of every block of 16 output rows it touches, and is released as soon as those
 // MMAs retire.  The accumulators (128 bytes of the row x 16 output rows x 2 weight digits, s32) live in TMEM, so
-// the whole ring is prefetch depth.
+// the whole ring is prefetch depth (and the chunks after it are prefetched as far as L2).
 //
 //   HBM --cp.async.bulk.tensor.2d (one 128 B x 32 rows box per panel, SWIZZLE_128B)--> ring slot
-//   tcgen05.mma.cta_group::1.kind::i8  D[128 bytes of the row][16 output rows] += A * B
+//   tcgen05.mma.cta_group::1.kind::i8  D[128 bytes of the row][8 output rows x 2 digits] += A * B
 //        A = the panel as it lies in the slot: MN-major (the 128 bytes of a row are contiguous), u8
 //        B = weight digit tile of (chunk, block) from the chunk record, K-major, s8
 //        one elected thread issues; tcgen05.commit releases the slot / publishes a finished block
@@ -24,6 +24,8 @@
 // Nothing but source pixels is read from HBM and nothing but final pixels is written.
 #include <cuda.h>
 
+#include <algorithm>
+
 #include "kernels.cuh"
 
 namespace slimg {
@@ -31,14 +33,17 @@ namespace slimg {
 namespace {
 
 constexpr int kThreads = 448;                // 14 warps
+constexpr int kWarps = kThreads / 32;
 constexpr int kP2Warps = 4;                  // warps 0..3: pass 2 (one per tile of 8 output columns)
 constexpr int kEpiWarp0 = 4, kEpiWarps = 8;  // warps 4..11: epilogue, two per TMEM lane quarter
 constexpr int kProducerWarp = 12, kMmaWarp = 13;
 constexpr int kMaxSlots = 12;
+constexpr int kMaxAcc = 8;                   // accumulator buffers per panel (16 TMEM columns each)
+constexpr int kMaxVBufs = 4;
 constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
-// tcgen05 instruction descriptor: D = s32, A = u8 MN-major, B = s8 K-major, M = 128, N = 32 (both weight digits of a
-// block's 16 rows in one instruction: the A panel is read from shared memory once)
-constexpr uint32_t kIdesc = (2u << 4) | (0u << 7) | (1u << 10) | (1u << 15) | (0u << 16) | ((32u >> 3) << 17) | ((128u >> 4) << 24);
+// tcgen05 instruction descriptor: D = s32, A = u8 MN-major, B = s8 K-major, M = 128, N = 16 (both weight digits of a
+// block's 8 rows in one instruction: the A panel is read from shared memory once)
+constexpr uint32_t kIdesc = (2u << 4) | (0u << 7) | (1u << 10) | (1u << 15) | (0u << 16) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
@@ -89,9 +94,15 @@ __device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t adesc, uint64_
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void tmem_ld8(uint32_t taddr, int (&r)[8]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(taddr));
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, int (&r)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr));
+}
+// same box as tma_load_2d, only as far as L2: the DRAM part of the latency is paid before the chunk gets a ring slot
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *map, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 // shared-memory matrix descriptors (cute/arch/mma_sm100_desc.hpp SmemDescriptor): address, LBO and SBO in 16-byte
@@ -124,58 +135,64 @@ __device__ __forceinline__ void sts8(uint32_t addr, uint32_t v) {
 // exact s32 -> f32 for |x| < 2^22 without the quarter-rate I2F
 __device__ __forceinline__ float int_to_float(int x) { return __int_as_float(x + 0x4B400000) - 12582912.0f; }
 __device__ __forceinline__ uint32_t quantize_channel(float t) {
-    t = fminf(fmaxf(t, 0.0f), 255.0f);      // clamp, then f32::round (half away; value is >= 0)
-    return uint32_t(floorf(t + 0.5f));
+    t = fminf(fmaxf(t, 0.0f), 255.0f) + 0.5f;      // clamp, then f32::round (half away; value is >= 0) = floor(t + 0.5):
+    return __float_as_uint(__fadd_rz(t, 8388608.0f)) & 0xffu;      // 2^23 + floor(t) by truncation, no FRND / F2I
 }
 
 struct SmemTail {
     uint64_t full[kMaxSlots];                // chunk (panels + record) landed
     uint64_t empty[kMaxSlots];               // every MMA that reads the slot has retired
-    uint64_t acc_full[4];                    // a block's accumulators are complete
-    uint64_t acc_empty[4];                   // the epilogue has drained the buffer
-    uint64_t v_full[2];                      // 8 rows of the intermediate are in V[buf]
-    uint64_t v_empty[2];                     // every pass-2 warp has read V[buf]
+    uint64_t acc_full[kMaxAcc];              // a block's accumulators are complete
+    uint64_t acc_empty[kMaxAcc];             // the epilogue has read the buffer out of TMEM
+    uint64_t v_full[kMaxVBufs];              // 8 rows of the intermediate are in V[buf]
+    uint64_t v_empty[kMaxVBufs];             // every pass-2 warp has read V[buf]
     uint32_t tmem_base;
 };
 
-// canvas pixels this CTA owns but does not compute: rows outside the kept rectangle and the margins left / right
-// of the kept columns (edge bands / strips extend to the canvas border)
-__device__ void fill_region(const TcParams &p, uint32_t *dst, int i0, int i1, int c0, int c1, int warp, int nwarps) {
-    const bool first_band = blockIdx.y == 0, last_band = blockIdx.y + 1 == gridDim.y;
-    const bool first_strip = blockIdx.x == 0, last_strip = blockIdx.x + 1 == gridDim.x;
-    const int fr0 = first_band ? 0 : int(p.foy) + i0, fr1 = last_band ? int(p.fh) : int(p.foy) + i1;
-    const int cx0 = first_strip ? 0 : int(p.fox) + c0, cx1 = last_strip ? int(p.fw) : int(p.fox) + c1;
-    const int kx0 = int(p.fox), kx1 = int(p.fox + p.pw), ky0 = int(p.foy), ky1 = int(p.foy + p.ph);
-    const int lane = threadIdx.x & 31, fw = int(p.fw);
-    const uint32_t fill = p.fill_post;
-#pragma unroll 1
-    for (int fr = fr0 + warp; fr < fr1; fr += nwarps) {
-        uint32_t *row = dst + size_t(fr) * fw;
-        if (fr < ky0 || fr >= ky1) {
-            for (int x = cx0 + lane; x < cx1; x += 32) row[x] = fill;
-        } else {
-            for (int x = cx0 + lane; x < kx0; x += 32) row[x] = fill;
-            for (int x = kx1 + lane; x < cx1; x += 32) row[x] = fill;
-        }
-    }
+// What is not computed: canvas rows outside the kept rectangle and the margins left / right of the kept columns
+// (fill_post).  Dedicated fill CTAs (blockIdx.x >= n_strips) write them with 16-byte stores, one canvas row per warp,
+// while the strip CTAs of the same image stream the source: the fill costs the strip pipeline nothing.
+__device__ __forceinline__ void fill_span(uint32_t *row, int x0, int x1, uint32_t v, int lane) {
+    if (x1 <= x0) return;
+    const int head = min(x1 - x0, int(((16u - (uint32_t(reinterpret_cast<uintptr_t>(row + x0)) & 15u)) & 15u) >> 2));
+    if (lane < head) row[x0 + lane] = v;
+    const int xb = x0 + head, nvec = (x1 - xb) >> 2;
+    const uint4 vv = make_uint4(v, v, v, v);
+    for (int i = lane; i < nvec; i += 32) reinterpret_cast<uint4 *>(row + xb)[i] = vv;
+    const int xt = xb + nvec * 4;
+    if (xt + lane < x1) row[xt + lane] = v;
 }
 
 template <int NCH2>
 __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
     constexpr int NDIG = 2;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t *dst = reinterpret_cast<uint32_t *>(p.dst + size_t(blockIdx.z) * p.dst_img_bytes);
+
+    if (blockIdx.x >= p.n_strips) {              // fill CTA: no shared memory, no barriers, no TMEM
+        const int part = int(blockIdx.x - p.n_strips) * int(gridDim.y) + int(blockIdx.y);
+        const int nparts = int(gridDim.x - p.n_strips) * int(gridDim.y);
+        const int fw = int(p.fw), kx0 = int(p.fox), kx1 = int(p.fox + p.pw), ky0 = int(p.foy), ky1 = int(p.foy + p.ph);
+#pragma unroll 1
+        for (int fr = part * kWarps + warp; fr < int(p.fh); fr += nparts * kWarps) {
+            uint32_t *row = dst + size_t(fr) * fw;
+            if (fr < ky0 || fr >= ky1) { fill_span(row, 0, fw, p.fill_post, lane); continue; }
+            fill_span(row, 0, kx0, p.fill_post, lane);
+            fill_span(row, kx1, fw, p.fill_post, lane);
+        }
+        return;
+    }
+
     const uint32_t ring = smem_u32(smem_raw);
     const uint32_t crec_bytes = p.crec_words * 4u;
     const uint32_t crec_base = ring + p.slots * p.slot_bytes;
     const uint32_t vbase = crec_base + p.slots * crec_bytes;
     const uint32_t vplane = 32u * p.pitch_v;                   // one limb of one buffer
-    const size_t tail_off = size_t(p.slots) * (p.slot_bytes + crec_bytes) + 4u * vplane;
+    const size_t tail_off = size_t(p.slots) * (p.slot_bytes + crec_bytes) + 2u * p.vbufs * vplane;
     SmemTail &tail = *reinterpret_cast<SmemTail *>(smem_raw + tail_off);
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    uint32_t *dst = reinterpret_cast<uint32_t *>(p.dst + size_t(blockIdx.z) * p.dst_img_bytes);
-
-    // ---- this CTA's strip and band (a range of 16-row blocks) -------------------------------------------
+    // ---- this CTA's strip and band (a range of 8-row blocks) -------------------------------------------
     const int strip = blockIdx.x;
     const int col0 = p.strip_col0[strip], col1 = p.strip_col0[strip + 1];
     const int blk0 = int((uint64_t(blockIdx.y) * p.n_blocks) / gridDim.y);
@@ -183,14 +200,13 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
     const int n_blk = blk1 - blk0;
     const int c_lo = n_blk > 0 ? p.blk_c0[blk0] : 0, c_hi = n_blk > 0 ? p.blk_c1[blk1 - 1] : -1;
     const int n_steps = c_hi - c_lo + 1;
-    const int i0 = blk0 * 16, i1 = min(int(p.ph), blk1 * 16);
     const int ntile = (col1 - col0 + 7) >> 3;
-    const int npan = int(p.n_panels), nbuf = int(p.nbuf), slots = int(p.slots);
+    const int npan = int(p.n_panels), nbuf = int(p.nbuf), slots = int(p.slots), nvb = int(p.vbufs);
 
     if (tid == 0) {
         for (int s = 0; s < slots; s++) { mbar_init(&tail.full[s], 1); mbar_init(&tail.empty[s], 1); }
-        for (int b = 0; b < 4; b++) { mbar_init(&tail.acc_full[b], 1); mbar_init(&tail.acc_empty[b], kEpiWarps); }
-        for (int b = 0; b < 2; b++) { mbar_init(&tail.v_full[b], kEpiWarps); mbar_init(&tail.v_empty[b], uint32_t(ntile)); }
+        for (int b = 0; b < nbuf; b++) { mbar_init(&tail.acc_full[b], 1); mbar_init(&tail.acc_empty[b], kEpiWarps); }
+        for (int b = 0; b < nvb; b++) { mbar_init(&tail.v_full[b], kEpiWarps); mbar_init(&tail.v_empty[b], uint32_t(ntile)); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == kMmaWarp) tmem_alloc(&tail.tmem_base, 512);
@@ -201,9 +217,19 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
 
     if (warp == kProducerWarp) {
         // ================= producer: one box per panel + the chunk record, per ring slot =================
+        // Lane l < npan loads panel l of the chunk; lane 31 the chunk record.  Chunks beyond the ring are prefetched as
+        // far as L2 (pf_chunks of them), so a chunk's DRAM latency is paid before it gets a slot.
         const int tx0 = p.strip_src0[strip] >> 1;                                   // 8-byte elements
         const int tr0 = int(blockIdx.z) * int(p.sh) + int(p.ry);
         const uint32_t step_bytes = uint32_t(npan) * 4096u + crec_bytes;
+        const int pf = int(p.pf_chunks);
+        int next_pf = 0;
+        auto prefetch_to = [&](int upto) {                      // chunks [next_pf, upto)
+            for (int s = next_pf; s < upto; s++)
+                if (lane < npan) tma_prefetch_2d(&tmap, tx0 + lane * 16, tr0 + (c_lo + s) * 32);
+            next_pf = max(next_pf, upto);
+        };
+        if (pf) { next_pf = min(n_steps, slots); prefetch_to(min(n_steps, slots + pf)); }
 #pragma unroll 1
         for (int s = 0; s < n_steps; s++) {
             const int slot = s % slots;
@@ -212,12 +238,13 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
             __syncwarp();
             const int c = c_lo + s;
             if (lane < npan)
-                tma_load_2d(ring + uint32_t(slot) * p.slot_bytes + uint32_t(lane) * 4096u, &tmap, tx0 + lane * 16, tr0 + c * 32, &tail.full[slot]);
+                tma_load_2d(ring + uint32_t(slot) * p.slot_bytes + uint32_t(lane) * 4096u, &tmap, tx0 + lane * 16, tr0 + ((p.debug & 4u) ? (c & 7) : c) * 32, &tail.full[slot]);
             else if (lane == 31)
                 bulk_g2s(crec_base + uint32_t(slot) * crec_bytes, p.crecs + size_t(c) * p.crec_words, crec_bytes, &tail.full[slot]);
+            if (pf) prefetch_to(min(n_steps, s + 1 + slots + pf));
         }
     } else if (warp == kMmaWarp) {
-        // ================= MMA issue: every (block, panel, digit) of the chunk ============================
+        // ================= MMA issue: every (block, panel) of the chunk =====================================
         // One elected thread runs the whole loop (tcgen05.mma / commit are single-thread instructions; a loop that
         // is uniform per construction keeps the compiler from wrapping every issue in an election).
         if (elect_one()) {
@@ -237,20 +264,20 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
                     if (b < blk0 || b >= blk1) continue;
                     const int use = (b - blk0) / nbuf, abuf = (b - blk0) - use * nbuf;
                     const bool starts = (flags >> i) & 1u, ends = (flags >> (8 + i)) & 1u;
-                    if (starts) {                                // the buffer's previous block must have been drained
+                    if (starts) {                                // the buffer's previous block must have been read out
                         mbar_wait(&tail.acc_empty[abuf], (uint32_t(use) & 1u) ^ 1u);
                         tc_fence_after();
                     }
                     const uint32_t acc = starts ? 0u : 1u;
-                    const uint64_t bd0 = b_desc0 + uint64_t(i) * (2u * 512u >> 4);     // digit tiles are contiguous: N = 32
+                    const uint64_t bd = b_desc0 + uint64_t(i) * (512u >> 4);          // one N = 16 tile per block
                     uint64_t ad = a_desc0;
-                    uint32_t dcol = tmem + uint32_t(abuf) * 32u;
+                    uint32_t dcol = tmem + uint32_t(abuf) * 16u;
                     if (!(p.debug & 1u)) {
 #pragma unroll 1
                         for (int pn = 0; pn < npan; pn++) {
-                            umma_i8(dcol, ad, bd0, acc);
+                            umma_i8(dcol, ad, bd, acc);
                             ad += 4096u >> 4;
-                            dcol += uint32_t(nbuf) * 32u;
+                            dcol += uint32_t(nbuf) * 16u;
                         }
                     }
                     if (ends) umma_commit(&tail.acc_full[abuf]);
@@ -261,6 +288,9 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
         __syncwarp();
     } else if (warp >= kEpiWarp0 && warp < kEpiWarp0 + kEpiWarps) {
         // ================= epilogue: TMEM -> 16-bit intermediate -> V planes ==============================
+        // A warp reads the TMEM lane quarter (warp & 3) -- 8 pixels x 4 channels of a panel -- for half of the strip's
+        // panels: 16 columns per panel = 8 rows x 2 digits, the next panel's load in flight while this one is
+        // recombined (exact s32), biased, shifted to 16 bits and stored as two u8 limbs, planar [channel][row][pixel].
         const int quarter = warp & 3, half = (warp - kEpiWarp0) >> 2;
         const int per = (npan + 1) >> 1;
         const int pn0 = half * per, pn1 = min(npan, pn0 + per);
@@ -268,44 +298,52 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
         const int sh1 = p.sh1;
         const uint32_t lane_addr = uint32_t(quarter * 32) << 16;
         // byte address of (row 0 of channel ch, pixel quarter*8 + lane/4 of panel 0): rows pitch_v apart, channel
-        // planes skewed by one word
-        const uint32_t v0 = vbase + uint32_t(8 * ch) * p.pitch_v + uint32_t(ch) * 4u + uint32_t(quarter * 8 + (lane >> 2));
+        // planes skewed by two words (a warp's 4 channels x 8 pixels then land in 8 distinct banks)
+        const uint32_t v0 = vbase + uint32_t(8 * ch) * p.pitch_v + uint32_t(ch) * 8u + uint32_t(quarter * 8 + (lane >> 2));
 #pragma unroll 1
         for (int bi = 0; bi < n_blk; bi++) {
             const int use = bi / nbuf, abuf = bi - use * nbuf;
-            int bias[16];
+            const int vuse = bi / nvb, vb = bi - vuse * nvb;
+            int bias[8];
 #pragma unroll
-            for (int r = 0; r < 16; r++) bias[r] = __ldg(p.bias + (size_t(blk0 + bi) * 16 + r) * 4 + ch);
+            for (int r = 0; r < 8; r++) bias[r] = __ldg(p.bias + (size_t(blk0 + bi) * 8 + r) * 4 + ch);
             mbar_wait(&tail.acc_full[abuf], uint32_t(use) & 1u);
             tc_fence_after();
-#pragma unroll
-            for (int h = 0; h < 2; h++) {
-                const int gi = 2 * bi + h;
-                const uint32_t vb = uint32_t(gi) & 1u;
-                mbar_wait(&tail.v_empty[vb], (uint32_t(gi >> 1) & 1u) ^ 1u);
-                const uint32_t vrow = v0 + vb * 2u * vplane;
+            int cur[16], nxt[16];
+            const uint32_t t0 = tmem + lane_addr + uint32_t(abuf) * 16u;
+            if (pn0 < pn1 && !(p.debug & 8u)) tmem_ld16(t0 + uint32_t(pn0 * nbuf) * 16u, cur);
+            mbar_wait(&tail.v_empty[vb], (uint32_t(vuse) & 1u) ^ 1u);
+            const uint32_t vrow = v0 + uint32_t(vb) * 2u * vplane;
 #pragma unroll 1
-                for (int pn = pn0; pn < ((p.debug & 8u) ? pn0 : pn1); pn++) {
-                    int lo[8], hi[8];
-                    const uint32_t taddr = tmem + lane_addr + uint32_t((pn * nbuf + abuf) * 32 + 8 * h);
-                    tmem_ld8(taddr, lo);
-                    tmem_ld8(taddr + 16u, hi);
+            for (int pn = pn0; pn < ((p.debug & 8u) ? pn0 : pn1); pn++) {
+                tmem_ld_wait();
+                if (pn + 1 < pn1) tmem_ld16(t0 + uint32_t((pn + 1) * nbuf) * 16u, nxt);
+                else {                                   // the block is out of TMEM: its buffer may be overwritten
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tail.acc_empty[abuf]);
+                }
+#pragma unroll
+                for (int r = 0; r < 8; r++) {
+                    const int x = cur[r] + (cur[8 + r] << 8) + bias[r];
+                    const uint32_t v = uint32_t(x >> sh1);
+                    const uint32_t a = vrow + uint32_t(r) * p.pitch_v + uint32_t(pn) * 32u;
+                    sts8(a, v);
+                    sts8(a + vplane, v >> 8);
+                }
+                if (pn + 1 < pn1) {
                     tmem_ld_wait();
 #pragma unroll
-                    for (int r = 0; r < 8; r++) {
-                        const int x = lo[r] + (hi[r] << 8) + bias[8 * h + r];
-                        const uint32_t v = uint32_t(x >> sh1);
-                        const uint32_t a = vrow + uint32_t(r) * p.pitch_v + uint32_t(pn) * 32u;
-                        sts8(a, v & 0xffu);
-                        sts8(a + vplane, v >> 8);
-                    }
+                    for (int r = 0; r < 16; r++) cur[r] = nxt[r];
                 }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&tail.v_full[vb]);
             }
-            tc_fence_before();
+            if (pn0 >= pn1 || (p.debug & 8u)) {          // a warp without panels still takes part in the hand-offs
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tail.acc_empty[abuf]);
+            }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tail.acc_empty[abuf]);
+            if (lane == 0) mbar_arrive(&tail.v_full[vb]);
         }
     } else if (warp < ntile) {
         // ================= pass 2: horizontal taps, 4 channels x 8 rows x 8 output columns per warp =======
@@ -331,17 +369,17 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
             for (int d = 0; d < NDIG; d++) s2[l][d] = p.s2[l][d];
 
 #pragma unroll 1
-        for (int gi = 0; gi < 2 * n_blk; gi++) {
-            const uint32_t buf = uint32_t(gi) & 1u;
-            const uint32_t vbuf = vbase + buf * 2u * vplane;
-            mbar_wait(&tail.v_full[buf], uint32_t(gi >> 1) & 1u);
+        for (int gi = 0; gi < n_blk; gi++) {
+            const int vuse = gi / nvb, buf = gi - vuse * nvb;
+            const uint32_t vbuf = vbase + uint32_t(buf) * 2u * vplane;
+            mbar_wait(&tail.v_full[buf], uint32_t(vuse) & 1u);
             if (p.debug & 2u) { __syncwarp(); if (lane == 0) mbar_arrive(&tail.v_empty[buf]); continue; }
 
             int acc[2][2][NDIG][4];            // [channel pair][limb][digit]
 #pragma unroll
-            for (int mt = 0; mt < 2; mt++) {   // channel pairs (0,1) and (2,3)
-                const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
-                const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
+            for (int mt = 0; mt < 2; mt++) {   // channel pairs (0,1) and (2,3); channel planes are skewed by two words
+                const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 8u + uint32_t(kb0 + t) * 4u;
+                const uint32_t r1 = r0 + 8u * p.pitch_v + 8u;
 #pragma unroll
                 for (int c = 0; c < NCH2; c++) {
 #pragma unroll
@@ -358,7 +396,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tail.v_empty[buf]);       // V[buf] may be overwritten (two groups on)
+            if (lane == 0) mbar_arrive(&tail.v_empty[buf]);       // V[buf] may be overwritten (vbufs blocks on)
 
             uint32_t px[2] = {0u, 0u};         // packed RGBA of columns ocol, ocol+1 of output row g
 #pragma unroll
@@ -372,7 +410,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
                         for (int d = 0; d < NDIG; d++) f = fmaf(int_to_float(acc[mt][l][d][i]), s2[l][d], f);
                     px[i & 1] |= quantize_channel(f) << (8 * (2 * mt + (i >> 1)));
                 }
-            const int i_row = (2 * blk0 + gi) * 8 + g;
+            const int i_row = (blk0 + gi) * 8 + g;
             if (i_row < int(p.ph)) {
                 uint32_t *o = dst + size_t(p.foy + i_row) * p.fw + p.fox + ocol;
                 if (ocol < col1) o[0] = px[0];
@@ -386,7 +424,6 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
         tc_fence_after();
         tmem_dealloc(tmem, 512);
     }
-    if (p.need_fill) fill_region(p, dst, i0, i1, col0, col1, warp, kThreads / 32);
 }
 
 }  // namespace
@@ -439,7 +476,14 @@ static cudaError_t launch_tc_t(const TcParams &p, uint32_t n_images, cudaStream_
         CUtensorMap map;
         cudaError_t e = make_panel_map(q, q.src, nz, map);
         if (e != cudaSuccess) return e;
-        resize_tc_kernel<NCH2><<<dim3(p.n_strips, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q, map);
+        // fill CTAs: one per ~2 MB of canvas that is not computed (at least one when anything is), spread over the bands
+        unsigned nfill = 0;
+        if (p.need_fill) {
+            const uint64_t bytes = (uint64_t(p.fw) * p.fh - uint64_t(p.pw) * p.ph) * 4u;
+            nfill = unsigned(std::min<uint64_t>(32, 1 + bytes / (2u << 20)));
+            nfill = (nfill + p.n_bands - 1) / p.n_bands;
+        }
+        resize_tc_kernel<NCH2><<<dim3(p.n_strips + nfill, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q, map);
         count_launch();
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
@@ -449,8 +493,8 @@ static cudaError_t launch_tc_t(const TcParams &p, uint32_t n_images, cudaStream_
 
 cudaError_t launch_resize_tc(const TcParams &p, uint32_t n_images, cudaStream_t stream) {
     if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
-    if (p.n_bands == 0 || p.n_bands > 65535 || p.n_strips == 0 || p.slots > uint32_t(kMaxSlots) || p.nbuf > 4 || p.nbuf < 2 ||
-        p.n_panels * p.nbuf * 32 > 512)
+    if (p.n_bands == 0 || p.n_bands > 65535 || p.n_strips == 0 || p.slots > uint32_t(kMaxSlots) || p.nbuf > uint32_t(kMaxAcc) ||
+        p.nbuf < 2 || p.n_panels * p.nbuf * 16 > 512 || p.vbufs < 2 || p.vbufs > uint32_t(kMaxVBufs))
         return cudaErrorInvalidValue;
     switch (p.nch2) {
         case 1: return launch_tc_t<1>(p, n_images, stream);

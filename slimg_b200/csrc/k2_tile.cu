@@ -11,7 +11,9 @@
 //           A straight from the staged rows with ldmatrix.m16n16.x2.trans.b8, B = weight digits from the plan (L2);
 //           digit recombination, >> to the 16-bit intermediate, two u8 limb planes per group in shared memory
 //   pass 2  per group and tile of 8 output columns:  D2[(channel,row) 16][8 columns] += A[16][32 px] * B[32][8] for
-//           both limbs; f32 recombination, clamp, round half away, packed RGBA stores to the final canvas position
+//           both limbs (upscales: both limbs in ONE K = 32, three MMAs instead of four); the limb / digit planes are
+//           recombined in integers, the constant term (fill taps, offset, rounding half) added, shifted, saturated and
+//           packed two channels per cvt.pack.sat; RGBA stores straight to the final canvas position
 // Two __syncthreads in all; several CTAs per SM overlap each other's staging and arithmetic.  Everything the tile does
 // not compute (canvas outside the kept rectangle, kept rows whose taps are all fill) is written by fill CTAs
 // (blockIdx.x == n_colblk), one canvas row per warp, 16-byte stores.
@@ -56,11 +58,11 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
 __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
     asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
-// exact s32 -> f32 for |x| < 2^22 without the quarter-rate I2F
-__device__ __forceinline__ float int_to_float(int x) { return __int_as_float(x + 0x4B400000) - 12582912.0f; }
-__device__ __forceinline__ uint32_t quantize_channel(float t) {
-    t = fminf(fmaxf(t, 0.0f), 255.0f) + 0.5f;      // clamp, then f32::round (half away; value is >= 0) = floor(t + 0.5):
-    return __float_as_uint(__fadd_rz(t, 8388608.0f)) & 0xffu;      // 2^23 + floor(t) by truncation, no FRND / F2I
+// d = (c << 16) | (sat_u8(hi) << 8) | sat_u8(lo): clamp to [0, 255] and pack, two channels per instruction
+__device__ __forceinline__ uint32_t pack_sat_u8(int hi, int lo, uint32_t c) {
+    uint32_t d;
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(hi), "r"(lo), "r"(c));
+    return d;
 }
 
 __device__ __forceinline__ void fill_span(uint32_t *row, int x0, int x1, uint32_t v, int lane) {
@@ -74,7 +76,7 @@ __device__ __forceinline__ void fill_span(uint32_t *row, int x0, int x1, uint32_
     if (xt + lane < x1) row[xt + lane] = v;
 }
 
-template <int NCH1, int NCH2>
+template <int NCH1, int NCH2, bool PACKED>
 __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TileParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -112,13 +114,19 @@ __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TilePara
     // ---- stage the source footprint: rows [y0, y0 + nrows) of the rectangle, pixels [s0, s0 + 4 nblk) ----------
     {
         const uint8_t *src = p.src + size_t(blockIdx.z) * p.src_img_bytes;
-        const int total = nrows * nblk;
-        for (int i = tid; i < total; i += kThreads) {
-            const int r = i / nblk, b = i - r * nblk;
-            const int px = s0 + 4 * b;
-            const uint32_t d = sbase + uint32_t(r) * p.pitch + uint32_t(b) * 16u;
-            if (px + 4 <= int(p.sw)) cp_async16(d, src + (size_t(p.ry + y0 + r) * p.sw + px) * 4);
-            else *reinterpret_cast<uint4 *>(smem_raw + size_t(r) * p.pitch + size_t(b) * 16) = make_uint4(0u, 0u, 0u, 0u);
+        // lanes across the blocks of a row (and, when a row has at most 16 blocks, across 2..16 rows): no division
+        const int bshift = nblk <= 1 ? 0 : min(5, 32 - __clz(nblk - 1));
+        const int bw = 1 << bshift, rpp = 32 >> bshift;
+        const int b0 = lane & (bw - 1);
+#pragma unroll 1
+        for (int r = warp * rpp + (lane >> bshift); r < nrows; r += kWarps * rpp) {
+            const uint8_t *srow = src + size_t(p.ry + y0 + r) * p.sw * 4;
+            const uint32_t drow = sbase + uint32_t(r) * p.pitch;
+            for (int b = b0; b < nblk; b += bw) {
+                const int px = s0 + 4 * b;
+                if (px + 4 <= int(p.sw)) cp_async16(drow + uint32_t(b) * 16u, srow + size_t(px) * 4);
+                else *reinterpret_cast<uint4 *>(smem_raw + size_t(r) * p.pitch + size_t(b) * 16) = make_uint4(0u, 0u, 0u, 0u);
+            }
         }
         asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
     }
@@ -190,56 +198,65 @@ __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TilePara
         const int ntile = (col1 - col0 + 7) >> 3;
         const int wpt = max(1, kWarps / T);              // warps that share a column tile
         const int tstep = kWarps / wpt;
+        const int sh2 = p.sh2;
+        constexpr int NB2 = PACKED ? 3 : NCH2 * 2;
 #pragma unroll 1
         for (int tile = warp / wpt; tile < ntile; tile += tstep) {
             const int kb0 = p.tile_kb0[cb * T + tile];
-            uint2 bw2[NCH2][2];
+            uint2 bw2[NB2];
 #pragma unroll
-            for (int c = 0; c < NCH2; c++)
-#pragma unroll
-                for (int d = 0; d < 2; d++)
-                    bw2[c][d] = __ldg(reinterpret_cast<const uint2 *>(p.b2) + ((size_t(cb * T + tile) * NCH2 + c) * 2 + d) * 32 + lane);
+            for (int i = 0; i < NB2; i++) bw2[i] = __ldg(reinterpret_cast<const uint2 *>(p.b2) + (size_t(cb * T + tile) * NB2 + i) * 32 + lane);
             const int ocol = col0 + tile * 8 + 2 * t;          // this lane's two kept output columns
-            float cxr[2][4];
+            int cxr[2][4];
 #pragma unroll
             for (int e = 0; e < 2; e++)
 #pragma unroll
-                for (int c = 0; c < 4; c++) cxr[e][c] = ocol + e < col1 ? p.cx[size_t(ocol + e) * 4 + c] : 0.0f;
+                for (int c = 0; c < 4; c++) cxr[e][c] = ocol + e < col1 ? p.cxi[size_t(ocol + e) * 4 + c] : 0;
 #pragma unroll 1
             for (int gi = warp % wpt; gi < ng; gi += wpt) {
                 if (__ldg(p.recs + size_t(g0 + gi) * p.rec_words + 2) == 0u) continue;
                 const uint32_t vbuf = vbase + uint32_t(gi) * 2u * vplane;
-                int acc[2][2][2][4];               // [channel pair][limb][digit]
+                int tsum[2][4];                    // [channel pair][i]: the pass-2 sum in units of 2^-sh2, before the constant term
 #pragma unroll
                 for (int mt = 0; mt < 2; mt++) {
                     const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
                     const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
+                    if (PACKED) {
+                        // K = [16 low-limb pixels | 16 high-limb pixels]: A = lo x w0, B = lo x w1 + hi x w0, C = hi x w1
+                        uint32_t a[4];
+                        a[0] = lds32(r0); a[1] = lds32(r1); a[2] = lds32(r0 + vplane); a[3] = lds32(r1 + vplane);
+                        int aa[4], ab[4], ac[4];
+                        imma_z(aa, a, bw2[0]); imma_z(ab, a, bw2[1]); imma_z(ac, a, bw2[2]);
 #pragma unroll
-                    for (int c = 0; c < NCH2; c++)
+                        for (int i = 0; i < 4; i++) tsum[mt][i] = (aa[i] >> 8) + ab[i] + (ac[i] << 8);
+                    } else {
+                        int acc[2][2][4];          // [limb][digit]
 #pragma unroll
-                        for (int l = 0; l < 2; l++) {
-                            uint32_t a[4];
-                            const uint32_t o = uint32_t(l) * vplane + uint32_t(c) * 32u;
-                            a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
+                        for (int c = 0; c < NCH2; c++)
 #pragma unroll
-                            for (int d = 0; d < 2; d++) {
-                                if (c == 0) imma_z(acc[mt][l][d], a, bw2[c][d]);
-                                else imma(acc[mt][l][d], a, bw2[c][d]);
+                            for (int l = 0; l < 2; l++) {
+                                uint32_t a[4];
+                                const uint32_t o = uint32_t(l) * vplane + uint32_t(c) * 32u;
+                                a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
+#pragma unroll
+                                for (int d = 0; d < 2; d++) {
+                                    if (c == 0) imma_z(acc[l][d], a, bw2[c * 2 + d]);
+                                    else imma(acc[l][d], a, bw2[c * 2 + d]);
+                                }
                             }
-                        }
-                }
-                uint32_t px[2] = {0u, 0u};         // packed RGBA of columns ocol, ocol+1 of output row g
 #pragma unroll
-                for (int mt = 0; mt < 2; mt++)
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {  // i = 0,1: channel 2mt, columns +0, +1; i = 2,3: channel 2mt+1
-                        float f = cxr[i & 1][2 * mt + (i >> 1)];
-#pragma unroll
-                        for (int l = 0; l < 2; l++)
-#pragma unroll
-                            for (int d = 0; d < 2; d++) f = fmaf(int_to_float(acc[mt][l][d][i]), p.s2[l][d], f);
-                        px[i & 1] |= quantize_channel(f) << (8 * (2 * mt + (i >> 1)));
+                        for (int i = 0; i < 4; i++) tsum[mt][i] = (acc[0][0][i] >> 8) + acc[0][1][i] + acc[1][0][i] + (acc[1][1][i] << 8);
                     }
+                }
+                // i = 0,1: channel 2mt, columns +0, +1; i = 2,3: channel 2mt+1.  Constant term (fill taps, offset, rounding
+                // half), shift, saturate, pack RGBA.
+                uint32_t px[2];
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+                    const int c0 = (tsum[0][e] + cxr[e][0]) >> sh2, c1 = (tsum[0][2 + e] + cxr[e][1]) >> sh2;
+                    const int c2 = (tsum[1][e] + cxr[e][2]) >> sh2, c3 = (tsum[1][2 + e] + cxr[e][3]) >> sh2;
+                    px[e] = pack_sat_u8(c1, c0, pack_sat_u8(c3, c2, 0u));
+                }
                 const int i_row = (g0 + gi) * 8 + g;
                 if (i_row < int(p.ph) && p.row_computed[i_row]) {
                     uint32_t *o = dst + size_t(p.foy + i_row) * p.fw + p.fox + ocol;
@@ -254,13 +271,13 @@ __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TilePara
     }
 }
 
-template <int NCH1, int NCH2>
+template <int NCH1, int NCH2, bool PACKED>
 cudaError_t launch_tile_t(const TileParams &p, uint32_t n_images, cudaStream_t stream) {
     static thread_local int configured_dev = -1;
     int dev = 0;
     cudaGetDevice(&dev);
     if (configured_dev != dev) {
-        cudaError_t e = cudaFuncSetAttribute(resize_tile_kernel<NCH1, NCH2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(resize_tile_kernel<NCH1, NCH2, PACKED>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
         if (e != cudaSuccess) return e;
         configured_dev = dev;
     }
@@ -269,7 +286,7 @@ cudaError_t launch_tile_t(const TileParams &p, uint32_t n_images, cudaStream_t s
         q.src = p.src + size_t(first) * p.src_img_bytes;
         q.dst = p.dst + size_t(first) * p.dst_img_bytes;
         const unsigned nz = n_images - first < 65535 ? n_images - first : 65535;
-        resize_tile_kernel<NCH1, NCH2><<<dim3(p.n_colblk + (p.need_fill ? 1u : 0u), p.n_rowblk, nz), kThreads, p.smem_bytes, stream>>>(q);
+        resize_tile_kernel<NCH1, NCH2, PACKED><<<dim3(p.n_colblk + (p.need_fill ? 1u : 0u), p.n_rowblk, nz), kThreads, p.smem_bytes, stream>>>(q);
         count_launch();
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;
@@ -282,7 +299,17 @@ cudaError_t launch_tile_t(const TileParams &p, uint32_t n_images, cudaStream_t s
 cudaError_t launch_resize_tile(const TileParams &p, uint32_t n_images, cudaStream_t stream) {
     if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
     if (p.n_rowblk == 0 || p.n_rowblk > 65535 || p.n_colblk == 0 || p.smem_bytes > 100 * 1024) return cudaErrorInvalidValue;
-#define SLIMG_TILE_CASE(A, B) if (p.nch1 == A && p.nch2 == B) return launch_tile_t<A, B>(p, n_images, stream);
+    if (p.packed) {
+        if (p.nch2 != 1) return cudaErrorInvalidValue;
+        switch (p.nch1) {
+            case 1: return launch_tile_t<1, 1, true>(p, n_images, stream);
+            case 2: return launch_tile_t<2, 1, true>(p, n_images, stream);
+            case 3: return launch_tile_t<3, 1, true>(p, n_images, stream);
+            case 4: return launch_tile_t<4, 1, true>(p, n_images, stream);
+        }
+        return cudaErrorInvalidValue;
+    }
+#define SLIMG_TILE_CASE(A, B) if (p.nch1 == A && p.nch2 == B) return launch_tile_t<A, B, false>(p, n_images, stream);
 #define SLIMG_TILE_ROW(A) SLIMG_TILE_CASE(A, 1) SLIMG_TILE_CASE(A, 2) SLIMG_TILE_CASE(A, 3) SLIMG_TILE_CASE(A, 4)
     SLIMG_TILE_ROW(1) SLIMG_TILE_ROW(2) SLIMG_TILE_ROW(3) SLIMG_TILE_ROW(4)
     return cudaErrorInvalidValue;

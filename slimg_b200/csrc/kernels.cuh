@@ -162,9 +162,10 @@ struct TileParams {
     const int32_t *rb_y0, *rb_rows;  // [n_rowblk]
     const int32_t *cb_src0, *cb_nblk;   // [n_colblk]
     const int32_t *tile_kb0;         // [n_colblk][tw / 8]
-    const uint32_t *b2;              // [n_colblk][tw / 8][nch2][2][32 lanes][2]
-    const float *cx;                 // [pw][4]
-    float s2[2][2];
+    const uint32_t *b2;              // [n_colblk][tw / 8][nch2][2][32 lanes][2]; packed: [n_colblk][tw / 8][3][32][2]
+    const int32_t *cxi;              // [pw][4] constant term + rounding half, units of 2^-sh2
+    int32_t sh2;                     // final right shift of the pass-2 integer sum
+    uint32_t packed;                 // 1: both limbs of the intermediate share one K = 32 (upscales)
     uint32_t pitch, pitch_v, rows_max, smem_bytes;
     uint32_t fw, fh, fox, foy;
     uint32_t fill_post, fill_pre_packed;
@@ -181,11 +182,11 @@ struct TcParams {
     uint32_t ry;                     // first row of the source rectangle
     uint32_t pw, ph;                 // columns / rows of the resize output that are kept
     int32_t nch2, sh1;               // 32-pixel chunks per pass-2 tile; right shift to the u16 intermediate
-    // vertical pass: blocks of 16 kept rows, chunks of 32 source-rectangle rows
+    // vertical pass: blocks of 8 kept rows, chunks of 32 source-rectangle rows
     uint32_t n_blocks, n_chunks, crec_words;
-    const uint32_t *crecs;           // [n_chunks][crec_words]: {first block, blocks, flags, chunk, ...12} + [blocks][2 digits][512 B] tiles
+    const uint32_t *crecs;           // [n_chunks][crec_words]: {first block, blocks, flags, chunk, ...12} + [blocks][512 B] tiles (N = 16: both digits)
     const int32_t *blk_c0, *blk_c1;  // [n_blocks] first / last chunk of a block
-    const int32_t *bias;             // [n_blocks*16][4]
+    const int32_t *bias;             // [n_blocks*8][4]
     // horizontal pass
     uint32_t n_strips, n_panels;
     const int32_t *strip_col0;       // [n_strips+1] first kept column of each strip
@@ -195,11 +196,12 @@ struct TcParams {
     const float *cx;                 // [pw][4] constant term per kept column and channel
     float s2[2][3];                  // scale of accumulator [limb][digit]
     // shared memory / TMEM geometry
-    uint32_t slots, slot_bytes, pitch_v, smem_bytes, nbuf;
+    uint32_t slots, slot_bytes, pitch_v, smem_bytes, nbuf, vbufs;
     // canvas
     uint32_t fw, fh, fox, foy;
     uint32_t fill_post, fill_pre_packed;
     uint32_t n_bands, need_fill, debug;
+    uint32_t pf_chunks;              // chunks prefetched into L2 beyond the ring (0 = off)
 };
 cudaError_t launch_resize_tc(const TcParams &p, uint32_t n_images, cudaStream_t stream);
 

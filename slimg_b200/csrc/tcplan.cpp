@@ -1,11 +1,13 @@
 // tcplan.cpp -- host-side plan of the tcgen05 resize pipeline (k2_tc.cu).
 //
 // Vertical pass (input-stationary): the source rectangle streams through shared memory in chunks of 32 rows.
-// For every chunk the plan lists the blocks of 16 kept output rows whose filter windows touch it, with one
-// weight tile per (block, digit): B[16 output rows][32 source rows] in s8, laid out as the canonical K-major,
-// no-swizzle operand of tcgen05.mma (8x16-byte core matrices).  The kernel multiplies the chunk (A operand,
-// M = 128 bytes of the row, MN-major, straight from the TMA-written ring) with each tile and accumulates in
-// TMEM; a block's accumulators are complete after its last chunk.
+// For every chunk the plan lists the blocks of 8 kept output rows whose filter windows touch it, with one weight
+// tile per block: B[N = 16: digit 0 of the 8 rows, digit 1 of the 8 rows][32 source rows] in s8, laid out as the
+// canonical K-major, no-swizzle operand of tcgen05.mma (8x16-byte core matrices).  The kernel multiplies the chunk
+// (A operand, M = 128 bytes of the row, MN-major, straight from the TMA-written ring) with each tile and accumulates
+// in TMEM; a block's accumulators are complete after its last chunk.  Blocks of 8 rows (round 1 had 16) are what the
+// horizontal pass consumes at a time, and halve the TMEM columns of a block: four accumulator buffers per panel
+// instead of two, so the MMA stream runs two blocks ahead of the epilogue.
 // Horizontal pass: as in vplan.cpp (mma.sync on the two u8 limbs of the 16-bit intermediate), pixels in
 // natural order.
 #include <algorithm>
@@ -23,6 +25,7 @@ constexpr int kMaxCh = 4;
 constexpr int kMaxPanels = 8;   // 8 panels x 2 accumulator buffers x 32 columns = all 512 TMEM columns
 constexpr size_t kSmemBudget = 227 * 1024 - 1024;
 constexpr uint32_t kTileBytes = 512, kLboB = 128, kSboB = 256;
+constexpr uint32_t kBlkRows = 8;   // kept output rows per accumulator block
 }  // namespace
 
 void build_tcplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, TcPlanHost &out) {
@@ -45,15 +48,15 @@ void build_tcplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, TcP
     if (Sy < kFrac + 2) return;
     out.sh1 = Sy - kFrac;
 
-    out.n_blocks = (g.ph + 15) / 16;
+    out.n_blocks = (g.ph + kBlkRows - 1) / kBlkRows;
     out.blk_c0.assign(out.n_blocks, 0);
     out.blk_c1.assign(out.n_blocks, 0);
-    out.bias.assign(size_t(out.n_blocks) * 16 * 4, 0);
+    out.bias.assign(size_t(out.n_blocks) * kBlkRows * 4, 0);
     int prev_c0 = 0, prev_c1 = 0;
     for (uint32_t b = 0; b < out.n_blocks; b++) {
         int lo = INT32_MAX, hi = -1;
-        for (uint32_t n = 0; n < 16 && b * 16 + n < g.ph; n++) {
-            const uint32_t o = g.py + b * 16 + n;
+        for (uint32_t n = 0; n < kBlkRows && b * kBlkRows + n < g.ph; n++) {
+            const uint32_t o = g.py + b * kBlkRows + n;
             lo = std::min(lo, ty.left[o]);
             hi = std::max(hi, ty.left[o] + ty.count[o]);
         }
@@ -74,7 +77,7 @@ void build_tcplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, TcP
             out.nb_max = std::max<uint32_t>(out.nb_max, uint32_t(cnt[c]));
         }
     if (out.nb_max == 0 || out.nb_max > 4) return;
-    out.crec_words = 16 + out.nb_max * ndig * (kTileBytes / 4);
+    out.crec_words = 16 + out.nb_max * (kTileBytes / 4);
     out.crecs.assign(size_t(out.n_chunks) * out.crec_words, 0u);
     for (uint32_t c = 0; c < out.n_chunks; c++) {
         uint32_t *r = &out.crecs[size_t(c) * out.crec_words];
@@ -89,7 +92,7 @@ void build_tcplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, TcP
     }
     std::vector<int64_t> q;
     for (uint32_t i = 0; i < g.ph; i++) {
-        const uint32_t o = g.py + i, b = i / 16, n = i % 16;
+        const uint32_t o = g.py + i, b = i / kBlkRows, n = i % kBlkRows;
         const int cntw = ty.count[o];
         quantise(&ty.w[size_t(o) * ty.max_taps], cntw, Sy, q);
         int64_t pos = 0, neg = 0;
@@ -101,9 +104,9 @@ void build_tcplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, TcP
             uint32_t *r = &out.crecs[size_t(c) * out.crec_words];
             const int bi = int(b) - int(r[0]);
             if (bi < 0 || bi >= int(r[1])) return;
-            for (int l = 0; l < ndig; l++) {
-                uint8_t *tile = reinterpret_cast<uint8_t *>(r + 16) + size_t(bi * ndig + l) * kTileBytes;
-                tile[(kk / 16) * kLboB + (n / 8) * kSboB + (n % 8) * 16 + (kk % 16)] = uint8_t(d[l]);
+            for (int l = 0; l < ndig; l++) {      // N index of the tile = 8 * digit + row
+                uint8_t *tile = reinterpret_cast<uint8_t *>(r + 16) + size_t(bi) * kTileBytes;
+                tile[(kk / 16) * kLboB + uint32_t(l) * kSboB + n * 16 + (kk % 16)] = uint8_t(d[l]);
             }
         }
         // bias = fill term + offset + rounding half; the 16-bit intermediate must stay in range
@@ -154,8 +157,8 @@ void build_tcplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, TcP
     if (cols == 0) return;
     out.n_panels = npan;
     out.n_strips = (g.pw + cols - 1) / cols;
-    out.nbuf = std::min<uint32_t>(4, 512 / (32 * npan));
-    if (out.nbuf < 2) return;
+    out.nbuf = std::min<uint32_t>(8, 512 / (16 * npan));      // accumulator buffers: 16 TMEM columns per (panel, block)
+    if (out.nbuf < out.nb_max + 1) return;                     // every block a chunk touches, plus one being drained
 
     const int64_t nblk = int64_t(npan) * 8;                     // 16-byte (4-pixel) blocks of a V row
     out.strip_col0.assign(out.n_strips + 1, 0);
@@ -216,12 +219,14 @@ void build_tcplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, TcP
     }
 
     // ---------------- shared memory ----------------
-    int64_t qv = (nblk + 3 + 3) / 4;                            // 16-byte units per V row = odd >= (nblk*4 + 12) / 16
+    int64_t qv = (nblk + 6 + 3) / 4;                            // 16-byte units per V row = odd >= (nblk*4 + 24) / 16 (2-word channel skew)
     if (qv % 2 == 0) qv++;
     out.pitch_v = uint32_t(qv * 16);
     out.slot_bytes = npan * 4096;
     const size_t crec_bytes = size_t(out.crec_words) * 4;
-    const size_t fixed = size_t(4) * 32 * out.pitch_v + 1024;
+    const char *vb_env = std::getenv("SLIMG_B200_TC_VBUFS");
+    out.vbufs = vb_env ? uint32_t(std::max(2, std::min(4, std::atoi(vb_env)))) : 3u;
+    const size_t fixed = size_t(2 * out.vbufs) * 32 * out.pitch_v + 1024;
     const char *slots_env = std::getenv("SLIMG_B200_TC_SLOTS");
     uint32_t slots = slots_env ? uint32_t(std::atoi(slots_env)) : 12;
     while (slots > 2 && slots * (out.slot_bytes + crec_bytes) + fixed > kSmemBudget) slots--;

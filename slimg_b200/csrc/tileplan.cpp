@@ -11,26 +11,30 @@
 // band structure at all.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 
 #include "host.h"
 #include "kernels.cuh"
 
+#define TILE_FAIL(code) do { if (std::getenv("SLIMG_B200_DEBUG")) std::fprintf(stderr, "[slimg_b200] tileplan rejects the geometry at check %d\n", code); return; } while (0)
+
 namespace slimg {
 
 namespace {
-constexpr int kFrac = 7, kOffset = 64, kMaxCh = 4;
+constexpr int kFrac = 7, kMaxCh = 4;
+constexpr int kOffset = 96;   // added to the 16-bit intermediate so undershoot stays >= 0: at some upscale phases the negative taps sum to -0.27 (x 255 = 69)
 const int kPerm[4] = {0, 2, 1, 3};   // k-slot -> pixel inside a 4-pixel block (pass-1 epilogue of k2_vfirst.cu / k2_tile.cu)
 }
 
 void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, bool forced, TilePlanHost &out) {
     out = TilePlanHost();
     const int ndig = 2;
-    if (!g.has_resize) return;
-    if (g.sw % 4 != 0 || g.sw < 4) return;           // 16-byte aligned source rows
-    if (g.pw == 0 || g.ph == 0 || g.rw == 0 || g.rh == 0) return;
+    if (!g.has_resize) TILE_FAIL(1);
+    if (g.sw % 4 != 0 || g.sw < 4) TILE_FAIL(2);           // 16-byte aligned source rows
+    if (g.pw == 0 || g.ph == 0 || g.rw == 0 || g.rh == 0) TILE_FAIL(3);
     const double ry = double(g.vh) / double(g.Rh), rx = double(g.vw) / double(g.Rw);
-    if (!forced && (ry > 3.5 || rx > 3.5)) return;   // larger downscales: the banded pipelines stream better
+    if (!forced && (ry > 3.5 || rx > 3.5)) TILE_FAIL(4);   // larger downscales: the banded pipelines stream better
 
     // output tile: as large as the footprint allows (a bigger tile re-reads less halo and amortises the weights)
     const bool up = ry <= 1.0 && rx <= 1.0;
@@ -45,9 +49,9 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
         const uint32_t o = g.py + i;
         for (int k = 0; k < ty.count[o]; k++) maxw_y = std::max(maxw_y, std::fabs(ty.w[size_t(o) * ty.max_taps + k]));
     }
-    if (!(maxw_y > 0.0f)) return;
+    if (!(maxw_y > 0.0f)) TILE_FAIL(5);
     const int Sy = pick_scale(maxw_y, ndig);
-    if (Sy < kFrac + 2) return;
+    if (Sy < kFrac + 2) TILE_FAIL(6);
     out.sh1 = Sy - kFrac;
     const uint32_t n_groups = (g.ph + 7) / 8;
     std::vector<int32_t> a0(n_groups, 0), need(n_groups, 0), nch(n_groups, 0);
@@ -64,7 +68,7 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
         a0[j] = lo; need[j] = hi; nch[j] = (hi - lo + 31) / 32;
         out.nch1 = std::max(out.nch1, nch[j]);
     }
-    if (out.nch1 == 0 || out.nch1 > kMaxCh) return;
+    if (out.nch1 == 0 || out.nch1 > kMaxCh) TILE_FAIL(7);
     // group record: {a0, need, chunks, -, ..., bias[8][4] from word 8} + [nch1][2 digits][32 lanes][2] weight fragments
     out.rec_words = 64 + uint32_t(out.nch1) * ndig * 64;
     out.recs.assign(size_t(n_groups) * out.rec_words, 0u);
@@ -82,7 +86,7 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
             for (int k = 0; k < cnt; k++) {
                 (q[k] > 0 ? pos : neg) += q[k];
                 int8_t d[3];
-                if (!split_digits(q[k], ndig, d)) return;
+                if (!split_digits(q[k], ndig, d)) TILE_FAIL(8);
                 const int row = ty.left[o] + k - a0[j];
                 for (int l = 0; l < ndig; l++) put_b(r + 64 + ((row / 32) * ndig + l) * 64, row % 32, int(n), d[l]);
             }
@@ -91,7 +95,7 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
                 const int64_t fillterm = std::llround(double(g.fill_pre[c]) * double(ty.fillw[o]) * std::ldexp(1.0, Sy));
                 const int64_t bias = fillterm + (int64_t(kOffset) << Sy) + (int64_t(1) << (out.sh1 - 1));
                 const int64_t lo_x = 255 * neg + bias, hi_x = 255 * pos + bias;
-                if (lo_x < 0 || (hi_x >> out.sh1) > 65535 || hi_x > INT32_MAX || bias > INT32_MAX) return;
+                if (lo_x < 0 || (hi_x >> out.sh1) > 65535 || hi_x > INT32_MAX || bias > INT32_MAX) TILE_FAIL(9);
                 r[8 + n * 4 + c] = uint32_t(int32_t(bias));
             }
         }
@@ -110,7 +114,7 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
         out.rb_y0[b] = lo; out.rb_rows[b] = hi - lo;
         out.rows_max = std::max<uint32_t>(out.rows_max, uint32_t(hi - lo));
     }
-    if (out.rows_max == 0) return;
+    if (out.rows_max == 0) TILE_FAIL(10);
 
     // ---------------- horizontal pass: column blocks of tw kept columns, tiles of 8 ----------------
     float maxw_x = 0.0f;
@@ -118,11 +122,12 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
         const uint32_t o = g.px + j;
         for (int k = 0; k < tx.count[o]; k++) maxw_x = std::max(maxw_x, std::fabs(tx.w[size_t(o) * tx.max_taps + k]));
     }
-    if (!(maxw_x > 0.0f)) return;
+    if (!(maxw_x > 0.0f)) TILE_FAIL(11);
     const int Sx = pick_scale(maxw_x, ndig);
-    if (Sx < 8) return;
-    for (int l = 0; l < 2; l++)
-        for (int d = 0; d < 2; d++) out.s2[l][d] = float(std::ldexp(1.0, 8 * l + 8 * d - Sx - kFrac));
+    if (Sx < 10) TILE_FAIL(12);
+    // pass-2 result in integers: t = (acc[lo][d0] >> 8) + acc[lo][d1] + acc[hi][d0] + (acc[hi][d1] << 8) + cxi is the output
+    // in units of 2^-(Sx + kFrac - 8); the byte is t >> sh2 (round-half-up folded into cxi), saturated
+    out.sh2 = Sx + kFrac - 8;
     auto span_of = [&](uint32_t c0, uint32_t c1, int64_t &lo, int64_t &hi) {
         lo = INT64_MAX; hi = -1;
         for (uint32_t j = c0; j < c1; j++) {
@@ -137,8 +142,9 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
     out.cb_src0.assign(out.n_colblk, 0);
     out.cb_nblk.assign(out.n_colblk, 0);
     out.tile_kb0.assign(size_t(out.n_colblk) * tiles_per_blk, 0);
-    out.cx.assign(size_t(g.pw) * 4, 0.0f);
+    out.cxi.assign(size_t(g.pw) * 4, 0);
     int64_t max_nblk = 1;
+    bool packable = true;                            // every tile's taps inside 16 staged pixels: both limbs share one K = 32
     for (uint32_t s = 0; s < out.n_colblk; s++) {
         const uint32_t c0 = s * tw, c1 = std::min(g.pw, c0 + tw);
         int64_t lo, hi;
@@ -157,9 +163,10 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
             const int64_t kb0 = (tlo - s0) / 4;
             out.tile_kb0[s * tiles_per_blk + t] = int32_t(kb0);
             out.nch2 = std::max(out.nch2, int((thi - s0 - kb0 * 4 + 31) / 32));
+            if (thi - s0 - kb0 * 4 > 16) packable = false;
         }
     }
-    if (out.nch2 == 0 || out.nch2 > kMaxCh) return;
+    if (out.nch2 == 0 || out.nch2 > kMaxCh) TILE_FAIL(13);
     // every tile runs nch2 chunks: V rows are allocated so that kb0 + 8 * nch2 words always exist
     out.v_words = uint32_t(std::max<int64_t>(max_nblk, 0));
     for (uint32_t s = 0; s < out.n_colblk; s++)
@@ -175,8 +182,10 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
         out.pitch_v = uint32_t(qv * 16);
         out.smem_bytes = out.rows_max * out.pitch + (th / 8) * 2u * 32u * out.pitch_v + 16;
     }
-    if (out.smem_bytes > 100 * 1024) return;         // two CTAs per SM at least
-    out.b2.assign(size_t(out.n_colblk) * tiles_per_blk * out.nch2 * ndig * 64, 0u);
+    if (out.smem_bytes > 100 * 1024) TILE_FAIL(14);         // two CTAs per SM at least
+    out.packed = packable && out.nch2 == 1 && !std::getenv("SLIMG_B200_TILE_NOPACK");
+    // packed: per tile three fragments -- A [w0 | 0], B [w1 | w0], C [0 | w1] over K = [16 low-limb px | 16 high-limb px]
+    out.b2.assign(size_t(out.n_colblk) * tiles_per_blk * (out.packed ? 3 : out.nch2 * ndig) * 64, 0u);
     for (uint32_t s = 0; s < out.n_colblk; s++) {
         const uint32_t c0 = s * tw, c1 = std::min(g.pw, c0 + tw);
         const int64_t s0 = out.cb_src0[s];
@@ -189,20 +198,29 @@ void build_tileplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, b
             for (int k = 0; k < cnt; k++) {
                 sum_q += q[k];
                 int8_t d[3];
-                if (!split_digits(q[k], ndig, d)) return;
+                if (!split_digits(q[k], ndig, d)) TILE_FAIL(15);
                 const int64_t rel = int64_t(g.rx) + tx.left[o] + k - s0;      // pixel inside the staged span
                 const int64_t blk = rel / 4 - kb0;
                 int slot = 0;
                 for (int z = 0; z < 4; z++) if (kPerm[z] == int(rel % 4)) slot = z;
                 const int64_t kk = blk * 4 + slot;                            // k index inside the tile's chunks
-                if (kk < 0 || kk >= 32 * out.nch2) return;
-                for (int l = 0; l < ndig; l++)
-                    put_b(&out.b2[(((size_t(s) * tiles_per_blk + t) * out.nch2 + size_t(kk / 32)) * ndig + l) * 64], int(kk % 32), int(n), d[l]);
+                if (kk < 0 || kk >= 32 * out.nch2) TILE_FAIL(16);
+                if (out.packed) {
+                    uint32_t *f = &out.b2[(size_t(s) * tiles_per_blk + t) * 3 * 64];
+                    put_b(f, int(kk), int(n), d[0]);                                        // low limb x digit 0
+                    put_b(f + 64, int(kk), int(n), d[1]); put_b(f + 64, 16 + int(kk), int(n), d[0]);
+                    put_b(f + 128, 16 + int(kk), int(n), d[1]);                             // high limb x digit 1
+                } else
+                    for (int l = 0; l < ndig; l++)
+                        put_b(&out.b2[(((size_t(s) * tiles_per_blk + t) * out.nch2 + size_t(kk / 32)) * ndig + l) * 64], int(kk % 32), int(n), d[l]);
             }
-            // constant term: fill taps of the horizontal pass minus the intermediate's offset
+            // constant term: fill taps of the horizontal pass minus the intermediate's offset, plus the rounding half,
+            // in units of 2^-sh2
             const double off = -double(kOffset) * double(sum_q) * std::ldexp(1.0, -Sx);
-            for (int c = 0; c < 4; c++)
-                out.cx[size_t(j) * 4 + c] = float(off + double(g.fill_pre[c]) * double(tx.fillw[o]));
+            for (int c = 0; c < 4; c++) {
+                const double cxv = off + double(g.fill_pre[c]) * double(tx.fillw[o]);
+                out.cxi[size_t(j) * 4 + c] = int32_t(std::llround(cxv * std::ldexp(1.0, out.sh2))) + (int32_t(1) << (out.sh2 - 1));
+            }
         }
     }
     for (uint32_t i = 0; i < g.ph; i++)

@@ -30,6 +30,23 @@ def pytest_collection_modifyitems(config, items):
             item.add_marker(skip)
 
 
+# ---- parity report: every resize comparison of the GPU session (max / mean abs error, kernel that served it) -----------
+PARITY_REPORT = []
+
+
+@pytest.fixture(scope="session", autouse=True)
+def _write_parity_report():
+    yield
+    if not PARITY_REPORT:
+        return
+    out = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    with open(os.path.join(out, "parity_report.txt"), "w") as fh:
+        fh.write("# case | input kind | out WxH | max abs err | mean abs err | kernel path\n")
+        for label, kind, w, h, mx, mean, path in PARITY_REPORT:
+            fh.write(f"{label} | {kind} | {w}x{h} | {mx} | {mean:.6f} | {path}\n")
+
+
 # ---- synthetic inputs ------------------------------------------------------------
 
 def gradient_image(w: int, h: int) -> np.ndarray:
