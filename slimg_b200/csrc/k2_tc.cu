@@ -25,6 +25,7 @@
 #include <cuda.h>
 
 #include <algorithm>
+#include <cstdio>
 
 #include "kernels.cuh"
 
@@ -101,6 +102,11 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, int (&r)[16]) {
                  : "r"(taddr));
 }
 // same box as tma_load_2d, only as far as L2: the DRAM part of the latency is paid before the chunk gets a ring slot
+// all panels of a chunk in ONE instruction: a 3-D view of the source (x, row, panel) whose third dimension steps 128 bytes
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, int c0, int c1, int c2, uint64_t *bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *map, int c0, int c1) {
     asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
 }
@@ -164,7 +170,8 @@ __device__ __forceinline__ void fill_span(uint32_t *row, int x0, int x1, uint32_
 }
 
 template <int NCH2>
-__global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap) {
+__global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap tmap,
+                                                                const __grid_constant__ CUtensorMap tmap3) {
     constexpr int NDIG = 2;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -237,9 +244,11 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
             if (lane == 0) mbar_arrive_expect_tx(&tail.full[slot], step_bytes);
             __syncwarp();
             const int c = c_lo + s;
-            if (lane < npan)
+            if (p.debug & 16u) {           // EXPERIMENT: one 3-D box for the whole chunk
+                if (lane == 0) tma_load_3d(ring + uint32_t(slot) * p.slot_bytes, &tmap3, tx0, tr0 + c * 32, 0, &tail.full[slot]);
+            } else if (lane < npan)
                 tma_load_2d(ring + uint32_t(slot) * p.slot_bytes + uint32_t(lane) * 4096u, &tmap, tx0 + lane * 16, tr0 + ((p.debug & 4u) ? (c & 7) : c) * 32, &tail.full[slot]);
-            else if (lane == 31)
+            if (lane == 31)
                 bulk_g2s(crec_base + uint32_t(slot) * crec_bytes, p.crecs + size_t(c) * p.crec_words, crec_bytes, &tail.full[slot]);
             if (pf) prefetch_to(min(n_steps, s + 1 + slots + pf));
         }
@@ -458,6 +467,20 @@ static cudaError_t make_panel_map(const TcParams &p, const uint8_t *src, uint32_
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
+// EXPERIMENT: (x, row, panel) view, panel stride 128 bytes, box = 128 B x 32 rows x n_panels
+static cudaError_t make_panel_map3(const TcParams &p, const uint8_t *src, uint32_t n_images, CUtensorMap &map) {
+    EncodeTiledFn enc = tc_encode_tiled_fn();
+    if (!enc) return cudaErrorNotSupported;
+    const cuuint64_t dims[3] = {cuuint64_t(p.sw) / 2, cuuint64_t(p.sh) * n_images, cuuint64_t(p.n_panels)};
+    const cuuint64_t strides[2] = {cuuint64_t(p.sw) * 4, 128};
+    const cuuint32_t box[3] = {16, 32, p.n_panels};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, const_cast<uint8_t *>(src), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
 template <int NCH2>
 static cudaError_t launch_tc_t(const TcParams &p, uint32_t n_images, cudaStream_t stream) {
     static thread_local int configured_dev = -1;
@@ -476,6 +499,14 @@ static cudaError_t launch_tc_t(const TcParams &p, uint32_t n_images, cudaStream_
         CUtensorMap map;
         cudaError_t e = make_panel_map(q, q.src, nz, map);
         if (e != cudaSuccess) return e;
+        CUtensorMap map3 = map;
+        if (q.debug & 16u) {
+            if (make_panel_map3(q, q.src, nz, map3) != cudaSuccess) {
+                static bool said = false;
+                if (!said) { std::fprintf(stderr, "[slimg_b200] 3-D panel map rejected by cuTensorMapEncodeTiled\n"); said = true; }
+                q.debug &= ~16u;
+            }
+        }
         // fill CTAs: one per ~2 MB of canvas that is not computed (at least one when anything is), spread over the bands
         unsigned nfill = 0;
         if (p.need_fill) {
@@ -483,7 +514,7 @@ static cudaError_t launch_tc_t(const TcParams &p, uint32_t n_images, cudaStream_
             nfill = unsigned(std::min<uint64_t>(32, 1 + bytes / (2u << 20)));
             nfill = (nfill + p.n_bands - 1) / p.n_bands;
         }
-        resize_tc_kernel<NCH2><<<dim3(p.n_strips + nfill, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q, map);
+        resize_tc_kernel<NCH2><<<dim3(p.n_strips + nfill, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q, map, map3);
         count_launch();
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;

@@ -65,8 +65,14 @@ def test_default_paths_are_the_intended_kernels(monkeypatch):
     assert ll.last_resize_path() in (ll.PATH_VFIRST, ll.PATH_TC)          # the integer tensor pipeline
     ll.crop(_ll_img(img), ll.CropMode.ASPECT_RATIO(1, 1))
     assert ll.last_resize_path() == ll.PATH_REMAP
-    ll.resize(_ll_img(noise_image(64, 64, 1)), ll.ResizeMode.EXACT(200, 20))      # up on x, down on y
-    assert ll.last_resize_path() == ll.PATH_GENERIC
+    ll.resize(_ll_img(noise_image(64, 64, 1)), ll.ResizeMode.EXACT(200, 20))      # up on x, down on y: one tile holds the footprint
+    assert ll.last_resize_path() == ll.PATH_TILE
+    ll.resize(_ll_img(noise_image(1024, 1024, 1)), ll.ResizeMode.SCALE(4.0))       # BASELINE C4b's shape
+    assert ll.last_resize_path() == ll.PATH_TILE
+    ll.resize(_ll_img(noise_image(63, 64, 1)), ll.ResizeMode.EXACT(200, 20))      # rows that are not 16-byte aligned: the f32 kernel
+    assert ll.last_resize_path() in (ll.PATH_GENERIC, ll.PATH_FEWTAPS)
+    ll.resize(_ll_img(noise_image(4000, 3000, 1)), ll.ResizeMode.FIT(400, 400))   # 10x: bands beyond the V-first ring
+    assert ll.last_resize_path() == ll.PATH_HFIRST
     before = ll.path_launches(ll.PATH_REMAP)
     ll.extend(_ll_img(img), ll.ExtendMode.ASPECT_RATIO(1, 1), ll.FillColor.TRANSPARENT())
     assert ll.path_launches(ll.PATH_REMAP) == before + 1
@@ -224,7 +230,7 @@ def test_convert_jpeg_file_is_byte_identical_to_the_cpu_encoder(monkeypatch):
                                    fill=WHITE, resize_mode=oracle.ResizeMode.width(160)), "noise", "convert jpeg pixels")
         # the reference's own settings (progressive + optimised tables, codec/jpeg.rs:61-63): a valid JPEG of that size
         prog = hc.jpeg_from_coefficients(ll.pipeline_jpeg(_ll_img(img), opts._to_c(), list(ql), list(qc)))
-        assert prog[:2] == b"\\xff\\xd8" and oracle.ref_jpeg_decode(prog, 160, 160).shape == (160, 160, 4)
+        assert prog[:2] == bytes([0xff, 0xd8]) and oracle.ref_jpeg_decode(prog, 160, 160).shape == (160, 160, 4)
         assert np.array_equal(oracle.ref_jpeg_decode(prog, 160, 160), oracle.ref_jpeg_decode(res.data, 160, 160))
     finally:
         ll.register_jpeg_entropy_coder(lambda coefs, q: hc.jpeg_from_coefficients(coefs))      # back to the reference's settings

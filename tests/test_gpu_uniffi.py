@@ -86,3 +86,42 @@ def test_convert_runs_the_pipeline_then_the_encoder_hook():
     with pytest.raises(U.UniffiError) as e:                  # no encoder linked -> SlimgError::Encode, after the pixel stages ran
         U.call("convert", _img(noise_image(16, 16)), U.w_options(1, 80))
     assert e.value.variant == "Encode"
+
+
+@pytest.mark.skipif(oracle.ref_lib() is None, reason="oracle/_ref not built")
+def test_convert_jpeg_through_the_coefficient_hook():
+    """Format::Jpeg with a coefficient-taking entropy coder installed (include/slimg_uniffi.h): convert runs
+    crop -> extend -> resize -> JPEG front end on the device and hands the planes to libjpeg-turbo's
+    jpeg_write_coefficients (slimg_b200/jpeg_handoff) -- the file equals the full CPU encoder's, byte for byte."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(U._build.LIB_PATH)), "libslimg_jpeg_handoff.so")
+    if not os.path.exists(path):
+        pytest.skip("libslimg_jpeg_handoff.so not built")
+    handoff = C.CDLL(path)
+    hook = C.cast(handoff.slimg_jpeg_handoff_hook, C.c_void_p)
+    L = U.lib()
+    L.slimg_b200_set_jpeg_coefficient_hook.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint32]
+    L.slimg_b200_kernel_launches.restype = C.c_uint64
+    # user = flags + 1: baseline scan script, optimised Huffman tables (what oracle.ref_jpeg_encode uses); Annex-K tables
+    L.slimg_b200_set_jpeg_coefficient_hook(hook, C.c_void_p(2 + 1), 0, 0)
+    try:
+        a = noise_image(401, 299, 71)
+        ql, qc = oracle.ref_jpeg_quant_table(70, 0), oracle.ref_jpeg_quant_table(70, 1)
+        opts = U.w_options(1, 70, crop=U.w_crop("region", 7, 9, 300, 200), extend=U.w_extend("size", 333, 257), fill=U.w_fill((10, 200, 30, 128)))
+        before = L.slimg_b200_kernel_launches()
+        data, fmt, w, h = U.r_pipeline_result(U.call("convert", _img(a), opts))
+        assert L.slimg_b200_kernel_launches() - before == 2          # K1 + K3; no pixel download in between
+        want_px = oracle.pipeline(a, crop_mode=oracle.CropMode.region(7, 9, 300, 200), extend_mode=oracle.ExtendMode.size(333, 257),
+                                  fill=(10, 200, 30, 128))
+        assert (fmt, w, h) == (1, 333, 257) and data == oracle.ref_jpeg_encode(want_px, ql, qc)
+        # with a resize in front: the file is a JPEG of the post-resize size (pipeline.rs:97-102) that decodes to the oracle's
+        # pixels within JPEG loss
+        opts = U.w_options(1, 90, resize=U.w_resize("width", 160), crop=U.w_crop("aspect", 16, 9), extend=U.w_extend("aspect", 1, 1))
+        data, fmt, w, h = U.r_pipeline_result(U.call("convert", _img(gradient := np.ascontiguousarray(np.tile(np.arange(400, dtype=np.uint8)[None, :, None] // 2, (300, 1, 4)))), opts))
+        assert (fmt, w, h) == (1, 160, 160) and data[:2] == b"\xff\xd8"
+        dec = oracle.ref_jpeg_decode(data, 160, 160)
+        want = oracle.pipeline(gradient, crop_mode=oracle.CropMode.aspect_ratio(16, 9), extend_mode=oracle.ExtendMode.aspect_ratio(1, 1),
+                               fill=(255, 255, 255, 255), resize_mode=oracle.ResizeMode.width(160))
+        assert np.abs(dec[..., :3].astype(int) - want[..., :3].astype(int)).mean() < 3.0
+    finally:
+        L.slimg_b200_set_jpeg_coefficient_hook(None, None, 1, 0)
