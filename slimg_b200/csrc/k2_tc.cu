@@ -64,6 +64,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         if (!ok && ++spins > kSpinLimit) asm volatile("trap;");
     } while (!ok);
 }
+// instrumented wait (debug & 32): cycles spent in the wait are added to `acc`
+__device__ __forceinline__ void mbar_wait_t(uint64_t *bar, uint32_t parity, bool timed, unsigned long long &acc) {
+    if (!timed) { mbar_wait(bar, parity); return; }
+    const long long t0 = clock64();
+    mbar_wait(bar, parity);
+    acc += (unsigned long long)(clock64() - t0);
+}
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
@@ -221,6 +228,9 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tail.tmem_base;
+    const bool timed = (p.debug & 32u) != 0 && p.stats != nullptr;
+    unsigned long long w0 = 0, w1 = 0;
+    const long long t_start = timed ? clock64() : 0;
 
     if (warp == kProducerWarp) {
         // ================= producer: one box per panel + the chunk record, per ring slot =================
@@ -240,7 +250,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
 #pragma unroll 1
         for (int s = 0; s < n_steps; s++) {
             const int slot = s % slots;
-            if (s >= slots) mbar_wait(&tail.empty[slot], uint32_t(s / slots - 1) & 1u);
+            if (s >= slots) mbar_wait_t(&tail.empty[slot], uint32_t(s / slots - 1) & 1u, timed, w0);
             if (lane == 0) mbar_arrive_expect_tx(&tail.full[slot], step_bytes);
             __syncwarp();
             const int c = c_lo + s;
@@ -260,7 +270,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
 #pragma unroll 1
             for (int s = 0; s < n_steps; s++) {
                 const int slot = s % slots;
-                mbar_wait(&tail.full[slot], uint32_t(s / slots) & 1u);
+                mbar_wait_t(&tail.full[slot], uint32_t(s / slots) & 1u, timed, w0);
                 tc_fence_after();
                 const uint32_t *rec = reinterpret_cast<const uint32_t *>(smem_raw + size_t(slots) * p.slot_bytes + size_t(slot) * crec_bytes);
                 const int first = int(rec[0]), nb = int(rec[1]);
@@ -274,7 +284,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
                     const int use = (b - blk0) / nbuf, abuf = (b - blk0) - use * nbuf;
                     const bool starts = (flags >> i) & 1u, ends = (flags >> (8 + i)) & 1u;
                     if (starts) {                                // the buffer's previous block must have been read out
-                        mbar_wait(&tail.acc_empty[abuf], (uint32_t(use) & 1u) ^ 1u);
+                        mbar_wait_t(&tail.acc_empty[abuf], (uint32_t(use) & 1u) ^ 1u, timed, w1);
                         tc_fence_after();
                     }
                     const uint32_t acc = starts ? 0u : 1u;
@@ -293,6 +303,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
                 }
                 umma_commit(&tail.empty[slot]);                  // the slot is free once everything issued so far retires
             }
+            if (timed) { atomicAdd(p.stats + 1, w0); atomicAdd(p.stats + 2, w1); w0 = w1 = 0; }
         }
         __syncwarp();
     } else if (warp >= kEpiWarp0 && warp < kEpiWarp0 + kEpiWarps) {
@@ -316,12 +327,12 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
             int bias[8];
 #pragma unroll
             for (int r = 0; r < 8; r++) bias[r] = __ldg(p.bias + (size_t(blk0 + bi) * 8 + r) * 4 + ch);
-            mbar_wait(&tail.acc_full[abuf], uint32_t(use) & 1u);
+            mbar_wait_t(&tail.acc_full[abuf], uint32_t(use) & 1u, timed, w0);
             tc_fence_after();
             int cur[16], nxt[16];
             const uint32_t t0 = tmem + lane_addr + uint32_t(abuf) * 16u;
             if (pn0 < pn1 && !(p.debug & 8u)) tmem_ld16(t0 + uint32_t(pn0 * nbuf) * 16u, cur);
-            mbar_wait(&tail.v_empty[vb], (uint32_t(vuse) & 1u) ^ 1u);
+            mbar_wait_t(&tail.v_empty[vb], (uint32_t(vuse) & 1u) ^ 1u, timed, w1);
             const uint32_t vrow = v0 + uint32_t(vb) * 2u * vplane;
 #pragma unroll 1
             for (int pn = pn0; pn < ((p.debug & 8u) ? pn0 : pn1); pn++) {
@@ -381,7 +392,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
         for (int gi = 0; gi < n_blk; gi++) {
             const int vuse = gi / nvb, buf = gi - vuse * nvb;
             const uint32_t vbuf = vbase + uint32_t(buf) * 2u * vplane;
-            mbar_wait(&tail.v_full[buf], uint32_t(vuse) & 1u);
+            mbar_wait_t(&tail.v_full[buf], uint32_t(vuse) & 1u, timed, w0);
             if (p.debug & 2u) { __syncwarp(); if (lane == 0) mbar_arrive(&tail.v_empty[buf]); continue; }
 
             int acc[2][2][NDIG][4];            // [channel pair][limb][digit]
@@ -426,6 +437,15 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
                 if (ocol + 1 < col1) o[1] = px[1];
             }
         }
+    }
+    if (timed && lane == 0) {
+        // 0: producer waits for a free slot; 1 / 2: MMA thread waits for a chunk / a free accumulator; 3 / 4: epilogue warps wait
+        // for a finished block / a free V buffer; 5: pass-2 warps wait for V; 6: role lifetime (per role thread); 7..: counts
+        const unsigned long long life = (unsigned long long)(clock64() - t_start);
+        if (warp == kProducerWarp) { atomicAdd(p.stats + 0, w0); atomicAdd(p.stats + 6, life); atomicAdd(p.stats + 7, 1ull); }
+        else if (warp == kMmaWarp) { atomicAdd(p.stats + 1, w0); atomicAdd(p.stats + 2, w1); }
+        else if (warp >= kEpiWarp0 && warp < kEpiWarp0 + kEpiWarps) { atomicAdd(p.stats + 3, w0); atomicAdd(p.stats + 4, w1); atomicAdd(p.stats + 8, life); atomicAdd(p.stats + 9, 1ull); }
+        else if (warp < ntile) { atomicAdd(p.stats + 5, w0); atomicAdd(p.stats + 10, life); atomicAdd(p.stats + 11, 1ull); }
     }
     tc_fence_before();
     __syncthreads();
@@ -514,7 +534,23 @@ static cudaError_t launch_tc_t(const TcParams &p, uint32_t n_images, cudaStream_
             nfill = unsigned(std::min<uint64_t>(32, 1 + bytes / (2u << 20)));
             nfill = (nfill + p.n_bands - 1) / p.n_bands;
         }
+        static unsigned long long *d_stats = nullptr;
+        if (q.debug & 32u) {
+            if (!d_stats) cudaMalloc((void **)&d_stats, 16 * sizeof(unsigned long long));
+            cudaMemsetAsync(d_stats, 0, 16 * sizeof(unsigned long long), stream);
+            q.stats = d_stats;
+        } else q.stats = nullptr;
         resize_tc_kernel<NCH2><<<dim3(p.n_strips + nfill, p.n_bands, nz), kThreads, p.smem_bytes, stream>>>(q, map, map3);
+        if (q.debug & 32u) {
+            unsigned long long h[16];
+            cudaMemcpyAsync(h, d_stats, sizeof h, cudaMemcpyDeviceToHost, stream);
+            cudaStreamSynchronize(stream);
+            const double n = double(h[7] ? h[7] : 1);
+            std::fprintf(stderr, "[slimg_b200] tc waits per strip CTA (kclk): producer/free-slot %.1f | mma/chunk %.1f mma/free-acc %.1f | epi/block-done %.1f epi/free-V %.1f (per warp) | "
+                                 "pass2/V %.1f (per warp) | lifetime producer %.1f epi %.1f pass2 %.1f | CTAs %.0f\n",
+                         h[0] / n / 1e3, h[1] / n / 1e3, h[2] / n / 1e3, h[3] / double(h[9] ? h[9] : 1) / 1e3, h[4] / double(h[9] ? h[9] : 1) / 1e3,
+                         h[5] / double(h[11] ? h[11] : 1) / 1e3, h[6] / n / 1e3, h[8] / double(h[9] ? h[9] : 1) / 1e3, h[10] / double(h[11] ? h[11] : 1) / 1e3, n);
+        }
         count_launch();
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;

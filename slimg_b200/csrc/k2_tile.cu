@@ -50,6 +50,12 @@ __device__ __forceinline__ void imma_c(int (&d)[4], const uint32_t (&a)[4], cons
                  : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "r"(c0), "r"(c1));
 }
+// C = {c0, c1} for fragment row g (columns 2t, 2t+1) and {c2, c3} for row g + 8
+__device__ __forceinline__ void imma_c4(int (&d)[4], const uint32_t (&a)[4], const uint2 &b, int c0, int c1, int c2, int c3) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "r"(c0), "r"(c1), "r"(c2), "r"(c3));
+}
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
     uint32_t v;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
@@ -77,7 +83,7 @@ __device__ __forceinline__ void fill_span(uint32_t *row, int x0, int x1, uint32_
 }
 
 template <int NCH1, int NCH2, bool PACKED>
-__global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TileParams p) {
+__global__ void __launch_bounds__(kThreads, 3) resize_tile_kernel(const TileParams p) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
@@ -111,6 +117,31 @@ __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TilePara
     const uint32_t vbase = sbase + p.rows_max * p.pitch;
     const uint32_t vplane = 32u * p.pitch_v;     // one limb of one group
 
+    // ---- work split (ng, T <= 8: powers of two by comparison, no integer division) and everything a warp reads from
+    // global memory for its FIRST group / tile, issued before the staging copies so the latencies overlap -------------
+    const int wpg = ng == 1 ? 8 : ng == 2 ? 4 : ng <= 4 ? 2 : 1;        // warps that share a group in pass 1
+    const int wpg_sh = ng == 1 ? 3 : ng == 2 ? 2 : ng <= 4 ? 1 : 0;
+    const int T = int(p.tw >> 3);
+    const int wpt = T == 1 ? 8 : T == 2 ? 4 : T <= 4 ? 2 : 1;           // warps that share a column tile in pass 2
+    const int wpt_sh = T == 1 ? 3 : T == 2 ? 2 : T <= 4 ? 1 : 0;
+    // groups whose rows are not pure fill, as a bit mask
+    uint32_t gmask;
+    {
+        const uint32_t nchw = lane < ng ? __ldg(p.recs + size_t(g0 + lane) * p.rec_words + 2) : 0u;
+        gmask = __ballot_sync(0xffffffffu, nchw != 0u);
+    }
+    const int gi_first = warp >> wpg_sh;
+    constexpr int NB2 = PACKED ? 3 : NCH2 * 2;
+    const int tile_first = warp >> wpt_sh;
+    const int ntile = (col1 - col0 + 7) >> 3;
+    uint2 bw2_first[NB2];
+    int kb0_first = 0;
+    if (tile_first < ntile) {
+        kb0_first = __ldg(p.tile_kb0 + cb * T + tile_first);
+#pragma unroll
+        for (int i = 0; i < NB2; i++) bw2_first[i] = __ldg(reinterpret_cast<const uint2 *>(p.b2) + (size_t(cb * T + tile_first) * NB2 + i) * 32 + lane);
+    }
+
     // ---- stage the source footprint: rows [y0, y0 + nrows) of the rectangle, pixels [s0, s0 + 4 nblk) ----------
     {
         const uint8_t *src = p.src + size_t(blockIdx.z) * p.src_img_bytes;
@@ -134,16 +165,15 @@ __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TilePara
 
     // ---- pass 1: vertical taps, 8 output rows x pairs of 16-byte blocks ------------------------------------------
     {
-        const int wpg = max(1, kWarps / ng);             // warps that share a group
-        const int gstep = kWarps / wpg;
+        const int gstep = kWarps >> wpg_sh;
         const int ch = g & 3, hh = g >> 2;
         const int sh1 = p.sh1;
         const int npair = nblk >> 1;
 #pragma unroll 1
-        for (int gi = warp / wpg; gi < ng; gi += gstep) {
+        for (int gi = gi_first; gi < ng; gi += gstep) {
+            if (!((gmask >> gi) & 1u)) continue;         // pure-fill rows
             const uint32_t *rec = p.recs + size_t(g0 + gi) * p.rec_words;
-            const int a0 = int(__ldg(rec)), nch = int(__ldg(rec + 2));
-            if (nch == 0) continue;                      // pure-fill rows
+            const int a0 = int(__ldg(rec));
             uint2 bw1[NCH1][2];
 #pragma unroll
             for (int c = 0; c < NCH1; c++)
@@ -155,7 +185,7 @@ __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TilePara
             for (int c = 0; c < NCH1; c++) rowoff[c] = sbase + uint32_t(min(a0 - y0 + 32 * c + lane, nrows - 1)) * p.pitch;
             const uint32_t vrow = vbase + uint32_t(gi) * 2u * vplane + uint32_t(8 * ch + 2 * t + hh) * p.pitch_v + uint32_t(ch) * 4u;
 #pragma unroll 1
-            for (int q = warp % wpg; q < npair; q += wpg) {
+            for (int q = warp & (wpg - 1); q < npair; q += wpg) {
                 const uint32_t boff = uint32_t(q) * 32u;
                 int acc[2][2][4];
 #pragma unroll
@@ -194,29 +224,34 @@ __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TilePara
 
     // ---- pass 2: horizontal taps, 4 channels x 8 rows x 8 output columns per step ---------------------------------
     {
-        const int T = int(p.tw >> 3);
-        const int ntile = (col1 - col0 + 7) >> 3;
-        const int wpt = max(1, kWarps / T);              // warps that share a column tile
-        const int tstep = kWarps / wpt;
+        const int tstep = kWarps >> wpt_sh;
         const int sh2 = p.sh2;
-        constexpr int NB2 = PACKED ? 3 : NCH2 * 2;
 #pragma unroll 1
-        for (int tile = warp / wpt; tile < ntile; tile += tstep) {
-            const int kb0 = p.tile_kb0[cb * T + tile];
+        for (int tile = tile_first; tile < ntile; tile += tstep) {
+            int kb0;
             uint2 bw2[NB2];
-#pragma unroll
-            for (int i = 0; i < NB2; i++) bw2[i] = __ldg(reinterpret_cast<const uint2 *>(p.b2) + (size_t(cb * T + tile) * NB2 + i) * 32 + lane);
             const int ocol = col0 + tile * 8 + 2 * t;          // this lane's two kept output columns
+            if (tile == tile_first) {
+                kb0 = kb0_first;
+#pragma unroll
+                for (int i = 0; i < NB2; i++) bw2[i] = bw2_first[i];
+            } else {
+                kb0 = p.tile_kb0[cb * T + tile];
+#pragma unroll
+                for (int i = 0; i < NB2; i++) bw2[i] = __ldg(reinterpret_cast<const uint2 *>(p.b2) + (size_t(cb * T + tile) * NB2 + i) * 32 + lane);
+            }
+            // constant term (fill taps, intermediate offset, rounding half) of columns ocol, ocol + 1: the initial value of the
+            // 2^-sh2 accumulator, [column][channel]
             int cxr[2][4];
 #pragma unroll
             for (int e = 0; e < 2; e++)
 #pragma unroll
-                for (int c = 0; c < 4; c++) cxr[e][c] = ocol + e < col1 ? p.cxi[size_t(ocol + e) * 4 + c] : 0;
+                for (int c = 0; c < 4; c++) cxr[e][c] = ocol + e < col1 ? __ldg(p.cxi + size_t(ocol + e) * 4 + c) : 0;
 #pragma unroll 1
-            for (int gi = warp % wpt; gi < ng; gi += wpt) {
-                if (__ldg(p.recs + size_t(g0 + gi) * p.rec_words + 2) == 0u) continue;
+            for (int gi = warp & (wpt - 1); gi < ng; gi += wpt) {
+                if (!((gmask >> gi) & 1u)) continue;
                 const uint32_t vbuf = vbase + uint32_t(gi) * 2u * vplane;
-                int tsum[2][4];                    // [channel pair][i]: the pass-2 sum in units of 2^-sh2, before the constant term
+                int tsum[2][4];                    // [channel pair][i]: the pass-2 sum in units of 2^-sh2, constant term included
 #pragma unroll
                 for (int mt = 0; mt < 2; mt++) {
                     const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
@@ -226,7 +261,8 @@ __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TilePara
                         uint32_t a[4];
                         a[0] = lds32(r0); a[1] = lds32(r1); a[2] = lds32(r0 + vplane); a[3] = lds32(r1 + vplane);
                         int aa[4], ab[4], ac[4];
-                        imma_z(aa, a, bw2[0]); imma_z(ab, a, bw2[1]); imma_z(ac, a, bw2[2]);
+                        imma_z(aa, a, bw2[0]); imma_z(ac, a, bw2[2]);
+                        imma_c4(ab, a, bw2[1], cxr[0][2 * mt], cxr[1][2 * mt], cxr[0][2 * mt + 1], cxr[1][2 * mt + 1]);   // the 2^-sh2 plane starts at the constant term
 #pragma unroll
                         for (int i = 0; i < 4; i++) tsum[mt][i] = (aa[i] >> 8) + ab[i] + (ac[i] << 8);
                     } else {
@@ -240,7 +276,9 @@ __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TilePara
                                 a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
 #pragma unroll
                                 for (int d = 0; d < 2; d++) {
-                                    if (c == 0) imma_z(acc[l][d], a, bw2[c * 2 + d]);
+                                    if (c == 0 && l == 0 && d == 1)      // the 2^-sh2 plane starts at the constant term
+                                        imma_c4(acc[l][d], a, bw2[c * 2 + d], cxr[0][2 * mt], cxr[1][2 * mt], cxr[0][2 * mt + 1], cxr[1][2 * mt + 1]);
+                                    else if (c == 0) imma_z(acc[l][d], a, bw2[c * 2 + d]);
                                     else imma(acc[l][d], a, bw2[c * 2 + d]);
                                 }
                             }
@@ -248,13 +286,11 @@ __global__ void __launch_bounds__(kThreads, 2) resize_tile_kernel(const TilePara
                         for (int i = 0; i < 4; i++) tsum[mt][i] = (acc[0][0][i] >> 8) + acc[0][1][i] + acc[1][0][i] + (acc[1][1][i] << 8);
                     }
                 }
-                // i = 0,1: channel 2mt, columns +0, +1; i = 2,3: channel 2mt+1.  Constant term (fill taps, offset, rounding
-                // half), shift, saturate, pack RGBA.
+                // i = 0,1: channel 2mt, columns +0, +1; i = 2,3: channel 2mt+1.  Shift, saturate, pack RGBA.
                 uint32_t px[2];
 #pragma unroll
                 for (int e = 0; e < 2; e++) {
-                    const int c0 = (tsum[0][e] + cxr[e][0]) >> sh2, c1 = (tsum[0][2 + e] + cxr[e][1]) >> sh2;
-                    const int c2 = (tsum[1][e] + cxr[e][2]) >> sh2, c3 = (tsum[1][2 + e] + cxr[e][3]) >> sh2;
+                    const int c0 = tsum[0][e] >> sh2, c1 = tsum[0][2 + e] >> sh2, c2 = tsum[1][e] >> sh2, c3 = tsum[1][2 + e] >> sh2;
                     px[e] = pack_sat_u8(c1, c0, pack_sat_u8(c3, c2, 0u));
                 }
                 const int i_row = (g0 + gi) * 8 + g;

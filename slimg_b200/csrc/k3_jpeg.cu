@@ -144,9 +144,68 @@ __device__ __forceinline__ void block_dct(int *scr, int l8, uint32_t lo, uint32_
     }
 }
 
+// ---- stage 2 on the tensor cores ---------------------------------------------------------------------------------
+// jpeg_fdct_islow is two passes of a LINEAR map with one rounding per output: mid = (M x + 1024) >> 11 along the rows,
+// coef = (M mid + 16384) >> 15 down the columns, with M the integer matrix the butterfly network of jfdctint.c:158-213
+// amounts to (rows 0 and 4 scaled by 8192 so that the `<< 2` / DESCALE(., 2) of the DC terms fit the same shifts).  Both
+// products are exact integer GEMMs: M in two signed base-256 digits, samples as u8, the 16-bit intermediate offset to
+// unsigned and split into two u8 limbs -- mma.sync.m16n8k32.u8.s8, bit-identical to the butterflies (every sum is exact;
+// the roundings are the same two shifts).  Verified against the real libjpeg-turbo like every other path.
+__constant__ int kDctM[8][8] = {
+    {8192, 8192, 8192, 8192, 8192, 8192, 8192, 8192},
+    {11363, 9633, 6437, 2260, -2260, -6437, -9633, -11363},
+    {10703, 4433, -4433, -10703, -10703, -4433, 4433, 10703},
+    {9633, -2259, -11362, -6436, 6436, 11362, 2259, -9633},
+    {8192, -8192, -8192, 8192, 8192, -8192, -8192, 8192},
+    {6437, -11362, 2261, 9633, -9633, -2261, 11362, -6437},
+    {4433, -10704, 10704, -4433, -4433, 10704, -10704, 4433},
+    {2260, -6436, 9633, -11363, 11363, -9633, 6436, -2260}};
+__device__ __forceinline__ int dct_lo(int m) { return ((m + 128) & 255) - 128; }        // balanced digits: m = 256 hi + lo
+__device__ __forceinline__ int dct_hi(int m) { return (m - dct_lo(m)) / 256; }
+__device__ __forceinline__ uint32_t pack_s8(int a, int b, int c, int d) {
+    return uint32_t(a & 0xff) | (uint32_t(b & 0xff) << 8) | (uint32_t(c & 0xff) << 16) | (uint32_t(d & 0xff) << 24);
+}
+__device__ __forceinline__ void imma_c2(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1, int c0, int c1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%10,%11};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(c0), "r"(c1));
+}
+// transposes an 8 x 8 matrix of 16-bit elements held one register per lane (row lane/4, columns 2(lane%4), +1)
+__device__ __forceinline__ uint32_t movmatrix_t(uint32_t a) {
+    uint32_t d;
+    asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
+    return d;
+}
+struct DctRegs {                 // per-lane constants of the two passes (lane = 4 g + t)
+    uint32_t w1lo[2], w1hi[2];   // pass 1, digit d: weights of output g over samples 4(t&1)..+3, for lanes t < 2 / t >= 2
+    uint32_t b2a, b2b, b2c;      // pass 2: [lo x L], [lo x H + hi x L], [hi x H] over k = (row 2t lo, hi, row 2t+1 lo, hi)
+    int c1[2], c2[2];            // rounding, level shift and limb offset, for outputs 2t and 2t+1
+};
+__device__ __forceinline__ DctRegs make_dct_regs(int lane) {
+    const int g = lane >> 2, t = lane & 3;
+    DctRegs r;
+    const int i0 = 4 * (t & 1);
+    const uint32_t wl = pack_s8(dct_lo(kDctM[g][i0]), dct_lo(kDctM[g][i0 + 1]), dct_lo(kDctM[g][i0 + 2]), dct_lo(kDctM[g][i0 + 3]));
+    const uint32_t wh = pack_s8(dct_hi(kDctM[g][i0]), dct_hi(kDctM[g][i0 + 1]), dct_hi(kDctM[g][i0 + 2]), dct_hi(kDctM[g][i0 + 3]));
+    r.w1lo[0] = t < 2 ? wl : 0u; r.w1lo[1] = t < 2 ? wh : 0u;
+    r.w1hi[0] = t < 2 ? 0u : wl; r.w1hi[1] = t < 2 ? 0u : wh;
+    const int ma = kDctM[g][2 * t], mb = kDctM[g][2 * t + 1];
+    r.b2a = pack_s8(dct_lo(ma), 0, dct_lo(mb), 0);
+    r.b2b = pack_s8(dct_hi(ma), dct_lo(ma), dct_hi(mb), dct_lo(mb));
+    r.b2c = pack_s8(0, dct_hi(ma), 0, dct_hi(mb));
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+        const int n = 2 * t + e;
+        // pass 1: x = M (s - 128) + 1024, and + 32768 << 11 so that the intermediate is unsigned: mid' = mid + 32768
+        r.c1[e] = 1024 + (32768 << 11) - (n == 0 ? 128 * 65536 : 0);
+        // pass 2: x = M (mid' - 32768) + 16384; 32768 * rowsum(M[0]) = 2^31 wraps, like the sum it is subtracted from
+        r.c2[e] = int(16384u - (n == 0 ? 0x80000000u : 0u));
+    }
+    return r;
+}
+
 // PIPE: 1 = the loads of stage-1 patch j+1 are issued before patch j is converted; 2 = additionally, the first patch of
 // the warp's NEXT tile is loaded before stage 2 of the current one (8 more live registers across the DCT)
-template <int PIPE, int MINB, bool UQ>
+template <int PIPE, int MINB, bool UQ, bool TENSOR>
 __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_kernel(const __grid_constant__ JpegParams p, const uint32_t n_images) {
     __shared__ __align__(16) WarpSmem wsm[kWarpsPerCta];
     const int lane = threadIdx.x & 31, l8 = lane & 7, q4 = lane >> 3;
@@ -166,6 +225,64 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
         qt[i >> 6][0][i & 63] = p.q.recip[i >> 6][i & 63]; qt[i >> 6][1][i & 63] = p.q.corr[i >> 6][i & 63]; qt[i >> 6][2][i & 63] = p.q.shift32[i >> 6][i & 63];
     }
     __syncthreads();
+
+    // tensor-core stage 2: this lane's matrix digits and its two quantisation entries (coefficients (2t, g), (2t+1, g))
+    const int g8 = lane >> 2, t4 = lane & 3;
+    DctRegs dr;
+    uint32_t qrec[2][2], qcor[2][2], qsh[2][2];          // [table][e]
+    if (TENSOR) {
+        dr = make_dct_regs(lane);
+#pragma unroll
+        for (int tb = 0; tb < 2; tb++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const int idx = (2 * t4 + e) * 8 + g8;
+                qrec[tb][e] = qt[tb][0][idx]; qcor[tb][e] = qt[tb][1][idx]; qsh[tb][e] = qt[tb][2][idx];
+            }
+    }
+    // DCT + quantisation of 8 blocks: 16 sample rows (two block rows, or Cb over Cr) x 32 samples (4 block columns) whose
+    // A fragment is a0..a3.  stq(h, j, word) stores one register = coefficients (g, 2t), (g, 2t+1) of block (h, j).
+    auto dct8 = [&](uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, int tb, auto &&store) {
+        int acc[4][2][4];
+#pragma unroll
+        for (int d = 0; d < 2; d++) {
+            if (d == 0) {
+                imma_c2(acc[0][0], a0, a1, a2, a3, dr.w1lo[0], 0u, dr.c1[0], dr.c1[1]);
+                imma_c2(acc[1][0], a0, a1, a2, a3, dr.w1hi[0], 0u, dr.c1[0], dr.c1[1]);
+                imma_c2(acc[2][0], a0, a1, a2, a3, 0u, dr.w1lo[0], dr.c1[0], dr.c1[1]);
+                imma_c2(acc[3][0], a0, a1, a2, a3, 0u, dr.w1hi[0], dr.c1[0], dr.c1[1]);
+            } else {
+                imma_c2(acc[0][1], a0, a1, a2, a3, dr.w1lo[1], 0u, 0, 0);
+                imma_c2(acc[1][1], a0, a1, a2, a3, dr.w1hi[1], 0u, 0, 0);
+                imma_c2(acc[2][1], a0, a1, a2, a3, 0u, dr.w1lo[1], 0, 0);
+                imma_c2(acc[3][1], a0, a1, a2, a3, 0u, dr.w1hi[1], 0, 0);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            uint32_t m[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) m[i] = uint32_t((acc[j][0][i] + (acc[j][1][i] << 8)) >> 11);      // mid + 32768, 16 bits
+            // rows g (block row 0) and g + 8 (block row 1), frequencies 2t, 2t+1 -> transposed: rows 2t, 2t+1 of frequency g
+            const uint32_t t0 = movmatrix_t(__byte_perm(m[0], m[1], 0x5410)), t1 = movmatrix_t(__byte_perm(m[2], m[3], 0x5410));
+            int da[4], db[4], dc[4];
+            imma_c2(da, t0, t1, 0u, 0u, dr.b2a, 0u, dr.c2[0], dr.c2[1]);
+            imma_c2(db, t0, t1, 0u, 0u, dr.b2b, 0u, 0, 0);
+            imma_c2(dc, t0, t1, 0u, 0u, dr.b2c, 0u, 0, 0);
+            int cf[4], qv[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                cf[i] = (da[i] + (db[i] << 8) + (dc[i] << 16)) >> 15;          // coefficient (u = 2t + (i & 1), u' = g), block row i >> 1
+                const int e = i & 1;
+                const uint32_t aa = uint32_t(cf[i] < 0 ? -cf[i] : cf[i]) + qcor[tb][e];
+                const uint32_t q = __umulhi(aa, qrec[tb][e]) >> qsh[tb][e];       // jcdctmgr.c:408-438, reciprocal form
+                qv[i] = cf[i] < 0 ? -int(q) : int(q);
+            }
+            // natural order wants (u, u') -> u * 8 + u': transpose back so a lane holds u = g, u' = 2t, 2t+1
+            store(0, j, movmatrix_t(__byte_perm(uint32_t(qv[0]), uint32_t(qv[1]), 0x5410)), UQ ? movmatrix_t(__byte_perm(uint32_t(cf[0]), uint32_t(cf[1]), 0x5410)) : 0u, qv[0]);
+            store(1, j, movmatrix_t(__byte_perm(uint32_t(qv[2]), uint32_t(qv[3]), 0x5410)), UQ ? movmatrix_t(__byte_perm(uint32_t(cf[2]), uint32_t(cf[3]), 0x5410)) : 0u, qv[2]);
+        }
+    };
 
     // the two 16-byte loads of stage-1 patch (pr, lane) of the tile at (x0, y0) of image `src`
     auto load_patch = [&](const uint32_t *src, int x0, int y0, int pr, uint32_t (&px)[2][4]) {
@@ -263,42 +380,79 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
         const int ybx0 = mx0 * 2, yby0 = my * 2;
         const int nby = min(2 * nm, int(p.y_wb) - ybx0);          // real Y block columns of the tile
         const int nrow = min(2, int(p.y_hb) - yby0);              // real Y block rows
+        if (TENSOR) {
+            // Y: 4 segments of 32 samples (4 block columns) x 16 rows (both block rows of the MCU row)
 #pragma unroll 1
-        for (int s = 0; s < ((p.debug & 2u) ? 0 : nrow * (kWMcus / 2)); s++) {
-            const int by2 = s / (kWMcus / 2), bx = (s - by2 * (kWMcus / 2)) * 4 + q4;
-            if ((s - by2 * (kWMcus / 2)) * 4 >= nby) continue;     // warp-uniform: the whole step lies right of the image
-            const uint2 v = *reinterpret_cast<const uint2 *>(&sm.ys[by2 * 8 + l8][min(bx, 2 * kWMcus - 1) * 2]);
-            int out[8], uq[8];
-            block_dct<UQ>(scr, l8, v.x, v.y, qt[0], out, uq);
-            if (bx < nby) {
-                if (l8 == 0) { sm.dc[0][by2][bx] = int16_t(out[0]); if (UQ) sm.dc[1][by2][bx] = int16_t(uq[0]); }
-                const size_t off = (size_t(yby0 + by2) * p.y_WB + ybx0 + bx) * 64 + l8;
-#pragma unroll
-                for (int k = 0; k < 8; k++) yout[off + k * 8] = int16_t(out[k]);
-                if (UQ) {
-#pragma unroll
-                    for (int k = 0; k < 8; k++) yuq[off + k * 8] = int16_t(uq[k]);
+            for (int sg = 0; sg < ((p.debug & 2u) ? 0 : 4); sg++) {
+                if (sg * 4 >= nby) break;                              // warp-uniform: the segment lies right of the image
+                const uint32_t a0 = sm.ys[g8][sg * 8 + t4], a1 = sm.ys[g8 + 8][sg * 8 + t4];
+                const uint32_t a2 = sm.ys[g8][sg * 8 + 4 + t4], a3 = sm.ys[g8 + 8][sg * 8 + 4 + t4];
+                dct8(a0, a1, a2, a3, 0, [&](int hb, int j, uint32_t wq, uint32_t wu, int dcq) {
+                    const int bx = sg * 4 + j;
+                    if (bx < nby && hb < nrow) {
+                        const size_t off = (size_t(yby0 + hb) * p.y_WB + ybx0 + bx) * 64 + g8 * 8 + 2 * t4;
+                        *reinterpret_cast<uint32_t *>(yout + off) = wq;
+                        if (UQ) *reinterpret_cast<uint32_t *>(yuq + off) = wu;
+                        // DC of the block (dummy-block patch): coefficient (0, 0) sits in lane 0 before AND after the transposes
+                        if (lane == 0) { sm.dc[0][hb][bx] = int16_t(dcq); if (UQ) sm.dc[1][hb][bx] = int16_t(wu & 0xffffu); }
+                    }
+                });
+            }
+            // chroma: Cb rows as fragment rows 0..7, Cr rows as rows 8..15; 2 segments of 4 block columns
+            const uint32_t *cbw = reinterpret_cast<const uint32_t *>(&sm.cb[0][0]), *crw = reinterpret_cast<const uint32_t *>(&sm.cr[0][0]);
+            constexpr int kCW = (kWW / 4 + 8) / 2;                     // words per chroma tile row
+#pragma unroll 1
+            for (int sg = 0; sg < ((p.debug & 2u) ? 0 : 2); sg++) {
+                if (sg * 4 >= nm) break;
+                const uint32_t a0 = cbw[g8 * kCW + sg * 8 + t4], a1 = crw[g8 * kCW + sg * 8 + t4];
+                const uint32_t a2 = cbw[g8 * kCW + sg * 8 + 4 + t4], a3 = crw[g8 * kCW + sg * 8 + 4 + t4];
+                dct8(a0, a1, a2, a3, 1, [&](int hb, int j, uint32_t wq, uint32_t wu, int) {
+                    const int bx = sg * 4 + j;
+                    if (bx < nm) {
+                        const size_t off = size_t(z) * p.c_img_elems + (size_t(my) * p.c_wb + mx0 + bx) * 64 + g8 * 8 + 2 * t4;
+                        *reinterpret_cast<uint32_t *>((hb ? p.cr : p.cb) + off) = wq;
+                        if (UQ) *reinterpret_cast<uint32_t *>((hb ? p.cru : p.cbu) + off) = wu;
+                    }
+                });
+            }
+        } else {
+#pragma unroll 1
+            for (int s = 0; s < ((p.debug & 2u) ? 0 : nrow * (kWMcus / 2)); s++) {
+                const int by2 = s / (kWMcus / 2), bx = (s - by2 * (kWMcus / 2)) * 4 + q4;
+                if ((s - by2 * (kWMcus / 2)) * 4 >= nby) continue;     // warp-uniform: the whole step lies right of the image
+                const uint2 v = *reinterpret_cast<const uint2 *>(&sm.ys[by2 * 8 + l8][min(bx, 2 * kWMcus - 1) * 2]);
+                int out[8], uq[8];
+                block_dct<UQ>(scr, l8, v.x, v.y, qt[0], out, uq);
+                if (bx < nby) {
+                    if (l8 == 0) { sm.dc[0][by2][bx] = int16_t(out[0]); if (UQ) sm.dc[1][by2][bx] = int16_t(uq[0]); }
+                    const size_t off = (size_t(yby0 + by2) * p.y_WB + ybx0 + bx) * 64 + l8;
+    #pragma unroll
+                    for (int k = 0; k < 8; k++) yout[off + k * 8] = int16_t(out[k]);
+                    if (UQ) {
+    #pragma unroll
+                        for (int k = 0; k < 8; k++) yuq[off + k * 8] = int16_t(uq[k]);
+                    }
                 }
             }
-        }
-        // chroma: steps of 4 blocks, Cb then Cr (both quantise with table 1)
-#pragma unroll 1
-        for (int s = 0; s < ((p.debug & 2u) ? 0 : 2 * (kWMcus / 4)); s++) {
-            const int pl = s / (kWMcus / 4), bx0 = (s - pl * (kWMcus / 4)) * 4, bx = bx0 + q4;
-            if (bx0 >= nm) continue;
-            const uint16_t(*f)[kWW / 4 + 8] = pl ? sm.cr : sm.cb;
-            const uint2 v = *reinterpret_cast<const uint2 *>(&f[l8][bx * 4]);
-            int out[8], uq[8];
-            block_dct<UQ>(scr, l8, v.x, v.y, qt[1], out, uq);
-            if (bx < nm) {
-                const size_t off = size_t(z) * p.c_img_elems + (size_t(my) * p.c_wb + mx0 + bx) * 64 + l8;
-                int16_t *d = (pl ? p.cr : p.cb) + off;
-#pragma unroll
-                for (int k = 0; k < 8; k++) d[k * 8] = int16_t(out[k]);
-                if (UQ) {
-                    int16_t *du = (pl ? p.cru : p.cbu) + off;
-#pragma unroll
-                    for (int k = 0; k < 8; k++) du[k * 8] = int16_t(uq[k]);
+            // chroma: steps of 4 blocks, Cb then Cr (both quantise with table 1)
+    #pragma unroll 1
+            for (int s = 0; s < ((p.debug & 2u) ? 0 : 2 * (kWMcus / 4)); s++) {
+                const int pl = s / (kWMcus / 4), bx0 = (s - pl * (kWMcus / 4)) * 4, bx = bx0 + q4;
+                if (bx0 >= nm) continue;
+                const uint16_t(*f)[kWW / 4 + 8] = pl ? sm.cr : sm.cb;
+                const uint2 v = *reinterpret_cast<const uint2 *>(&f[l8][bx * 4]);
+                int out[8], uq[8];
+                block_dct<UQ>(scr, l8, v.x, v.y, qt[1], out, uq);
+                if (bx < nm) {
+                    const size_t off = size_t(z) * p.c_img_elems + (size_t(my) * p.c_wb + mx0 + bx) * 64 + l8;
+                    int16_t *d = (pl ? p.cr : p.cb) + off;
+    #pragma unroll
+                    for (int k = 0; k < 8; k++) d[k * 8] = int16_t(out[k]);
+                    if (UQ) {
+                        int16_t *du = (pl ? p.cru : p.cbu) + off;
+    #pragma unroll
+                        for (int k = 0; k < 8; k++) du[k * 8] = int16_t(uq[k]);
+                    }
                 }
             }
         }
@@ -336,17 +490,20 @@ cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStr
     const unsigned mcus_x = p.c_wb, mcus_y = p.c_hb;
     const bool uq = p.yu != nullptr;
     if (uq && (!p.cbu || !p.cru)) return cudaErrorInvalidValue;
-    // SLIMG_B200_JPEG_VAR (A/B): 0 = no stage-1 prefetch, 1 = patch j+1 in flight while patch j is converted (default),
+    // SLIMG_B200_JPEG_VAR (A/B): 5 (default) / 6 / 7 = stage 2 on the tensor cores at 6 / 8 / 6 CTAs per SM (7: with the
+    // stage-1 prefetch); CUDA-core stage 2: 0 = no stage-1 prefetch, 1 = patch j+1 in flight while patch j is converted,
     // 2 = also the next tile's first patch across stage 2 (80 registers, 6 CTAs/SM), 3 / 4 = as 1 with 7 / 6 CTAs/SM.  Round 1 measured occupancy (32 warps/SM at <= 64 registers)
     // above everything else: <unroll 1, 8 CTAs/SM> 67.9 us, <1, 6> 69.2 us, <unroll 4, 4> 79.7 us per 24 MP image.
     const char *var_env = std::getenv("SLIMG_B200_JPEG_VAR");
-    const int var = var_env ? std::atoi(var_env) : 1;
+    const int var = var_env ? std::atoi(var_env) : 5;
     using Kern = void (*)(const JpegParams, const uint32_t);
     Kern kern;
-#define SLIMG_K3_PICK(U)                                                                                         \
-    (var == 0 ? jpeg_frontend_warp_kernel<0, 8, U> : var == 2 ? jpeg_frontend_warp_kernel<2, 6, U>                \
-     : var == 3 ? jpeg_frontend_warp_kernel<1, 7, U> : var == 4 ? jpeg_frontend_warp_kernel<1, 6, U>              \
-                                                                : jpeg_frontend_warp_kernel<1, 8, U>)
+#define SLIMG_K3_PICK(U)                                                                                                     \
+    (var == 0 ? jpeg_frontend_warp_kernel<0, 8, U, false> : var == 1 ? jpeg_frontend_warp_kernel<1, 8, U, false>              \
+     : var == 2 ? jpeg_frontend_warp_kernel<2, 6, U, false> : var == 3 ? jpeg_frontend_warp_kernel<1, 7, U, false>            \
+     : var == 4 ? jpeg_frontend_warp_kernel<1, 6, U, false> : var == 6 ? jpeg_frontend_warp_kernel<0, 8, U, true>             \
+     : var == 7 ? jpeg_frontend_warp_kernel<1, 6, U, true> : var == 8 ? jpeg_frontend_warp_kernel<0, 5, U, true>               \
+     : var == 9 ? jpeg_frontend_warp_kernel<0, 4, U, true> : jpeg_frontend_warp_kernel<0, 6, U, true>)
     kern = uq ? SLIMG_K3_PICK(true) : SLIMG_K3_PICK(false);
 #undef SLIMG_K3_PICK
     int dev = 0, sms = 148, per_sm = 4;

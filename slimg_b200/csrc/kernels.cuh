@@ -202,6 +202,7 @@ struct TcParams {
     uint32_t fill_post, fill_pre_packed;
     uint32_t n_bands, need_fill, debug;
     uint32_t pf_chunks;              // chunks prefetched into L2 beyond the ring (0 = off)
+    unsigned long long *stats;       // debug & 32: cycles each role spent waiting on each barrier (device, 16 counters)
 };
 cudaError_t launch_resize_tc(const TcParams &p, uint32_t n_images, cudaStream_t stream);
 
