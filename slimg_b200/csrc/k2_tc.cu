@@ -42,9 +42,9 @@ constexpr int kMaxSlots = 12;
 constexpr int kMaxAcc = 8;                   // accumulator buffers per panel (16 TMEM columns each)
 constexpr int kMaxVBufs = 4;
 constexpr uint32_t kSpinLimit = 1u << 27;    // a wedged pipeline traps instead of hanging the GPU
-// tcgen05 instruction descriptor: D = s32, A = u8 MN-major, B = s8 K-major, M = 128, N = 16 (both weight digits of a
-// block's 8 rows in one instruction: the A panel is read from shared memory once)
-constexpr uint32_t kIdesc = (2u << 4) | (0u << 7) | (1u << 10) | (1u << 15) | (0u << 16) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
+// tcgen05 instruction descriptor: D = s32, A = u8 MN-major, B = s8 K-major, M = 128; N = 16 per block (both weight digits
+// of its 8 rows), times the number of blocks one instruction covers
+constexpr uint32_t kIdescBase = (2u << 4) | (0u << 7) | (1u << 10) | (1u << 15) | (0u << 16) | ((128u >> 4) << 24);     // N goes to bits 17..22
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
@@ -94,10 +94,10 @@ __device__ __forceinline__ bool elect_one() {
     asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
     return pred != 0;
 }
-__device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+__device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
-                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate) : "memory");
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -263,43 +263,74 @@ __global__ void __launch_bounds__(kThreads, 1) resize_tc_kernel(const TcParams p
             if (pf) prefetch_to(min(n_steps, s + 1 + slots + pf));
         }
     } else if (warp == kMmaWarp) {
-        // ================= MMA issue: every (block, panel) of the chunk =====================================
-        // One elected thread runs the whole loop (tcgen05.mma / commit are single-thread instructions; a loop that
-        // is uniform per construction keeps the compiler from wrapping every issue in an election).
+        // ================= MMA issue ==========================================================================
+        // One elected thread runs the whole loop (tcgen05.mma / commit are single-thread instructions).  Per chunk: the
+        // blocks that CONTINUE through it sit in adjacent accumulator buffers, so one instruction per panel covers them
+        // all (N = 16 x blocks: the panel is read from shared memory once; a second instruction only where the buffer ring
+        // wraps); a block that STARTS in the chunk gets its own instruction, the one that overwrites instead of
+        // accumulating.  The loop is kept free of divisions and generic loads: this thread paces the whole CTA
+        // (measured: ~1100 clk per chunk of scalar overhead in the first version, more than the chunk's 870-clk budget).
         if (elect_one()) {
+            int t_first = blk0, fm = 0, fu = 0;          // tracked block (>= blk0), its accumulator buffer and use count
 #pragma unroll 1
             for (int s = 0; s < n_steps; s++) {
                 const int slot = s % slots;
                 mbar_wait_t(&tail.full[slot], uint32_t(s / slots) & 1u, timed, w0);
                 tc_fence_after();
-                const uint32_t *rec = reinterpret_cast<const uint32_t *>(smem_raw + size_t(slots) * p.slot_bytes + size_t(slot) * crec_bytes);
-                const int first = int(rec[0]), nb = int(rec[1]);
-                const uint32_t flags = rec[2];
-                const uint64_t a_desc0 = desc_a(ring + uint32_t(slot) * p.slot_bytes);
-                const uint64_t b_desc0 = desc_b(crec_base + uint32_t(slot) * crec_bytes + 64u);
+                const uint32_t rec_s = crec_base + uint32_t(slot) * crec_bytes;
+                const int first = int(lds32(rec_s)), nb = int(lds32(rec_s + 4u));
+                const uint32_t flags = lds32(rec_s + 8u);
+                const int i_lo = max(0, blk0 - first), i_hi = min(nb, blk1 - first);
+                if (i_lo < i_hi) {
+                    // advance the tracked block to the first block of this chunk that belongs to the band
+                    for (int d = first + i_lo - t_first; d > 0; d--) { if (++fm == nbuf) { fm = 0; fu++; } }
+                    t_first = first + i_lo;
+                    const uint64_t a_desc0 = desc_a(ring + uint32_t(slot) * p.slot_bytes);
+                    const uint64_t b_desc0 = desc_b(rec_s + 64u);
+                    int i = i_lo, ab = fm, use = fu;
+                    // continuing blocks first (they are the older ones), in runs that do not wrap around the buffer ring
+                    while (i < i_hi && !((flags >> i) & 1u)) {
+                        int len = 1;
+                        while (i + len < i_hi && !((flags >> (i + len)) & 1u) && ab + len < nbuf) len++;
+                        if (!(p.debug & 1u)) {
+                            const uint32_t idesc = kIdescBase | (uint32_t(len * 16) >> 3 << 17);
+                            const uint64_t bd = b_desc0 + uint64_t(i) * (512u >> 4);
+                            uint64_t ad = a_desc0;
+                            uint32_t dcol = tmem + uint32_t(ab) * 16u;
 #pragma unroll 1
-                for (int i = 0; i < nb; i++) {
-                    const int b = first + i;
-                    if (b < blk0 || b >= blk1) continue;
-                    const int use = (b - blk0) / nbuf, abuf = (b - blk0) - use * nbuf;
-                    const bool starts = (flags >> i) & 1u, ends = (flags >> (8 + i)) & 1u;
-                    if (starts) {                                // the buffer's previous block must have been read out
-                        mbar_wait_t(&tail.acc_empty[abuf], (uint32_t(use) & 1u) ^ 1u, timed, w1);
-                        tc_fence_after();
-                    }
-                    const uint32_t acc = starts ? 0u : 1u;
-                    const uint64_t bd = b_desc0 + uint64_t(i) * (512u >> 4);          // one N = 16 tile per block
-                    uint64_t ad = a_desc0;
-                    uint32_t dcol = tmem + uint32_t(abuf) * 16u;
-                    if (!(p.debug & 1u)) {
-#pragma unroll 1
-                        for (int pn = 0; pn < npan; pn++) {
-                            umma_i8(dcol, ad, bd, acc);
-                            ad += 4096u >> 4;
-                            dcol += uint32_t(nbuf) * 16u;
+                            for (int pn = 0; pn < npan; pn++) {
+                                umma_i8(dcol, ad, bd, idesc, 1u);
+                                ad += 4096u >> 4;
+                                dcol += uint32_t(nbuf) * 16u;
+                            }
                         }
+                        i += len; ab += len;
+                        if (ab >= nbuf) { ab -= nbuf; use++; }
                     }
-                    if (ends) umma_commit(&tail.acc_full[abuf]);
+                    // blocks that start here: wait until the buffer's previous block has been read out, then overwrite
+                    for (; i < i_hi; i++) {
+                        mbar_wait_t(&tail.acc_empty[ab], (uint32_t(use) & 1u) ^ 1u, timed, w1);
+                        tc_fence_after();
+                        if (!(p.debug & 1u)) {
+                            const uint32_t idesc = kIdescBase | (16u >> 3 << 17);
+                            const uint64_t bd = b_desc0 + uint64_t(i) * (512u >> 4);
+                            uint64_t ad = a_desc0;
+                            uint32_t dcol = tmem + uint32_t(ab) * 16u;
+#pragma unroll 1
+                            for (int pn = 0; pn < npan; pn++) {
+                                umma_i8(dcol, ad, bd, idesc, 0u);
+                                ad += 4096u >> 4;
+                                dcol += uint32_t(nbuf) * 16u;
+                            }
+                        }
+                        if (++ab == nbuf) { ab = 0; use++; }
+                    }
+                    // blocks that end here are complete once everything issued so far retires
+                    ab = fm;
+                    for (i = i_lo; i < i_hi; i++) {
+                        if ((flags >> (8 + i)) & 1u) umma_commit(&tail.acc_full[ab]);
+                        if (++ab == nbuf) ab = 0;
+                    }
                 }
                 umma_commit(&tail.empty[slot]);                  // the slot is free once everything issued so far retires
             }
@@ -546,7 +577,8 @@ static cudaError_t launch_tc_t(const TcParams &p, uint32_t n_images, cudaStream_
             cudaMemcpyAsync(h, d_stats, sizeof h, cudaMemcpyDeviceToHost, stream);
             cudaStreamSynchronize(stream);
             const double n = double(h[7] ? h[7] : 1);
-            std::fprintf(stderr, "[slimg_b200] tc waits per strip CTA (kclk): producer/free-slot %.1f | mma/chunk %.1f mma/free-acc %.1f | epi/block-done %.1f epi/free-V %.1f (per warp) | "
+            static int printed = 0;
+            if (printed++ < 2) std::fprintf(stderr, "[slimg_b200] tc waits per strip CTA (kclk): producer/free-slot %.1f | mma/chunk %.1f mma/free-acc %.1f | epi/block-done %.1f epi/free-V %.1f (per warp) | "
                                  "pass2/V %.1f (per warp) | lifetime producer %.1f epi %.1f pass2 %.1f | CTAs %.0f\n",
                          h[0] / n / 1e3, h[1] / n / 1e3, h[2] / n / 1e3, h[3] / double(h[9] ? h[9] : 1) / 1e3, h[4] / double(h[9] ? h[9] : 1) / 1e3,
                          h[5] / double(h[11] ? h[11] : 1) / 1e3, h[6] / n / 1e3, h[8] / double(h[9] ? h[9] : 1) / 1e3, h[10] / double(h[11] ? h[11] : 1) / 1e3, n);

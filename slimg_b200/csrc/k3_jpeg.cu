@@ -165,9 +165,14 @@ __device__ __forceinline__ int dct_hi(int m) { return (m - dct_lo(m)) / 256; }
 __device__ __forceinline__ uint32_t pack_s8(int a, int b, int c, int d) {
     return uint32_t(a & 0xff) | (uint32_t(b & 0xff) << 8) | (uint32_t(c & 0xff) << 16) | (uint32_t(d & 0xff) << 24);
 }
-__device__ __forceinline__ void imma_c2(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1, int c0, int c1) {
-    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%10,%11};"
-                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(c0), "r"(c1));
+// m16n8k16 u8 x s8: A = 2 registers (rows g and g + 8, k = 4t..4t+3), B = 1 register, C given as four registers / as zero
+__device__ __forceinline__ void imma16_c(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t b, int c0, int c1, int c2, int c3) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%7,%8,%9,%10};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(b), "r"(c0), "r"(c1), "r"(c2), "r"(c3));
+}
+__device__ __forceinline__ void imma16_z(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t b) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%7,%7,%7,%7};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(a0), "r"(a1), "r"(b), "r"(0));
 }
 // transposes an 8 x 8 matrix of 16-bit elements held one register per lane (row lane/4, columns 2(lane%4), +1)
 __device__ __forceinline__ uint32_t movmatrix_t(uint32_t a) {
@@ -178,7 +183,7 @@ __device__ __forceinline__ uint32_t movmatrix_t(uint32_t a) {
 struct DctRegs {                 // per-lane constants of the two passes (lane = 4 g + t)
     uint32_t w1lo[2], w1hi[2];   // pass 1, digit d: weights of output g over samples 4(t&1)..+3, for lanes t < 2 / t >= 2
     uint32_t b2a, b2b, b2c;      // pass 2: [lo x L], [lo x H + hi x L], [hi x H] over k = (row 2t lo, hi, row 2t+1 lo, hi)
-    int c1[2], c2[2];            // rounding, level shift and limb offset, for outputs 2t and 2t+1
+    int c1[4], c2[4];            // rounding, level shift and limb offset, for outputs 2t and 2t+1 ({e0, e1, e0, e1}: the MMA's C quad)
 };
 __device__ __forceinline__ DctRegs make_dct_regs(int lane) {
     const int g = lane >> 2, t = lane & 3;
@@ -196,9 +201,9 @@ __device__ __forceinline__ DctRegs make_dct_regs(int lane) {
     for (int e = 0; e < 2; e++) {
         const int n = 2 * t + e;
         // pass 1: x = M (s - 128) + 1024, and + 32768 << 11 so that the intermediate is unsigned: mid' = mid + 32768
-        r.c1[e] = 1024 + (32768 << 11) - (n == 0 ? 128 * 65536 : 0);
+        r.c1[e] = r.c1[2 + e] = 1024 + (32768 << 11) - (n == 0 ? 128 * 65536 : 0);
         // pass 2: x = M (mid' - 32768) + 16384; 32768 * rowsum(M[0]) = 2^31 wraps, like the sum it is subtracted from
-        r.c2[e] = int(16384u - (n == 0 ? 0x80000000u : 0u));
+        r.c2[e] = r.c2[2 + e] = int(16384u - (n == 0 ? 0x80000000u : 0u));
     }
     return r;
 }
@@ -241,23 +246,22 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
             }
     }
     // DCT + quantisation of 8 blocks: 16 sample rows (two block rows, or Cb over Cr) x 32 samples (4 block columns) whose
-    // A fragment is a0..a3.  stq(h, j, word) stores one register = coefficients (g, 2t), (g, 2t+1) of block (h, j).
-    auto dct8 = [&](uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, int tb, auto &&store) {
+    // A fragment is a0..a3.  Block (hb, j) goes to q[hb] + 64 j (this lane's two coefficients (g, 2t), (g, 2t+1) as one
+    // 32-bit store: a warp writes the 128 bytes of a block); nv block columns are real, ok1 says whether row 1 is.
+    // dcs: where lane 0 leaves the blocks' DC terms (dummy-block patch, Y only).
+    auto dct8 = [&](uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, int tb, int16_t *q0, int16_t *q1, int16_t *u0, int16_t *u1,
+                    int nv, bool ok1, int16_t *dcs, int dcs_row) {
+        // pass 1 (rows): block column j takes samples 8j..8j+7 = half of a K = 16 step: j = 0, 1 from (a0, a1), j = 2, 3 from
+        // (a2, a3), the weights masked to the lanes that hold that half
         int acc[4][2][4];
-#pragma unroll
-        for (int d = 0; d < 2; d++) {
-            if (d == 0) {
-                imma_c2(acc[0][0], a0, a1, a2, a3, dr.w1lo[0], 0u, dr.c1[0], dr.c1[1]);
-                imma_c2(acc[1][0], a0, a1, a2, a3, dr.w1hi[0], 0u, dr.c1[0], dr.c1[1]);
-                imma_c2(acc[2][0], a0, a1, a2, a3, 0u, dr.w1lo[0], dr.c1[0], dr.c1[1]);
-                imma_c2(acc[3][0], a0, a1, a2, a3, 0u, dr.w1hi[0], dr.c1[0], dr.c1[1]);
-            } else {
-                imma_c2(acc[0][1], a0, a1, a2, a3, dr.w1lo[1], 0u, 0, 0);
-                imma_c2(acc[1][1], a0, a1, a2, a3, dr.w1hi[1], 0u, 0, 0);
-                imma_c2(acc[2][1], a0, a1, a2, a3, 0u, dr.w1lo[1], 0, 0);
-                imma_c2(acc[3][1], a0, a1, a2, a3, 0u, dr.w1hi[1], 0, 0);
-            }
-        }
+        imma16_c(acc[0][0], a0, a1, dr.w1lo[0], dr.c1[0], dr.c1[1], dr.c1[2], dr.c1[3]);
+        imma16_c(acc[1][0], a0, a1, dr.w1hi[0], dr.c1[0], dr.c1[1], dr.c1[2], dr.c1[3]);
+        imma16_c(acc[2][0], a2, a3, dr.w1lo[0], dr.c1[0], dr.c1[1], dr.c1[2], dr.c1[3]);
+        imma16_c(acc[3][0], a2, a3, dr.w1hi[0], dr.c1[0], dr.c1[1], dr.c1[2], dr.c1[3]);
+        imma16_z(acc[0][1], a0, a1, dr.w1lo[1]);
+        imma16_z(acc[1][1], a0, a1, dr.w1hi[1]);
+        imma16_z(acc[2][1], a2, a3, dr.w1lo[1]);
+        imma16_z(acc[3][1], a2, a3, dr.w1hi[1]);
 #pragma unroll
         for (int j = 0; j < 4; j++) {
             uint32_t m[4];
@@ -266,9 +270,9 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
             // rows g (block row 0) and g + 8 (block row 1), frequencies 2t, 2t+1 -> transposed: rows 2t, 2t+1 of frequency g
             const uint32_t t0 = movmatrix_t(__byte_perm(m[0], m[1], 0x5410)), t1 = movmatrix_t(__byte_perm(m[2], m[3], 0x5410));
             int da[4], db[4], dc[4];
-            imma_c2(da, t0, t1, 0u, 0u, dr.b2a, 0u, dr.c2[0], dr.c2[1]);
-            imma_c2(db, t0, t1, 0u, 0u, dr.b2b, 0u, 0, 0);
-            imma_c2(dc, t0, t1, 0u, 0u, dr.b2c, 0u, 0, 0);
+            imma16_c(da, t0, t1, dr.b2a, dr.c2[0], dr.c2[1], dr.c2[2], dr.c2[3]);
+            imma16_z(db, t0, t1, dr.b2b);
+            imma16_z(dc, t0, t1, dr.b2c);
             int cf[4], qv[4];
 #pragma unroll
             for (int i = 0; i < 4; i++) {
@@ -279,8 +283,26 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
                 qv[i] = cf[i] < 0 ? -int(q) : int(q);
             }
             // natural order wants (u, u') -> u * 8 + u': transpose back so a lane holds u = g, u' = 2t, 2t+1
-            store(0, j, movmatrix_t(__byte_perm(uint32_t(qv[0]), uint32_t(qv[1]), 0x5410)), UQ ? movmatrix_t(__byte_perm(uint32_t(cf[0]), uint32_t(cf[1]), 0x5410)) : 0u, qv[0]);
-            store(1, j, movmatrix_t(__byte_perm(uint32_t(qv[2]), uint32_t(qv[3]), 0x5410)), UQ ? movmatrix_t(__byte_perm(uint32_t(cf[2]), uint32_t(cf[3]), 0x5410)) : 0u, qv[2]);
+            const uint32_t w0 = movmatrix_t(__byte_perm(uint32_t(qv[0]), uint32_t(qv[1]), 0x5410));
+            const uint32_t w1 = movmatrix_t(__byte_perm(uint32_t(qv[2]), uint32_t(qv[3]), 0x5410));
+            uint32_t x0 = 0u, x1 = 0u;
+            if (UQ) {
+                x0 = movmatrix_t(__byte_perm(uint32_t(cf[0]), uint32_t(cf[1]), 0x5410));
+                x1 = movmatrix_t(__byte_perm(uint32_t(cf[2]), uint32_t(cf[3]), 0x5410));
+            }
+            if (j < nv) {
+                *reinterpret_cast<uint32_t *>(q0 + j * 64) = w0;
+                if (UQ) *reinterpret_cast<uint32_t *>(u0 + j * 64) = x0;
+                if (ok1) {
+                    *reinterpret_cast<uint32_t *>(q1 + j * 64) = w1;
+                    if (UQ) *reinterpret_cast<uint32_t *>(u1 + j * 64) = x1;
+                }
+                // DC of the block: coefficient (0, 0) sits in lane 0 before AND after the transposes
+                if (dcs && lane == 0) {
+                    dcs[j] = int16_t(qv[0]); dcs[dcs_row + j] = int16_t(qv[2]);
+                    if (UQ) { dcs[2 * dcs_row + j] = int16_t(x0 & 0xffffu); dcs[3 * dcs_row + j] = int16_t(x1 & 0xffffu); }
+                }
+            }
         }
     };
 
@@ -387,16 +409,10 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
                 if (sg * 4 >= nby) break;                              // warp-uniform: the segment lies right of the image
                 const uint32_t a0 = sm.ys[g8][sg * 8 + t4], a1 = sm.ys[g8 + 8][sg * 8 + t4];
                 const uint32_t a2 = sm.ys[g8][sg * 8 + 4 + t4], a3 = sm.ys[g8 + 8][sg * 8 + 4 + t4];
-                dct8(a0, a1, a2, a3, 0, [&](int hb, int j, uint32_t wq, uint32_t wu, int dcq) {
-                    const int bx = sg * 4 + j;
-                    if (bx < nby && hb < nrow) {
-                        const size_t off = (size_t(yby0 + hb) * p.y_WB + ybx0 + bx) * 64 + g8 * 8 + 2 * t4;
-                        *reinterpret_cast<uint32_t *>(yout + off) = wq;
-                        if (UQ) *reinterpret_cast<uint32_t *>(yuq + off) = wu;
-                        // DC of the block (dummy-block patch): coefficient (0, 0) sits in lane 0 before AND after the transposes
-                        if (lane == 0) { sm.dc[0][hb][bx] = int16_t(dcq); if (UQ) sm.dc[1][hb][bx] = int16_t(wu & 0xffffu); }
-                    }
-                });
+                const size_t off = (size_t(yby0) * p.y_WB + ybx0 + sg * 4) * 64 + g8 * 8 + 2 * t4;
+                const size_t row1 = size_t(p.y_WB) * 64;
+                dct8(a0, a1, a2, a3, 0, yout + off, yout + off + row1, UQ ? yuq + off : nullptr, UQ ? yuq + off + row1 : nullptr,
+                     min(4, nby - sg * 4), nrow > 1, &sm.dc[0][0][sg * 4], 2 * kWMcus);
             }
             // chroma: Cb rows as fragment rows 0..7, Cr rows as rows 8..15; 2 segments of 4 block columns
             const uint32_t *cbw = reinterpret_cast<const uint32_t *>(&sm.cb[0][0]), *crw = reinterpret_cast<const uint32_t *>(&sm.cr[0][0]);
@@ -406,14 +422,9 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
                 if (sg * 4 >= nm) break;
                 const uint32_t a0 = cbw[g8 * kCW + sg * 8 + t4], a1 = crw[g8 * kCW + sg * 8 + t4];
                 const uint32_t a2 = cbw[g8 * kCW + sg * 8 + 4 + t4], a3 = crw[g8 * kCW + sg * 8 + 4 + t4];
-                dct8(a0, a1, a2, a3, 1, [&](int hb, int j, uint32_t wq, uint32_t wu, int) {
-                    const int bx = sg * 4 + j;
-                    if (bx < nm) {
-                        const size_t off = size_t(z) * p.c_img_elems + (size_t(my) * p.c_wb + mx0 + bx) * 64 + g8 * 8 + 2 * t4;
-                        *reinterpret_cast<uint32_t *>((hb ? p.cr : p.cb) + off) = wq;
-                        if (UQ) *reinterpret_cast<uint32_t *>((hb ? p.cru : p.cbu) + off) = wu;
-                    }
-                });
+                const size_t off = size_t(z) * p.c_img_elems + (size_t(my) * p.c_wb + mx0 + sg * 4) * 64 + g8 * 8 + 2 * t4;
+                dct8(a0, a1, a2, a3, 1, p.cb + off, p.cr + off, UQ ? p.cbu + off : nullptr, UQ ? p.cru + off : nullptr,
+                     min(4, nm - sg * 4), true, nullptr, 0);
             }
         } else {
 #pragma unroll 1
