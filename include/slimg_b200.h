@@ -181,6 +181,30 @@ slimg_status slimg_b200_pipeline_jpeg(const slimg_image *in, const slimg_pipelin
                                       const uint16_t qt_luma[64], const uint16_t qt_chroma[64], uint32_t flags,
                                       slimg_jpeg_coefs *out);
 
+/* ---- colour planes for the other lossy encoders: what webp::Encoder::from_rgba (codec/webp.rs:25-30 ->
+ * libwebp WebPPictureImportRGBA) and ravif::Encoder::encode_rgba (codec/avif.rs:28-47) compute from the RGBA buffer before
+ * their own transforms.  libwebp and ravif are absent from the reference tree: restated from their published sources,
+ * PARITY UNPINNED.  ravif's optional clean-up of the colour of fully transparent pixels is not built. ---- */
+enum { SLIMG_PLANES_WEBP_YUV420 = 1,    /* u8: Y w x h; U, V ceil(w/2) x ceil(h/2) (BT.601 studio range, gamma-domain chroma averaging);
+                                           A w x h only when some pixel is not opaque */
+       SLIMG_PLANES_AVIF_YCBCR444_8 = 2,   /* u8:  Y, Cb, Cr, A w x h (BT.601 full range) */
+       SLIMG_PLANES_AVIF_YCBCR444_10 = 3   /* u16: same, 10 bits */ };
+typedef struct {
+    uint32_t width, height, kind;
+    uint32_t chroma_width, chroma_height;
+    uint32_t bytes_per_sample;          /* 1 or 2 */
+    int32_t  has_alpha;                 /* WebP: 0 = every pixel opaque, `a` is NULL */
+    void *y, *cb, *cr, *a;              /* host, one allocation; release with slimg_b200_planes_free */
+} slimg_planes;
+/* pixel stages (opts may be all-None) and the plane conversion back to back on the device: the resized image never leaves HBM */
+slimg_status slimg_b200_pipeline_planes(const slimg_image *in, const slimg_pipeline_options *opts, int order, int kind,
+                                        slimg_planes *out);
+void slimg_b200_planes_free(slimg_planes *p);
+/* device-resident batch: planes packed per image; for WebP `a` may be NULL (alpha ignored: treated as opaque), else a scratch
+ * of n * ceil(h/2) bytes + n u32 flags is taken from `scratch` (n * ceil(h/2) + 4 n bytes, zeroed by the call) */
+slimg_status slimg_b200_color_planes_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h, int kind,
+                                                  void *y, void *cb, void *cr, void *a, void *scratch, void *stream);
+
 /* ---- batched, device-resident variants (what bench.py's `value` times) ----
  * `src` / `dst` are DEVICE pointers on the current CUDA device; images are packed back to back
  * (n * w*h*4 bytes in, n * out_w*out_h*4 bytes out).  `stream` is a cudaStream_t (NULL = default

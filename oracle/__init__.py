@@ -335,3 +335,25 @@ def quantize(ws: np.ndarray, qt: np.ndarray) -> np.ndarray:
     out = np.empty(64, np.int16)
     lib().so_quantize(_ptr(w, C.POINTER(C.c_int32)), _ptr(q, _u16p), _ptr(out, _i16p))
     return out.reshape(8, 8)
+
+
+# ---- colour-plane pre-stages of the WebP / AVIF encoders (parity unpinned: libwebp / ravif are absent) ----
+
+def webp_yuva(img: np.ndarray):
+    """libwebp's RGBA -> YUV 4:2:0 (+ A) import.  -> (y [h,w], u, v [ceil(h/2), ceil(w/2)], a [h,w] or None)."""
+    img = _as_rgba(img)
+    h, w = img.shape[:2]
+    y = np.zeros((h, w), np.uint8); a = np.zeros((h, w), np.uint8)
+    u = np.zeros(((h + 1) // 2, (w + 1) // 2), np.uint8); v = np.zeros_like(u)
+    lib().so_webp_yuva.restype = C.c_int
+    has_alpha = lib().so_webp_yuva(_ptr(img, _u8p), C.c_uint32(w), C.c_uint32(h), _ptr(y, _u8p), _ptr(u, _u8p), _ptr(v, _u8p), _ptr(a, _u8p))
+    return y, u, v, (a if has_alpha else None)
+
+
+def avif_planes(img: np.ndarray, depth: int = 10):
+    """ravif's RGBA -> YCbCr 4:4:4 (BT.601, full range) + alpha plane, uint16 [h,w] each."""
+    img = _as_rgba(img)
+    h, w = img.shape[:2]
+    out = [np.zeros((h, w), np.uint16) for _ in range(4)]
+    lib().so_avif_planes(_ptr(img, _u8p), C.c_uint32(w), C.c_uint32(h), C.c_int(depth), *[_ptr(o, _u16p) for o in out])
+    return tuple(out)

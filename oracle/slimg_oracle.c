@@ -566,3 +566,129 @@ void so_jpeg_frontend_unquantised(const uint8_t *rgba, uint32_t w, uint32_t h, i
 {
     so_jpeg_frontend(rgba, w, h, NULL, NULL, yc, cbc, crc);
 }
+
+/* ======================================================================================================================
+ * Colour-plane pre-stages of the other encoders.  BOTH ARE PARITY-UNPINNED: libwebp (libwebp-sys 0.9.6)
+ * and ravif 0.13 are crates.io dependencies that are absent from /root/reference; the arithmetic below restates their
+ * published sources from memory, and the reference's tests at these boundaries check only magic bytes and dimensions
+ * (crates/slimg-core/src/codec/webp.rs:25-30 Encoder::from_rgba -> WebPPictureImportRGBA; codec/avif.rs:28-47
+ * ravif::Encoder::encode_rgba).
+ * ====================================================================================================================== */
+#include <math.h>
+
+/* ---- libwebp src/enc/picture_csp_enc.c: ImportYUVAFromRGBA, the default (non-iterative) path ---- */
+enum { kWGammaFix = 12, kWGammaScale = (1 << 12) - 1, kWGammaTabFix = 7, kWGammaTabScale = 1 << 7, kWGammaTabRounder = 1 << 6,
+       kWGammaTabSize = 1 << (12 - 7), kWAlphaFix = 19, kWYuvFix = 16, kWYuvHalf = 1 << 15 };
+static uint16_t w_gamma_to_linear[256];
+static int w_linear_to_gamma[kWGammaTabSize + 1];
+static int w_tables_ready = 0;
+
+void so_webp_gamma_tables(uint16_t g2l[256], int32_t l2g[33])       /* InitGammaTables: kGamma = 0.80 */
+{
+    const double gamma = 0.80, norm = 1.0 / 255.0, scale = (double)(1 << kWGammaTabFix) / kWGammaScale;
+    for (int v = 0; v <= 255; v++) g2l[v] = (uint16_t)(pow(norm * v, gamma) * kWGammaScale + .5);
+    for (int v = 0; v <= kWGammaTabSize; v++) l2g[v] = (int32_t)(255. * pow(scale * v, 1. / gamma) + .5);
+}
+static void w_init(void)
+{
+    if (w_tables_ready) return;
+    int32_t l2g[33];
+    so_webp_gamma_tables(w_gamma_to_linear, l2g);
+    for (int i = 0; i <= kWGammaTabSize; i++) w_linear_to_gamma[i] = l2g[i];
+    w_tables_ready = 1;
+}
+static uint32_t w_g2l(uint8_t v) { return w_gamma_to_linear[v]; }
+static int w_l2g(uint32_t base_value, int shift)                    /* LinearToGamma = (Interpolate(v << shift) + rounder) >> fix */
+{
+    const uint32_t v = base_value << shift;
+    const int tab_pos = (int)(v >> (kWGammaTabFix + 2));
+    const int x = (int)(v & ((kWGammaTabScale << 2) - 1));
+    const int v0 = w_linear_to_gamma[tab_pos], v1 = w_linear_to_gamma[tab_pos + 1];
+    const int y = v1 * x + v0 * ((kWGammaTabScale << 2) - x);
+    return (y + kWGammaTabRounder) >> kWGammaTabFix;
+}
+static int w_rgb_to_y(int r, int g, int b, int rounding) { return (16839 * r + 33059 * g + 6420 * b + rounding + (16 << kWYuvFix)) >> kWYuvFix; }
+static int w_clip_uv(int uv, int rounding)
+{
+    uv = (uv + rounding + (128 << (kWYuvFix + 2))) >> (kWYuvFix + 2);
+    return (uv & ~0xff) == 0 ? uv : uv < 0 ? 0 : 255;
+}
+static int w_rgb_to_u(int r, int g, int b, int rounding) { return w_clip_uv(-9719 * r - 19081 * g + 28800 * b, rounding); }
+static int w_rgb_to_v(int r, int g, int b, int rounding) { return w_clip_uv(28800 * r - 24116 * g - 4684 * b, rounding); }
+
+/* One chroma sample from the (up to) 2 x 2 pixels p[0..3] (p[1] = right neighbour or p[0] again at an odd right edge, p[2..3]
+ * = the row below or the same row again at an odd bottom edge): AccumulateRGB / AccumulateRGBA + WebPConvertRGBA32ToUV. */
+static void w_chroma(const uint8_t *p[4], int wide, int with_alpha, uint8_t *u, uint8_t *v)
+{
+    int rgb[3];
+    uint32_t a = wide ? (uint32_t)(p[0][3] + p[1][3] + p[2][3] + p[3][3]) : 2u * (uint32_t)(p[0][3] + p[2][3]);
+    for (int c = 0; c < 3; c++) {
+        if (!with_alpha || a == 4 * 0xff || a == 0) {
+            rgb[c] = wide ? w_l2g(w_g2l(p[0][c]) + w_g2l(p[1][c]) + w_g2l(p[2][c]) + w_g2l(p[3][c]), 0)       /* SUM4 */
+                          : w_l2g(w_g2l(p[0][c]) + w_g2l(p[2][c]), 1);                                        /* SUM2 */
+        } else {                                                                                               /* LinearToGammaWeighted */
+            const uint32_t sum = p[0][3] * w_g2l(p[0][c]) + p[1][3] * w_g2l(p[1][c]) + p[2][3] * w_g2l(p[2][c]) + p[3][3] * w_g2l(p[3][c]);
+            const uint32_t inv = (1u << kWAlphaFix) / a;                                                       /* kInvAlpha[a] */
+            rgb[c] = w_l2g((uint32_t)(((uint64_t)sum * inv) >> (kWAlphaFix - 2)), 0);                          /* DIVIDE_BY_ALPHA */
+        }
+    }
+    *u = (uint8_t)w_rgb_to_u(rgb[0], rgb[1], rgb[2], kWYuvHalf << 2);
+    *v = (uint8_t)w_rgb_to_v(rgb[0], rgb[1], rgb[2], kWYuvHalf << 2);
+}
+
+/* y: w x h, u / v: ceil(w/2) x ceil(h/2), a: w x h (written only when some alpha != 255); returns has_alpha */
+int so_webp_yuva(const uint8_t *rgba, uint32_t w, uint32_t h, uint8_t *y, uint8_t *u, uint8_t *v, uint8_t *a)
+{
+    w_init();
+    int has_alpha = 0;
+    for (size_t i = 0; i < (size_t)w * h; i++) has_alpha |= rgba[4 * i + 3] != 0xff;          /* CheckNonOpaque */
+    const uint32_t uvw = (w + 1) / 2;
+    for (uint32_t yy = 0; yy < h; yy++)
+        for (uint32_t x = 0; x < w; x++) {
+            const uint8_t *p = rgba + ((size_t)yy * w + x) * 4;
+            y[(size_t)yy * w + x] = (uint8_t)w_rgb_to_y(p[0], p[1], p[2], kWYuvHalf);
+            if (has_alpha) a[(size_t)yy * w + x] = p[3];
+        }
+    for (uint32_t cy = 0; cy < (h + 1) / 2; cy++) {
+        const uint32_t y0 = 2 * cy, y1 = (2 * cy + 1 < h) ? 2 * cy + 1 : 2 * cy;              /* odd height: the last row twice */
+        /* rows_have_alpha: the weighted path is taken only when these two rows contain some alpha != 255 */
+        int rows_alpha = 0;
+        if (has_alpha)
+            for (uint32_t x = 0; x < w; x++) rows_alpha |= rgba[((size_t)y0 * w + x) * 4 + 3] != 0xff || rgba[((size_t)y1 * w + x) * 4 + 3] != 0xff;
+        for (uint32_t cx = 0; cx < uvw; cx++) {
+            const uint32_t x0 = 2 * cx;
+            const int wide = x0 + 1 < w;
+            const uint32_t x1 = wide ? x0 + 1 : x0;
+            const uint8_t *p[4] = { rgba + ((size_t)y0 * w + x0) * 4, rgba + ((size_t)y0 * w + x1) * 4,
+                                    rgba + ((size_t)y1 * w + x0) * 4, rgba + ((size_t)y1 * w + x1) * 4 };
+            w_chroma(p, wide, rows_alpha, &u[(size_t)cy * uvw + cx], &v[(size_t)cy * uvw + cx]);
+        }
+    }
+    return has_alpha;
+}
+
+/* ---- ravif src/av1encoder.rs: rgb_to_ycbcr (BT.601, full range, 4:4:4), 8 or 10 bits; alpha as its own plane ---- */
+static float so_f32_round(float x) { return x < 0.0f ? -floorf(-x + 0.5f) : floorf(x + 0.5f); }   /* f32::round: half away from zero */
+void so_avif_planes(const uint8_t *rgba, uint32_t w, uint32_t h, int depth, uint16_t *y, uint16_t *cb, uint16_t *cr, uint16_t *a)
+{
+    const float m0 = 0.2990f, m1 = 0.5870f, m2 = 0.1140f;
+    const float max_value = (float)((1 << depth) - 1);
+    const float scale = max_value / 255.f;
+    const float shift = so_f32_round(max_value * 0.5f);
+    const float kb = 0.5f / (1.f - m2), kr = 0.5f / (1.f - m0);
+    for (size_t i = 0; i < (size_t)w * h; i++) {
+        const float r = (float)rgba[4 * i], g = (float)rgba[4 * i + 1], b = (float)rgba[4 * i + 2];
+        volatile float t0 = scale * m0, t1 = scale * m1, t2 = scale * m2;          /* no contraction: every product rounds to f32 */
+        volatile float p0 = t0 * r, p1 = t1 * g, p2 = t2 * b;
+        volatile float s01 = p0 + p1;
+        const float yv = s01 + p2;
+        volatile float db = b * scale, dr = r * scale;
+        const float cbv = fmaf(db - yv, kb, shift), crv = fmaf(dr - yv, kr, shift);  /* mul_add: ONE rounding */
+        const float yr = so_f32_round(yv), br = so_f32_round(cbv), rr = so_f32_round(crv);
+        y[i] = (uint16_t)(yr < 0 ? 0 : yr > max_value ? max_value : yr);            /* `as u8 / u16` saturates */
+        cb[i] = (uint16_t)(br < 0 ? 0 : br > max_value ? max_value : br);
+        cr[i] = (uint16_t)(rr < 0 ? 0 : rr > max_value ? max_value : rr);
+        /* alpha plane: 8 bit as is; 10 bit as ravif's to_ten(): (x << 2) | (x >> 6) */
+        a[i] = depth == 8 ? rgba[4 * i + 3] : (uint16_t)(((uint16_t)rgba[4 * i + 3] << 2) | (rgba[4 * i + 3] >> 6));
+    }
+}

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libslimg_b200.so")
-SOURCES = ["geometry.cpp", "taps.cpp", "fastplan.cpp", "vplan.cpp", "tcplan.cpp", "tileplan.cpp", "k1_remap.cu", "k2_resize.cu", "k2_fast.cu", "k2_vfirst.cu", "k2_tc.cu", "k2_tile.cu", "k3_jpeg.cu", "api.cu", "uniffi_abi.cpp"]
+SOURCES = ["geometry.cpp", "taps.cpp", "fastplan.cpp", "vplan.cpp", "tcplan.cpp", "tileplan.cpp", "k1_remap.cu", "k2_resize.cu", "k2_fast.cu", "k2_vfirst.cu", "k2_tc.cu", "k2_tile.cu", "k3_jpeg.cu", "k4_planes.cu", "api.cu", "uniffi_abi.cpp"]
 HEADERS = ["host.h", "kernels.cuh", os.path.join("..", "..", "include", "slimg_b200.h"),
            os.path.join("..", "..", "include", "slimg_uniffi.h")]
 

@@ -60,6 +60,12 @@ class CJpegCoefs(C.Structure):
                 ("y_uq", C.POINTER(C.c_int16)), ("cb_uq", C.POINTER(C.c_int16)), ("cr_uq", C.POINTER(C.c_int16))]
 
 
+class CPlanes(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("kind", C.c_uint32), ("chroma_width", C.c_uint32),
+                ("chroma_height", C.c_uint32), ("bytes_per_sample", C.c_uint32), ("has_alpha", C.c_int32),
+                ("y", C.c_void_p), ("cb", C.c_void_p), ("cr", C.c_void_p), ("a", C.c_void_p)]
+
+
 class CBatchConfig(C.Structure):
     _fields_ = [("n_devices", C.c_int32), ("streams_per_device", C.c_int32), ("device_ids", C.POINTER(C.c_int32))]
 
@@ -67,6 +73,7 @@ class CBatchConfig(C.Structure):
 ORDER_CONVERT, ORDER_CHAIN = 0, 1
 QT_ANNEX_K, QT_MOZJPEG = 0, 1
 JPEG_UNQUANTISED = 1
+PLANES_WEBP_YUV420, PLANES_AVIF_YCBCR444_8, PLANES_AVIF_YCBCR444_10 = 1, 2, 3
 PATH_NONE, PATH_REMAP, PATH_GENERIC, PATH_FEWTAPS, PATH_HFIRST, PATH_VFIRST, PATH_TC, PATH_TILE = range(8)
 PATH_NAMES = ("none", "remap", "generic", "fewtaps", "hfirst", "vfirst", "tc", "tile")
 
@@ -82,6 +89,7 @@ ABI_SYMBOLS = (
     "slimg_b200_pipeline_source_window", "slimg_b200_jpeg_frontend_ex", "slimg_b200_pipeline_jpeg",
     "slimg_b200_jpeg_frontend_batch_device_ex", "slimg_b200_pipeline_jpeg_batch_device",
     "slimg_b200_pipeline_jpeg_batch_host", "slimg_b200_last_resize_path", "slimg_b200_path_launches",
+    "slimg_b200_pipeline_planes", "slimg_b200_planes_free", "slimg_b200_color_planes_batch_device",
 )
 
 _lib: Optional[C.CDLL] = None
@@ -132,6 +140,9 @@ def library() -> C.CDLL:
         "slimg_b200_jpeg_frontend_batch_device_ex": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), vp, vp, vp, vp, vp, vp, vp]),
         "slimg_b200_pipeline_jpeg_batch_device": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(CPipelineOptions), C.c_int, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), vp, C.c_size_t, vp, vp, vp, vp, vp, vp, vp]),
         "slimg_b200_pipeline_jpeg_batch_host": (C.c_int32, [C.POINTER(CImage), C.c_uint32, C.POINTER(CPipelineOptions), C.c_int, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.c_uint32, C.POINTER(CBatchConfig), C.POINTER(CJpegCoefs), C.POINTER(C.c_int)]),
+        "slimg_b200_pipeline_planes": (C.c_int, [C.POINTER(CImage), C.POINTER(CPipelineOptions), C.c_int, C.c_int, C.POINTER(CPlanes)]),
+        "slimg_b200_planes_free": (None, [C.POINTER(CPlanes)]),
+        "slimg_b200_color_planes_batch_device": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, vp, vp, vp, vp, vp, vp]),
         "slimg_b200_last_resize_path": (C.c_int32, []),
         "slimg_b200_path_launches": (C.c_uint64, [C.c_int32]),
     }
@@ -451,6 +462,37 @@ def pipeline_jpeg(image: ImageData, options: CPipelineOptions, qt_luma, qt_chrom
     _check(library().slimg_b200_pipeline_jpeg(C.byref(cin), C.byref(options), order, ql, qc, flags, C.byref(out)))
     del keep
     return _take_coefs(out)
+
+
+@dataclass
+class ColorPlanes:
+    """Planes of one image as bytes (u8, or little-endian u16 for the 10-bit kind); ``a`` is None for an opaque WebP import."""
+    width: int
+    height: int
+    kind: int
+    chroma_width: int
+    chroma_height: int
+    bytes_per_sample: int
+    y: bytes
+    cb: bytes
+    cr: bytes
+    a: Optional[bytes]
+
+
+def pipeline_planes(image: ImageData, options: CPipelineOptions, kind: int, order: int = ORDER_CONVERT) -> "ColorPlanes":
+    """Pixel stages + the colour-plane import of the WebP / AVIF encoder, back to back on the device."""
+    cin, keep = _in_image(image)
+    out = CPlanes()
+    _check(library().slimg_b200_pipeline_planes(C.byref(cin), C.byref(options), order, kind, C.byref(out)))
+    del keep
+    try:
+        yb = out.width * out.height * out.bytes_per_sample
+        cb = out.chroma_width * out.chroma_height * out.bytes_per_sample
+        return ColorPlanes(out.width, out.height, out.kind, out.chroma_width, out.chroma_height, out.bytes_per_sample,
+                           C.string_at(out.y, yb), C.string_at(out.cb, cb), C.string_at(out.cr, cb),
+                           C.string_at(out.a, yb) if out.a else None)
+    finally:
+        library().slimg_b200_planes_free(C.byref(out))
 
 
 def last_resize_path() -> int:

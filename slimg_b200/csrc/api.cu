@@ -4,6 +4,7 @@
 // rayon `par_iter` over files does (cli/src/commands/mod.rs:64-72, crop.rs:112, extend.rs:114,
 // convert.rs:60).
 #include <atomic>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -741,6 +742,43 @@ static slimg_status run_jpeg_device(const uint8_t *src, uint32_t n, uint32_t w, 
 }
 
 
+// libwebp InitGammaTables (picture_csp_enc.c): kGamma = 0.80, 12-bit linear scale, 32-entry inverse table
+static void webp_gamma_tables(uint16_t g2l[256], int32_t l2g[33]) {
+    const double gamma = 0.80, norm = 1.0 / 255.0, scale = double(1 << 7) / 4095.0;
+    for (int v = 0; v <= 255; v++) g2l[v] = uint16_t(std::pow(norm * v, gamma) * 4095.0 + .5);
+    for (int v = 0; v <= 32; v++) l2g[v] = int32_t(255. * std::pow(scale * v, 1. / gamma) + .5);
+}
+
+static slimg_status run_planes_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h, int kind, void *y, void *cb,
+                                      void *cr, void *a, void *scratch, cudaStream_t stream) {
+    const size_t px = size_t(w) * h;
+    if (kind == SLIMG_PLANES_WEBP_YUV420) {
+        WebpPlanesParams p{};
+        p.src = src; p.src_img_bytes = px * 4; p.y_img_bytes = px;
+        p.uv_img_bytes = size_t((w + 1) / 2) * ((h + 1) / 2);
+        p.w = w; p.h = h;
+        p.y = static_cast<uint8_t *>(y); p.u = static_cast<uint8_t *>(cb); p.v = static_cast<uint8_t *>(cr); p.a = static_cast<uint8_t *>(a);
+        if (a && scratch) {
+            const size_t rows = size_t(n) * ((h + 1) / 2);
+            p.row_alpha = static_cast<uint8_t *>(scratch);
+            p.any_alpha = reinterpret_cast<uint32_t *>(static_cast<uint8_t *>(scratch) + ((rows + 3) & ~size_t(3)));
+            CU(cudaMemsetAsync(p.any_alpha, 0, size_t(n) * 4, stream));
+        }
+        webp_gamma_tables(p.g2l, p.l2g);
+        CU(launch_webp_planes(p, n, stream));
+        return SLIMG_OK;
+    }
+    if (kind == SLIMG_PLANES_AVIF_YCBCR444_8 || kind == SLIMG_PLANES_AVIF_YCBCR444_10) {
+        AvifPlanesParams p{};
+        p.src = src; p.src_img_bytes = px * 4; p.w = w; p.h = h;
+        p.depth = kind == SLIMG_PLANES_AVIF_YCBCR444_8 ? 8 : 10;
+        p.y = y; p.cb = cb; p.cr = cr; p.a = a;
+        CU(launch_avif_planes(p, n, stream));
+        return SLIMG_OK;
+    }
+    return fail(SLIMG_ERR_IMAGE, "unknown plane kind");
+}
+
 // what a convert-to-JPEG call wants after the pixel stages
 struct JpegRequest {
     const uint16_t *ql, *qc;
@@ -1114,6 +1152,82 @@ int32_t slimg_b200_pipeline_jpeg_batch_host(const slimg_image *in, uint32_t n, c
     for (uint32_t i = 0; out && i < n; i++) std::memset(&out[i], 0, sizeof out[i]);
     const JpegRequest jq{qt_luma, qt_chroma, flags, nullptr};
     return batch_host(in, n, opts, order, cfg, nullptr, &jq, out, statuses);
+}
+
+slimg_status slimg_b200_color_planes_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h, int kind, void *y,
+                                                  void *cb, void *cr, void *a, void *scratch, void *stream) {
+    if (n && (!src || !y || !cb || !cr)) return fail(SLIMG_ERR_IMAGE, "null argument");
+    if (kind != SLIMG_PLANES_WEBP_YUV420 && !a && n) return fail(SLIMG_ERR_IMAGE, "the AVIF planes include alpha");
+    if (w == 0 || h == 0) return fail(SLIMG_ERR_ENCODE, "image has a zero dimension");
+    slimg_status st = check_device();
+    if (st != SLIMG_OK) return st;
+    return run_planes_device(src, n, w, h, kind, y, cb, cr, a, scratch, static_cast<cudaStream_t>(stream));
+}
+
+slimg_status slimg_b200_pipeline_planes(const slimg_image *in, const slimg_pipeline_options *opts, int order, int kind,
+                                        slimg_planes *out) {
+    if (!opts || !out) return fail(SLIMG_ERR_IMAGE, "null argument");
+    if (kind < SLIMG_PLANES_WEBP_YUV420 || kind > SLIMG_PLANES_AVIF_YCBCR444_10) return fail(SLIMG_ERR_IMAGE, "unknown plane kind");
+    slimg_status st = validate_image(in, *opts, order);
+    if (st != SLIMG_OK) return st;
+    PipeGeom g;
+    if ((st = build_geometry(in->width, in->height, *opts, order, g)) != SLIMG_OK) return st;
+    if ((st = check_device()) != SLIMG_OK) return st;
+    const bool identity = !opts->has_resize && !opts->has_crop && !opts->has_extend;
+    const size_t src_bytes = size_t(g.sw) * g.sh * 4, dst_bytes = size_t(g.fw) * g.fh * 4, px = size_t(g.fw) * g.fh;
+    const bool webp = kind == SLIMG_PLANES_WEBP_YUV420;
+    const uint32_t cw = webp ? (g.fw + 1) / 2 : g.fw, chh = webp ? (g.fh + 1) / 2 : g.fh;
+    const size_t bps = kind == SLIMG_PLANES_AVIF_YCBCR444_10 ? 2 : 1;
+    const size_t y_bytes = px * bps, c_bytes = size_t(cw) * chh * bps;
+    const size_t rows = (size_t(chh) + 3) & ~size_t(3);
+    const size_t total = y_bytes * 2 + c_bytes * 2;                 // y, cb, cr, a
+    cudaStream_t stream = cudaStreamPerThread;
+    uint8_t *d_src = nullptr, *d_dst = nullptr, *d_pl = nullptr, *d_scr = nullptr;
+    uint8_t *host = static_cast<uint8_t *>(std::malloc(total ? total : 1));
+    if (!host) return fail(SLIMG_ERR_IMAGE, "out of host memory");
+    auto cleanup = [&](slimg_status s) {
+        if (d_src) cudaFreeAsync(d_src, stream);
+        if (d_dst) cudaFreeAsync(d_dst, stream);
+        if (d_pl) cudaFreeAsync(d_pl, stream);
+        if (d_scr) cudaFreeAsync(d_scr, stream);
+        if (s != SLIMG_OK) std::free(host);
+        return s;
+    };
+    cudaError_t e;
+    RingLease lease;
+    if ((e = cudaMallocAsync((void **)&d_src, src_bytes, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    if (!identity && (e = cudaMallocAsync((void **)&d_dst, dst_bytes, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    if ((e = cudaMallocAsync((void **)&d_pl, total, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    if (webp && (e = cudaMallocAsync((void **)&d_scr, rows + 4, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "cudaMallocAsync"));
+    uint32_t r0 = 0, r1 = g.sh, c0 = 0, c1 = g.sw;
+    if (!identity && (st = source_window(g, r0, r1, c0, c1)) != SLIMG_OK) return cleanup(st);
+    if (r1 > r0 && c1 > c0) {
+        const size_t off = size_t(r0) * g.sw * 4;
+        if ((e = copy_h2d(d_src + off, in->data + off, size_t(r1 - r0) * g.sw * 4, stream, lease)) != cudaSuccess) return cleanup(cuda_fail(e, "H2D"));
+    }
+    const uint8_t *d_pixels = d_src;
+    if (!identity) {
+        if ((st = run_pipeline_device(g, d_src, 1, d_dst, stream)) != SLIMG_OK) return cleanup(st);
+        d_pixels = d_dst;
+    }
+    uint8_t *dy = d_pl, *dcb = dy + y_bytes, *dcr = dcb + c_bytes, *da = dcr + c_bytes;
+    if ((st = run_planes_device(d_pixels, 1, g.fw, g.fh, kind, dy, dcb, dcr, da, d_scr, stream)) != SLIMG_OK) return cleanup(st);
+    uint32_t any_alpha = 1;
+    if ((e = copy_d2h(host, d_pl, total, stream, lease)) != cudaSuccess) return cleanup(cuda_fail(e, "D2H"));
+    if (webp && (e = cudaMemcpyAsync(&any_alpha, d_scr + rows, 4, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return cleanup(cuda_fail(e, "D2H"));
+    if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return cleanup(cuda_fail(e, "plane kernels"));
+    cleanup(SLIMG_OK);
+    std::memset(out, 0, sizeof *out);
+    out->width = g.fw; out->height = g.fh; out->kind = uint32_t(kind);
+    out->chroma_width = cw; out->chroma_height = chh; out->bytes_per_sample = uint32_t(bps);
+    out->has_alpha = any_alpha ? 1 : 0;
+    out->y = host; out->cb = host + y_bytes; out->cr = host + y_bytes + c_bytes;
+    out->a = (webp && !any_alpha) ? nullptr : host + y_bytes + 2 * c_bytes;
+    return SLIMG_OK;
+}
+
+void slimg_b200_planes_free(slimg_planes *p) {
+    if (p && p->y) { std::free(p->y); p->y = p->cb = p->cr = p->a = nullptr; }
 }
 
 int32_t slimg_b200_last_resize_path(void) { return t_last_path; }

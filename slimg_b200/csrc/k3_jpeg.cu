@@ -501,12 +501,13 @@ cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStr
     const unsigned mcus_x = p.c_wb, mcus_y = p.c_hb;
     const bool uq = p.yu != nullptr;
     if (uq && (!p.cbu || !p.cru)) return cudaErrorInvalidValue;
-    // SLIMG_B200_JPEG_VAR (A/B): 5 (default) / 6 / 7 = stage 2 on the tensor cores at 6 / 8 / 6 CTAs per SM (7: with the
-    // stage-1 prefetch); CUDA-core stage 2: 0 = no stage-1 prefetch, 1 = patch j+1 in flight while patch j is converted,
-    // 2 = also the next tile's first patch across stage 2 (80 registers, 6 CTAs/SM), 3 / 4 = as 1 with 7 / 6 CTAs/SM.  Round 1 measured occupancy (32 warps/SM at <= 64 registers)
-    // above everything else: <unroll 1, 8 CTAs/SM> 67.9 us, <1, 6> 69.2 us, <unroll 4, 4> 79.7 us per 24 MP image.
+    // SLIMG_B200_JPEG_VAR (A/B, 24 MP q = 70 on B200, profiles/r02_k3_variants.txt): stage 2 on the tensor cores -- 8 (default:
+    // 5 CTAs/SM, 92 registers, no spills) 63.9 us, 5 (6 CTAs/SM) 65.4, 6 (8 CTAs/SM, spills) 69.7, 9 (4 CTAs/SM) 68.7, 7 = 5 with the
+    // stage-1 prefetch; stage 2 on the CUDA cores -- 0 65.1 us, 1 (patch j+1 in flight while patch j is converted) 66.8,
+    // 2 (also the next tile's first patch across stage 2) 65.2, 3 / 4 = as 1 with 7 / 6 CTAs/SM 65.5 / 64.2.  The load
+    // prefetch buys nothing: the kernel is bound by instruction issue, not by exposed load latency.
     const char *var_env = std::getenv("SLIMG_B200_JPEG_VAR");
-    const int var = var_env ? std::atoi(var_env) : 5;
+    const int var = var_env ? std::atoi(var_env) : 8;
     using Kern = void (*)(const JpegParams, const uint32_t);
     Kern kern;
 #define SLIMG_K3_PICK(U)                                                                                                     \

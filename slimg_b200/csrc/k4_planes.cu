@@ -1,0 +1,169 @@
+// k4_planes.cu -- the colour-plane pre-stages of the reference's other lossy encoders, so that a WebP or
+// AVIF convert can keep the resized image in HBM and hand the encoder the planes it would have computed itself:
+//   WebP  codec/webp.rs:25-30  webp::Encoder::from_rgba -> libwebp WebPPictureImportRGBA: RGBA -> Y (every pixel) and
+//         U / V (one per 2 x 2, averaged in the "gamma 0.80" domain of picture_csp_enc.c, alpha-weighted where the block
+//         is partly transparent), plus the alpha plane when any pixel is not opaque
+//   AVIF  codec/avif.rs:28-47  ravif::Encoder::encode_rgba: RGBA -> YCbCr 4:4:4, BT.601 full range, 8 or 10 bits, f32
+//         arithmetic with one fused multiply-add per chroma sample, plus the alpha plane
+// Both libraries are crates.io dependencies absent from the reference tree: the arithmetic is restated from their published
+// sources (oracle/slimg_oracle.c holds the CPU restatement the tests compare with) -- PARITY UNPINNED, said so in DESIGN.md.
+// Roofline: HBM (4 B/px read; 1.5 - 2.5 B/px written for WebP, 4 - 8 B/px for AVIF); pure streaming kernels.
+#include "kernels.cuh"
+
+namespace slimg {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ int w_l2g(const int *l2g, uint32_t base_value, int shift) {      // LinearToGamma
+    const uint32_t v = base_value << shift;
+    const int tab_pos = int(v >> 9), x = int(v & 511u);
+    const int y = l2g[tab_pos + 1] * x + l2g[tab_pos] * (512 - x);
+    return (y + 64) >> 7;
+}
+__device__ __forceinline__ int w_clip_uv(int uv) {
+    uv = (uv + (1 << 17) + (128 << 18)) >> 18;
+    return min(max(uv, 0), 255);
+}
+
+// one thread = one chroma sample = (up to) 2 x 2 pixels; grid.z = image
+__global__ void __launch_bounds__(kThreads) webp_planes_kernel(const WebpPlanesParams p) {
+    __shared__ uint16_t g2l[256];
+    __shared__ int l2g[33];
+    for (int i = threadIdx.x; i < 256; i += kThreads) g2l[i] = p.g2l[i];
+    if (threadIdx.x < 33) l2g[threadIdx.x] = p.l2g[threadIdx.x];
+    __syncthreads();
+    const int cx = blockIdx.x * 64 + (threadIdx.x & 63), cy = blockIdx.y * 4 + (threadIdx.x >> 6);
+    const int w = int(p.w), h = int(p.h), uvw = (w + 1) >> 1, uvh = (h + 1) >> 1;
+    if (cx >= uvw || cy >= uvh) return;
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(p.src + size_t(blockIdx.z) * p.src_img_bytes);
+    const int x0 = 2 * cx, y0 = 2 * cy;
+    const bool wide = x0 + 1 < w, tall = y0 + 1 < h;
+    const int x1 = wide ? x0 + 1 : x0, y1 = tall ? y0 + 1 : y0;
+    uint32_t px[4];
+    if (wide && (w & 1) == 0) {                       // 8-byte loads: two pixels of a row
+        const uint2 a = __ldg(reinterpret_cast<const uint2 *>(src + size_t(y0) * w + x0));
+        const uint2 b = __ldg(reinterpret_cast<const uint2 *>(src + size_t(y1) * w + x0));
+        px[0] = a.x; px[1] = a.y; px[2] = b.x; px[3] = b.y;
+    } else {
+        px[0] = __ldg(src + size_t(y0) * w + x0); px[1] = __ldg(src + size_t(y0) * w + x1);
+        px[2] = __ldg(src + size_t(y1) * w + x0); px[3] = __ldg(src + size_t(y1) * w + x1);
+    }
+    uint8_t *Y = p.y + size_t(blockIdx.z) * p.y_img_bytes;
+    uint8_t *A = p.a ? p.a + size_t(blockIdx.z) * p.y_img_bytes : nullptr;
+    int yv[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {                     // VP8RGBToY
+        const int r = px[k] & 0xff, g = (px[k] >> 8) & 0xff, b = (px[k] >> 16) & 0xff;
+        yv[k] = (16839 * r + 33059 * g + 6420 * b + (1 << 15) + (16 << 16)) >> 16;
+    }
+    Y[size_t(y0) * w + x0] = uint8_t(yv[0]);
+    if (wide) Y[size_t(y0) * w + x1] = uint8_t(yv[1]);
+    if (tall) { Y[size_t(y1) * w + x0] = uint8_t(yv[2]); if (wide) Y[size_t(y1) * w + x1] = uint8_t(yv[3]); }
+    if (A) {
+        A[size_t(y0) * w + x0] = uint8_t(px[0] >> 24);
+        if (wide) A[size_t(y0) * w + x1] = uint8_t(px[1] >> 24);
+        if (tall) { A[size_t(y1) * w + x0] = uint8_t(px[2] >> 24); if (wide) A[size_t(y1) * w + x1] = uint8_t(px[3] >> 24); }
+    }
+    // chroma: AccumulateRGB / AccumulateRGBA.  The alpha-weighted form is used only in row pairs that contain a pixel
+    // that is not opaque (libwebp decides per pair of rows); row_alpha[cy] was computed by the scan kernel.
+    const bool rows_alpha = p.row_alpha && p.row_alpha[size_t(blockIdx.z) * uvh + cy];
+    const uint32_t asum = wide ? (px[0] >> 24) + (px[1] >> 24) + (px[2] >> 24) + (px[3] >> 24) : 2u * ((px[0] >> 24) + (px[2] >> 24));
+    int rgb[3];
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const uint32_t v0 = g2l[(px[0] >> (8 * c)) & 0xff], v1 = g2l[(px[1] >> (8 * c)) & 0xff];
+        const uint32_t v2 = g2l[(px[2] >> (8 * c)) & 0xff], v3 = g2l[(px[3] >> (8 * c)) & 0xff];
+        if (!rows_alpha || asum == 4u * 0xffu || asum == 0u) rgb[c] = wide ? w_l2g(l2g, v0 + v1 + v2 + v3, 0) : w_l2g(l2g, v0 + v2, 1);
+        else {
+            const uint32_t sum = (px[0] >> 24) * v0 + (px[1] >> 24) * v1 + (px[2] >> 24) * v2 + (px[3] >> 24) * v3;
+            const uint32_t inv = (1u << 19) / asum;
+            rgb[c] = w_l2g(l2g, uint32_t((uint64_t(sum) * inv) >> 17), 0);
+        }
+    }
+    const size_t uvo = size_t(blockIdx.z) * p.uv_img_bytes + size_t(cy) * uvw + cx;
+    p.u[uvo] = uint8_t(w_clip_uv(-9719 * rgb[0] - 19081 * rgb[1] + 28800 * rgb[2]));
+    p.v[uvo] = uint8_t(w_clip_uv(28800 * rgb[0] - 24116 * rgb[1] - 4684 * rgb[2]));
+}
+
+// CheckNonOpaque per pair of rows: row_alpha[img][cy] = some alpha of rows 2cy, 2cy+1 is not 255; any[img] = OR of them
+__global__ void __launch_bounds__(kThreads) webp_alpha_scan_kernel(const WebpPlanesParams p) {
+    const int cy = blockIdx.x, w = int(p.w), h = int(p.h);
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(p.src + size_t(blockIdx.z) * p.src_img_bytes);
+    const int y0 = 2 * cy, y1 = min(2 * cy + 1, h - 1);
+    int found = 0;
+    for (int x = threadIdx.x; x < w; x += kThreads)
+        found |= ((__ldg(src + size_t(y0) * w + x) >> 24) != 0xffu) | ((__ldg(src + size_t(y1) * w + x) >> 24) != 0xffu);
+    found = __syncthreads_or(found);
+    if (threadIdx.x == 0) {
+        p.row_alpha[size_t(blockIdx.z) * ((h + 1) >> 1) + cy] = uint8_t(found != 0);
+        if (found) p.any_alpha[blockIdx.z] = 1u;
+    }
+}
+
+__device__ __forceinline__ float round_away(float x) { return x < 0.0f ? -floorf(0.5f - x) : floorf(x + 0.5f); }
+
+// one thread = 4 pixels (one 16-byte load); DEPTH 8: u8 planes, 10: u16 planes
+template <int DEPTH>
+__global__ void __launch_bounds__(kThreads) avif_planes_kernel(const AvifPlanesParams p) {
+    using T = typename std::conditional<DEPTH == 8, uint8_t, uint16_t>::type;
+    const size_t n = size_t(p.w) * p.h, i0 = (size_t(blockIdx.x) * kThreads + threadIdx.x) * 4;
+    if (i0 >= n) return;
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(p.src + size_t(blockIdx.z) * p.src_img_bytes);
+    uint32_t px[4];
+    const int cnt = n - i0 < 4 ? int(n - i0) : 4;
+    if (cnt == 4 && (p.src_img_bytes & 15) == 0 && (reinterpret_cast<uintptr_t>(p.src) & 15) == 0) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(src + i0));
+        px[0] = v.x; px[1] = v.y; px[2] = v.z; px[3] = v.w;
+    } else
+        for (int k = 0; k < cnt; k++) px[k] = __ldg(src + i0 + k);
+    constexpr float m0 = 0.2990f, m1 = 0.5870f, m2 = 0.1140f;
+    const float max_value = float((1 << DEPTH) - 1);
+    const float scale = __fdiv_rn(max_value, 255.f);
+    const float shift = round_away(__fmul_rn(max_value, 0.5f));
+    const float kb = __fdiv_rn(0.5f, __fsub_rn(1.f, m2)), kr = __fdiv_rn(0.5f, __fsub_rn(1.f, m0));
+    const float t0 = __fmul_rn(scale, m0), t1 = __fmul_rn(scale, m1), t2 = __fmul_rn(scale, m2);
+    T *Y = reinterpret_cast<T *>(p.y) + size_t(blockIdx.z) * n, *Cb = reinterpret_cast<T *>(p.cb) + size_t(blockIdx.z) * n;
+    T *Cr = reinterpret_cast<T *>(p.cr) + size_t(blockIdx.z) * n, *A = reinterpret_cast<T *>(p.a) + size_t(blockIdx.z) * n;
+    for (int k = 0; k < cnt; k++) {
+        const float r = float(px[k] & 0xff), g = float((px[k] >> 8) & 0xff), b = float((px[k] >> 16) & 0xff);
+        const uint32_t al = px[k] >> 24;
+        // every product and sum rounds to f32 (the reference build does not contract); the chroma terms are ONE fused multiply-add
+        const float yv = __fadd_rn(__fadd_rn(__fmul_rn(t0, r), __fmul_rn(t1, g)), __fmul_rn(t2, b));
+        const float cbv = __fmaf_rn(__fsub_rn(__fmul_rn(b, scale), yv), kb, shift);
+        const float crv = __fmaf_rn(__fsub_rn(__fmul_rn(r, scale), yv), kr, shift);
+        Y[i0 + k] = T(fminf(fmaxf(round_away(yv), 0.f), max_value));
+        Cb[i0 + k] = T(fminf(fmaxf(round_away(cbv), 0.f), max_value));
+        Cr[i0 + k] = T(fminf(fmaxf(round_away(crv), 0.f), max_value));
+        A[i0 + k] = DEPTH == 8 ? T(al) : T((al << 2) | (al >> 6));
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_webp_planes(const WebpPlanesParams &p, uint32_t n_images, cudaStream_t stream) {
+    if (n_images == 0 || p.w == 0 || p.h == 0) return cudaSuccess;
+    if (n_images > 65535) return cudaErrorInvalidValue;
+    const unsigned uvw = (p.w + 1) / 2, uvh = (p.h + 1) / 2;
+    if (p.row_alpha) {
+        webp_alpha_scan_kernel<<<dim3(uvh, 1, n_images), kThreads, 0, stream>>>(p);
+        count_launch();
+    }
+    webp_planes_kernel<<<dim3((uvw + 63) / 64, (uvh + 3) / 4, n_images), kThreads, 0, stream>>>(p);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_avif_planes(const AvifPlanesParams &p, uint32_t n_images, cudaStream_t stream) {
+    if (n_images == 0 || p.w == 0 || p.h == 0) return cudaSuccess;
+    if (n_images > 65535 || (p.depth != 8 && p.depth != 10)) return cudaErrorInvalidValue;
+    const size_t n = size_t(p.w) * p.h;
+    const unsigned blocks = unsigned((n + size_t(kThreads) * 4 - 1) / (size_t(kThreads) * 4));
+    if (p.depth == 8) avif_planes_kernel<8><<<dim3(blocks, 1, n_images), kThreads, 0, stream>>>(p);
+    else avif_planes_kernel<10><<<dim3(blocks, 1, n_images), kThreads, 0, stream>>>(p);
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace slimg

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <cstddef>
 #include <cstdint>
+#include <type_traits>
 
 #include "../../include/slimg_b200.h"
 
@@ -224,6 +225,26 @@ struct JpegParams {
     uint32_t debug;                    // experiment switches (SLIMG_B200_JPEG_DEBUG), 0 in production
 };
 cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStream_t stream);
+
+// ---- K4: colour planes for the WebP / AVIF encoders (k4_planes.cu) ---------------------------------------------------
+struct WebpPlanesParams {
+    const uint8_t *src;                // RGBA8, n images back to back
+    size_t src_img_bytes, y_img_bytes, uv_img_bytes;
+    uint32_t w, h;
+    uint8_t *y, *u, *v, *a;            // y / a: w x h; u / v: ceil(w/2) x ceil(h/2); a may be NULL
+    uint8_t *row_alpha;                // [n][ceil(h/2)] scratch: a row pair holds a pixel that is not opaque (NULL: treat all as opaque)
+    uint32_t *any_alpha;               // [n] OR of row_alpha (must be zeroed by the caller)
+    uint16_t g2l[256];                 // libwebp kGammaToLinearTab
+    int32_t l2g[33];                   // libwebp kLinearToGammaTab
+};
+cudaError_t launch_webp_planes(const WebpPlanesParams &p, uint32_t n_images, cudaStream_t stream);
+struct AvifPlanesParams {
+    const uint8_t *src;
+    size_t src_img_bytes;
+    uint32_t w, h, depth;              // depth 8: u8 planes; 10: u16 planes
+    void *y, *cb, *cr, *a;             // w x h each, n images back to back
+};
+cudaError_t launch_avif_planes(const AvifPlanesParams &p, uint32_t n_images, cudaStream_t stream);
 
 // process-wide count of kernels launched by this library (slimg_b200_kernel_launches)
 void count_launch(uint64_t n = 1);
