@@ -316,6 +316,37 @@ def config_table(ll, torch, peak, main_src):
     pixel_config("C4b 1024x1024 -> Scale(4.0)", 1024, 1024, dict(resize=ll.ResizeMode.SCALE(4.0)), ll.ORDER_CONVERT, 64,
                  4_194_304 + 67_108_864, lambda a: oracle.resize(a, R.scale(4.0)))
 
+    pixel_config("GUI thumbnail 4000x3000 -> Fit(400,400)", 4000, 3000, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 64,
+                 48_000_000 + 400 * 300 * 4, lambda a: oracle.resize(a, R.fit(400, 400)))
+
+    # colour planes for the WebP / AVIF encoders, 24 MP batch; planes vs the oracle's restatement (unpinned)
+    nb = 16
+    srcp = main_src[:nb]
+    n_px = SRC_W * SRC_H
+    for name, kind, bps, csz in (("WebP import: RGBA -> YUV 4:2:0 + A (libwebp gamma-domain chroma), 6000x4000", ll.PLANES_WEBP_YUV420, 1, n_px // 4),
+                                 ("AVIF import: RGBA -> YCbCr 4:4:4 10-bit + A (ravif, BT.601 full range), 6000x4000", ll.PLANES_AVIF_YCBCR444_10, 2, n_px)):
+        dt = torch.uint8 if bps == 1 else torch.int16
+        py, pa = torch.empty((nb, n_px), dtype=dt, device="cuda"), torch.empty((nb, n_px), dtype=dt, device="cuda")
+        pcb, pcr = torch.empty((nb, csz), dtype=dt, device="cuda"), torch.empty((nb, csz), dtype=dt, device="cuda")
+        scr = torch.zeros((nb * (SRC_H // 2) + 4 * nb + 64,), dtype=torch.uint8, device="cuda")
+        lib = ll.library()
+        ms = timed(lambda: ll._check(lib.slimg_b200_color_planes_batch_device(srcp.data_ptr(), nb, SRC_W, SRC_H, kind, py.data_ptr(), pcb.data_ptr(),
+                                                                              pcr.data_ptr(), pa.data_ptr(), scr.data_ptr(), stream)))
+        img0 = srcp[0].cpu().numpy()
+        if kind == ll.PLANES_WEBP_YUV420:
+            wy, wu, wv, wa = oracle.webp_yuva(img0)
+            diff = int(np.count_nonzero(py[0].cpu().numpy().reshape(wy.shape) != wy)) + int(np.count_nonzero(pcb[0].cpu().numpy().reshape(wu.shape) != wu)) \
+                + int(np.count_nonzero(pcr[0].cpu().numpy().reshape(wv.shape) != wv)) + int(np.count_nonzero(pa[0].cpu().numpy().reshape(wy.shape) != wa))
+            alg = n_px * 4 + n_px * 2 + 2 * csz
+        else:
+            want = oracle.avif_planes(img0, 10)
+            diff = sum(int(np.count_nonzero(t[0].cpu().numpy().view(np.uint16).reshape(wv.shape) != wv)) for t, wv in zip((py, pcb, pcr, pa), want))
+            alg = n_px * 4 + n_px * 2 * 4
+        us = ms / nb * 1e3
+        out[name] = {"us_per_image": us, "mpx_per_s": n_px / us, "algorithmic_bytes": alg, "frac": alg / (us * 1e-6) / 1e9 / peak, "batch": nb,
+                     "kernel": "webp_planes_kernel" if bps == 1 else "avif_planes_kernel", "differing_samples": diff, "parity": "unpinned (libwebp / ravif absent)"}
+        del py, pa, pcb, pcr, scr
+
     # C5: JPEG front end, q = 70, 24 MP batch; MozJPEG's table set (the reference encoder) -- coefficients vs the oracle
     nb = 32
     g = ll.jpeg_geometry(SRC_W, SRC_H)
