@@ -161,7 +161,10 @@ enum { SLIMG_QT_ANNEX_K = 0,            /* libjpeg-turbo jcparam.c:73-92 */
        SLIMG_QT_MOZJPEG = 1 };          /* MozJPEG default table set 3, luma == chroma */
 
 /* flags of the JPEG entry points */
-enum { SLIMG_JPEG_UNQUANTISED = 1 };    /* also return the un-quantised coefficient planes */
+enum { SLIMG_JPEG_UNQUANTISED = 1,      /* also return the un-quantised coefficient planes */
+       SLIMG_JPEG_DERINGING = 2 };      /* MozJPEG's front-end defaults: overshoot deringing of blocks that hold clipped
+                                           whites before the DCT, quantised values clamped to 10 bits.  mozjpeg-sys is not in the reference
+                                           tree: restated from its published source, parity unpinned. */
 
 void slimg_b200_jpeg_geometry(uint32_t w, uint32_t h, slimg_jpeg_geometry *g);
 /* jpeg_set_quality(q, force_baseline = FALSE): jcparam.c:28-65,130-168 */
@@ -220,7 +223,7 @@ slimg_status slimg_b200_jpeg_frontend_batch_device(const uint8_t *src, uint32_t 
 slimg_status slimg_b200_jpeg_frontend_batch_device_ex(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
                                                       const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
                                                       int16_t *y, int16_t *cb, int16_t *cr,
-                                                      int16_t *y_uq, int16_t *cb_uq, int16_t *cr_uq, void *stream);
+                                                      int16_t *y_uq, int16_t *cb_uq, int16_t *cr_uq, uint32_t flags, void *stream);
 /* pixel pipeline + JPEG front end on device-resident batches; `pixels` is device scratch for the n final images
  * (n * out_w*out_h*4 bytes, the pipeline's output, which the front end reads back from HBM / L2) */
 slimg_status slimg_b200_pipeline_jpeg_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
@@ -228,7 +231,7 @@ slimg_status slimg_b200_pipeline_jpeg_batch_device(const uint8_t *src, uint32_t 
                                                    const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
                                                    uint8_t *pixels, size_t pixels_capacity,
                                                    int16_t *y, int16_t *cb, int16_t *cr,
-                                                   int16_t *y_uq, int16_t *cb_uq, int16_t *cr_uq, void *stream);
+                                                   int16_t *y_uq, int16_t *cb_uq, int16_t *cr_uq, uint32_t flags, void *stream);
 
 /* ---- batched, host buffers: the `--jobs` scheduler (cli/src/commands/mod.rs:64-72 and the
  * par_iter sites crop.rs:112, extend.rs:114, convert.rs:60).  Images are independent (and may differ in size: a

@@ -241,6 +241,23 @@ def jpeg_frontend(img: np.ndarray, qt_luma: np.ndarray, qt_chroma: np.ndarray):
     return y, cb, cr
 
 
+def jpeg_frontend_mozjpeg(img: np.ndarray, qt_luma: np.ndarray, qt_chroma: np.ndarray):
+    """The planes with MozJPEG's front-end defaults: overshoot deringing, 10-bit clamp (restated, unpinned)."""
+    img = _as_rgba(img)
+    h, w = img.shape[:2]
+    y, cb, cr = _coef_planes(jpeg_geometry(w, h))
+    ql = np.ascontiguousarray(qt_luma, np.uint16); qc = np.ascontiguousarray(qt_chroma, np.uint16)
+    lib().so_jpeg_frontend_mozjpeg(_ptr(img, _u8p), C.c_uint32(w), C.c_uint32(h), _ptr(ql, _u16p), _ptr(qc, _u16p),
+                                   _ptr(y, _i16p), _ptr(cb, _i16p), _ptr(cr, _i16p))
+    return y, cb, cr
+
+
+def preprocess_deringing(block: np.ndarray, dc_quant: int) -> np.ndarray:
+    ws = np.ascontiguousarray(block, np.int32).reshape(64).copy()
+    lib().so_preprocess_deringing(ws.ctypes.data_as(C.POINTER(C.c_int32)), C.c_uint16(dc_quant))
+    return ws.reshape(8, 8)
+
+
 def jpeg_frontend_unquantised(img: np.ndarray):
     """The DCT output before quantisation (jfdctint.c:143-286, scaled by 8), same plane layout."""
     img = _as_rgba(img)

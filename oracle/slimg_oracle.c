@@ -477,6 +477,55 @@ void so_quantize(const int32_t ws[64], const uint16_t qt[64], int16_t out[64])
 /* qt == NULL: keep the DCT output un-quantised (what MozJPEG copies aside for its trellis pass, SURVEY.md App. B --
  * mozjpeg-sys is not in the reference tree, so only the value, jfdctint.c's output, is pinned; that MozJPEG stores it
  * per block is restated from memory) */
+/* MozJPEG's overshoot deringing (jcdctmgr.c preprocess_deringing + catmull_rom of mozjpeg-sys 2.2.3 -- NOT in the
+ * reference tree: restated from the published source, PARITY UNPINNED).  Runs of samples at the maximum (walked in zig-zag
+ * order) are replaced by a Catmull-Rom curve that overshoots by at most min(31, 2 * DC quantiser, headroom of the block's DC):
+ * the clipped whites of text and line art then cost fewer bits and ring less after decoding. */
+static int so_dering = 0;      /* set by so_jpeg_frontend_mozjpeg for the duration of the call (test infrastructure, single-threaded) */
+static const int so_zigzag[64] = { 0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14,
+                                   21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60,
+                                   61, 54, 47, 55, 62, 63 };          /* jpeg_natural_order, jutils.c:56 */
+static float so_catmull_rom(int v1, int v2, int v3, int v4, float t, int size)
+{
+    const int tan1 = (v3 - v1) * size, tan2 = (v4 - v2) * size;
+    const float t2 = t * t, t3 = t2 * t;
+    const float f1 = 2.f * t3 - 3.f * t2 + 1.f, f2 = -2.f * t3 + 3.f * t2, f3 = t3 - 2.f * t2 + t, f4 = t3 - t2;
+    return v2 * f1 + tan1 * f3 + v3 * f2 + tan2 * f4;
+}
+void so_preprocess_deringing(int32_t data[64], uint16_t dc_quant)
+{
+    const int maxsample = 255 - 128, size = 64;
+    int sum = 0, count = 0;
+    for (int i = 0; i < size; i++) { sum += data[i]; if (data[i] >= maxsample) count++; }
+    if (!count || count == size) return;
+    int room = (maxsample * size - sum) / count, cap = 2 * (int)dc_quant < 31 ? 2 * (int)dc_quant : 31;
+    const int maxovershoot = maxsample + (cap < room ? cap : room);
+    int n = 0;
+    do {
+        if (data[so_zigzag[n]] < maxsample) { n++; continue; }
+        const int start = n;
+        while (++n < size && data[so_zigzag[n]] >= maxsample) {}
+        const int end = n;
+        const int f1 = data[so_zigzag[start >= 1 ? start - 1 : 0]], f2 = data[so_zigzag[start >= 2 ? start - 2 : 0]];
+        const int l1 = data[so_zigzag[end < size - 1 ? end : size - 1]], l2 = data[so_zigzag[end < size - 2 ? end + 1 : size - 1]];
+        int fslope = f1 - f2 > maxsample - f1 ? f1 - f2 : maxsample - f1;
+        int lslope = l1 - l2 > maxsample - l1 ? l1 - l2 : maxsample - l1;
+        if (start == 0) fslope = lslope;
+        if (end == size) lslope = fslope;
+        const int length = end - start;
+        const float step = 1.f / (float)(length + 1);
+        float position = step;
+        for (int i = start; i < end; i++, position += step) {
+            const int tmp = (int)ceilf(so_catmull_rom(maxsample - fslope, maxsample, maxsample, maxsample - lslope, position, length));
+            data[so_zigzag[i]] = tmp < maxovershoot ? tmp : maxovershoot;
+        }
+        n++;
+    } while (n < size);
+}
+
+/* qt == NULL: keep the DCT output un-quantised (what MozJPEG copies aside for its trellis pass, SURVEY.md App. B --
+ * mozjpeg-sys is not in the reference tree, so only the value, jfdctint.c's output, is pinned; that MozJPEG stores it
+ * per block is restated from memory) */
 static void so_do_block(const uint8_t *plane, size_t stride, uint32_t bx, uint32_t by,
                         const uint16_t qt[64], int16_t *out)
 {
@@ -484,13 +533,14 @@ static void so_do_block(const uint8_t *plane, size_t stride, uint32_t bx, uint32
     for (int r = 0; r < 8; r++)
         for (int c = 0; c < 8; c++)
             ws[r * 8 + c] = (int32_t)plane[((size_t)by * 8 + r) * stride + (size_t)bx * 8 + c] - 128; /* convsamp :373-400 */
+    if (so_dering && qt) so_preprocess_deringing(ws, qt[0]);
     so_fdct_islow(ws);
     if (qt) so_quantize(ws, qt, out);
     else for (int i = 0; i < 64; i++) out[i] = (int16_t)ws[i];
+    if (so_dering && qt)           /* MozJPEG clamps the quantised values to MAX_COEF_BITS = 10 bits when deringing is on */
+        for (int i = 0; i < 64; i++) out[i] = out[i] < -1023 ? -1023 : out[i] > 1023 ? 1023 : out[i];
 }
 
-/* one component: real blocks from the padded sample plane, then the dummy blocks of
- * jccoefct.c:286-294 (right edge) and :301-319 (bottom rows) */
 static void so_component(const uint8_t *plane, size_t stride, uint32_t wb, uint32_t hb,
                          uint32_t WB, uint32_t HB, uint32_t hs, const uint16_t qt[64], int16_t *coef)
 {
@@ -691,4 +741,13 @@ void so_avif_planes(const uint8_t *rgba, uint32_t w, uint32_t h, int depth, uint
         /* alpha plane: 8 bit as is; 10 bit as ravif's to_ten(): (x << 2) | (x >> 6) */
         a[i] = depth == 8 ? rgba[4 * i + 3] : (uint16_t)(((uint16_t)rgba[4 * i + 3] << 2) | (rgba[4 * i + 3] >> 6));
     }
+}
+
+/* The planes as MozJPEG's front end computes them with its defaults (overshoot_deringing = TRUE).  UNPINNED. */
+void so_jpeg_frontend_mozjpeg(const uint8_t *rgba, uint32_t w, uint32_t h, const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                              int16_t *yc, int16_t *cbc, int16_t *crc)
+{
+    so_dering = 1;
+    so_jpeg_frontend(rgba, w, h, qt_luma, qt_chroma, yc, cbc, crc);
+    so_dering = 0;
 }

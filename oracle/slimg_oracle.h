@@ -85,6 +85,11 @@ void so_rgb_ycc(uint8_t r, uint8_t g, uint8_t b, uint8_t out[3]);          /* jc
 void so_fdct_islow(int32_t blk[64]);                                        /* jfdctint.c:143-286 */
 void so_quantize(const int32_t ws[64], const uint16_t qt[64], int16_t out[64]); /* jcdctmgr.c:173-221,408-438 */
 
+/* MozJPEG's defaults: overshoot deringing before the DCT, quantised values clamped to 10 bits (mozjpeg-sys 2.2.3, absent: unpinned) */
+void so_preprocess_deringing(int32_t data[64], uint16_t dc_quant);
+void so_jpeg_frontend_mozjpeg(const uint8_t *rgba, uint32_t w, uint32_t h, const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
+                              int16_t *y, int16_t *cb, int16_t *cr);
+
 /* ---- colour-plane pre-stages of the WebP / AVIF encoders -- parity unpinned, see slimg_oracle.c ---- */
 void so_webp_gamma_tables(uint16_t g2l[256], int32_t l2g[33]);
 int so_webp_yuva(const uint8_t *rgba, uint32_t w, uint32_t h, uint8_t *y, uint8_t *u, uint8_t *v, uint8_t *a);

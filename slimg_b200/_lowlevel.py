@@ -72,7 +72,7 @@ class CBatchConfig(C.Structure):
 
 ORDER_CONVERT, ORDER_CHAIN = 0, 1
 QT_ANNEX_K, QT_MOZJPEG = 0, 1
-JPEG_UNQUANTISED = 1
+JPEG_UNQUANTISED, JPEG_DERINGING = 1, 2
 PLANES_WEBP_YUV420, PLANES_AVIF_YCBCR444_8, PLANES_AVIF_YCBCR444_10 = 1, 2, 3
 PATH_NONE, PATH_REMAP, PATH_GENERIC, PATH_FEWTAPS, PATH_HFIRST, PATH_VFIRST, PATH_TC, PATH_TILE = range(8)
 PATH_NAMES = ("none", "remap", "generic", "fewtaps", "hfirst", "vfirst", "tc", "tile")
@@ -137,8 +137,8 @@ def library() -> C.CDLL:
         "slimg_b200_host_free": (None, [vp]),
         "slimg_b200_jpeg_frontend_ex": (C.c_int, [C.POINTER(CImage), C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.c_uint32, C.POINTER(CJpegCoefs)]),
         "slimg_b200_pipeline_jpeg": (C.c_int, [C.POINTER(CImage), C.POINTER(CPipelineOptions), C.c_int, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.c_uint32, C.POINTER(CJpegCoefs)]),
-        "slimg_b200_jpeg_frontend_batch_device_ex": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), vp, vp, vp, vp, vp, vp, vp]),
-        "slimg_b200_pipeline_jpeg_batch_device": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(CPipelineOptions), C.c_int, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), vp, C.c_size_t, vp, vp, vp, vp, vp, vp, vp]),
+        "slimg_b200_jpeg_frontend_batch_device_ex": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), vp, vp, vp, vp, vp, vp, C.c_uint32, vp]),
+        "slimg_b200_pipeline_jpeg_batch_device": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(CPipelineOptions), C.c_int, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), vp, C.c_size_t, vp, vp, vp, vp, vp, vp, C.c_uint32, vp]),
         "slimg_b200_pipeline_jpeg_batch_host": (C.c_int32, [C.POINTER(CImage), C.c_uint32, C.POINTER(CPipelineOptions), C.c_int, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.c_uint32, C.POINTER(CBatchConfig), C.POINTER(CJpegCoefs), C.POINTER(C.c_int)]),
         "slimg_b200_pipeline_planes": (C.c_int, [C.POINTER(CImage), C.POINTER(CPipelineOptions), C.c_int, C.c_int, C.POINTER(CPlanes)]),
         "slimg_b200_planes_free": (None, [C.POINTER(CPlanes)]),
@@ -518,21 +518,21 @@ def jpeg_frontend_batch_device(src_ptr: int, n: int, w: int, h: int, qt_luma, qt
 
 
 def jpeg_frontend_batch_device_ex(src_ptr, n, w, h, qt_luma, qt_chroma, y_ptr, cb_ptr, cr_ptr, yu_ptr, cbu_ptr, cru_ptr,
-                                  stream: int = 0) -> None:
+                                  stream: int = 0, flags: int = 0) -> None:
     ql = (C.c_uint16 * 64)(*qt_luma)
     qc = (C.c_uint16 * 64)(*qt_chroma)
     _check(library().slimg_b200_jpeg_frontend_batch_device_ex(src_ptr, n, w, h, ql, qc, y_ptr, cb_ptr, cr_ptr,
-                                                              yu_ptr, cbu_ptr, cru_ptr, stream))
+                                                              yu_ptr, cbu_ptr, cru_ptr, flags, stream))
 
 
 def pipeline_jpeg_batch_device(src_ptr, n, w, h, options: CPipelineOptions, order, qt_luma, qt_chroma, pixels_ptr,
                                pixels_capacity, y_ptr, cb_ptr, cr_ptr, yu_ptr=None, cbu_ptr=None, cru_ptr=None,
-                               stream: int = 0) -> None:
+                               stream: int = 0, flags: int = 0) -> None:
     ql = (C.c_uint16 * 64)(*qt_luma)
     qc = (C.c_uint16 * 64)(*qt_chroma)
     _check(library().slimg_b200_pipeline_jpeg_batch_device(src_ptr, n, w, h, C.byref(options), order, ql, qc, pixels_ptr,
                                                            pixels_capacity, y_ptr, cb_ptr, cr_ptr, yu_ptr, cbu_ptr, cru_ptr,
-                                                           stream))
+                                                           flags, stream))
 
 
 def device_count() -> int:

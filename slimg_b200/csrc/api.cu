@@ -725,12 +725,14 @@ static void jpeg_geometry(uint32_t w, uint32_t h, slimg_jpeg_geometry &g) {
 
 static slimg_status run_jpeg_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h, const uint16_t ql[64],
                                     const uint16_t qc[64], int16_t *y, int16_t *cb, int16_t *cr, int16_t *yu, int16_t *cbu,
-                                    int16_t *cru, cudaStream_t stream) {
+                                    int16_t *cru, uint32_t flags, cudaStream_t stream) {
     slimg_jpeg_geometry g;
     jpeg_geometry(w, h, g);
     JpegParams p{};
     p.src = src; p.y = y; p.cb = cb; p.cr = cr;
     p.yu = yu; p.cbu = cbu; p.cru = cru;
+    p.deringing = (flags & SLIMG_JPEG_DERINGING) ? 1u : 0u;
+    p.dc_quant[0] = ql[0]; p.dc_quant[1] = qc[0];
     p.src_img_bytes = size_t(w) * h * 4;
     p.y_img_elems = size_t(g.y_HB) * g.y_WB * 64;
     p.c_img_elems = size_t(g.c_HB) * g.c_WB * 64;
@@ -855,7 +857,7 @@ static slimg_status pipeline_one(const slimg_image *in, const slimg_pipeline_opt
     if (jpeg) {
         int16_t *dy = d_coef, *dcb = dy + ye, *dcr = dcb + ce;
         int16_t *dyu = uq ? dcr + ce : nullptr, *dcbu = uq ? dyu + ye : nullptr, *dcru = uq ? dcbu + ce : nullptr;
-        if ((st = run_jpeg_device(d_pixels, 1, g.fw, g.fh, jpeg->ql, jpeg->qc, dy, dcb, dcr, dyu, dcbu, dcru, stream)) != SLIMG_OK)
+        if ((st = run_jpeg_device(d_pixels, 1, g.fw, g.fh, jpeg->ql, jpeg->qc, dy, dcb, dcr, dyu, dcbu, dcru, jpeg->flags, stream)) != SLIMG_OK)
             return cleanup(st);
         if ((e = copy_d2h(host_out, reinterpret_cast<const uint8_t *>(d_coef), coef_elems * 2, stream, lease)) != cudaSuccess)
             return cleanup(cuda_fail(e, "D2H"));
@@ -989,26 +991,27 @@ void slimg_b200_jpeg_quant_table(int quality, int which, int base, uint16_t out[
 slimg_status slimg_b200_jpeg_frontend_batch_device_ex(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
                                                       const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
                                                       int16_t *y, int16_t *cb, int16_t *cr, int16_t *y_uq, int16_t *cb_uq,
-                                                      int16_t *cr_uq, void *stream) {
+                                                      int16_t *cr_uq, uint32_t flags, void *stream) {
     if (!qt_luma || !qt_chroma || (n && (!src || !y || !cb || !cr))) return fail(SLIMG_ERR_IMAGE, "null argument");
     if ((y_uq || cb_uq || cr_uq) && !(y_uq && cb_uq && cr_uq)) return fail(SLIMG_ERR_IMAGE, "un-quantised planes: all three or none");
     if (w == 0 || h == 0) return fail(SLIMG_ERR_ENCODE, "image has a zero dimension");
     slimg_status st = check_device();
     if (st != SLIMG_OK) return st;
-    return run_jpeg_device(src, n, w, h, qt_luma, qt_chroma, y, cb, cr, y_uq, cb_uq, cr_uq, static_cast<cudaStream_t>(stream));
+    return run_jpeg_device(src, n, w, h, qt_luma, qt_chroma, y, cb, cr, y_uq, cb_uq, cr_uq, flags, static_cast<cudaStream_t>(stream));
 }
 
 slimg_status slimg_b200_jpeg_frontend_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
                                                    const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
                                                    int16_t *y, int16_t *cb, int16_t *cr, void *stream) {
-    return slimg_b200_jpeg_frontend_batch_device_ex(src, n, w, h, qt_luma, qt_chroma, y, cb, cr, nullptr, nullptr, nullptr, stream);
+    return slimg_b200_jpeg_frontend_batch_device_ex(src, n, w, h, qt_luma, qt_chroma, y, cb, cr, nullptr, nullptr, nullptr, 0, stream);
 }
 
 slimg_status slimg_b200_pipeline_jpeg_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
                                                    const slimg_pipeline_options *opts, int order,
                                                    const uint16_t qt_luma[64], const uint16_t qt_chroma[64],
                                                    uint8_t *pixels, size_t pixels_capacity, int16_t *y, int16_t *cb,
-                                                   int16_t *cr, int16_t *y_uq, int16_t *cb_uq, int16_t *cr_uq, void *stream) {
+                                                   int16_t *cr, int16_t *y_uq, int16_t *cb_uq, int16_t *cr_uq, uint32_t flags,
+                                                   void *stream) {
     if (!opts || !qt_luma || !qt_chroma || (n && (!src || !pixels || !y || !cb || !cr))) return fail(SLIMG_ERR_IMAGE, "null argument");
     if ((y_uq || cb_uq || cr_uq) && !(y_uq && cb_uq && cr_uq)) return fail(SLIMG_ERR_IMAGE, "un-quantised planes: all three or none");
     if (w == 0 || h == 0) return fail(bad_buffer_status(*opts, order), "image has a zero dimension");
@@ -1019,7 +1022,7 @@ slimg_status slimg_b200_pipeline_jpeg_batch_device(const uint8_t *src, uint32_t 
     if ((st = check_device()) != SLIMG_OK) return st;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if ((st = run_pipeline_device(g, src, n, pixels, s)) != SLIMG_OK) return st;
-    return run_jpeg_device(pixels, n, g.fw, g.fh, qt_luma, qt_chroma, y, cb, cr, y_uq, cb_uq, cr_uq, s);
+    return run_jpeg_device(pixels, n, g.fw, g.fh, qt_luma, qt_chroma, y, cb, cr, y_uq, cb_uq, cr_uq, flags, s);
 }
 
 slimg_status slimg_b200_jpeg_frontend_ex(const slimg_image *in, const uint16_t qt_luma[64], const uint16_t qt_chroma[64],

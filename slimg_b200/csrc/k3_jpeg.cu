@@ -208,9 +208,83 @@ __device__ __forceinline__ DctRegs make_dct_regs(int lane) {
     return r;
 }
 
+// ---- MozJPEG's overshoot deringing (optional; mozjpeg-sys is not in the reference tree: restated, parity unpinned) -----------
+// jcdctmgr.c preprocess_deringing: in a block that holds some but not only samples at the maximum, every run of maximum samples
+// (walked in zig-zag order) is replaced by a Catmull-Rom curve through its neighbours' slopes, capped at
+// 127 + min(31, 2 * DC quantiser, headroom of the block's DC).  Such blocks are rare in photographs and the overshoot leaves
+// the u8 range, so they are redone by ONE LANE each after the tile's regular pass (scalar butterflies, the same arithmetic
+// as jfdctint.c), and overwrite what the regular pass stored.
+__constant__ uint8_t kZigzag[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
+                                    35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+__device__ __noinline__ void dering_block(int *d, int dc_quant) {
+    constexpr int maxsample = 127, size = 64;
+    int sum = 0, count = 0;
+    for (int i = 0; i < size; i++) { sum += d[i]; count += d[i] >= maxsample; }
+    if (!count || count == size) return;
+    const int maxovershoot = maxsample + min(min(31, 2 * dc_quant), (maxsample * size - sum) / count);
+    int n = 0;
+    do {
+        if (d[kZigzag[n]] < maxsample) { n++; continue; }
+        const int start = n;
+        while (++n < size && d[kZigzag[n]] >= maxsample) {}
+        const int end = n;
+        const int f1 = d[kZigzag[start >= 1 ? start - 1 : 0]], f2 = d[kZigzag[start >= 2 ? start - 2 : 0]];
+        const int l1 = d[kZigzag[end < size - 1 ? end : size - 1]], l2 = d[kZigzag[end < size - 2 ? end + 1 : size - 1]];
+        int fslope = max(f1 - f2, maxsample - f1), lslope = max(l1 - l2, maxsample - l1);
+        if (start == 0) fslope = lslope;
+        if (end == size) lslope = fslope;
+        const int length = end - start;
+        const float step = __fdiv_rn(1.f, float(length + 1));
+        float position = step;
+        const int v1 = maxsample - fslope, v4 = maxsample - lslope;
+        const int tan1 = (maxsample - v1) * length, tan2 = (v4 - maxsample) * length;
+        for (int i = start; i < end; i++, position = __fadd_rn(position, step)) {
+            // catmull_rom(v1, max, max, v4, t, length) in the reference's operation order, no contraction
+            const float t = position, t2 = __fmul_rn(t, t), t3 = __fmul_rn(t2, t);
+            const float c1 = __fadd_rn(__fsub_rn(__fmul_rn(2.f, t3), __fmul_rn(3.f, t2)), 1.f);
+            const float c2 = __fadd_rn(__fmul_rn(-2.f, t3), __fmul_rn(3.f, t2));
+            const float c3 = __fadd_rn(__fsub_rn(t3, __fmul_rn(2.f, t2)), t);
+            const float c4 = __fsub_rn(t3, t2);
+            const float val = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(float(maxsample), c1), __fmul_rn(float(tan1), c3)), __fmul_rn(float(maxsample), c2)),
+                                        __fmul_rn(float(tan2), c4));
+            d[kZigzag[i]] = min(int(ceilf(val)), maxovershoot);
+        }
+        n++;
+    } while (n < size);
+}
+// the whole block on one lane: dering, islow FDCT (rows, then columns), quantise, clamp to 10 bits (MozJPEG does when deringing is on)
+template <bool UQ>
+__device__ __noinline__ void slow_block(int *d, int dc_quant, const uint32_t (*qt)[64], int16_t *q_out, int16_t *u_out) {
+    dering_block(d, dc_quant);
+    for (int r = 0; r < 8; r++) {
+        int in[8], out[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) in[k] = d[r * 8 + k];
+        fdct8<1>(in, out);
+#pragma unroll
+        for (int k = 0; k < 8; k++) d[r * 8 + k] = out[k];
+    }
+    for (int c = 0; c < 8; c++) {
+        int in[8], out[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) in[k] = d[k * 8 + c];
+        fdct8<2>(in, out);
+#pragma unroll
+        for (int k = 0; k < 8; k++) d[k * 8 + c] = out[k];
+    }
+    for (int i = 0; i < 64; i++) {
+        const int t = d[i];
+        if (UQ) u_out[i] = int16_t(t);
+        const uint32_t a = uint32_t(t < 0 ? -t : t) + qt[1][i];
+        int q = int(__umulhi(a, qt[0][i]) >> qt[2][i]);
+        q = min(q, 1023);
+        q_out[i] = int16_t(t < 0 ? -q : q);
+    }
+}
+
 // PIPE: 1 = the loads of stage-1 patch j+1 are issued before patch j is converted; 2 = additionally, the first patch of
 // the warp's NEXT tile is loaded before stage 2 of the current one (8 more live registers across the DCT)
-template <int PIPE, int MINB, bool UQ, bool TENSOR>
+template <int PIPE, int MINB, bool UQ, bool TENSOR, bool DERING>
 __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_kernel(const __grid_constant__ JpegParams p, const uint32_t n_images) {
     __shared__ __align__(16) WarpSmem wsm[kWarpsPerCta];
     const int lane = threadIdx.x & 31, l8 = lane & 7, q4 = lane >> 3;
@@ -280,7 +354,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
                 const int e = i & 1;
                 const uint32_t aa = uint32_t(cf[i] < 0 ? -cf[i] : cf[i]) + qcor[tb][e];
                 const uint32_t q = __umulhi(aa, qrec[tb][e]) >> qsh[tb][e];       // jcdctmgr.c:408-438, reciprocal form
-                qv[i] = cf[i] < 0 ? -int(q) : int(q);
+                qv[i] = cf[i] < 0 ? -int(DERING ? min(q, 1023u) : q) : int(DERING ? min(q, 1023u) : q);
             }
             // natural order wants (u, u') -> u * 8 + u': transpose back so a lane holds u = g, u' = 2t, 2t+1
             const uint32_t w0 = movmatrix_t(__byte_perm(uint32_t(qv[0]), uint32_t(qv[1]), 0x5410));
@@ -468,6 +542,52 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta, MINB) jpeg_frontend_warp_ke
             }
         }
         __syncwarp();
+        if (DERING) {
+            // blocks with some but not only samples at 255: redone by one lane each (48 candidates per tile: 32 Y, 8 Cb, 8 Cr)
+#pragma unroll 1
+            for (int it = 0; it < 2; it++) {
+                const int idx = it * 32 + lane;
+                bool flagged = false;
+                int comp = 0, by2 = 0, bx = 0;              // comp 0 = Y, 1 = Cb, 2 = Cr
+                const uint32_t *rows = nullptr;
+                int pitch = 0;
+                if (idx < 48) {
+                    if (idx < 32) { comp = 0; by2 = idx >> 4; bx = idx & 15; rows = &sm.ys[by2 * 8][bx * 2]; pitch = kWW / 4 + 4; }
+                    else { comp = 1 + ((idx - 32) >> 3); bx = (idx - 32) & 7; rows = reinterpret_cast<const uint32_t *>(comp == 1 ? &sm.cb[0][0] : &sm.cr[0][0]) + bx * 2; pitch = (kWW / 4 + 8) / 2; }
+                    const bool real = comp == 0 ? (bx < nby && by2 < nrow) : bx < nm;
+                    if (real) {
+                        int cnt = 0;
+#pragma unroll
+                        for (int r = 0; r < 8; r++) cnt += __popc(__vcmpeq4(rows[r * pitch], 0xffffffffu)) + __popc(__vcmpeq4(rows[r * pitch + 1], 0xffffffffu));
+                        flagged = cnt != 0 && cnt != 64 * 8;        // __vcmpeq4 sets all 8 bits of an equal byte
+                    }
+                }
+                if (__any_sync(0xffffffffu, flagged)) {
+                    if (flagged) {
+                        int d[64];
+#pragma unroll
+                        for (int r = 0; r < 8; r++) {
+                            const uint32_t lo = rows[r * pitch], hi = rows[r * pitch + 1];
+#pragma unroll
+                            for (int k = 0; k < 4; k++) { d[r * 8 + k] = int((lo >> (8 * k)) & 0xff) - 128; d[r * 8 + 4 + k] = int((hi >> (8 * k)) & 0xff) - 128; }
+                        }
+                        const int tb = comp == 0 ? 0 : 1;
+                        int16_t *qo, *uo = nullptr;
+                        if (comp == 0) {
+                            const size_t off = (size_t(yby0 + by2) * p.y_WB + ybx0 + bx) * 64;
+                            qo = yout + off; if (UQ) uo = yuq + off;
+                        } else {
+                            const size_t off = size_t(z) * p.c_img_elems + (size_t(my) * p.c_wb + mx0 + bx) * 64;
+                            qo = (comp == 1 ? p.cb : p.cr) + off; if (UQ) uo = (comp == 1 ? p.cbu : p.cru) + off;
+                        }
+                        slow_block<UQ>(d, int(p.dc_quant[tb]), qt[tb], qo, uo);
+                        if (comp == 0) { sm.dc[0][by2][bx] = qo[0]; if (UQ) sm.dc[1][by2][bx] = uo[0]; }
+                    }
+                    __syncwarp();
+                }
+            }
+            __syncwarp();
+        }
         // dummy Y blocks (jccoefct.c:286-294 right edge, :301-319 bottom rows; edge tiles only): AC = 0, DC = the DC of
         // the last real block to the left / of the MCU's last block in the row above
         if (nby < 2 * nm || nrow < 2) {
@@ -510,14 +630,15 @@ cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStr
     const int var = var_env ? std::atoi(var_env) : 8;
     using Kern = void (*)(const JpegParams, const uint32_t);
     Kern kern;
-#define SLIMG_K3_PICK(U)                                                                                                     \
-    (var == 0 ? jpeg_frontend_warp_kernel<0, 8, U, false> : var == 1 ? jpeg_frontend_warp_kernel<1, 8, U, false>              \
-     : var == 2 ? jpeg_frontend_warp_kernel<2, 6, U, false> : var == 3 ? jpeg_frontend_warp_kernel<1, 7, U, false>            \
-     : var == 4 ? jpeg_frontend_warp_kernel<1, 6, U, false> : var == 6 ? jpeg_frontend_warp_kernel<0, 8, U, true>             \
-     : var == 7 ? jpeg_frontend_warp_kernel<1, 6, U, true> : var == 8 ? jpeg_frontend_warp_kernel<0, 5, U, true>               \
-     : var == 9 ? jpeg_frontend_warp_kernel<0, 4, U, true> : jpeg_frontend_warp_kernel<0, 6, U, true>)
+#define SLIMG_K3_PICK(U)                                                                                                            \
+    (var == 0 ? jpeg_frontend_warp_kernel<0, 8, U, false, false> : var == 1 ? jpeg_frontend_warp_kernel<1, 8, U, false, false>         \
+     : var == 2 ? jpeg_frontend_warp_kernel<2, 6, U, false, false> : var == 3 ? jpeg_frontend_warp_kernel<1, 7, U, false, false>       \
+     : var == 4 ? jpeg_frontend_warp_kernel<1, 6, U, false, false> : var == 6 ? jpeg_frontend_warp_kernel<0, 8, U, true, false>        \
+     : var == 7 ? jpeg_frontend_warp_kernel<1, 6, U, true, false> : var == 5 ? jpeg_frontend_warp_kernel<0, 6, U, true, false>         \
+     : var == 9 ? jpeg_frontend_warp_kernel<0, 4, U, true, false> : jpeg_frontend_warp_kernel<0, 5, U, true, false>)
     kern = uq ? SLIMG_K3_PICK(true) : SLIMG_K3_PICK(false);
 #undef SLIMG_K3_PICK
+    if (p.deringing) kern = uq ? jpeg_frontend_warp_kernel<0, 5, true, true, true> : jpeg_frontend_warp_kernel<0, 5, false, true, true>;
     int dev = 0, sms = 148, per_sm = 4;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -27,64 +27,92 @@ __device__ __forceinline__ int w_clip_uv(int uv) {
     return min(max(uv, 0), 255);
 }
 
-// one thread = one chroma sample = (up to) 2 x 2 pixels; grid.z = image
+// one thread = 4 x 2 pixels = two chroma samples (two 16-byte loads, word stores of Y / A, halfword stores of U / V);
+// grid.z = image
 __global__ void __launch_bounds__(kThreads) webp_planes_kernel(const WebpPlanesParams p) {
     __shared__ uint16_t g2l[256];
     __shared__ int l2g[33];
     for (int i = threadIdx.x; i < 256; i += kThreads) g2l[i] = p.g2l[i];
     if (threadIdx.x < 33) l2g[threadIdx.x] = p.l2g[threadIdx.x];
     __syncthreads();
-    const int cx = blockIdx.x * 64 + (threadIdx.x & 63), cy = blockIdx.y * 4 + (threadIdx.x >> 6);
+    const int qx = blockIdx.x * 64 + (threadIdx.x & 63), cy = blockIdx.y * 4 + (threadIdx.x >> 6);       // quad column, chroma row
     const int w = int(p.w), h = int(p.h), uvw = (w + 1) >> 1, uvh = (h + 1) >> 1;
-    if (cx >= uvw || cy >= uvh) return;
+    const int x0 = 4 * qx, y0 = 2 * cy;
+    if (x0 >= w || cy >= uvh) return;
     const uint32_t *src = reinterpret_cast<const uint32_t *>(p.src + size_t(blockIdx.z) * p.src_img_bytes);
-    const int x0 = 2 * cx, y0 = 2 * cy;
-    const bool wide = x0 + 1 < w, tall = y0 + 1 < h;
-    const int x1 = wide ? x0 + 1 : x0, y1 = tall ? y0 + 1 : y0;
-    uint32_t px[4];
-    if (wide && (w & 1) == 0) {                       // 8-byte loads: two pixels of a row
-        const uint2 a = __ldg(reinterpret_cast<const uint2 *>(src + size_t(y0) * w + x0));
-        const uint2 b = __ldg(reinterpret_cast<const uint2 *>(src + size_t(y1) * w + x0));
-        px[0] = a.x; px[1] = a.y; px[2] = b.x; px[3] = b.y;
+    const bool tall = y0 + 1 < h;
+    const int y1 = tall ? y0 + 1 : y0;                     // odd height: the last row twice
+    const bool vec = (w & 3) == 0 && (p.src_img_bytes & 15) == 0 && (reinterpret_cast<uintptr_t>(p.src) & 15) == 0;
+    uint32_t px[2][4];
+    if (vec) {
+        const uint4 a = __ldg(reinterpret_cast<const uint4 *>(src + size_t(y0) * w + x0));
+        const uint4 b = __ldg(reinterpret_cast<const uint4 *>(src + size_t(y1) * w + x0));
+        px[0][0] = a.x; px[0][1] = a.y; px[0][2] = a.z; px[0][3] = a.w;
+        px[1][0] = b.x; px[1][1] = b.y; px[1][2] = b.z; px[1][3] = b.w;
     } else {
-        px[0] = __ldg(src + size_t(y0) * w + x0); px[1] = __ldg(src + size_t(y0) * w + x1);
-        px[2] = __ldg(src + size_t(y1) * w + x0); px[3] = __ldg(src + size_t(y1) * w + x1);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int x = min(x0 + k, w - 1);
+            px[0][k] = __ldg(src + size_t(y0) * w + x); px[1][k] = __ldg(src + size_t(y1) * w + x);
+        }
     }
     uint8_t *Y = p.y + size_t(blockIdx.z) * p.y_img_bytes;
     uint8_t *A = p.a ? p.a + size_t(blockIdx.z) * p.y_img_bytes : nullptr;
-    int yv[4];
 #pragma unroll
-    for (int k = 0; k < 4; k++) {                     // VP8RGBToY
-        const int r = px[k] & 0xff, g = (px[k] >> 8) & 0xff, b = (px[k] >> 16) & 0xff;
-        yv[k] = (16839 * r + 33059 * g + 6420 * b + (1 << 15) + (16 << 16)) >> 16;
-    }
-    Y[size_t(y0) * w + x0] = uint8_t(yv[0]);
-    if (wide) Y[size_t(y0) * w + x1] = uint8_t(yv[1]);
-    if (tall) { Y[size_t(y1) * w + x0] = uint8_t(yv[2]); if (wide) Y[size_t(y1) * w + x1] = uint8_t(yv[3]); }
-    if (A) {
-        A[size_t(y0) * w + x0] = uint8_t(px[0] >> 24);
-        if (wide) A[size_t(y0) * w + x1] = uint8_t(px[1] >> 24);
-        if (tall) { A[size_t(y1) * w + x0] = uint8_t(px[2] >> 24); if (wide) A[size_t(y1) * w + x1] = uint8_t(px[3] >> 24); }
+    for (int r = 0; r < 2; r++) {
+        if (r == 1 && !tall) break;
+        uint32_t yw = 0u, aw = 0u;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {                     // VP8RGBToY
+            const uint32_t v = px[r][k];
+            const int yv = (16839 * int(v & 0xff) + 33059 * int((v >> 8) & 0xff) + 6420 * int((v >> 16) & 0xff) + (1 << 15) + (16 << 16)) >> 16;
+            yw |= uint32_t(yv) << (8 * k);
+            aw |= (v >> 24) << (8 * k);
+        }
+        const size_t o = size_t(r ? y1 : y0) * w + x0;
+        if (vec) {
+            *reinterpret_cast<uint32_t *>(Y + o) = yw;
+            if (A) *reinterpret_cast<uint32_t *>(A + o) = aw;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (x0 + k < w) { Y[o + k] = uint8_t(yw >> (8 * k)); if (A) A[o + k] = uint8_t(aw >> (8 * k)); }
+        }
     }
     // chroma: AccumulateRGB / AccumulateRGBA.  The alpha-weighted form is used only in row pairs that contain a pixel
     // that is not opaque (libwebp decides per pair of rows); row_alpha[cy] was computed by the scan kernel.
     const bool rows_alpha = p.row_alpha && p.row_alpha[size_t(blockIdx.z) * uvh + cy];
-    const uint32_t asum = wide ? (px[0] >> 24) + (px[1] >> 24) + (px[2] >> 24) + (px[3] >> 24) : 2u * ((px[0] >> 24) + (px[2] >> 24));
-    int rgb[3];
+    uint32_t uvp[2] = {0u, 0u};                            // U and V of the two samples, packed
 #pragma unroll
-    for (int c = 0; c < 3; c++) {
-        const uint32_t v0 = g2l[(px[0] >> (8 * c)) & 0xff], v1 = g2l[(px[1] >> (8 * c)) & 0xff];
-        const uint32_t v2 = g2l[(px[2] >> (8 * c)) & 0xff], v3 = g2l[(px[3] >> (8 * c)) & 0xff];
-        if (!rows_alpha || asum == 4u * 0xffu || asum == 0u) rgb[c] = wide ? w_l2g(l2g, v0 + v1 + v2 + v3, 0) : w_l2g(l2g, v0 + v2, 1);
-        else {
-            const uint32_t sum = (px[0] >> 24) * v0 + (px[1] >> 24) * v1 + (px[2] >> 24) * v2 + (px[3] >> 24) * v3;
-            const uint32_t inv = (1u << 19) / asum;
-            rgb[c] = w_l2g(l2g, uint32_t((uint64_t(sum) * inv) >> 17), 0);
+    for (int e = 0; e < 2; e++) {
+        const int xa = x0 + 2 * e;
+        if (xa >= w) break;
+        const bool wide = xa + 1 < w;
+        const uint32_t q0 = px[0][2 * e], q1 = px[0][wide ? 2 * e + 1 : 2 * e], q2 = px[1][2 * e], q3 = px[1][wide ? 2 * e + 1 : 2 * e];
+        const uint32_t asum = wide ? (q0 >> 24) + (q1 >> 24) + (q2 >> 24) + (q3 >> 24) : 2u * ((q0 >> 24) + (q2 >> 24));
+        int rgb[3];
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const uint32_t v0 = g2l[(q0 >> (8 * c)) & 0xff], v1 = g2l[(q1 >> (8 * c)) & 0xff];
+            const uint32_t v2 = g2l[(q2 >> (8 * c)) & 0xff], v3 = g2l[(q3 >> (8 * c)) & 0xff];
+            if (!rows_alpha || asum == 4u * 0xffu || asum == 0u) rgb[c] = wide ? w_l2g(l2g, v0 + v1 + v2 + v3, 0) : w_l2g(l2g, v0 + v2, 1);
+            else {
+                const uint32_t sum = (q0 >> 24) * v0 + (q1 >> 24) * v1 + (q2 >> 24) * v2 + (q3 >> 24) * v3;
+                const uint32_t inv = (1u << 19) / asum;
+                rgb[c] = w_l2g(l2g, uint32_t((uint64_t(sum) * inv) >> 17), 0);
+            }
         }
+        uvp[0] |= uint32_t(w_clip_uv(-9719 * rgb[0] - 19081 * rgb[1] + 28800 * rgb[2])) << (8 * e);
+        uvp[1] |= uint32_t(w_clip_uv(28800 * rgb[0] - 24116 * rgb[1] - 4684 * rgb[2])) << (8 * e);
     }
-    const size_t uvo = size_t(blockIdx.z) * p.uv_img_bytes + size_t(cy) * uvw + cx;
-    p.u[uvo] = uint8_t(w_clip_uv(-9719 * rgb[0] - 19081 * rgb[1] + 28800 * rgb[2]));
-    p.v[uvo] = uint8_t(w_clip_uv(28800 * rgb[0] - 24116 * rgb[1] - 4684 * rgb[2]));
+    const size_t uvo = size_t(blockIdx.z) * p.uv_img_bytes + size_t(cy) * uvw + 2 * qx;
+    if (vec) {                                             // w % 4 == 0: uvw is even, 2 qx + 1 < uvw
+        *reinterpret_cast<uint16_t *>(p.u + uvo) = uint16_t(uvp[0]);
+        *reinterpret_cast<uint16_t *>(p.v + uvo) = uint16_t(uvp[1]);
+    } else {
+        p.u[uvo] = uint8_t(uvp[0]); p.v[uvo] = uint8_t(uvp[1]);
+        if (2 * qx + 1 < uvw) { p.u[uvo + 1] = uint8_t(uvp[0] >> 8); p.v[uvo + 1] = uint8_t(uvp[1] >> 8); }
+    }
 }
 
 // CheckNonOpaque per pair of rows: row_alpha[img][cy] = some alpha of rows 2cy, 2cy+1 is not 255; any[img] = OR of them
@@ -126,18 +154,30 @@ __global__ void __launch_bounds__(kThreads) avif_planes_kernel(const AvifPlanesP
     const float t0 = __fmul_rn(scale, m0), t1 = __fmul_rn(scale, m1), t2 = __fmul_rn(scale, m2);
     T *Y = reinterpret_cast<T *>(p.y) + size_t(blockIdx.z) * n, *Cb = reinterpret_cast<T *>(p.cb) + size_t(blockIdx.z) * n;
     T *Cr = reinterpret_cast<T *>(p.cr) + size_t(blockIdx.z) * n, *A = reinterpret_cast<T *>(p.a) + size_t(blockIdx.z) * n;
-    for (int k = 0; k < cnt; k++) {
-        const float r = float(px[k] & 0xff), g = float((px[k] >> 8) & 0xff), b = float((px[k] >> 16) & 0xff);
-        const uint32_t al = px[k] >> 24;
+    T vy[4], vb[4], vr[4], va[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t v = k < cnt ? px[k] : 0u;
+        const float r = float(v & 0xff), g = float((v >> 8) & 0xff), b = float((v >> 16) & 0xff);
+        const uint32_t al = v >> 24;
         // every product and sum rounds to f32 (the reference build does not contract); the chroma terms are ONE fused multiply-add
         const float yv = __fadd_rn(__fadd_rn(__fmul_rn(t0, r), __fmul_rn(t1, g)), __fmul_rn(t2, b));
         const float cbv = __fmaf_rn(__fsub_rn(__fmul_rn(b, scale), yv), kb, shift);
         const float crv = __fmaf_rn(__fsub_rn(__fmul_rn(r, scale), yv), kr, shift);
-        Y[i0 + k] = T(fminf(fmaxf(round_away(yv), 0.f), max_value));
-        Cb[i0 + k] = T(fminf(fmaxf(round_away(cbv), 0.f), max_value));
-        Cr[i0 + k] = T(fminf(fmaxf(round_away(crv), 0.f), max_value));
-        A[i0 + k] = DEPTH == 8 ? T(al) : T((al << 2) | (al >> 6));
+        vy[k] = T(fminf(fmaxf(round_away(yv), 0.f), max_value));
+        vb[k] = T(fminf(fmaxf(round_away(cbv), 0.f), max_value));
+        vr[k] = T(fminf(fmaxf(round_away(crv), 0.f), max_value));
+        va[k] = DEPTH == 8 ? T(al) : T((al << 2) | (al >> 6));
     }
+    const bool vec = cnt == 4 && (n & 3) == 0;                 // plane rows of 4 samples are then 4- / 8-byte aligned (cudaMalloc'ed planes)
+    auto put = [&](T *dst, const T (&v)[4]) {
+        if (vec) {
+            if (DEPTH == 8) *reinterpret_cast<uint32_t *>(dst + i0) = uint32_t(v[0]) | (uint32_t(v[1]) << 8) | (uint32_t(v[2]) << 16) | (uint32_t(v[3]) << 24);
+            else *reinterpret_cast<uint2 *>(dst + i0) = make_uint2(uint32_t(v[0]) | (uint32_t(v[1]) << 16), uint32_t(v[2]) | (uint32_t(v[3]) << 16));
+        } else
+            for (int k = 0; k < cnt; k++) dst[i0 + k] = v[k];
+    };
+    put(Y, vy); put(Cb, vb); put(Cr, vr); put(A, va);
 }
 
 }  // namespace
@@ -150,7 +190,7 @@ cudaError_t launch_webp_planes(const WebpPlanesParams &p, uint32_t n_images, cud
         webp_alpha_scan_kernel<<<dim3(uvh, 1, n_images), kThreads, 0, stream>>>(p);
         count_launch();
     }
-    webp_planes_kernel<<<dim3((uvw + 63) / 64, (uvh + 3) / 4, n_images), kThreads, 0, stream>>>(p);
+    webp_planes_kernel<<<dim3(((p.w + 3) / 4 + 63) / 64, (uvh + 3) / 4, n_images), kThreads, 0, stream>>>(p);
     count_launch();
     return cudaGetLastError();
 }

@@ -223,6 +223,8 @@ struct JpegParams {
     uint32_t y_wb, y_hb, y_WB, y_HB, c_wb, c_hb;
     QuantDev q;
     uint32_t debug;                    // experiment switches (SLIMG_B200_JPEG_DEBUG), 0 in production
+    uint32_t deringing;                // 1: MozJPEG's overshoot deringing before the DCT + 10-bit clamp of the quantised values
+    uint32_t dc_quant[2];              // DC quantiser of the luma / chroma table (deringing's overshoot cap)
 };
 cudaError_t launch_jpeg_frontend(const JpegParams &p, uint32_t n_images, cudaStream_t stream);
 

@@ -342,3 +342,35 @@ def test_in_library_multi_device_scheduler_uses_every_visible_gpu():
     assert failed == 0
     for img, out in zip(imgs, outs):
         assert np.array_equal(out, _np(ll.pipeline(_ll_img(img), opts, ll.ORDER_CONVERT)))
+
+
+# ---- MozJPEG's front-end defaults: overshoot deringing + 10-bit clamp (restated, unpinned) -----------------------------
+
+def _line_art(w, h, seed):
+    """White paper, dark strokes: the clipped whites MozJPEG's deringing is made for."""
+    rng = np.random.default_rng(seed)
+    img = np.full((h, w, 4), 255, np.uint8)
+    for _ in range(max(4, w * h // 900)):
+        x, y = int(rng.integers(0, w)), int(rng.integers(0, h))
+        img[y:y + int(rng.integers(1, 9)), x:x + int(rng.integers(1, 40)), :3] = rng.integers(0, 200, 3)
+    return img
+
+
+@pytest.mark.parametrize("kind,w,h,q", [("lineart", 640, 480, 70), ("lineart", 333, 257, 30), ("noise", 250, 131, 70), ("white", 64, 48, 70),
+                                        ("gradient", 320, 200, 90), ("lineart", 1920, 1080, 100)])
+def test_jpeg_frontend_with_mozjpeg_deringing(kind, w, h, q):
+    img = {"lineart": lambda: _line_art(w, h, 5), "noise": lambda: noise_image(w, h, 12), "white": lambda: constant_image(w, h, 255),
+           "gradient": lambda: gradient_image(w, h)}[kind]()
+    ql, qc = ll.jpeg_quant_table(q, 0, ll.QT_MOZJPEG), ll.jpeg_quant_table(q, 1, ll.QT_MOZJPEG)
+    want = oracle.jpeg_frontend_mozjpeg(img, np.array(ql, np.uint16), np.array(qc, np.uint16))
+    plain = oracle.jpeg_frontend(img, np.array(ql, np.uint16), np.array(qc, np.uint16))
+    c = ll.jpeg_frontend_ex(_ll_img(img), ql, qc, ll.JPEG_DERINGING)
+    for g, wv, name in zip(_coef_planes(c), want, ("y", "cb", "cr")):
+        assert np.array_equal(g, wv), f"{name}: {np.count_nonzero(g != wv)} coefficients differ"
+    if kind == "lineart":
+        assert any(not np.array_equal(a, b) for a, b in zip(want, plain))       # the stage did something
+    if kind in ("white", "gradient") and q < 100:
+        assert all(np.array_equal(a, b) for a, b in zip(want, plain))           # nothing to dering, nothing clamped
+    # the side output is the DCT of the deringed block (what MozJPEG keeps for trellis)
+    cu = ll.jpeg_frontend_ex(_ll_img(img), ql, qc, ll.JPEG_DERINGING | ll.JPEG_UNQUANTISED)
+    assert (cu.y, cu.cb, cu.cr) == (c.y, c.cb, c.cr) and cu.y_uq is not None

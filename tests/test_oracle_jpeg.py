@@ -67,3 +67,34 @@ def test_coefficient_handoff_writes_the_same_jpeg(w, h):
     prog = oracle.ref_jpeg_write_coefficients(y, cb, cr, w, h, ql, qc, progressive=True)     # codec/jpeg.rs:61
     assert prog[:3] == b"\xff\xd8\xff"
     assert np.array_equal(oracle.ref_jpeg_decode(prog, w, h), oracle.ref_jpeg_decode(oracle.ref_jpeg_encode(img, ql, qc), w, h))
+
+
+# ---- MozJPEG's overshoot deringing (restated from memory of mozjpeg-sys 2.2.3: parity unpinned) ----------------------------
+
+def test_deringing_leaves_blocks_without_or_only_maximum_samples_alone():
+    rng = np.random.default_rng(3)
+    b = rng.integers(-128, 127, (8, 8)).astype(np.int32)          # no sample at 127
+    assert np.array_equal(oracle.preprocess_deringing(b, 12), b)
+    full = np.full((8, 8), 127, np.int32)
+    assert np.array_equal(oracle.preprocess_deringing(full, 12), full)
+
+
+def test_deringing_overshoots_only_the_maximum_runs_and_within_its_cap():
+    b = np.full((8, 8), -100, np.int32)
+    b[2:6, 2:6] = 127
+    out = oracle.preprocess_deringing(b, 10)
+    changed = out != b
+    assert changed.any() and (b[changed] == 127).all()              # only clipped samples move
+    assert out.max() <= 127 + min(31, 2 * 10) and (out[changed] >= 127).all()
+    # the cap follows the DC quantiser and the DC headroom of the block
+    assert oracle.preprocess_deringing(b, 2).max() <= 127 + 4
+    almost = np.full((8, 8), 127, np.int32)
+    almost[0, 0] = 126                                              # headroom (127 * 64 - sum) / count = 1 / 63 = 0
+    assert oracle.preprocess_deringing(almost, 50).max() == 127
+
+
+def test_mozjpeg_front_end_equals_libjpeg_where_nothing_clips():
+    img = (noise_image(64, 48, 2) // 2 + 32).astype(np.uint8)       # samples in 32..159: no block reaches 255
+    ql, qc = oracle.jpeg_quant_table(70, 0, 1), oracle.jpeg_quant_table(70, 1, 1)
+    for a, b in zip(oracle.jpeg_frontend_mozjpeg(img, ql, qc), oracle.jpeg_frontend(img, ql, qc)):
+        assert np.array_equal(a, b)
