@@ -519,7 +519,7 @@ size_t vfirst_smem_tail_bytes() { return sizeof(SmemTail); }
 
 cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStream_t stream) {
     if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
-    if (p.n_bands == 0 || p.n_bands > 65535 || p.n_strips == 0 || p.nch1 > 4 || p.nch2 > 4) return cudaErrorInvalidValue;
+    if (p.n_bands == 0 || p.n_bands > 65535 || p.n_strips == 0 || p.nch1 > 6 || p.nch2 > 6) return cudaErrorInvalidValue;
     if (p.ring_rows % kStepRows != 0 || p.ring_rows / kStepRows > kMaxSteps) return cudaErrorInvalidValue;
 #define SLIMG_VF_CASE(A, B, U) if (p.nch1 == A && p.nch2 == B && p.unit == U) return launch_vf_t<2, A, B, U>(p, n_images, stream);
 #define SLIMG_VF_ROW(A, U) SLIMG_VF_CASE(A, 1, U) SLIMG_VF_CASE(A, 2, U) SLIMG_VF_CASE(A, 3, U) SLIMG_VF_CASE(A, 4, U)
@@ -528,6 +528,9 @@ cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStrea
     SLIMG_VF_ALL(3)
     SLIMG_VF_ALL(4)
     SLIMG_VF_ALL(5)
+    // bands of 5 - 6 chunks (downscales of ~9x to ~11x: thumbnails of 12 MP photos), UNIT = 4 only
+    SLIMG_VF_CASE(5, 5, 4) SLIMG_VF_CASE(5, 6, 4) SLIMG_VF_CASE(6, 5, 4) SLIMG_VF_CASE(6, 6, 4)
+    SLIMG_VF_CASE(4, 5, 4) SLIMG_VF_CASE(5, 4, 4)
     return cudaErrorInvalidValue;
 }
 

@@ -22,7 +22,7 @@ namespace {
 constexpr int kFrac = 7;        // fractional bits of the 16-bit intermediate
 constexpr int kOffset = 64;     // added to the intermediate so Lanczos undershoot stays >= 0
 constexpr int kPrefetchRows = 64;   // a whole group's worth of new rows must be in flight while the previous group computes
-constexpr int kMaxCh = 4;          // chunk stride of the fragment tables (the kernel's NCH1 / NCH2)
+constexpr int kMaxCh = 6;          // most 32-row / 32-pixel chunks per band (the kernel's NCH1 / NCH2): ratios up to ~11x
 constexpr double kLookGroups = 2.0;  // ring depth wanted beyond the current band, in groups of 8 output rows
 constexpr size_t kSmemBudget = 227 * 1024 - 2048;
 const int kPerm[4] = {0, 2, 1, 3};   // k-slot -> pixel inside a 4-pixel block (k2_vfirst.cu, pass-1 epilogue)
@@ -241,6 +241,15 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     uint32_t cols = 0;
     int unit = 0;
     bool early = false;
+    // most chunks any 8-column tile needs, whatever strip it ends up in (its k range starts on a 4-pixel block)
+    int nch2_pre = 1;
+    for (uint32_t c0 = 0; c0 < g.pw; c0 += 8) {
+        int64_t tlo, thi;
+        span_of(c0, std::min(g.pw, c0 + 8), tlo, thi);
+        if (thi >= 0) nch2_pre = std::max<int>(nch2_pre, int((thi - (tlo & ~int64_t(3)) + 31) / 32));
+    }
+    if (nch2_pre > kMaxCh) return;
+    const int64_t min_blocks = 8 * std::max(4, nch2_pre);      // every tile runs nch2 chunks of 8 blocks inside the staged span
     auto max_padded = [&](uint32_t cand, int u, int &crit) {
         int64_t worst = 0;
         crit = 0;
@@ -253,7 +262,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
             worst = std::max(worst, pad_blocks((hi - (lo & ~int64_t(3)) + 3) / 4, c1 - c0, u, upw));
             crit = std::max(crit, upw * u);                       // blocks of the busiest warp
         }
-        return std::max<int64_t>(worst, 8 * kMaxCh);
+        return std::max<int64_t>(worst, min_blocks);
     };
     // Widest strips whose ring still runs `kLookGroups` groups ahead of the band being filtered: the ring is refilled
     // once per group, so a shallow ring leaves too few bytes in flight however wide the strip is (measured on B200:
@@ -272,6 +281,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         int64_t best_blk = INT64_MAX;
         for (int u = 5; u >= 3; u--) {
             if (unit_env && std::atoi(unit_env) != u) continue;
+            if ((out.nch1 > 4 || nch2_pre > 4) && u != 4) continue;      // k2_vfirst.cu instantiates the long-band kernels for UNIT = 4
             int crit;
             const int64_t blk = max_padded(even, u, crit);
             if (crit < best_crit || (crit == best_crit && blk < best_blk)) { best_blk = blk; best_u = u; best_crit = crit; }

@@ -25,6 +25,8 @@ PATH_CASES = [
     ("down16 (bands beyond the V-first ring)", 4000, 3000, ("exact", 250, 188), None, None, None, "convert"),
     ("portrait, side padding takes part in the taps", 1000, 3000, ("width", 400), None, ("aspect", 16, 9), (7, 99, 201, 255), "convert"),
     ("odd crop x on a 1200-wide source", 1200, 900, ("width", 300), ("region", 7, 5, 1100, 800), None, None, "convert"),
+    ("down10 (5-chunk bands: the GUI thumbnail of a 12 MP photo)", 4000, 3000, ("fit", 400, 400), None, None, None, "convert"),
+    ("down11 with crop and padding", 3300, 2200, ("width", 300), ("aspect", 4, 3), ("aspect", 1, 1), (9, 8, 7, 255), "chain"),
     ("down2", 1024, 768, ("scale", 0.5), None, None, None, "convert"),
     ("down1.5", 900, 600, ("width", 600), None, None, None, "convert"),
 ]
@@ -71,7 +73,9 @@ def test_default_paths_are_the_intended_kernels(monkeypatch):
     assert ll.last_resize_path() == ll.PATH_TILE
     ll.resize(_ll_img(noise_image(63, 64, 1)), ll.ResizeMode.EXACT(200, 20))      # rows that are not 16-byte aligned: the f32 kernel
     assert ll.last_resize_path() in (ll.PATH_GENERIC, ll.PATH_FEWTAPS)
-    ll.resize(_ll_img(noise_image(4000, 3000, 1)), ll.ResizeMode.FIT(400, 400))   # 10x: bands beyond the V-first ring
+    ll.resize(_ll_img(noise_image(4000, 3000, 1)), ll.ResizeMode.FIT(400, 400))   # 10x (the GUI's thumbnail of a 12 MP photo): 5-chunk bands
+    assert ll.last_resize_path() == ll.PATH_VFIRST
+    ll.resize(_ll_img(noise_image(6000, 4000, 1)), ll.ResizeMode.FIT(400, 400))   # 15x: bands beyond the V-first ring
     assert ll.last_resize_path() == ll.PATH_HFIRST
     before = ll.path_launches(ll.PATH_REMAP)
     ll.extend(_ll_img(img), ll.ExtendMode.ASPECT_RATIO(1, 1), ll.FillColor.TRANSPARENT())
