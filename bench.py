@@ -604,6 +604,33 @@ def main():
             e2e["pageable"]["frac_of_pinned"] = e2e["pageable"]["value"] / e2e_value
             del page_in, page_out
 
+        # a folder of photos is not one geometry: eight source sizes in one batch through the same call (one plan per
+        # geometry from the library's plan cache, images of different sizes interleaved on the worker streams)
+        if not args.no_pageable:
+            sizes = [(4000, 3000), (6000, 4000), (7680, 4320), (1024, 1024), (3000, 4000), (1920, 1080), (2048, 2048), (4000, 6000)]
+            fit = ll.make_options(resize=ll.ResizeMode.FIT(800, 800))
+            offs, o = [], 0
+            for i in range(nb):
+                w, h = sizes[i % len(sizes)]
+                offs.append((o, w, h))
+                o += w * h * 4
+            assert o <= nb * in_bytes and 800 * 800 * 4 <= out_bytes
+            mixed_px = sum(w * h for _, w, h in offs)
+
+            def mixed_step():
+                for i, (off, w, h) in enumerate(offs):
+                    cin[i] = ll.CImage(w, h, pin_in + off, w * h * 4)
+                    cout[i] = ll.CImage(0, 0, pin_out + i * out_bytes, out_bytes)
+                if lib.slimg_b200_pipeline_batch_host(cin, nb, C.byref(fit), ll.ORDER_CONVERT, C.byref(cfg), cout, st):
+                    raise SystemExit("mixed-size e2e batch failed: " + lib.slimg_b200_last_error().decode())
+
+            m_steps = max(3, min(args.steps, 4))
+            dt_m, step_ms_m = timed_e2e(mixed_step, m_steps)
+            e2e["mixed_sizes"] = {"value": _shard.whole_job_throughput(m_steps * mixed_px / 1e6, world, dt_m), "unit": "Mpx/s",
+                                  "what": "12 MP / 24 MP / 8K / 1024^2 / portrait / 1080p / 2048^2 photos in one batch, Fit(800, 800), pinned buffers",
+                                  "images_per_gpu_per_step": nb, "geometries": len(sizes), "steps": m_steps, "step_ms": step_ms_m,
+                                  "host_image_bytes_per_step": o}
+
         # the library's own multi-device scheduler: ONE process (rank 0) feeding every GPU of the box (n_devices = world),
         # no Python per rank -- the `--jobs` analogue proper; the other ranks wait
         if world > 1:

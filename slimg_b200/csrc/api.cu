@@ -346,7 +346,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path
             v.b2 = (const uint32_t *)plan->v_b2.p; v.cx = (const float *)plan->v_cx.p;
             for (int l = 0; l < 2; l++)
                 for (int d = 0; d < 3; d++) v.s2[l][d] = vp.s2[l][d];
-            v.vbufs = vp.vbufs; v.ring_rows = vp.ring_rows; v.pitch = vp.pitch; v.pitch_v = vp.pitch_v; v.smem_bytes = vp.smem_bytes;
+            v.vbufs = vp.vbufs; v.cohorts = vp.cohorts; v.ring_rows = vp.ring_rows; v.pitch = vp.pitch; v.pitch_v = vp.pitch_v; v.smem_bytes = vp.smem_bytes;
             v.fw = g.fw; v.fh = g.fh; v.fox = g.fox; v.foy = g.foy;
             v.fill_post = pack_fill(g.fill_post); v.fill_pre_packed = pack_fill(g.fill_pre);
             v.n_bands = 1; v.need_fill = (vp.need_fill ? 1u : 0u) | (vp.rows_pure_fill ? 2u : 0u);

@@ -110,6 +110,7 @@ struct VPlanHost {
     // shared-memory geometry
     uint32_t ring_rows = 0, pitch = 0, pitch_v = 0, smem_bytes = 0;
     uint32_t vbufs = 3;                    // V buffers (k2_vfirst.cu): 2..4
+    uint32_t cohorts = 1;                  // pass-1 warp cohorts: cohort k filters groups k, k + cohorts, ... (k2_vfirst.cu)
     bool need_fill = false, rows_pure_fill = false;
 };
 void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int ndig, VPlanHost &out);

@@ -201,13 +201,14 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
     // They meet only on mbarriers: no CTA-wide barrier inside the band loop.
     const int ntile = (col1 - col0 + 7) >> 3;
     const int n_p1 = kWarps - 2 - ntile;
+    const int nco = int(p.cohorts), csize = n_p1 / nco;         // warps of one pass-1 cohort
     const uint32_t rec_bytes = p.rec_words * 4u;
     if (tid == 0) {
         for (int s = 0; s < nst; s++) mbar_init(&tail.full[s], 1);
         for (int b = 0; b < kRecBufs; b++) mbar_init(&tail.rec_full[b], 1);
         for (int b = 0; b < int(p.vbufs); b++) {
             mbar_init(&tail.go[b], 1);
-            mbar_init(&tail.v_full[b], uint32_t(n_p1));
+            mbar_init(&tail.v_full[b], uint32_t(csize));
             mbar_init(&tail.v_empty[b], uint32_t(ntile));
             tail.pos[b] = 0;
         }
@@ -370,7 +371,15 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         // Static ownership: warp w1 of the n_p1 pass-1 warps computes units [w1*upw, (w1+1)*upw) of UNIT blocks in
         // every group (the plan pads the staged span to n_p1*upw*UNIT blocks), so there is no queue and one
         // barrier wait per group.
-        const int w1 = warp - ntile;
+        // Cohorts: with nco = 2 the warps of cohort 0 filter groups 0, 2, 4, ... and those of cohort 1 groups 1, 3, 5, ...
+        // Two groups are in flight at once, each warp owns twice the blocks of half the groups, and the barrier round
+        // trip, the weight fragments and the set-up of a group are paid once per two units.  Neighbouring warps are in
+        // different cohorts and the pairing flips every four warps, so every SM sub-partition hosts both cohorts and
+        // one's multiplies fill the other's epilogue.
+        const int w1a = warp - ntile;
+        const int co = nco == 1 ? 0 : nco == 2 ? (((w1a >> 2) + w1a) & 1) : w1a % nco;
+        const int w1 = nco == 1 ? w1a : nco == 2 ? (w1a >> 1) : w1a / nco;             // rank inside the cohort
+        if (w1 >= csize) return;                           // n_p1 is not a multiple of nco: the last warps have no role
         const int upw_all = p.strip_upw[strip];
         const int upw = max(0, min(upw_all, p.strip_nunits[strip] - w1 * upw_all));     // this warp's units
         const int sh1 = p.sh1;
@@ -378,9 +387,9 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         const int ring_rows = int(p.ring_rows);
         const uint32_t boff0 = uint32_t(w1 * upw_all) * (UNIT * 16u);
 
-        uint32_t buf = 0, par = 0;
+        uint32_t buf = uint32_t(co) % p.vbufs, par = uint32_t(co) / p.vbufs;     // nco <= 3, vbufs >= 2
 #pragma unroll 1
-        for (int it = 0; it < n_iter; it++, buf = buf + 1 == p.vbufs ? 0 : buf + 1, par ^= buf == 0 ? 1u : 0u) {
+        for (int it = co; it < n_iter; it += nco) {
             const uint32_t *rec = recbuf + uint32_t(it & (kRecBufs - 1)) * p.rec_words;
             mbar_wait(&tail.go[buf], par);
             const int pos = tail.pos[buf];
@@ -446,6 +455,8 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&tail.v_full[buf]);        // this warp's share of V[buf] is written
+            buf += uint32_t(nco);
+            while (buf >= p.vbufs) { buf -= p.vbufs; par ^= 1u; }
         }
     }
 }
@@ -521,6 +532,7 @@ cudaError_t launch_resize_vfirst(const VfParams &p, uint32_t n_images, cudaStrea
     if (n_images == 0 || p.fw == 0 || p.fh == 0) return cudaSuccess;
     if (p.n_bands == 0 || p.n_bands > 65535 || p.n_strips == 0 || p.nch1 > 6 || p.nch2 > 6) return cudaErrorInvalidValue;
     if (p.ring_rows % kStepRows != 0 || p.ring_rows / kStepRows > kMaxSteps) return cudaErrorInvalidValue;
+    if (p.cohorts < 1 || p.cohorts > 3 || p.vbufs < 2) return cudaErrorInvalidValue;
 #define SLIMG_VF_CASE(A, B, U) if (p.nch1 == A && p.nch2 == B && p.unit == U) return launch_vf_t<2, A, B, U>(p, n_images, stream);
 #define SLIMG_VF_ROW(A, U) SLIMG_VF_CASE(A, 1, U) SLIMG_VF_CASE(A, 2, U) SLIMG_VF_CASE(A, 3, U) SLIMG_VF_CASE(A, 4, U)
 #define SLIMG_VF_ALL(U) SLIMG_VF_ROW(1, U) SLIMG_VF_ROW(2, U) SLIMG_VF_ROW(3, U) SLIMG_VF_ROW(4, U)

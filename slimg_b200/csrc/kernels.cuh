@@ -130,6 +130,7 @@ struct VfParams {
     // shared memory geometry
     uint32_t ring_rows, pitch, pitch_v, smem_bytes;
     uint32_t vbufs;                  // V (vertical-pass result) buffers: pass 1 may run this many groups ahead of pass 2
+    uint32_t cohorts;                // pass-1 warps work in this many cohorts, cohort k on groups k, k + cohorts, ...
     // canvas
     uint32_t fw, fh, fox, foy;
     uint32_t fill_post, fill_pre_packed;

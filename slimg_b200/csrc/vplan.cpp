@@ -210,7 +210,8 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     // pass 1 splits a strip's 16-byte blocks statically: units of `unit` blocks, upw consecutive units per warp
     // over the (kVfWarps - 2 - tiles) pass-1 warps (the last warps may own fewer, or none)
     auto pad_blocks = [&](int64_t raw, uint32_t ncols, int unit, int &upw) {
-        const int64_t n_p1 = kVfWarps - 2 - int64_t((ncols + 7) / 8);   // k2_vfirst.cu: all warps - producer - signaller - tiles
+        // k2_vfirst.cu: all warps - producer - signaller - tiles, split into cohorts that take turns on the groups
+        const int64_t n_p1 = std::max<int64_t>(1, (kVfWarps - 2 - int64_t((ncols + 7) / 8)) / int64_t(out.cohorts));
         const int64_t nunits = (raw + unit - 1) / unit;
         upw = int((nunits + n_p1 - 1) / n_p1);
         return nunits * unit;
@@ -236,6 +237,21 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     // same rule measured 4-11 % slower) keep 4 V buffers and two groups of ring look-ahead.
     const bool short_bands = out.nch1 == 3 && !std::getenv("SLIMG_B200_NO_SHORT_BAND_POLICY");
     out.vbufs = vbufs_env ? uint32_t(std::min(kVfMaxVBufs, std::max(2, std::atoi(vbufs_env)))) : (short_bands ? 3u : 4u);
+    // Pass-1 cohorts (k2_vfirst.cu): two groups in flight, each on half the warps.  Measured on B200 (24 MP source unless
+    // noted; us per image with 1 / 2 / 3 cohorts): 7.5x chain 18.76 / 18.31 / 17.98, 6x 20.33 / 18.72 / 20.24, 3x 39.29 /
+    // 36.02 / 35.48, 12 MP 5x 12.16 / 12.00 / 12.32, 12 MP 10x 16.43 / 16.13 / 16.70; but 8K 4x (7 pass-1 warps: one
+    // idles) 36.66 / 37.23 / 39.20, and 2x (one-chunk bands, 6 warps) 70.10 / 69.76 / 64.98.  Rule: two cohorts when the
+    // pass-1 warp count is even (odd counts measured within noise either way: one cohort), three where one-chunk bands
+    // meet a multiple of three.
+    const char *cohorts_env = std::getenv("SLIMG_B200_COHORTS");
+    auto cohorts_for = [&](uint32_t width) {
+        const int n_p1 = kVfWarps - 2 - int((width + 7) / 8);
+        if (cohorts_env) return uint32_t(std::min(std::max(1, n_p1), std::min(3, std::max(1, std::atoi(cohorts_env)))));
+        if (n_p1 < 4) return 1u;
+        if (out.nch1 == 1 && n_p1 % 3 == 0) return 3u;
+        if (n_p1 % 2 == 1) return 1u;                     // an odd count would leave a warp without a role
+        return 2u;
+    };
     const double look_min = short_bands ? 1.5 : kLookGroups;
     const int min_p1 = short_bands ? 7 : 1;              // pass-1 warps a strip must leave (tiles take one warp each)
     uint32_t cols = 0;
@@ -277,6 +293,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         // even the strips out first (keeps the multiple of 8)
         const uint32_t ns = (g.pw + cand - 1) / cand;
         const uint32_t even = std::min<uint32_t>(cand, ((g.pw + ns - 1) / ns + 7) / 8 * 8);
+        out.cohorts = cohorts_for(even);
         int best_u = 0, best_crit = INT32_MAX;
         int64_t best_blk = INT64_MAX;
         for (int u = 5; u >= 3; u--) {
@@ -303,6 +320,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     }
     if (cols == 0) { cols = fb_cols; unit = fb_unit; early = fb_early; ring_rows = fb_ring; }
     if (cols == 0) return;
+    out.cohorts = cohorts_for(cols);
     out.unit = unit;
     out.early_go = early;
     out.ring_rows = ring_rows;

@@ -31,8 +31,8 @@ int main(int argc, char **argv) {
     printf("tile: ok=%d tile=%ux%u blocks=%ux%u rows_max=%u nch1=%d nch2=%d pitch=%u pitch_v=%u v_words=%u smem=%u sh1=%d\n", int(lp.ok), lp.tw, lp.th,
            lp.n_colblk, lp.n_rowblk, lp.rows_max, lp.nch1, lp.nch2, lp.pitch, lp.pitch_v, lp.v_words, lp.smem_bytes, lp.sh1);
     VPlanHost vp; build_vplan(g, tx, ty, 2, vp);
-    printf("vfirst: ok=%d strips=%u cols=%d unit=%d vbufs=%u ring=%u pitch=%u smem=%u nch1=%d nch2=%d recs=%u\n", int(vp.ok), vp.n_strips,
-           vp.ok ? vp.strip_col0[1] : 0, vp.unit, vp.vbufs, vp.ring_rows, vp.pitch, vp.smem_bytes, vp.nch1, vp.nch2, vp.n_recs);
+    printf("vfirst: ok=%d strips=%u cols=%d unit=%d upw=%d nunits=%d co=%u vbufs=%u ring=%u pitch=%u smem=%u nch1=%d nch2=%d recs=%u\n", int(vp.ok), vp.n_strips,
+           vp.ok ? vp.strip_col0[1] : 0, vp.unit, vp.ok ? vp.strip_upw[0] : 0, vp.ok ? vp.strip_nunits[0] : 0, vp.cohorts, vp.vbufs, vp.ring_rows, vp.pitch, vp.smem_bytes, vp.nch1, vp.nch2, vp.n_recs);
     TcPlanHost tp; build_tcplan(g, tx, ty, tp);
     printf("tc: ok=%d strips=%u cols=%d panels=%u nbuf=%u vbufs=%u slots=%u blocks=%u chunks=%u nb_max=%u nch2=%d pitch_v=%u smem=%u\n", int(tp.ok), tp.n_strips,
            tp.ok ? tp.strip_col0[1] : 0, tp.n_panels, tp.nbuf, tp.vbufs, tp.slots, tp.n_blocks, tp.n_chunks, tp.nb_max, tp.nch2, tp.pitch_v, tp.smem_bytes);
