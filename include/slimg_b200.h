@@ -207,6 +207,22 @@ void slimg_b200_planes_free(slimg_planes *p);
  * of n * ceil(h/2) bytes + n u32 flags is taken from `scratch` (n * ceil(h/2) + 4 n bytes, zeroed by the call) */
 slimg_status slimg_b200_color_planes_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h, int kind,
                                                   void *y, void *cb, void *cr, void *a, void *scratch, void *stream);
+/* The WebP case of the call above for callers that must not allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The row-flag scratch the conversion needs lives in a static __device__ array inside the library
+ * (SLIMG_WEBP_STATIC_SCRATCH_BYTES, held by every GPU that loads the library until the process exits); the call
+ * performs no cudaMalloc / cudaFree and calls no allocating routine: it enqueues a memset, two kernels and one
+ * device-to-device copy on `stream` and returns.  Same arguments and same planes as the call above with
+ * kind = SLIMG_PLANES_WEBP_YUV420 and a non-NULL `a`; `any_alpha` (device, n u32, may be NULL) receives 1 for every image
+ * that holds a pixel that is not opaque, else 0.  Limit: n * ceil(h/2) rounded up to 4, + 4 n bytes, must fit the static
+ * scratch (e.g. 60 images 8640 rows high, or 1 image of up to 524 000 rows); beyond it the call fails with
+ * SLIMG_ERR_IMAGE and a message naming the limit.  Every call on a device shares the one array: calls that overlap on
+ * the GPU (different streams, or graphs replayed concurrently) race on it and must be serialised by the caller; calls
+ * on one stream are safe, and each call clears the flags the previous one left. */
+#define SLIMG_WEBP_STATIC_SCRATCH_BYTES 262144
+slimg_status slimg_b200_webp_planes_batch_device_static(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h,
+                                                        void *y, void *u, void *v, void *a, uint32_t *any_alpha,
+                                                        void *stream);
 
 /* ---- batched, device-resident variants (what bench.py's `value` times) ----
  * `src` / `dst` are DEVICE pointers on the current CUDA device; images are packed back to back

@@ -90,6 +90,7 @@ ABI_SYMBOLS = (
     "slimg_b200_jpeg_frontend_batch_device_ex", "slimg_b200_pipeline_jpeg_batch_device",
     "slimg_b200_pipeline_jpeg_batch_host", "slimg_b200_last_resize_path", "slimg_b200_path_launches",
     "slimg_b200_pipeline_planes", "slimg_b200_planes_free", "slimg_b200_color_planes_batch_device",
+    "slimg_b200_webp_planes_batch_device_static",
 )
 
 _lib: Optional[C.CDLL] = None
@@ -143,6 +144,7 @@ def library() -> C.CDLL:
         "slimg_b200_pipeline_planes": (C.c_int, [C.POINTER(CImage), C.POINTER(CPipelineOptions), C.c_int, C.c_int, C.POINTER(CPlanes)]),
         "slimg_b200_planes_free": (None, [C.POINTER(CPlanes)]),
         "slimg_b200_color_planes_batch_device": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, vp, vp, vp, vp, vp, vp]),
+        "slimg_b200_webp_planes_batch_device_static": (C.c_int, [vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp, vp]),
         "slimg_b200_last_resize_path": (C.c_int32, []),
         "slimg_b200_path_launches": (C.c_uint64, [C.c_int32]),
     }

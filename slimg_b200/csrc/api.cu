@@ -1167,6 +1167,29 @@ slimg_status slimg_b200_color_planes_batch_device(const uint8_t *src, uint32_t n
     return run_planes_device(src, n, w, h, kind, y, cb, cr, a, scratch, static_cast<cudaStream_t>(stream));
 }
 
+// the WebP planes conversion with its scratch in a static __device__ array (k4_planes.cu): no cudaMalloc / cudaFree, no
+// allocating routine of any library on this path -- only a memset, two kernel launches and one device-to-device copy
+slimg_status slimg_b200_webp_planes_batch_device_static(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h, void *y,
+                                                        void *u, void *v, void *a, uint32_t *any_alpha, void *stream) {
+    if (n && (!src || !y || !u || !v || !a)) return fail(SLIMG_ERR_IMAGE, "null argument");
+    if (w == 0 || h == 0) return fail(SLIMG_ERR_ENCODE, "image has a zero dimension");
+    if (n > 65535) return fail(SLIMG_ERR_IMAGE, "at most 65535 images per call");
+    if (webp_static_scratch_need(n, h) > kWebpStaticScratchBytes)
+        return fail(SLIMG_ERR_IMAGE, "n * ceil(h/2) row flags + 4 n bytes exceed the static scratch (SLIMG_WEBP_STATIC_SCRATCH_BYTES = 262144): "
+                                     "split the batch or use slimg_b200_color_planes_batch_device with caller scratch");
+    slimg_status st = check_device();
+    if (st != SLIMG_OK) return st;
+    const size_t px = size_t(w) * h;
+    WebpPlanesParams p{};
+    p.src = src; p.src_img_bytes = px * 4; p.y_img_bytes = px;
+    p.uv_img_bytes = size_t((w + 1) / 2) * ((h + 1) / 2);
+    p.w = w; p.h = h;
+    p.y = static_cast<uint8_t *>(y); p.u = static_cast<uint8_t *>(u); p.v = static_cast<uint8_t *>(v); p.a = static_cast<uint8_t *>(a);
+    webp_gamma_tables(p.g2l, p.l2g);
+    CU(launch_webp_planes_static(p, n, any_alpha, static_cast<cudaStream_t>(stream)));
+    return SLIMG_OK;
+}
+
 slimg_status slimg_b200_pipeline_planes(const slimg_image *in, const slimg_pipeline_options *opts, int order, int kind,
                                         slimg_planes *out) {
     if (!opts || !out) return fail(SLIMG_ERR_IMAGE, "null argument");

@@ -8,6 +8,8 @@
 // Both libraries are crates.io dependencies absent from the reference tree: the arithmetic is restated from their published
 // sources (oracle/slimg_oracle.c holds the CPU restatement the tests compare with) -- PARITY UNPINNED, said so in DESIGN.md.
 // Roofline: HBM (4 B/px read; 1.5 - 2.5 B/px written for WebP, 4 - 8 B/px for AVIF); pure streaming kernels.
+#include <mutex>
+
 #include "kernels.cuh"
 
 namespace slimg {
@@ -193,6 +195,58 @@ cudaError_t launch_webp_planes(const WebpPlanesParams &p, uint32_t n_images, cud
     webp_planes_kernel<<<dim3(((p.w + 3) / 4 + 63) / 64, (uvh + 3) / 4, n_images), kThreads, 0, stream>>>(p);
     count_launch();
     return cudaGetLastError();
+}
+
+// ---- the variant that allocates nothing (slimg_b200_webp_planes_batch_device_static) ---------------------------------
+// The scratch of the WebP planes conversion -- one byte per pair of rows ("this pair holds a pixel that is not opaque")
+// and one u32 flag per image -- lives in this file-scope array instead of memory the caller allocated.  Every GPU
+// that loads the library holds these kWebpStaticScratchBytes until the process exits; every call on a device shares
+// them, so calls that overlap on the GPU race (see include/slimg_b200.h).
+__device__ __align__(256) uint8_t g_webp_static_scratch[kWebpStaticScratchBytes];
+
+// In host code `g_webp_static_scratch` is a host-side stand-in, not a device address: the address a kernel can use
+// comes from cudaGetSymbolAddress, asked once per device with that device current.
+static cudaError_t webp_static_scratch(uint8_t **out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static uint8_t *addr[kMaxDevices] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void *ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_webp_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (!ptr) return cudaErrorInvalidSymbol;
+        addr[dev] = static_cast<uint8_t *>(ptr);
+    }
+    *out = addr[dev];
+    return cudaSuccess;
+}
+
+size_t webp_static_scratch_need(uint32_t n_images, uint32_t h) {
+    const size_t rows = size_t(n_images) * ((size_t(h) + 1) / 2);
+    return ((rows + 3) & ~size_t(3)) + size_t(n_images) * 4;
+}
+
+// same two kernels as launch_webp_planes; p.row_alpha / p.any_alpha are set here.  any_out (device, n u32, may be NULL)
+// receives the per-image "has a pixel that is not opaque" flags.
+cudaError_t launch_webp_planes_static(WebpPlanesParams p, uint32_t n_images, uint32_t *any_out, cudaStream_t stream) {
+    if (n_images == 0 || p.w == 0 || p.h == 0) return cudaSuccess;
+    if (webp_static_scratch_need(n_images, p.h) > kWebpStaticScratchBytes) return cudaErrorInvalidValue;
+    uint8_t *scratch = nullptr;
+    cudaError_t e = webp_static_scratch(&scratch);
+    if (e != cudaSuccess) return e;
+    const size_t rows = size_t(n_images) * ((size_t(p.h) + 1) / 2);
+    p.row_alpha = scratch;                                   // fully rewritten by the scan kernel
+    p.any_alpha = reinterpret_cast<uint32_t *>(scratch + ((rows + 3) & ~size_t(3)));
+    // the flags are only ever SET by the scan kernel: the previous call's must go
+    if ((e = cudaMemsetAsync(p.any_alpha, 0, size_t(n_images) * 4, stream)) != cudaSuccess) return e;
+    if ((e = launch_webp_planes(p, n_images, stream)) != cudaSuccess) return e;
+    if (any_out) e = cudaMemcpyAsync(any_out, p.any_alpha, size_t(n_images) * 4, cudaMemcpyDeviceToDevice, stream);
+    return e;
 }
 
 cudaError_t launch_avif_planes(const AvifPlanesParams &p, uint32_t n_images, cudaStream_t stream) {

@@ -241,6 +241,10 @@ struct WebpPlanesParams {
     int32_t l2g[33];                   // libwebp kLinearToGammaTab
 };
 cudaError_t launch_webp_planes(const WebpPlanesParams &p, uint32_t n_images, cudaStream_t stream);
+// the same conversion with its scratch in a file-scope __device__ array of k4_planes.cu: nothing is allocated
+constexpr size_t kWebpStaticScratchBytes = 256 * 1024;      // == SLIMG_WEBP_STATIC_SCRATCH_BYTES (include/slimg_b200.h)
+size_t webp_static_scratch_need(uint32_t n_images, uint32_t h);
+cudaError_t launch_webp_planes_static(WebpPlanesParams p, uint32_t n_images, uint32_t *any_out, cudaStream_t stream);
 struct AvifPlanesParams {
     const uint8_t *src;
     size_t src_img_bytes;
