@@ -88,7 +88,7 @@ struct ResizePlan {
     FastResizeParams fparams{};
     // V-first integer tensor pipeline (k2_vfirst.cu), preferred when the geometry qualifies
     bool vfirst = false;
-    DevArray v_recs, v_rowc, v_col0, v_src0, v_nblk, v_bytes, v_upw, v_nunits, v_kb0, v_tnch, v_b2, v_cx;
+    DevArray v_recs, v_rowc, v_col0, v_src0, v_nblk, v_bytes, v_upw, v_nunits, v_kb0, v_tnch, v_b2, v_cx, v_cxi;
     VfParams vparams{};
     // integer tile kernel (k2_tile.cu): ratios below ~3.5x and upscales
     bool tile = false;
@@ -330,7 +330,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path
             if ((e = plan->v_recs.upload(vp.recs)) || (e = plan->v_rowc.upload(vp.row_computed)) || (e = plan->v_col0.upload(vp.strip_col0)) ||
                 (e = plan->v_src0.upload(vp.strip_src0)) || (e = plan->v_nblk.upload(vp.strip_nblk)) ||
                 (e = plan->v_bytes.upload(vp.strip_bytes)) || (e = plan->v_upw.upload(vp.strip_upw)) || (e = plan->v_nunits.upload(vp.strip_nunits)) || (e = plan->v_kb0.upload(vp.tile_kb0)) ||
-                (e = plan->v_tnch.upload(vp.tile_nch)) || (e = plan->v_b2.upload(vp.b2)) || (e = plan->v_cx.upload(vp.cx)))
+                (e = plan->v_tnch.upload(vp.tile_nch)) || (e = plan->v_b2.upload(vp.b2)) || (e = plan->v_cx.upload(vp.cx)) || (e = plan->v_cxi.upload(vp.cxi)))
                 return cuda_fail(e, "uploading V-first resize plan");
             VfParams &v = plan->vparams;
             v.sw = g.sw; v.sh = g.sh; v.ry = g.ry; v.pw = g.pw; v.ph = g.ph;
@@ -343,7 +343,7 @@ static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path
             v.strip_nblk = (const int32_t *)plan->v_nblk.p; v.strip_bytes = (const int32_t *)plan->v_bytes.p;
             v.strip_upw = (const int32_t *)plan->v_upw.p; v.strip_nunits = (const int32_t *)plan->v_nunits.p; v.unit = vp.unit; v.early_go = vp.early_go ? 1u : 0u;
             v.tile_kb0 = (const int32_t *)plan->v_kb0.p; v.tile_nch = (const int32_t *)plan->v_tnch.p;
-            v.b2 = (const uint32_t *)plan->v_b2.p; v.cx = (const float *)plan->v_cx.p;
+            v.b2 = (const uint32_t *)plan->v_b2.p; v.cx = (const float *)plan->v_cx.p; v.cxi = (const int32_t *)plan->v_cxi.p; v.sh2 = vp.sh2;
             for (int l = 0; l < 2; l++)
                 for (int d = 0; d < 3; d++) v.s2[l][d] = vp.s2[l][d];
             v.vbufs = vp.vbufs; v.cohorts = vp.cohorts; v.ring_rows = vp.ring_rows; v.pitch = vp.pitch; v.pitch_v = vp.pitch_v; v.smem_bytes = vp.smem_bytes;

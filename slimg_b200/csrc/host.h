@@ -106,6 +106,8 @@ struct VPlanHost {
     std::vector<int32_t> tile_kb0, tile_nch;                    // [n_strips][8]
     std::vector<uint32_t> b2;              // [n_strips][8][nch2][ndig][32][2]
     std::vector<float> cx;                 // [pw][4]
+    std::vector<int32_t> cxi;              // [pw][4] the same constant term + rounding half, in units of 2^-sh2 (integer epilogue)
+    int sh2 = 0;
     float s2[2][3] = {{0, 0, 0}, {0, 0, 0}};
     // shared-memory geometry
     uint32_t ring_rows = 0, pitch = 0, pitch_v = 0, smem_bytes = 0;

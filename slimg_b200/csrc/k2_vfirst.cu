@@ -105,6 +105,18 @@ __device__ __forceinline__ void imma_c(int (&d)[4], const uint32_t (&a)[4], cons
                  : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "r"(c0), "r"(c1));
 }
+// C = {c0, c1} for fragment row g (columns 2t, 2t+1) and {c2, c3} for row g + 8
+__device__ __forceinline__ void imma_c4(int (&d)[4], const uint32_t (&a)[4], const uint2 &b, int c0, int c1, int c2, int c3) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "r"(c0), "r"(c1), "r"(c2), "r"(c3));
+}
+// d = (c << 16) | (sat_u8(hi) << 8) | sat_u8(lo): clamp to [0, 255] and pack, two channels per instruction
+__device__ __forceinline__ uint32_t pack_sat_u8(int hi, int lo, uint32_t c) {
+    uint32_t d;
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(hi), "r"(lo), "r"(c));
+    return d;
+}
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
     uint32_t v;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
@@ -303,16 +315,23 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             for (int d = 0; d < NDIG; d++)
                 bw2[c][d] = __ldg(reinterpret_cast<const uint2 *>(p.b2) + ((size_t(strip * 8 + tile) * NCH2 + c) * NDIG + d) * 32 + lane);
         const int ocol = col0 + tile * 8 + 2 * t;          // this lane's two kept output columns
+        constexpr bool kIntEpi = NDIG == 2;                // two-digit plans: the sum never leaves the integers
         float cxr[2][4];                                   // [column ocol+e][channel]
+        int cxq[2][4];                                     // the same in units of 2^-sh2, rounding half included
 #pragma unroll
         for (int e = 0; e < 2; e++)
 #pragma unroll
-            for (int c = 0; c < 4; c++) cxr[e][c] = ocol + e < col1 ? p.cx[size_t(ocol + e) * 4 + c] : 0.0f;
+            for (int c = 0; c < 4; c++) {
+                cxr[e][c] = !kIntEpi && ocol + e < col1 ? p.cx[size_t(ocol + e) * 4 + c] : 0.0f;
+                cxq[e][c] = kIntEpi && ocol + e < col1 ? __ldg(p.cxi + size_t(ocol + e) * 4 + c) : 0;
+            }
         float s2[2][NDIG];
 #pragma unroll
         for (int l = 0; l < 2; l++)
 #pragma unroll
             for (int d = 0; d < NDIG; d++) s2[l][d] = p.s2[l][d];
+        const int sh2 = p.sh2;
+        const bool all_rows = (p.need_fill & 2u) == 0;
         int j_next = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words)) : 0;
 
         uint32_t buf = 0, par = 0;
@@ -324,46 +343,92 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             mbar_wait(&tail.v_full[buf], par);
 
             if (p.debug & 2u) { __syncwarp(); if (lane == 0) mbar_arrive(&tail.v_empty[buf]); continue; }
-            int acc[2][2][NDIG][4];            // [channel pair][limb][digit]
+            uint32_t px[2] = {0u, 0u};         // packed RGBA of columns ocol, ocol+1 of output row g
+            if (kIntEpi) {
+                // three accumulators per channel pair, by weight: low limb x digit 0 (2^-8), low x digit 1 + high x digit 0
+                // (2^0, starts at the constant term), high x digit 1 (2^8)
+                int tsum[2][4];
 #pragma unroll
-            for (int mt = 0; mt < 2; mt++) {   // channel pairs (0,1) and (2,3)
-                const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
-                const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
+                for (int mt = 0; mt < 2; mt++) {   // channel pairs (0,1) and (2,3)
+                    const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
+                    const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
+                    int aa[4], ab[4], ac[4];
 #pragma unroll
-                for (int c = 0; c < NCH2; c++) {
+                    for (int c = 0; c < NCH2; c++) {
 #pragma unroll
-                    for (int l = 0; l < 2; l++) {
-                        uint32_t a[4];
-                        const uint32_t o = uint32_t(l) * vplane + uint32_t(c) * 32u;
-                        a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
+                        for (int l = 0; l < 2; l++) {
+                            uint32_t a[4];
+                            const uint32_t o = uint32_t(l) * vplane + uint32_t(c) * 32u;
+                            a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
+                            if (l == 0) {
+                                if (c == 0) {
+                                    imma_z(aa, a, bw2[c][0]);
+                                    imma_c4(ab, a, bw2[c][NDIG - 1], cxq[0][2 * mt], cxq[1][2 * mt], cxq[0][2 * mt + 1], cxq[1][2 * mt + 1]);
+                                } else {
+                                    imma(aa, a, bw2[c][0]);
+                                    imma(ab, a, bw2[c][NDIG - 1]);
+                                }
+                            } else {
+                                imma(ab, a, bw2[c][0]);
+                                if (c == 0) imma_z(ac, a, bw2[c][NDIG - 1]);
+                                else imma(ac, a, bw2[c][NDIG - 1]);
+                            }
+                        }
+                    }
 #pragma unroll
-                        for (int d = 0; d < NDIG; d++) {
-                            if (c == 0) imma_z(acc[mt][l][d], a, bw2[c][d]);
-                            else imma(acc[mt][l][d], a, bw2[c][d]);
+                    for (int i = 0; i < 4; i++) tsum[mt][i] = (aa[i] >> 8) + ab[i] + (ac[i] << 8);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tail.v_empty[buf]);       // V[buf] may be overwritten (vbufs groups on)
+                // i = 0,1: channel 2mt, columns +0, +1; i = 2,3: channel 2mt+1.  Shift, saturate, pack RGBA.
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+                    const int c0 = tsum[0][e] >> sh2, c1 = tsum[0][2 + e] >> sh2, c2 = tsum[1][e] >> sh2, c3 = tsum[1][2 + e] >> sh2;
+                    px[e] = pack_sat_u8(c1, c0, pack_sat_u8(c3, c2, 0u));
+                }
+            } else {
+                int acc[2][2][NDIG][4];            // [channel pair][limb][digit]
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++) {
+                    const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
+                    const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
+#pragma unroll
+                    for (int c = 0; c < NCH2; c++) {
+#pragma unroll
+                        for (int l = 0; l < 2; l++) {
+                            uint32_t a[4];
+                            const uint32_t o = uint32_t(l) * vplane + uint32_t(c) * 32u;
+                            a[0] = lds32(r0 + o); a[1] = lds32(r1 + o); a[2] = lds32(r0 + o + 16u); a[3] = lds32(r1 + o + 16u);
+#pragma unroll
+                            for (int d = 0; d < NDIG; d++) {
+                                if (c == 0) imma_z(acc[mt][l][d], a, bw2[c][d]);
+                                else imma(acc[mt][l][d], a, bw2[c][d]);
+                            }
                         }
                     }
                 }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tail.v_empty[buf]);
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {  // i = 0,1: channel 2mt, columns +0, +1; i = 2,3: channel 2mt+1
+                        float f = cxr[i & 1][2 * mt + (i >> 1)];
+#pragma unroll
+                        for (int l = 0; l < 2; l++)
+#pragma unroll
+                            for (int d = 0; d < NDIG; d++) f = fmaf(int_to_float(acc[mt][l][d][i]), s2[l][d], f);
+                        px[i & 1] |= quantize_channel(f) << (8 * (2 * mt + (i >> 1)));
+                    }
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tail.v_empty[buf]);       // V[buf] may be overwritten (vbufs groups on)
-
-            uint32_t px[2] = {0u, 0u};         // packed RGBA of columns ocol, ocol+1 of output row g
-#pragma unroll
-            for (int mt = 0; mt < 2; mt++)
-#pragma unroll
-                for (int i = 0; i < 4; i++) {  // i = 0,1: channel 2mt, columns +0, +1; i = 2,3: channel 2mt+1
-                    float f = cxr[i & 1][2 * mt + (i >> 1)];
-#pragma unroll
-                    for (int l = 0; l < 2; l++)
-#pragma unroll
-                        for (int d = 0; d < NDIG; d++) f = fmaf(int_to_float(acc[mt][l][d][i]), s2[l][d], f);
-                    px[i & 1] |= quantize_channel(f) << (8 * (2 * mt + (i >> 1)));
-                }
             const int i_row = j * 8 + g;
-            if (i_row < int(p.ph) && p.row_computed[i_row]) {
+            if (i_row < int(p.ph) && (all_rows || p.row_computed[i_row])) {
                 uint32_t *o = dst + size_t(p.foy + i_row) * p.fw + p.fox + ocol;
-                if (ocol < col1) o[0] = px[0];
-                if (ocol + 1 < col1) o[1] = px[1];
+                if (ocol + 1 < col1 && (reinterpret_cast<uintptr_t>(o) & 7) == 0) *reinterpret_cast<uint2 *>(o) = make_uint2(px[0], px[1]);
+                else {
+                    if (ocol < col1) o[0] = px[0];
+                    if (ocol + 1 < col1) o[1] = px[1];
+                }
             }
         }
     } else {

@@ -126,6 +126,8 @@ struct VfParams {
     const int32_t *tile_nch;         // [n_strips][8] 32-pixel chunks of the tile's k range
     const uint32_t *b2;              // [n_strips][8][4][ndig][32 lanes][2]
     const float *cx;                 // [pw][4] constant term per kept column and channel
+    const int32_t *cxi;              // [pw][4] the same + the rounding half, in units of 2^-sh2 (two-digit plans: integer epilogue)
+    int32_t sh2;
     float s2[2][3];                  // scale of accumulator [limb][digit]
     // shared memory geometry
     uint32_t ring_rows, pitch, pitch_v, smem_bytes;

@@ -177,7 +177,10 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     }
     if (!(maxw_x > 0.0f)) return;
     const int Sx = pick_scale(maxw_x, ndig);
-    if (Sx < 8) return;
+    if (Sx < 10) return;
+    // two-digit plans finish pass 2 in integers: t = (acc[lo][d0] >> 8) + acc[lo][d1] + acc[hi][d0] + (acc[hi][d1] << 8) + cxi is
+    // the output in units of 2^-sh2; the byte is t >> sh2 (the rounding half is folded into cxi), saturated
+    out.sh2 = Sx + kFrac - 8;
     for (int l = 0; l < 2; l++)
         for (int d = 0; d < 3; d++) out.s2[l][d] = d < ndig ? float(std::ldexp(1.0, 8 * l + 8 * d - Sx - kFrac)) : 0.0f;
 
@@ -336,6 +339,7 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     out.tile_kb0.assign(size_t(out.n_strips) * 8, 0);
     out.tile_nch.assign(size_t(out.n_strips) * 8, 0);
     out.cx.assign(size_t(g.pw) * 4, 0.0f);
+    out.cxi.assign(size_t(g.pw) * 4, 0);
     int64_t max_nblk = 1;
     // first sweep: geometry and the chunk count
     for (uint32_t s = 0; s < out.n_strips; s++) {
@@ -404,8 +408,11 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
             }
             // constant term: fill taps of the horizontal pass minus the intermediate's offset
             const double off = -double(kOffset) * double(sum_q) * std::ldexp(1.0, -Sx);
-            for (int c = 0; c < 4; c++)
-                out.cx[size_t(j) * 4 + c] = float(off + double(g.fill_pre[c]) * double(tx.fillw[o]));
+            for (int c = 0; c < 4; c++) {
+                const double cxv = off + double(g.fill_pre[c]) * double(tx.fillw[o]);
+                out.cx[size_t(j) * 4 + c] = float(cxv);
+                out.cxi[size_t(j) * 4 + c] = int32_t(std::llround(cxv * std::ldexp(1.0, out.sh2))) + (int32_t(1) << (out.sh2 - 1));
+            }
         }
     }
 

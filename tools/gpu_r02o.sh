@@ -1,0 +1,9 @@
+set -x
+mkdir -p gpurun_out
+OLD=$PWD/slimg_b200/lib/libslimg_b200_old.so
+( for rep in 1 2; do for c in c3 c4a c1 r6 r3 r2 thumb; do
+    AB=new timeout 120 python tools/time_config.py $c
+    AB=old SLIMG_B200_LIB=$OLD timeout 120 python tools/time_config.py $c
+  done; done
+) > gpurun_out/configs_o.txt 2>&1
+timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_paths_jpeg.py -m gpu -q -x > gpurun_out/pytest_gpu_o.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu_o.log
