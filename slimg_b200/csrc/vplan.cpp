@@ -302,6 +302,11 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         for (int u = 5; u >= 3; u--) {
             if (unit_env && std::atoi(unit_env) != u) continue;
             if ((out.nch1 > 4 || nch2_pre > 4) && u != 4) continue;      // k2_vfirst.cu instantiates the long-band kernels for UNIT = 4
+            // Measured on B200 with two cohorts (us per image, units of 3 / 4 / 5 blocks): 4-chunk bands (7.5x, 24 MP) - /
+            // 17.53 / 16.91 -- the fatter unit wins although it leaves a warp of each cohort idle; 3-chunk bands 10.94 /
+            // 10.93 / 11.54 (12 MP 5x), 18.67 / 18.85 / 26.66 (6x), 20.59 / 20.07 / 21.69 (5.5x); 2-chunk bands 30.53 / 31.10 /
+            // 34.53 (8K 4x), 32.45 / 32.57 / 32.78 (3x).  So: 5-block units for 4-chunk bands only.
+            if (!unit_env && out.nch1 <= 4 && nch2_pre <= 4 && (u == 5) != (out.nch1 == 4)) continue;
             int crit;
             const int64_t blk = max_padded(even, u, crit);
             if (crit < best_crit || (crit == best_crit && blk < best_blk)) { best_blk = blk; best_u = u; best_crit = crit; }
@@ -319,6 +324,10 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         if (!fb_cols) { fb_cols = even; fb_ring = rr; fb_unit = best_u; fb_early = e; }
         const double look = (double(rr) - 32.0 * out.nch1) / rows_per_group;
         const int n_p1 = kVfWarps - 2 - int((even + 7) / 8);
+        // an odd number of tiles leaves an odd number of pass-1 warps, which cannot pair up into two cohorts: the next
+        // narrower width can (measured on B200 after the integer epilogue: 8K 4x 56 columns 33.8 us, 48 columns 30.8;
+        // 12 MP 5x 40 columns 11.63, 32 columns 11.57).  Odd widths stay as the fallback when nothing else fits.
+        if (n_p1 % 2 == 1 && even > 8 && !cols_env && !std::getenv("SLIMG_B200_ODD_STRIPS")) continue;
         if ((look >= look_min && n_p1 >= min_p1) || cols_env) { cols = even; unit = best_u; early = e; ring_rows = rr; }
     }
     if (cols == 0) { cols = fb_cols; unit = fb_unit; early = fb_early; ring_rows = fb_ring; }
