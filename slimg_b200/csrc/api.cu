@@ -354,7 +354,10 @@ static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path
             const char *dbg_env = std::getenv("SLIMG_B200_VF_DEBUG");
             v.debug = dbg_env ? uint32_t(std::atoi(dbg_env)) : 0u;
             const char *pf_env = std::getenv("SLIMG_B200_PREFETCH_STEPS");
-            v.pf_steps = pf_env ? uint32_t(std::atoi(pf_env)) : 16u;  // ring steps prefetched into L2 ahead of the ring (measured: 8-16 best, 32 worse)
+            // ring steps prefetched into L2 ahead of the ring: 8 - 16 measured best for bands of 3+ chunks (32 worse); bands of 1 - 2
+            // chunks (ratios below ~4.5x) have wide strips and a ring that already runs 3+ groups ahead -- the prefetch only costs
+            // the TMA engine there (8K 4x 30.75 with, 29.88 us without; 3x 32.61 / 32.30; 2x 57.00 / 56.45)
+            v.pf_steps = pf_env ? uint32_t(std::atoi(pf_env)) : (vp.nch1 <= 2 ? 0u : 16u);
             plan->vfirst = true;
         }
     }

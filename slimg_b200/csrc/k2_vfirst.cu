@@ -233,14 +233,16 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         // One tiled TMA copy per ring step (a box of 16 source rows of the strip; the source batch is one tall
         // 2-D tensor of 8-byte elements, rows past its end and columns past the row end read as zero), one
         // linear bulk copy per group record.  Lane l issues step next_issue + l: a refill is one pass of the warp.
-        int next_issue = 0;
+        int next_issue = 0, issue_base = 0;              // issue_base: the multiple of nst at or below next_issue (no division per group)
         const int tc0 = p.strip_src0[strip] >> 1;                                   // 8-byte elements
         const int tr0 = int(blockIdx.z) * int(p.sh) + int(p.ry) + ys;
         const uint32_t step_bytes = kStepRows * p.pitch;
         auto issue_steps = [&](int upto) {
             const int step = next_issue + lane;                 // at most nst <= 32 steps are ever issued at once
+            if (next_issue >= issue_base + nst) issue_base += nst;     // next_issue advances by at most nst per call
             if (step < upto) {
-                const int slot = step % nst;
+                int slot = step - issue_base;
+                if (slot >= nst) slot -= nst;
                 mbar_arrive_expect_tx(&tail.full[slot], step_bytes);
                 tma_load_2d(ring + uint32_t(slot) * step_bytes, &tmap, tc0, tr0 + ((p.debug & 4u) ? (step & 7) : step) * kStepRows, &tail.full[slot]);
             }
@@ -273,7 +275,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             a_next = it + 2 < n_iter ? int(__ldg(p.recs + size_t(rec0 + it + 2) * p.rec_words + 1)) : ye;
             mbar_wait(&tail.v_full[buf], par);
             if (++buf == p.vbufs) { buf = 0; par ^= 1u; }
-            issue_steps(min(n_steps, (a_cur - ys) / kStepRows + nst));
+            issue_steps(min(n_steps, int(uint32_t(a_cur - ys) / uint32_t(kStepRows)) + nst));
             if (p.pf_steps) prefetch_steps(min(n_steps, next_issue + int(p.pf_steps)));
             if (it + kRecBufs < n_iter) issue_rec(it + kRecBufs);   // the record buffer of this group is free
         }
@@ -281,10 +283,17 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         // ================= signaller: does the waiting for pass 1 =======================================
         // Group `it` may start when its record and source rows have landed and pass 2 has drained V[it & 1].
         // Lane l waits for ring step first + l; then one arrive on go[]: pass-1 warps wait on a single barrier.
-        const int ring_rows = int(p.ring_rows);
         int a0 = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words + 1)) : 0;
         int need = n_iter > 0 ? int(__ldg(p.recs + size_t(rec0) * p.rec_words + 2)) : 0;
         uint32_t buf = 0, par = 0;
+        // Ring slot and barrier phase of a step without a division per group: short groups (ratios below 4x: 16 - 32 source
+        // rows each) were paced by this warp's ~150 dependent scalar instructions (24 MP 2x 57.1 -> 49.7 us, 1.5x 93.0 -> 74.8,
+        // 8K 4x 30.9 -> 29.3).  The 4-chunk instances keep the divisions: with them removed the same kernel measured 6 %
+        // SLOWER on the 7.5x headline (16.99 vs 18.07 us, same results; the pass-1 loop's schedule and register allocation
+        // shift with the code around it: 119 vs 123 registers).
+        constexpr bool kDivFree = NCH1 != 4;
+        int wrap_base = 0;                                  // ring steps [wrap_base, wrap_base + nst) complete phase wrap_par of their barriers
+        uint32_t wrap_par = 0;
 #pragma unroll 1
         for (int it = 0; it < n_iter; it++) {
             const int a0_cur = a0, need_cur = need;
@@ -292,14 +301,22 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                 a0 = int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words + 1));
                 need = int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words + 2));
             }
-            const int first = (a0_cur - ys) / kStepRows, last = (need_cur - ys + kStepRows - 1) / kStepRows;
-            const int step = first + lane;                   // a band spans at most 128 rows + alignment: <= 9 steps
-            if (step < last) mbar_wait(&tail.full[step % nst], uint32_t(step / nst) & 1u);
+            const int first = int(uint32_t(a0_cur - ys) / uint32_t(kStepRows)), last = int(uint32_t(need_cur - ys + kStepRows - 1) / uint32_t(kStepRows));
+            while (first >= wrap_base + nst) { wrap_base += nst; wrap_par ^= 1u; }      // band starts move down monotonically
+            const int step = first + lane;                   // a band spans at most 192 rows + alignment: <= 13 steps
+            if (!kDivFree) {
+                if (step < last) mbar_wait(&tail.full[step % nst], uint32_t(step / nst) & 1u);
+            } else if (step < last) {
+                int slot = step - wrap_base;
+                uint32_t ph = wrap_par;
+                if (slot >= nst) { slot -= nst; ph ^= 1u; }
+                mbar_wait(&tail.full[slot], ph);
+            }
             mbar_wait(&tail.rec_full[it & (kRecBufs - 1)], uint32_t(it / kRecBufs) & 1u);
             mbar_wait(&tail.v_empty[buf], par ^ 1u);        // V[buf] was last read by pass 2 vbufs groups ago
             __syncwarp();
             if (lane == 0) {
-                tail.pos[buf] = (a0_cur - ys) % ring_rows;
+                tail.pos[buf] = kDivFree ? (first - wrap_base) * kStepRows + ((a0_cur - ys) & (kStepRows - 1)) : (a0_cur - ys) % int(p.ring_rows);
                 mbar_arrive(&tail.go[buf]);                  // release: pos is visible to the waiters
             }
             if (++buf == p.vbufs) { buf = 0; par ^= 1u; }
