@@ -319,6 +319,10 @@ def config_table(ll, torch, peak, main_src):
     pixel_config("GUI thumbnail 4000x3000 -> Fit(400,400)", 4000, 3000, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 64,
                  48_000_000 + 400 * 300 * 4, lambda a: oracle.resize(a, R.fit(400, 400)))
 
+    # rows that are not 16-byte aligned (width % 4 != 0): one K1 copy into a padded pitch, then the same tensor pipeline
+    pixel_config("5998x4000 -> Width(800) (rows not 16-byte aligned: re-pitched on the device)", 5998, 4000, dict(resize=ll.ResizeMode.WIDTH(800)),
+                 ll.ORDER_CONVERT, 32, 5998 * 4000 * 4 + 800 * 534 * 4, lambda a: oracle.resize(a, R.width(800)))
+
     # colour planes for the WebP / AVIF encoders, 24 MP batch; planes vs the oracle's restatement (unpinned)
     nb = 16
     srcp = main_src[:nb]

@@ -14,7 +14,9 @@ from test_gpu_parity import _close, _ll_img, _np
 SWEEP = [(6000, 416, int(round(6000 / r)), max(8, int(round(416 / r)))) for r in
          (1.3, 1.5, 2.0, 2.5, 3.0, 3.5, 4.0, 4.5, 5.0, 5.5, 6.0, 6.5, 7.0, 7.5, 8.0, 8.5, 9.0, 10.0, 10.9)]
 SWEEP += [(6000, 416, 800, 208), (6000, 416, 3000, 60), (4000, 600, 500, 300), (2400, 800, 1000, 90), (1600, 1200, 200, 700),
-          (7680, 264, 1920, 66), (5472, 364, 720, 48), (1024, 768, 400, 300), (804, 804, 100, 100)]
+          (7680, 264, 1920, 66), (5472, 364, 720, 48), (1024, 768, 400, 300), (804, 804, 100, 100),
+          # rows that are not 16-byte aligned: re-pitched on the device, then the same kernels (api.cu: run_pipeline_device)
+          (5998, 416, 800, 55), (1366, 768, 683, 384), (4001, 300, 801, 60), (2047, 511, 300, 100)]
 
 
 @pytest.mark.gpu

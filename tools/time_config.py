@@ -20,6 +20,9 @@ CFG = {
     "up2": (2048, 2048, dict(resize=ll.ResizeMode.SCALE(2.0)), ll.ORDER_CONVERT, 32),
     "thumb": (4000, 3000, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 64),          # gui/src-tauri/src/commands.rs:129-133
     "thumb24": (6000, 4000, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 64),
+    "odd24": (5998, 4000, dict(resize=ll.ResizeMode.WIDTH(800)), ll.ORDER_CONVERT, 32),          # rows not 16-byte aligned: the f32 fallback
+    "odd2": (1366, 768, dict(resize=ll.ResizeMode.WIDTH(683)), ll.ORDER_CONVERT, 256),
+    "odd2a": (1368, 768, dict(resize=ll.ResizeMode.WIDTH(684)), ll.ORDER_CONVERT, 256),
     "thumbs": (1024, 768, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 256),
 }
 name = sys.argv[1]
