@@ -112,6 +112,7 @@ struct VPlanHost {
     // shared-memory geometry
     uint32_t ring_rows = 0, pitch = 0, pitch_v = 0, smem_bytes = 0;
     uint32_t vbufs = 3;                    // V buffers (k2_vfirst.cu): 2..4
+    uint32_t vbufs_pref = 3;               // the band-length rule's choice, before the 16-column retry (vplan.cpp)
     uint32_t cohorts = 1;                  // pass-1 warp cohorts: cohort k filters groups k, k + cohorts, ... (k2_vfirst.cu)
     bool need_fill = false, rows_pure_fill = false;
 };

@@ -290,13 +290,20 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
     const char *ring_env = std::getenv("SLIMG_B200_RING_STEPS");
     const uint32_t ring_cap = std::min(512u, ring_env ? uint32_t(std::atoi(ring_env)) * 16 : 512u);
     uint32_t fb_cols = 0, fb_ring = 0; int fb_unit = 0; bool fb_early = false;      // fallback: widest fitting candidate
-    uint32_t ring_rows = 0;
+    uint32_t ring_rows = 0, vb_sel = out.vbufs, fb_vb = out.vbufs;
+    out.vbufs_pref = out.vbufs;
     for (uint32_t cand = 64; cand >= 8 && cols == 0; cand -= 8) {
         if (cols_env && uint32_t(std::atoi(cols_env)) != cand) continue;
         // even the strips out first (keeps the multiple of 8)
         const uint32_t ns = (g.pw + cand - 1) / cand;
         const uint32_t even = std::min<uint32_t>(cand, ((g.pw + ns - 1) / ns + 7) / 8 * 8);
         out.cohorts = cohorts_for(even);
+        // 16 columns is the last width with two pass-2 tiles and an even pass-1 warp count: below it a CTA filters 8 columns
+        // per 45-tap halo.  Before giving it up, give V buffers to the ring (measured on B200, 24 MP: 7.48x 37.4 us with
+        // 8 columns / 4 buffers, 22.1 with 16 / 2; 8x 35.1 -> 20.8)
+        const uint32_t vb_pref = out.vbufs_pref;
+        for (uint32_t vb = vb_pref; vb >= (even == 16 && !vbufs_env ? 2u : vb_pref) && cols == 0; vb--) {
+        out.vbufs = vb;
         int best_u = 0, best_crit = INT32_MAX;
         int64_t best_blk = INT64_MAX;
         for (int u = 5; u >= 3; u--) {
@@ -321,17 +328,20 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         // deepen the ring as far as shared memory allows: every extra step is 16 more rows in flight
         uint32_t rr = e ? ring_early : ring_min;
         while (rr + 16 <= ring_cap && smem_for(best_blk, rr + 16, pch, pv) <= kSmemBudget) rr += 16;
-        if (!fb_cols) { fb_cols = even; fb_ring = rr; fb_unit = best_u; fb_early = e; }
+        if (!fb_cols) { fb_cols = even; fb_ring = rr; fb_unit = best_u; fb_early = e; fb_vb = vb; }
         const double look = (double(rr) - 32.0 * out.nch1) / rows_per_group;
         const int n_p1 = kVfWarps - 2 - int((even + 7) / 8);
         // an odd number of tiles leaves an odd number of pass-1 warps, which cannot pair up into two cohorts: the next
         // narrower width can (measured on B200 after the integer epilogue: 8K 4x 56 columns 33.8 us, 48 columns 30.8;
         // 12 MP 5x 40 columns 11.63, 32 columns 11.57).  Odd widths stay as the fallback when nothing else fits.
         if (n_p1 % 2 == 1 && even > 8 && !cols_env && !std::getenv("SLIMG_B200_ODD_STRIPS")) continue;
-        if ((look >= look_min && n_p1 >= min_p1) || cols_env) { cols = even; unit = best_u; early = e; ring_rows = rr; }
+        if ((look >= look_min && n_p1 >= min_p1) || cols_env) { cols = even; unit = best_u; early = e; ring_rows = rr; vb_sel = vb; }
+        }
+        out.vbufs = vb_pref;
     }
-    if (cols == 0) { cols = fb_cols; unit = fb_unit; early = fb_early; ring_rows = fb_ring; }
+    if (cols == 0) { cols = fb_cols; unit = fb_unit; early = fb_early; ring_rows = fb_ring; vb_sel = fb_vb; }
     if (cols == 0) return;
+    out.vbufs = vb_sel;
     out.cohorts = cohorts_for(cols);
     out.unit = unit;
     out.early_go = early;

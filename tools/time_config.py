@@ -21,6 +21,11 @@ CFG = {
     "thumb": (4000, 3000, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 64),          # gui/src-tauri/src/commands.rs:129-133
     "thumb24": (6000, 4000, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 64),
     "odd24": (5998, 4000, dict(resize=ll.ResizeMode.WIDTH(800)), ll.ORDER_CONVERT, 32),          # rows not 16-byte aligned: the f32 fallback
+    "r748": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(802)), ll.ORDER_CONVERT, 32),
+    "r7": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(856)), ll.ORDER_CONVERT, 32),
+    "r8": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(752)), ll.ORDER_CONVERT, 32),
+    "r86": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(700)), ll.ORDER_CONVERT, 32),
+    "r8b": (4000, 3000, dict(resize=ll.ResizeMode.WIDTH(500)), ll.ORDER_CONVERT, 64),
     "odd2": (1366, 768, dict(resize=ll.ResizeMode.WIDTH(683)), ll.ORDER_CONVERT, 256),
     "odd2a": (1368, 768, dict(resize=ll.ResizeMode.WIDTH(684)), ll.ORDER_CONVERT, 256),
     "thumbs": (1024, 768, dict(resize=ll.ResizeMode.FIT(400, 400)), ll.ORDER_CONVERT, 256),
