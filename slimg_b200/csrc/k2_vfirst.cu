@@ -12,7 +12,8 @@
 // takes the bytes as they are at 2028 MAC/clk/SM (profiles/r01_microbench_b200.txt).
 //
 // Data flow of one CTA (a strip of <= 64 output columns x a band of output rows of one image):
-//   HBM --cp.async.bulk (TMA engine, one copy per source row)--> ring of source rows in shared memory
+//   HBM --cp.async.bulk.tensor.2d (TMA engine, one box of 16 source rows per copy; the same boxes are prefetched
+//        into L2 16 steps ahead for bands of 3+ chunks)--> ring of source rows in shared memory
 //   pass 1, per group of 8 output rows:  D1[16 bytes of the row][8 rows] += A[16][32 rows] * B[32][8]
 //        A comes straight out of the ring with ldmatrix.m16n16.x2.trans.b8: the transposing load
 //        hands every lane 4 consecutive SOURCE ROWS of one byte column, which is exactly the A
@@ -22,16 +23,21 @@
 //        epilogue: recombine the digit planes (exact s32), add fill/offset/rounding, >> to a u16 with
 //        7 fractional bits, split into two u8 limbs and store them planar ([channel][row][pixel]).
 //   pass 2, per group: D2[(channel,row) 16][8 output columns] += A[16][32 px] * B[32][8] for both limbs
-//        epilogue: s32 -> f32 recombination, clamp, round half away from zero, pack RGBA, stage the
-//        8 x strip output rows in shared memory and write them out as whole rows.
+//        three accumulators per channel pair, by weight: low limb x digit 0, low x digit 1 + high x digit 0 (it
+//        starts at the constant term: fill taps, intermediate offset, rounding half, as the MMA's C operand),
+//        high x digit 1.  Epilogue in integers: (a >> 8) + b + (c << 8), one shift, cvt.pack.sat.u8.s32, and
+//        8-byte stores straight to the final canvas position.
 // Nothing but source pixels is read from HBM and nothing but final pixels is written: the f32
 // intermediate of the reference (38-51 MB per image) never exists.
 //
-// Grid: x = strips, y = bands of output-row groups, z = image.  512 threads, one CTA per SM: the first
-// (strip columns / 8) warps run pass 2, the others pass 1; one CTA barrier per group.
+// Grid: x = strips (+ fill CTAs), y = bands of output-row groups, z = image.  512 threads, one CTA per SM: the
+// first (strip columns / 8) warps run pass 2, the next ones pass 1 -- in 1 to 3 cohorts that take turns on the
+// groups, so two or three groups are in flight -- then a signaller warp and a producer warp.  They meet only on
+// mbarriers: there is no CTA-wide barrier in the band loop.
 #include <cuda.h>
 
 #include <algorithm>
+#include <cstdio>
 
 #include "kernels.cuh"
 
@@ -133,6 +139,20 @@ __device__ __forceinline__ uint32_t quantize_channel(float t) {
     return __float_as_uint(__fadd_rz(t, 8388608.0f)) & 0xffu;      // 2^23 + floor(t) by truncation, no FRND / F2I
 }
 
+// -DSLIMG_VF_EXPERIMENT (python -m slimg_b200._build with SLIMG_B200_NVCC_EXTRA): cycles every role spends in its
+// mbarrier waits, printed by one strip CTA of the first launches when SLIMG_B200_VF_DEBUG has bit 32 set -- the numbers
+// of profiles/r02c_role_waits.txt.  Expands to nothing in the production build.
+#ifdef SLIMG_VF_EXPERIMENT
+__device__ int g_vf_prints = 0;
+#define VF_TIMED(acc, stmt) { const long long t__ = clock64(); stmt; acc += clock64() - t__; }
+#define VF_REPORT(role) \
+    if ((p.debug & 32u) && blockIdx.x == 3 && blockIdx.y == gridDim.y / 2 && blockIdx.z == 0 && lane == 0 && atomicAdd(&g_vf_prints, 1) < 48) \
+        printf("[vf] %s warp %2d groups %d total %lld wait0 %lld wait1 %lld wait2 %lld\n", role, warp, n_iter, clock64() - t_begin, w0, w1, w2);
+#else
+#define VF_TIMED(acc, stmt) stmt;
+#define VF_REPORT(role)
+#endif
+
 struct SmemTail {                             // after the ring, the V planes and the two group records
     uint64_t full[kMaxSteps];                // ring step landed (tx bytes)
     uint64_t rec_full[kRecBufs];                  // group record landed (tx bytes)
@@ -227,6 +247,10 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+#ifdef SLIMG_VF_EXPERIMENT
+    const long long t_begin = clock64();
+    long long w0 = 0, w1 = 0, w2 = 0;
+#endif
 
     if (warp == kWarps - 1) {
         // ================= producer ====================================================================
@@ -273,12 +297,13 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         for (int it = 0; it < n_iter; it++) {
             const int a_cur = a_next;
             a_next = it + 2 < n_iter ? int(__ldg(p.recs + size_t(rec0 + it + 2) * p.rec_words + 1)) : ye;
-            mbar_wait(&tail.v_full[buf], par);
+            VF_TIMED(w0, mbar_wait(&tail.v_full[buf], par))
             if (++buf == p.vbufs) { buf = 0; par ^= 1u; }
             issue_steps(min(n_steps, int(uint32_t(a_cur - ys) / uint32_t(kStepRows)) + nst));
             if (p.pf_steps) prefetch_steps(min(n_steps, next_issue + int(p.pf_steps)));
             if (it + kRecBufs < n_iter) issue_rec(it + kRecBufs);   // the record buffer of this group is free
         }
+        VF_REPORT("producer ")
     } else if (warp == kWarps - 2) {
         // ================= signaller: does the waiting for pass 1 =======================================
         // Group `it` may start when its record and source rows have landed and pass 2 has drained V[it & 1].
@@ -305,15 +330,15 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             while (first >= wrap_base + nst) { wrap_base += nst; wrap_par ^= 1u; }      // band starts move down monotonically
             const int step = first + lane;                   // a band spans at most 192 rows + alignment: <= 13 steps
             if (!kDivFree) {
-                if (step < last) mbar_wait(&tail.full[step % nst], uint32_t(step / nst) & 1u);
+                if (step < last) VF_TIMED(w0, mbar_wait(&tail.full[step % nst], uint32_t(step / nst) & 1u))
             } else if (step < last) {
                 int slot = step - wrap_base;
                 uint32_t ph = wrap_par;
                 if (slot >= nst) { slot -= nst; ph ^= 1u; }
-                mbar_wait(&tail.full[slot], ph);
+                VF_TIMED(w0, mbar_wait(&tail.full[slot], ph))
             }
-            mbar_wait(&tail.rec_full[it & (kRecBufs - 1)], uint32_t(it / kRecBufs) & 1u);
-            mbar_wait(&tail.v_empty[buf], par ^ 1u);        // V[buf] was last read by pass 2 vbufs groups ago
+            VF_TIMED(w1, mbar_wait(&tail.rec_full[it & (kRecBufs - 1)], uint32_t(it / kRecBufs) & 1u))
+            VF_TIMED(w2, mbar_wait(&tail.v_empty[buf], par ^ 1u))        // V[buf] was last read by pass 2 vbufs groups ago
             __syncwarp();
             if (lane == 0) {
                 tail.pos[buf] = kDivFree ? (first - wrap_base) * kStepRows + ((a0_cur - ys) & (kStepRows - 1)) : (a0_cur - ys) % int(p.ring_rows);
@@ -321,6 +346,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             }
             if (++buf == p.vbufs) { buf = 0; par ^= 1u; }
         }
+        VF_REPORT("signaller")
     } else if (warp < ntile) {
         // ================= pass 2: horizontal taps, 4 channels x 8 rows x 8 output columns per warp =======
         const int tile = warp;
@@ -357,7 +383,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             const int j = j_next;
             if (it + 1 < n_iter) j_next = int(__ldg(p.recs + size_t(rec0 + it + 1) * p.rec_words));
             const uint32_t vbuf = vbase + buf * 2u * vplane;
-            mbar_wait(&tail.v_full[buf], par);
+            VF_TIMED(w0, mbar_wait(&tail.v_full[buf], par))
 
             if (p.debug & 2u) { __syncwarp(); if (lane == 0) mbar_arrive(&tail.v_empty[buf]); continue; }
             uint32_t px[2] = {0u, 0u};         // packed RGBA of columns ocol, ocol+1 of output row g
@@ -448,6 +474,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
                 }
             }
         }
+        VF_REPORT("pass2    ")
     } else {
         // ================= pass 1: vertical taps of 8 output rows over the strip =======================
         // Static ownership: warp w1 of the n_p1 pass-1 warps computes units [w1*upw, (w1+1)*upw) of UNIT blocks in
@@ -473,7 +500,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
 #pragma unroll 1
         for (int it = co; it < n_iter; it += nco) {
             const uint32_t *rec = recbuf + uint32_t(it & (kRecBufs - 1)) * p.rec_words;
-            mbar_wait(&tail.go[buf], par);
+            VF_TIMED(w0, mbar_wait(&tail.go[buf], par))
             const int pos = tail.pos[buf];
             uint2 bw1[NCH1][NDIG];
 #pragma unroll
@@ -540,6 +567,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             buf += uint32_t(nco);
             while (buf >= p.vbufs) { buf -= p.vbufs; par ^= 1u; }
         }
+        VF_REPORT("pass1    ")
     }
 }
 
