@@ -204,7 +204,8 @@ slimg_status slimg_b200_pipeline_planes(const slimg_image *in, const slimg_pipel
                                         slimg_planes *out);
 void slimg_b200_planes_free(slimg_planes *p);
 /* device-resident batch: planes packed per image; for WebP `a` may be NULL (alpha ignored: treated as opaque), else a scratch
- * of n * ceil(h/2) bytes + n u32 flags is taken from `scratch` (n * ceil(h/2) + 4 n bytes, zeroed by the call) */
+ * of n * ceil(h/2) bytes + n u32 flags is taken from `scratch` (n * ceil(h/2) rounded up to 4, + 4 n bytes; the flags -- 1 for
+ * an image that holds a pixel that is not opaque -- are the last 4 n bytes and are zeroed by the call) */
 slimg_status slimg_b200_color_planes_batch_device(const uint8_t *src, uint32_t n, uint32_t w, uint32_t h, int kind,
                                                   void *y, void *cb, void *cr, void *a, void *scratch, void *stream);
 /* The WebP case of the call above for callers that must not allocate (code under CUDA graph capture, tight serving

@@ -800,7 +800,9 @@ static slimg_status run_planes_device(const uint8_t *src, uint32_t n, uint32_t w
         p.y = static_cast<uint8_t *>(y); p.u = static_cast<uint8_t *>(cb); p.v = static_cast<uint8_t *>(cr); p.a = static_cast<uint8_t *>(a);
         if (a && scratch) {
             const size_t rows = size_t(n) * ((h + 1) / 2);
-            p.row_alpha = static_cast<uint8_t *>(scratch);
+            // the planes kernel decides per 2 x 2 block and raises the per-image flag itself: no scan pass over the source
+            // (row_alpha stays NULL; the flags keep their place behind the n * ceil(h/2) bytes the scan used to fill)
+            p.row_alpha = nullptr;
             p.any_alpha = reinterpret_cast<uint32_t *>(static_cast<uint8_t *>(scratch) + ((rows + 3) & ~size_t(3)));
             CU(cudaMemsetAsync(p.any_alpha, 0, size_t(n) * 4, stream));
         }

@@ -24,6 +24,13 @@ __device__ __forceinline__ int w_l2g(const int *l2g, uint32_t base_value, int sh
     const int y = l2g[tab_pos + 1] * x + l2g[tab_pos] * (512 - x);
     return (y + 64) >> 7;
 }
+// libwebp's kInvAlpha: (1 << 19) / a for the alpha sum of a 2 x 2 block, a table instead of three integer divisions per block
+struct InvAlphaTab {
+    uint32_t v[1024];
+    constexpr InvAlphaTab() : v() { for (uint32_t a = 1; a < 1024; a++) v[a] = (1u << 19) / a; }
+};
+__device__ const InvAlphaTab kInvAlpha{};
+
 __device__ __forceinline__ int w_clip_uv(int uv) {
     uv = (uv + (1 << 17) + (128 << 18)) >> 18;
     return min(max(uv, 0), 255);
@@ -81,9 +88,24 @@ __global__ void __launch_bounds__(kThreads) webp_planes_kernel(const WebpPlanesP
                 if (x0 + k < w) { Y[o + k] = uint8_t(yw >> (8 * k)); if (A) A[o + k] = uint8_t(aw >> (8 * k)); }
         }
     }
-    // chroma: AccumulateRGB / AccumulateRGBA.  The alpha-weighted form is used only in row pairs that contain a pixel
-    // that is not opaque (libwebp decides per pair of rows); row_alpha[cy] was computed by the scan kernel.
-    const bool rows_alpha = p.row_alpha && p.row_alpha[size_t(blockIdx.z) * uvh + cy];
+    // chroma: AccumulateRGB / AccumulateRGBA.  libwebp takes the alpha-aware form in row pairs that contain a pixel that
+    // is not opaque -- and that form falls back to the plain sum for every 2 x 2 block whose alphas are all 255 (or all
+    // 0), so the per-row decision never changes a sample: the block's own alpha sum decides.  A caller that ran the
+    // scan kernel (row_alpha != NULL: the variant with static scratch) gets the same samples from its flags.
+    const bool rows_alpha = p.row_alpha ? p.row_alpha[size_t(blockIdx.z) * uvh + cy] != 0 : p.any_alpha != nullptr;
+    if (!p.row_alpha && p.any_alpha) {                     // no scan pass: this thread reports what it saw
+        bool seen = false;
+#pragma unroll
+        for (int r = 0; r < 2; r++)
+#pragma unroll
+            for (int k = 0; k < 4; k++) seen |= (px[r][k] >> 24) != 0xffu;
+        // one store per warp at most, and none once the flag is up: millions of stores to one word serialise in L2
+        const unsigned active = __activemask();
+        if (__any_sync(active, seen) && (threadIdx.x & 31) == __ffs(active) - 1) {
+            volatile uint32_t *flag = p.any_alpha + blockIdx.z;
+            if (*flag == 0u) *flag = 1u;
+        }
+    }
     uint32_t uvp[2] = {0u, 0u};                            // U and V of the two samples, packed
 #pragma unroll
     for (int e = 0; e < 2; e++) {
@@ -100,7 +122,7 @@ __global__ void __launch_bounds__(kThreads) webp_planes_kernel(const WebpPlanesP
             if (!rows_alpha || asum == 4u * 0xffu || asum == 0u) rgb[c] = wide ? w_l2g(l2g, v0 + v1 + v2 + v3, 0) : w_l2g(l2g, v0 + v2, 1);
             else {
                 const uint32_t sum = (q0 >> 24) * v0 + (q1 >> 24) * v1 + (q2 >> 24) * v2 + (q3 >> 24) * v3;
-                const uint32_t inv = (1u << 19) / asum;
+                const uint32_t inv = __ldg(&kInvAlpha.v[asum]);       // 0 < asum < 1020 here
                 rgb[c] = w_l2g(l2g, uint32_t((uint64_t(sum) * inv) >> 17), 0);
             }
         }

@@ -102,7 +102,7 @@ def test_planes_follow_the_pixel_stages_on_the_device():
     pxa = np.frombuffer(px.data, np.uint8).reshape(px.height, px.width, 4)
     before = ll.kernel_launches()
     got = ll.pipeline_planes(_ll_img(img), opts, ll.PLANES_WEBP_YUV420)
-    assert ll.kernel_launches() - before == 3          # K2, alpha scan, planes
+    assert ll.kernel_launches() - before == 2          # K2, planes (the per-block alpha rule needs no scan pass)
     y, u, v, a = oracle.webp_yuva(pxa)
     assert (got.width, got.height) == (400, 400)
     assert np.array_equal(np.frombuffer(got.y, np.uint8).reshape(400, 400), y) and np.array_equal(np.frombuffer(got.cb, np.uint8).reshape(200, 200), u)
