@@ -156,6 +156,20 @@ __global__ void __launch_bounds__(kThreads) webp_alpha_scan_kernel(const WebpPla
 
 __device__ __forceinline__ float round_away(float x) { return x < 0.0f ? -floorf(0.5f - x) : floorf(x + 0.5f); }
 
+// The conversion pipe (I2F, FRND, F2I: 16 lanes / clk / SM) would bound this kernel -- twelve such instructions per pixel
+// are 64 us per 24 MP image -- so bytes become floats and floats become samples on the FP32 and ALU pipes:
+//   byte -> f32: the byte dropped into the mantissa of 2^23, minus 2^23 (exact)
+//   f32 -> sample: clamp to [0, max] first, then floor(t + 0.5) as the mantissa of (t + 0.5) + 2^23 added toward zero.
+//   Same value as clamp(round_away(x)): below 0 both give 0, above max both give max, in between round_away(x) =
+//   floor(x + 0.5) with the same rounded sum x + 0.5.
+__device__ __forceinline__ float byte_to_float(uint32_t v, int byte) {
+    return __int_as_float(int(__byte_perm(v, 0x4B000000u, 0x7650 + byte))) - 8388608.0f;      // bytes: [v.byte, 0, 0, 0x4B]
+}
+__device__ __forceinline__ uint32_t round_clamp(float x, float max_value) {
+    const float t = fminf(fmaxf(x, 0.0f), max_value) + 0.5f;
+    return __float_as_uint(__fadd_rz(t, 8388608.0f)) & 0x7ffu;
+}
+
 // one thread = 4 pixels (one 16-byte load); DEPTH 8: u8 planes, 10: u16 planes
 template <int DEPTH>
 __global__ void __launch_bounds__(kThreads) avif_planes_kernel(const AvifPlanesParams p) {
@@ -182,15 +196,15 @@ __global__ void __launch_bounds__(kThreads) avif_planes_kernel(const AvifPlanesP
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         const uint32_t v = k < cnt ? px[k] : 0u;
-        const float r = float(v & 0xff), g = float((v >> 8) & 0xff), b = float((v >> 16) & 0xff);
+        const float r = byte_to_float(v, 0), g = byte_to_float(v, 1), b = byte_to_float(v, 2);
         const uint32_t al = v >> 24;
         // every product and sum rounds to f32 (the reference build does not contract); the chroma terms are ONE fused multiply-add
         const float yv = __fadd_rn(__fadd_rn(__fmul_rn(t0, r), __fmul_rn(t1, g)), __fmul_rn(t2, b));
         const float cbv = __fmaf_rn(__fsub_rn(__fmul_rn(b, scale), yv), kb, shift);
         const float crv = __fmaf_rn(__fsub_rn(__fmul_rn(r, scale), yv), kr, shift);
-        vy[k] = T(fminf(fmaxf(round_away(yv), 0.f), max_value));
-        vb[k] = T(fminf(fmaxf(round_away(cbv), 0.f), max_value));
-        vr[k] = T(fminf(fmaxf(round_away(crv), 0.f), max_value));
+        vy[k] = T(round_clamp(yv, max_value));
+        vb[k] = T(round_clamp(cbv, max_value));
+        vr[k] = T(round_clamp(crv, max_value));
         va[k] = DEPTH == 8 ? T(al) : T((al << 2) | (al >> 6));
     }
     const bool vec = cnt == 4 && (n & 3) == 0;                 // plane rows of 4 samples are then 4- / 8-byte aligned (cudaMalloc'ed planes)
