@@ -247,15 +247,32 @@ __global__ void __launch_bounds__(kThreads, 3) resize_tile_kernel(const TilePara
             for (int e = 0; e < 2; e++)
 #pragma unroll
                 for (int c = 0; c < 4; c++) cxr[e][c] = ocol + e < col1 ? __ldg(p.cxi + size_t(ocol + e) * 4 + c) : 0;
+            // everything that does not depend on the group, once per tile: the V addresses of this lane's fragment rows, the
+            // output pointer of its row in group 0, whether its two pixels go out as one 8-byte store
+            uint32_t rbase[2];
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) rbase[mt] = vbase + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
+            const uint32_t r1off = 8u * p.pitch_v + 4u, gstride = 2u * vplane;
+            uint32_t *const orow0 = dst + size_t(p.foy + g0 * 8 + g) * p.fw + p.fox + ocol;
+            const size_t ostride = size_t(8) * p.fw;
+            const bool pair_ok = ocol + 1 < col1 && (reinterpret_cast<uintptr_t>(orow0) & 7) == 0 && (p.fw & 1u) == 0;
+            const bool all_rows = (p.need_fill & 2u) == 0;
+            uint32_t todo = gmask;                            // groups of this warp that hold computed rows
+            if (wpt > 1) {
+                uint32_t mine = 0u;
+                for (int gi = warp & (wpt - 1); gi < ng; gi += wpt) mine |= 1u << gi;
+                todo &= mine;
+            }
 #pragma unroll 1
-            for (int gi = warp & (wpt - 1); gi < ng; gi += wpt) {
-                if (!((gmask >> gi) & 1u)) continue;
-                const uint32_t vbuf = vbase + uint32_t(gi) * 2u * vplane;
+            while (todo) {
+                const int gi = __ffs(int(todo)) - 1;
+                todo &= todo - 1u;
+                const uint32_t goff = uint32_t(gi) * gstride;
                 int tsum[2][4];                    // [channel pair][i]: the pass-2 sum in units of 2^-sh2, constant term included
 #pragma unroll
                 for (int mt = 0; mt < 2; mt++) {
-                    const uint32_t r0 = vbuf + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
-                    const uint32_t r1 = r0 + 8u * p.pitch_v + 4u;
+                    const uint32_t r0 = rbase[mt] + goff;
+                    const uint32_t r1 = r0 + r1off;
                     if (PACKED) {
                         // K = [16 low-limb pixels | 16 high-limb pixels]: A = lo x w0, B = lo x w1 + hi x w0, C = hi x w1
                         uint32_t a[4];
@@ -294,9 +311,9 @@ __global__ void __launch_bounds__(kThreads, 3) resize_tile_kernel(const TilePara
                     px[e] = pack_sat_u8(c1, c0, pack_sat_u8(c3, c2, 0u));
                 }
                 const int i_row = (g0 + gi) * 8 + g;
-                if (i_row < int(p.ph) && p.row_computed[i_row]) {
-                    uint32_t *o = dst + size_t(p.foy + i_row) * p.fw + p.fox + ocol;
-                    if (ocol + 1 < col1 && (reinterpret_cast<uintptr_t>(o) & 7) == 0) *reinterpret_cast<uint2 *>(o) = make_uint2(px[0], px[1]);
+                if (i_row < int(p.ph) && (all_rows || p.row_computed[i_row])) {
+                    uint32_t *o = orow0 + size_t(gi) * ostride;
+                    if (pair_ok) *reinterpret_cast<uint2 *>(o) = make_uint2(px[0], px[1]);
                     else {
                         if (ocol < col1) o[0] = px[0];
                         if (ocol + 1 < col1) o[1] = px[1];
