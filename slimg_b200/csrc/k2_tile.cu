@@ -254,7 +254,8 @@ __global__ void __launch_bounds__(kThreads, 3) resize_tile_kernel(const TilePara
             for (int mt = 0; mt < 2; mt++) rbase[mt] = vbase + uint32_t(16 * mt + g) * p.pitch_v + uint32_t(2 * mt) * 4u + uint32_t(kb0 + t) * 4u;
             const uint32_t r1off = 8u * p.pitch_v + 4u, gstride = 2u * vplane;
             uint32_t *const orow0 = dst + size_t(p.foy + g0 * 8 + g) * p.fw + p.fox + ocol;
-            const size_t ostride = size_t(8) * p.fw;
+            const uint32_t ostride = 8u * p.fw;                  // pixels between the rows of consecutive groups (64 fw < 2^32)
+            const int rows_left = int(p.ph) - (g0 * 8 + g);      // kept rows from this lane's row of group 0 on
             const bool pair_ok = ocol + 1 < col1 && (reinterpret_cast<uintptr_t>(orow0) & 7) == 0 && (p.fw & 1u) == 0;
             const bool all_rows = (p.need_fill & 2u) == 0;
             uint32_t todo = gmask;                            // groups of this warp that hold computed rows
@@ -310,9 +311,8 @@ __global__ void __launch_bounds__(kThreads, 3) resize_tile_kernel(const TilePara
                     const int c0 = tsum[0][e] >> sh2, c1 = tsum[0][2 + e] >> sh2, c2 = tsum[1][e] >> sh2, c3 = tsum[1][2 + e] >> sh2;
                     px[e] = pack_sat_u8(c1, c0, pack_sat_u8(c3, c2, 0u));
                 }
-                const int i_row = (g0 + gi) * 8 + g;
-                if (i_row < int(p.ph) && (all_rows || p.row_computed[i_row])) {
-                    uint32_t *o = orow0 + size_t(gi) * ostride;
+                if (gi * 8 < rows_left && (all_rows || p.row_computed[(g0 + gi) * 8 + g])) {
+                    uint32_t *o = orow0 + uint32_t(gi) * ostride;
                     if (pair_ok) *reinterpret_cast<uint2 *>(o) = make_uint2(px[0], px[1]);
                     else {
                         if (ocol < col1) o[0] = px[0];

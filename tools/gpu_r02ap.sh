@@ -1,7 +1,7 @@
 set -x
 mkdir -p gpurun_out
 OLD=$PWD/slimg_b200/lib/libslimg_b200_old.so
-( for rep in 1 2; do for c in c3 c3conv c4a c1 r3 r2 thumb; do
+( for rep in 1 2; do for c in c4a r3 r2 r15 thumbs c3 c1; do
     AB=new timeout 120 python tools/time_config.py $c
     AB=old SLIMG_B200_LIB=$OLD timeout 120 python tools/time_config.py $c
   done; done ) > gpurun_out/configs_ap.txt 2>&1
