@@ -635,6 +635,39 @@ def main():
                                   "images_per_gpu_per_step": nb, "geometries": len(sizes), "steps": m_steps, "step_ms": step_ms_m,
                                   "host_image_bytes_per_step": o}
 
+        # the other extreme: no two images of the run share a geometry (user crops, scans): every image costs a plan on the
+        # host (taps, fixed-point weights, strip layout: 5-8 ms for 12 MP) before its kernel can start; the scheduler's workers
+        # build their plans concurrently, outside the cache lock
+        if not args.no_pageable:
+            uniq = {"k": 0}
+
+            def unique_step():
+                for i in range(nb):
+                    w = 4000 - 4 * (uniq["k"] % 400)
+                    uniq["k"] += 1
+                    cin[i] = ll.CImage(w, 3000, pin_in + i * in_bytes, w * 3000 * 4)
+                    cout[i] = ll.CImage(0, 0, pin_out + i * out_bytes, out_bytes)
+                if lib.slimg_b200_pipeline_batch_host(cin, nb, C.byref(fit), ll.ORDER_CONVERT, C.byref(cfg), cout, st):
+                    raise SystemExit("unique-size e2e batch failed: " + lib.slimg_b200_last_error().decode())
+
+            k0 = None
+            u_steps = 3
+            for _ in range(2):
+                unique_step()
+            barrier()
+            k0 = uniq["k"]
+            t0 = time.perf_counter()
+            px_u = 0
+            for _ in range(u_steps):
+                kk = uniq["k"]
+                unique_step()
+                px_u += sum((4000 - 4 * ((kk + i) % 400)) * 3000 for i in range(nb))
+            torch.cuda.synchronize()
+            dt_u = _shard.max_over_ranks(time.perf_counter() - t0, device="cuda")
+            e2e["unique_sizes"] = {"value": _shard.whole_job_throughput(px_u / 1e6, world, dt_u), "unit": "Mpx/s",
+                                   "what": "every image a geometry of its own (3000 rows, widths 4000, 3996, ... never repeated inside the plan cache's reach), Fit(800, 800), pinned buffers: one host-side plan per image",
+                                   "images_per_gpu_per_step": nb, "steps": u_steps, "streams_per_device": 4}
+
         # the library's own multi-device scheduler: ONE process (rank 0) feeding every GPU of the box (n_devices = world),
         # no Python per rank -- the `--jobs` analogue proper; the other ranks wait
         if world > 1:

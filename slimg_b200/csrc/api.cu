@@ -45,20 +45,72 @@ static uint32_t pack_fill(const uint8_t f[4]) {
 
 // All tables of a plan live in one or two device slabs: a plan costs one cudaMalloc instead of ~30, and dropping it is
 // one cudaFree (mixed-size corpora build a plan per geometry).
+//
+// Slabs are recycled, not freed: cudaFree synchronises the whole device, and a corpus in which every image has its own
+// geometry evicts a plan per image (measured on the host-fed bench, 32 unique 12 MP geometries per step: 3.3 Gpx/s with a
+// cudaFree per eviction).  A dropped plan's slabs go to a per-device graveyard; kernels that were enqueued with the plan
+// may still be running, so the graveyard is turned into the free list only behind ONE cudaDeviceSynchronize per
+// kGraveyardSlabs retired slabs.
+constexpr size_t kGraveyardSlabs = 16;
+struct SlabPool {
+    std::mutex mu;
+    std::vector<std::pair<void *, size_t>> free_list, graveyard;
+};
+static SlabPool &slab_pool(int dev) {
+    // never destroyed: plans that live in other statics retire their slabs here while the process exits
+    static SlabPool *pools = new SlabPool[64];
+    return pools[dev >= 0 && dev < 64 ? dev : 0];
+}
 struct PlanArena {
-    std::vector<void *> slabs;
+    std::vector<std::pair<void *, size_t>> slabs;
     size_t used = 0, cap = 0;
-    ~PlanArena() { for (void *s : slabs) cudaFree(s); }
+    int device = 0;
+    PlanArena() { if (cudaGetDevice(&device) != cudaSuccess) { cudaGetLastError(); device = 0; } }
+    ~PlanArena() {
+        if (slabs.empty()) return;
+        SlabPool &pool = slab_pool(device);
+        std::lock_guard<std::mutex> lk(pool.mu);
+        for (auto &s : slabs) pool.graveyard.push_back(s);
+    }
+    static void *take(SlabPool &pool, size_t bytes, size_t &got) {       // pool.mu held
+        for (size_t i = 0; i < pool.free_list.size(); i++)
+            if (pool.free_list[i].second >= bytes && pool.free_list[i].second <= 2 * bytes) {
+                void *s = pool.free_list[i].first;
+                got = pool.free_list[i].second;
+                pool.free_list.erase(pool.free_list.begin() + i);
+                return s;
+            }
+        return nullptr;
+    }
     cudaError_t alloc(size_t bytes, void **p) {
         const size_t need = (bytes + 255) & ~size_t(255);
         if (slabs.empty() || used + need > cap) {
-            const size_t slab = std::max<size_t>(need, size_t(4) << 20);
+            size_t slab = std::max<size_t>(need, size_t(4) << 20);
+            SlabPool &pool = slab_pool(device);
             void *s = nullptr;
-            cudaError_t e = cudaMalloc(&s, slab);
-            if (e != cudaSuccess) return e;
-            slabs.push_back(s); used = 0; cap = slab;
+            size_t reap = 0;                           // retired slabs as of now: only these are safe behind the synchronise below
+            {
+                std::lock_guard<std::mutex> lk(pool.mu);
+                s = take(pool, slab, slab);
+                if (!s && pool.graveyard.size() >= kGraveyardSlabs) reap = pool.graveyard.size();
+            }
+            if (reap) {
+                // every kernel that was enqueued with one of these plans was enqueued before its plan was dropped, i.e. before
+                // this point: after the synchronise nothing can touch them (slabs retired meanwhile stay in the graveyard)
+                cudaError_t e = cudaDeviceSynchronize();
+                if (e != cudaSuccess) return e;
+                std::lock_guard<std::mutex> lk(pool.mu);
+                for (size_t i = 0; i < reap; i++) pool.free_list.push_back(pool.graveyard[i]);
+                pool.graveyard.erase(pool.graveyard.begin(), pool.graveyard.begin() + reap);
+                s = take(pool, slab, slab);
+            }
+            if (!s) {
+                cudaError_t e = cudaMalloc(&s, slab);
+                if (e != cudaSuccess) return e;
+            }
+            slabs.push_back({s, slab}); used = 0; cap = slab;
         }
-        *p = static_cast<uint8_t *>(slabs.back()) + used;
+        *p = static_cast<uint8_t *>(slabs.back().first) + used;
         used += need;
         return cudaSuccess;
     }
@@ -424,7 +476,7 @@ static slimg_status get_resize_plan(const PipeGeom &g, std::shared_ptr<ResizePla
     // miss on the same geometry both build it; the second insert is dropped)
     slimg_status st = build_resize_plan(g, path, out);
     if (st != SLIMG_OK) return st;
-    std::shared_ptr<ResizePlan> victim;                 // freed after the lock is released (cudaFree synchronises)
+    std::shared_ptr<ResizePlan> victim;                 // dropped after the lock is released (its slabs go to the graveyard)
     {
         std::lock_guard<std::mutex> lk(ctx.mu);
         auto it = ctx.plans.find(key);
