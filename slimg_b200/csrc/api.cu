@@ -55,6 +55,7 @@ constexpr size_t kGraveyardSlabs = 16;
 struct SlabPool {
     std::mutex mu;
     std::vector<std::pair<void *, size_t>> free_list, graveyard;
+    uint64_t retired = 0, reaped = 0;       // slabs ever pushed to / taken from the graveyard: its front is slab number `reaped`
 };
 static SlabPool &slab_pool(int dev) {
     // never destroyed: plans that live in other statics retire their slabs here while the process exits
@@ -70,7 +71,7 @@ struct PlanArena {
         if (slabs.empty()) return;
         SlabPool &pool = slab_pool(device);
         std::lock_guard<std::mutex> lk(pool.mu);
-        for (auto &s : slabs) pool.graveyard.push_back(s);
+        for (auto &s : slabs) { pool.graveyard.push_back(s); pool.retired++; }
     }
     static void *take(SlabPool &pool, size_t bytes, size_t &got) {       // pool.mu held
         for (size_t i = 0; i < pool.free_list.size(); i++)
@@ -88,11 +89,11 @@ struct PlanArena {
             size_t slab = std::max<size_t>(need, size_t(4) << 20);
             SlabPool &pool = slab_pool(device);
             void *s = nullptr;
-            size_t reap = 0;                           // retired slabs as of now: only these are safe behind the synchronise below
+            uint64_t reap = 0;                         // slabs retired so far: only those are safe behind the synchronise below
             {
                 std::lock_guard<std::mutex> lk(pool.mu);
                 s = take(pool, slab, slab);
-                if (!s && pool.graveyard.size() >= kGraveyardSlabs) reap = pool.graveyard.size();
+                if (!s && pool.graveyard.size() >= kGraveyardSlabs) reap = pool.retired;
             }
             if (reap) {
                 // every kernel that was enqueued with one of these plans was enqueued before its plan was dropped, i.e. before
@@ -100,8 +101,10 @@ struct PlanArena {
                 cudaError_t e = cudaDeviceSynchronize();
                 if (e != cudaSuccess) return e;
                 std::lock_guard<std::mutex> lk(pool.mu);
-                for (size_t i = 0; i < reap; i++) pool.free_list.push_back(pool.graveyard[i]);
-                pool.graveyard.erase(pool.graveyard.begin(), pool.graveyard.begin() + reap);
+                size_t n = 0;                          // another worker may have reaped part of them meanwhile
+                while (pool.reaped + n < reap && n < pool.graveyard.size()) pool.free_list.push_back(pool.graveyard[n++]);
+                pool.graveyard.erase(pool.graveyard.begin(), pool.graveyard.begin() + n);
+                pool.reaped += n;
                 s = take(pool, slab, slab);
             }
             if (!s) {
@@ -413,9 +416,10 @@ static slimg_status build_resize_plan(const PipeGeom &g, const std::string &path
             plan->vfirst = true;
         }
     }
-    // H-first tensor-core path (kept for A/B comparison)
+    // H-first tensor-core path: what serves bands beyond the V-first ring (and A/B runs).  Not planned when a better plan
+    // exists: its 1.5 - 2.5 ms of host work per geometry would be a quarter of a corpus of unique sizes.
     FastPlanHost fp;
-    build_fast_plan(g, tx, ty, fp);
+    if (!plan->vfirst && !plan->tile && !plan->tc) build_fast_plan(g, tx, ty, fp);
     if (fp.ok && path != "generic" && std::getenv("SLIMG_B200_FORCE_GENERIC") == nullptr) {
         std::vector<VQuad> vquads(fp.vrow_w.size() / 32);
         for (size_t y = 0; y < vquads.size() * 4; y++) {

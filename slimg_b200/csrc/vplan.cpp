@@ -35,13 +35,14 @@ void quantise(const float *w, int cnt, int S, std::vector<int64_t> &q) {
     double sum_w = 0.0;
     int64_t sum_q = 0;
     int big = 0;
+    const double scale = std::ldexp(1.0, S);
     for (int i = 0; i < cnt; i++) {
         sum_w += double(w[i]);
-        q[i] = std::llround(double(w[i]) * std::ldexp(1.0, S));
+        q[i] = std::llround(double(w[i]) * scale);
         sum_q += q[i];
         if (std::fabs(w[i]) > std::fabs(w[big])) big = i;
     }
-    if (cnt) q[big] += std::llround(sum_w * std::ldexp(1.0, S)) - sum_q;
+    if (cnt) q[big] += std::llround(sum_w * scale) - sum_q;
 }
 
 bool split_digits(int64_t x, int ndig, int8_t d[3]) {

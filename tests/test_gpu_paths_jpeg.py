@@ -317,6 +317,22 @@ def test_plan_cache_survives_more_geometries_than_it_holds():
                 _close(got, oracle.resize(img, oracle.ResizeMode.scale(0.5)), "noise", f"plan cache churn {w}x{h}")
 
 
+def test_unique_geometries_through_the_scheduler_recycle_plan_slabs():
+    """Every image its own geometry, eight workers building and dropping plans at once (api.cu: SlabPool -- retired slabs
+    are recycled behind one device synchronise per 16, never cudaFree'd on the hot path).  300 geometries through the
+    64-entry cache, three batches; every output equals the single-image call's."""
+    opts = ll.make_options(resize=ll.ResizeMode.SCALE(0.5))
+    dev = (C.c_int32 * 1)(0)
+    cfg = ll.CBatchConfig(1, 8, dev)
+    for rep in range(3):
+        sizes = [(96 + 4 * ((rep * 100 + k) % 300), 40 + (k % 5)) for k in range(100)]
+        imgs = [noise_image(w, h, (rep * 100 + k) % 50) for k, (w, h) in enumerate(sizes)]
+        failed, st, outs = _batch(imgs, opts, ll.ORDER_CONVERT, pinned=False, cfg=C.byref(cfg))
+        assert failed == 0 and not any(st)
+        for k in range(0, 100, 7):
+            assert np.array_equal(outs[k], _np(ll.pipeline(_ll_img(imgs[k]), opts, ll.ORDER_CONVERT))), (rep, k)
+
+
 def test_batch_jpeg_host_scheduler():
     lib = ll.library()
     sizes = [(640, 480), (333, 257), (3, 3), (1000, 334)]

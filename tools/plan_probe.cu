@@ -41,6 +41,7 @@ int main(int argc, char **argv) {
            vp.ok ? vp.strip_col0[1] : 0, vp.unit, vp.ok ? vp.strip_upw[0] : 0, vp.ok ? vp.strip_nunits[0] : 0, vp.cohorts, vp.vbufs, vp.ring_rows, vp.pitch, vp.smem_bytes, vp.nch1, vp.nch2, vp.n_recs);
     TcPlanHost tp; build_tcplan(g, tx, ty, tp);
     double t4 = now();
+    { double t5 = now(); FastPlanHost fp; build_fast_plan(g, tx, ty, fp); printf("fastplan ms %.2f ok=%d\n", now() - t5, int(fp.ok)); }
     printf("host ms: taps %.2f  tileplan %.2f  vplan %.2f  tcplan %.2f\n", t1 - t0, t2 - t1, t3 - t2, t4 - t3);
     printf("tc: ok=%d strips=%u cols=%d panels=%u nbuf=%u vbufs=%u slots=%u blocks=%u chunks=%u nb_max=%u nch2=%d pitch_v=%u smem=%u\n", int(tp.ok), tp.n_strips,
            tp.ok ? tp.strip_col0[1] : 0, tp.n_panels, tp.nbuf, tp.vbufs, tp.slots, tp.n_blocks, tp.n_chunks, tp.nb_max, tp.nch2, tp.pitch_v, tp.smem_bytes);
