@@ -161,7 +161,7 @@ struct SmemTail {                             // after the ring, the V planes an
     uint64_t rec_full[kRecBufs];                  // group record landed (tx bytes)
     uint64_t go[kMaxVBufs];                     // producer: record + source rows of the group are in, V[buf] is free
     uint64_t v_full[kMaxVBufs];                 // every pass-1 warp is done with the group: V complete, band rows released
-    uint64_t v_empty[kMaxVBufs];                // every pass-2 warp has read V
+    uint64_t v_empty[kMaxVBufs];                // every pass-2 warp has read V and the producer has seen v_full
     int pos[kMaxVBufs];                           // ring row of the group's band start (written by the producer before `go`)
 };
 
@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
         for (int b = 0; b < int(p.vbufs); b++) {
             mbar_init(&tail.go[b], 1);
             mbar_init(&tail.v_full[b], uint32_t(csize));
-            mbar_init(&tail.v_empty[b], uint32_t(ntile));
+            mbar_init(&tail.v_empty[b], uint32_t(ntile) + 1u);       // every pass-2 warp and the producer (see its loop)
             tail.pos[b] = 0;
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -301,6 +301,11 @@ __global__ void __launch_bounds__(kThreads, 1) resize_vfirst_kernel(const VfPara
             const int a_cur = a_next;
             a_next = it + 2 < n_iter ? int(__ldg(p.recs + size_t(rec0 + it + 2) * p.rec_words + 1)) : ye;
             VF_TIMED(w0, mbar_wait(&tail.v_full[buf], par))
+            // The producer acknowledges the phase like a pass-2 warp does: V[buf] is handed to group it + vbufs only after
+            // every waiter on v_full[buf] has seen this phase.  Without it the barrier could complete a second phase while
+            // this warp was still behind the first (the ring holds rows for several groups ahead, so pass 1 and pass 2 do
+            // not depend on the producer in the short run), and a parity wait that is two phases late never returns.
+            if (lane == 0) mbar_arrive(&tail.v_empty[buf]);
             if (++buf == p.vbufs) { buf = 0; par ^= 1u; }
             issue_steps(min(n_steps, int(uint32_t(a_cur - ys) / uint32_t(kStepRows)) + nst));
             if (p.pf_steps) prefetch_steps(min(n_steps, next_issue + int(p.pf_steps)));
