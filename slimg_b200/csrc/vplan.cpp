@@ -336,7 +336,20 @@ void build_vplan(const PipeGeom &g, const AxisTaps &tx, const AxisTaps &ty, int 
         // narrower width can (measured on B200 after the integer epilogue: 8K 4x 56 columns 33.8 us, 48 columns 30.8;
         // 12 MP 5x 40 columns 11.63, 32 columns 11.57).  Odd widths stay as the fallback when nothing else fits.
         if (n_p1 % 2 == 1 && even > 8 && !cols_env && !std::getenv("SLIMG_B200_ODD_STRIPS")) continue;
-        if ((look >= look_min && n_p1 >= min_p1) || cols_env) { cols = even; unit = best_u; early = e; ring_rows = rr; vb_sel = vb; }
+        if ((look >= look_min && n_p1 >= min_p1) || cols_env) {
+            cols = even; unit = best_u; early = e; ring_rows = rr; vb_sel = vb;
+            // Two cohorts need two V buffers; a third only helps when the ring already runs well ahead.  Where it does not
+            // (look-ahead under 2.5 groups), its shared memory goes to the ring (measured on B200, 24 MP: 6x 18.99 -> 17.78 us,
+            // 5.5x 21.02 -> 19.83, look-ahead 2.0 -> 2.7 groups; 12 MP 5x, whose ring runs 3.2 groups ahead, 10.50 -> 11.09
+            // the other way and keeps three)
+            if (short_bands && vb == 3 && out.cohorts == 2 && look < 2.5 && !vbufs_env) {
+                out.vbufs = 2;
+                uint32_t rr2 = rr;
+                while (rr2 + 16 <= ring_cap && smem_for(best_blk, rr2 + 16, pch, pv) <= kSmemBudget) rr2 += 16;
+                if (rr2 > rr) { ring_rows = rr2; vb_sel = 2; }
+                out.vbufs = vb;
+            }
+        }
         }
         out.vbufs = vb_pref;
     }

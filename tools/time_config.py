@@ -25,6 +25,7 @@ CFG = {
     "r7": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(856)), ll.ORDER_CONVERT, 32),
     "r8": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(752)), ll.ORDER_CONVERT, 32),
     "r86": (6000, 4000, dict(resize=ll.ResizeMode.WIDTH(700)), ll.ORDER_CONVERT, 32),
+    "r57": (4000, 3000, dict(resize=ll.ResizeMode.WIDTH(700)), ll.ORDER_CONVERT, 64),
     "r8b": (4000, 3000, dict(resize=ll.ResizeMode.WIDTH(500)), ll.ORDER_CONVERT, 64),
     "odd2": (1366, 768, dict(resize=ll.ResizeMode.WIDTH(683)), ll.ORDER_CONVERT, 256),
     "odd2a": (1368, 768, dict(resize=ll.ResizeMode.WIDTH(684)), ll.ORDER_CONVERT, 256),
